@@ -1,0 +1,190 @@
+// CPU harness for anglican_b200/csrc/exact_fold.cuh.
+//
+// Mirrors, sequentially, the structure of the CUDA resampler (classify tiles
+// from an approximate prefix -> per-tile parity-transducer aggregates -> chain
+// resolve -> per-element replay -> pointer counting) so that the arithmetic of
+// the header can be checked on a machine without a GPU against the oracle's
+// literal wheel (oracle/anglican_oracle.c: orc_resample_weights).
+//
+// Built by tests/test_exact_fold_host.py with g++; not part of the product.
+#include <cstdint>
+#include <cstdio>
+#include <cstdlib>
+#include <vector>
+
+#include "../../anglican_b200/csrc/exact_fold.cuh"
+
+using namespace apop;
+
+namespace {
+
+const int LANE_ITEMS = 8;
+
+// exact fold of one tile starting from S_in, emulating the device algorithm:
+// lanes of LANE_ITEMS elements, lane aggregates, exclusive compose-scan, replay.
+// Iterates on binade crossings.  Writes S_i (inclusive edges); returns S_out.
+double tile_exact_fold(double S_in, const double* w, int n, double* edges, int* iters) {
+    int pos = 0;
+    double S = S_in;
+    int it = 0;
+    std::vector<Xd> agg((n + LANE_ITEMS - 1) / LANE_ITEMS);
+    while (pos < n) {
+        ++it;
+        const int e = ctx_of(S);
+        const i64 s_in = units_of(S);
+        const int nl = (n + LANE_ITEMS - 1) / LANE_ITEMS;
+        for (int l = 0; l < nl; ++l) {
+            Xd t = xd_identity();
+            for (int j = 0; j < LANE_ITEMS; ++j) {
+                int i = l * LANE_ITEMS + j;
+                if (i >= n || i < pos) continue;
+                i64 f; int up, tie;
+                quantize(w[i], e, f, up, tie);
+                xd_push(t, f, up, tie);
+            }
+            agg[l] = t;
+        }
+        // exclusive scan + replay
+        Xd run = xd_identity();
+        int cross = -1;
+        for (int l = 0; l < nl && cross < 0; ++l) {
+            i64 s = xd_apply(s_in, run);
+            for (int j = 0; j < LANE_ITEMS; ++j) {
+                int i = l * LANE_ITEMS + j;
+                if (i >= n || i < pos) continue;
+                i64 f; int up, tie;
+                quantize(w[i], e, f, up, tie);
+                i64 s2 = step_units(s, f, up, tie);
+                if (s2 >= kTwo53) { cross = i; break; }
+                s = s2;
+                edges[i] = from_units(s, e);
+            }
+            run = xd_compose(run, agg[l]);
+        }
+        if (cross < 0) { S = (n > pos) ? edges[n - 1] : S; pos = n; break; }
+        double Sprev = (cross == pos) ? S : edges[cross - 1];
+        S = Sprev + w[cross];                 // the crossing add, hardware fp64
+        edges[cross] = S;
+        pos = cross + 1;
+    }
+    if (iters) *iters += it;
+    return S;
+}
+
+} // namespace
+
+extern "C" {
+
+// Full emulation.  Returns 0 on success.  emission[j] = particle of pointer j,
+// lap[j] = 0/1.  stats[0]=#hard tiles lap0, stats[1]=#hard tiles lap1,
+// stats[2]=crossing iterations, stats[3]=comb segments.
+int host_exact_resample(const double* w, int64_t n, int64_t n_new, double u, int tile,
+                        int32_t* emission, int32_t* lap_out, double* total_out,
+                        int64_t* stats) {
+    const int64_t nt = (n + tile - 1) / tile;
+    // approximate prefix (pairwise-ish: per tile plain sums, then scan)
+    std::vector<double> tsum(nt), ain(nt + 1);
+    for (int64_t t = 0; t < nt; ++t) {
+        // deliberately a different summation order than the fold (reverse)
+        double s = 0;
+        int64_t hi = (t + 1) * tile < n ? (t + 1) * tile : n;
+        for (int64_t i = hi - 1; i >= t * tile; --i) s += w[i];
+        tsum[t] = s;
+    }
+    ain[0] = 0;
+    for (int64_t t = 0; t < nt; ++t) ain[t + 1] = ain[t] + tsum[t];
+    const double atot = ain[nt];
+
+    std::vector<double> edges(tile);
+    std::vector<double> sin0(nt + 1), sin1(nt + 1);
+    int iters = 0;
+    int64_t hard0 = 0, hard1 = 0;
+    // ---- lap 0 chain
+    double S = 0.0;
+    for (int64_t t = 0; t < nt; ++t) {
+        int64_t lo = t * tile, hi = lo + tile < n ? lo + tile : n;
+        int cls = classify_tile(ain[t], ain[t + 1], hi);
+        sin0[t] = S;
+        if (cls == kCtxHard) {
+            ++hard0;
+            S = tile_exact_fold(S, w + lo, (int)(hi - lo), edges.data(), &iters);
+        } else {
+            if (ctx_of(S) != cls) return -11;          // classification must be sound
+            Xd a = xd_identity();
+            for (int64_t i = lo; i < hi; ++i) {
+                i64 f; int up, tie;
+                quantize(w[i], cls, f, up, tie);
+                xd_push(a, f, up, tie);
+            }
+            i64 s = xd_apply(units_of(S), a);
+            if (s >= kTwo53) return -12;
+            S = from_units(s, cls);
+        }
+    }
+    sin0[nt] = S;
+    const double total = S;
+    if (total_out) *total_out = total;
+    Comb comb;
+    comb_build(comb, total, u, n_new);
+    if (comb.err) return -13;
+    // ---- lap 1 chain (continues from total; acc is not reset: smc.cljc:133-136)
+    for (int64_t t = 0; t < nt; ++t) {
+        int64_t lo = t * tile, hi = lo + tile < n ? lo + tile : n;
+        sin1[t] = S;
+        if (S > comb.xlast) { sin1[t + 1] = S; for (int64_t q = t + 1; q <= nt; ++q) sin1[q] = S; break; }
+        int cls = classify_tile(atot + ain[t], atot + ain[t + 1], n + hi);
+        if (cls == kCtxHard) {
+            ++hard1;
+            S = tile_exact_fold(S, w + lo, (int)(hi - lo), edges.data(), &iters);
+        } else {
+            if (ctx_of(S) != cls) return -14;
+            Xd a = xd_identity();
+            for (int64_t i = lo; i < hi; ++i) {
+                i64 f; int up, tie;
+                quantize(w[i], cls, f, up, tie);
+                xd_push(a, f, up, tie);
+            }
+            i64 s = xd_apply(units_of(S), a);
+            if (s >= kTwo53) return -15;
+            S = from_units(s, cls);
+        }
+        sin1[t + 1] = S;
+    }
+    // ---- replay: per element exact edges -> counts -> emission
+    int hint = 0;
+    const int64_t J = comb_count_below(comb, total, hint);
+    int64_t written = 0;
+    for (int lapi = 0; lapi < 2; ++lapi) {
+        hint = 0;
+        for (int64_t t = 0; t < nt; ++t) {
+            int64_t lo = t * tile, hi = lo + tile < n ? lo + tile : n;
+            double Sin = lapi ? sin1[t] : sin0[t];
+            if (lapi && Sin > comb.xlast) break;
+            tile_exact_fold(Sin, w + lo, (int)(hi - lo), edges.data(), nullptr);
+            int64_t c_prev = comb_count_below(comb, Sin, hint);
+            for (int64_t i = lo; i < hi; ++i) {
+                int64_t c = comb_count_below(comb, edges[i - lo], hint);
+                if (lapi == 0 && c > J) return -16;
+                for (int64_t j = c_prev; j < c; ++j) {
+                    if (j >= n_new) return -17;
+                    emission[j] = (int32_t)i;
+                    lap_out[j] = lapi;
+                    ++written;
+                }
+                c_prev = c;
+            }
+        }
+    }
+    if (written != n_new) return -18;
+    if (stats) { stats[0] = hard0; stats[1] = hard1; stats[2] = iters; stats[3] = comb.nseg; }
+    return 0;
+}
+
+// exact comb values, for direct comparison with repeated addition
+void host_comb_values(double total, double u, int64_t n_new, double* out) {
+    Comb comb;
+    comb_build(comb, total, u, n_new);
+    for (int64_t j = 0; j < n_new; ++j) out[j] = comb_value(comb, j);
+}
+
+} // extern "C"
