@@ -1,0 +1,197 @@
+// apop_internal.cuh — context, workspace and small device helpers shared by
+// the translation units of libanglican_pop.so.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string>
+#include <vector>
+
+#include "../../include/anglican_pop.h"
+#include "exact_fold.cuh"
+
+namespace apop {
+
+constexpr int TB = 512;          // threads per tile CTA
+constexpr int IPT = 8;           // elements per thread (blocked arrangement)
+constexpr int TILE = TB * IPT;   // particles per tile
+constexpr int NWARP = TB / 32;
+
+// error bits raised by kernels
+enum {
+    EB_NAN = 1,          // NaN log-weight
+    EB_ZERO = 2,         // total weight not > 0 / not finite
+    EB_CTX = 4,          // classification / chain context mismatch (internal)
+    EB_COMB = 8,         // comb table overflow / stuck comb
+    EB_COUNT = 16        // emitted offspring count mismatch (internal)
+};
+
+struct ResampleInfo {
+    double m;            // max log-weight (0 in explicit-weights mode)
+    double atot;         // approximate total weight (tree sum)
+    double asq;          // approximate sum of squared weights
+    double ess;
+    double log_mean_approx;
+    double u;            // resampling uniform
+    double total;        // exact sequential-fold total (smc.cljc:94)
+    double step;         // total / n_new
+    double new_lw;       // log(step) + m  (smc.cljc:98-103)
+    double wx_sum[4];    // spare accumulators (filtering mean numerator, ...)
+    long long J;         // emissions of the first lap
+    long long n_new;
+    int err;
+    int nh0, nh1;        // hard tile counts per lap
+    int first_skip1;     // first tile skipped in lap 1
+    int weights_mode;
+    int pad;
+};
+
+struct Column {
+    void* ptr = nullptr;
+    int dtype = 0;
+    int width = 0;
+    bool used = false;
+};
+
+struct Timer {
+    cudaEvent_t a = nullptr, b = nullptr;
+    double total_ms = 0.0;
+    int64_t count = 0;
+    bool open = false;
+    std::vector<std::pair<cudaEvent_t, cudaEvent_t>> pending;
+};
+
+struct ParamArena {
+    char* dev = nullptr;
+    char* host = nullptr;
+    size_t cap = 0, off = 0;
+};
+
+struct ResampleWS {
+    int64_t nt = 0;
+    double *tmax = nullptr, *tsum = nullptr, *tsum2 = nullptr, *ain = nullptr;
+    int *cls0 = nullptr, *cls1 = nullptr, *hard0 = nullptr, *hard1 = nullptr;
+    Xd *agg0 = nullptr, *agg1 = nullptr;
+    double *sin0 = nullptr, *sin1 = nullptr;
+    Comb* comb = nullptr;
+    ResampleInfo* info = nullptr;      // device
+    ResampleInfo* info_host = nullptr; // pinned
+    double* edges = nullptr;           // multinomial only, lazily allocated
+};
+
+} // namespace apop
+
+struct apop_ctx {
+    int device = 0;
+    int rank = 0, world = 1;
+    int64_t n = 0;            // local particles
+    int64_t n_global = 0;
+    int64_t g0 = 0;           // global id of local particle 0
+    uint64_t seed = 0;
+    uint32_t step = 0;
+    cudaStream_t stream = nullptr;
+    std::string err;
+    std::vector<apop::Column> cols;
+    int64_t launches = 0;
+    apop::ResampleWS ws;
+    void* scratch = nullptr;      // gather scratch
+    size_t scratch_bytes = 0;
+    apop::Timer timers[16];
+    void* nccl = nullptr;         // ncclComm_t
+    apop::ParamArena arena;       // staged distribution parameters
+    // last fused sweep
+    struct SweepState* sweep = nullptr;
+};
+
+namespace apop {
+
+int set_err(apop_ctx* c, int code, const char* fmt, ...);
+#define APOP_CUDA(ctx, call)                                                        \
+    do {                                                                            \
+        cudaError_t e__ = (call);                                                   \
+        if (e__ != cudaSuccess)                                                     \
+            return apop::set_err(ctx, APOP_ERR_CUDA, "%s failed: %s (%s:%d)", #call, \
+                                 cudaGetErrorString(e__), __FILE__, __LINE__);      \
+    } while (0)
+#define APOP_TRY(expr)               \
+    do {                             \
+        int rc__ = (expr);           \
+        if (rc__ != APOP_OK) return rc__; \
+    } while (0)
+
+Column* get_col(apop_ctx* c, apop_col h, int dtype, int width);
+int ensure_scratch(apop_ctx* c, size_t bytes);
+int ensure_resample_ws(apop_ctx* c);
+int param_upload(apop_ctx* c, const void* host, size_t bytes, void** dev);
+
+// resample pipeline entry points (resample.cu)
+struct ResampleArgs {
+    const double* lw;        // log-weights (or NULL in weights mode)
+    const double* w;         // explicit weights (weights mode)
+    int64_t n;
+    int64_t n_new;
+    double u;                // NaN -> draw from stream
+    int order;
+    int32_t* anc_out;        // n_new entries
+    int64_t out_offset;      // added to every written slot (CSMC keeps slot 0)
+    bool have_partials;      // tile partials (tmax/tsum/tsum2) already in ws
+};
+int resample_enqueue(apop_ctx* c, const ResampleArgs& a);
+int resample_fetch_info(apop_ctx* c, ResampleInfo* out);   // syncs
+int info_to_status(apop_ctx* c, const ResampleInfo& info);
+int multinomial_enqueue(apop_ctx* c, const double* lw, const double* w, const double* uni,
+                        int64_t n_new, int32_t* anc);
+int gather_enqueue(apop_ctx* c, const int32_t* anc, int64_t n_new, Column* col);
+
+// ---------------------------------------------------------------- device
+#if defined(__CUDACC__)
+
+__device__ __forceinline__ double weight_from_lw(double lw, double m) {
+    // smc.cljc:78-82
+    if (lw == m) return 1.0;
+    if (!(lw > -INFINITY)) return 0.0;
+    return exp(lw - m);
+}
+
+// blocked load of IPT consecutive doubles per thread; out-of-range -> fill
+__device__ __forceinline__ void load_blocked(const double* __restrict__ p, int64_t base,
+                                             int64_t n, double (&v)[IPT], double fill) {
+    const int64_t i0 = base + (int64_t)threadIdx.x * IPT;
+    if (i0 + IPT <= n && ((((uintptr_t)(p + i0)) & 15) == 0)) {
+        const double2* q = reinterpret_cast<const double2*>(p + i0);
+#pragma unroll
+        for (int j = 0; j < IPT / 2; ++j) {
+            double2 t = __ldg(q + j);
+            v[2 * j] = t.x;
+            v[2 * j + 1] = t.y;
+        }
+    } else {
+#pragma unroll
+        for (int j = 0; j < IPT; ++j) v[j] = (i0 + j < n) ? p[i0 + j] : fill;
+    }
+}
+
+__device__ __forceinline__ double warp_max(double v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v = fmax(v, __shfl_xor_sync(0xffffffffu, v, o));
+    return v;
+}
+__device__ __forceinline__ double warp_sum(double v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+__device__ __forceinline__ i64 shfl_up_i64(i64 v, int d) {
+    int lo = __shfl_up_sync(0xffffffffu, (int)(v & 0xffffffffLL), d);
+    int hi = __shfl_up_sync(0xffffffffu, (int)(v >> 32), d);
+    return ((i64)hi << 32) | (u64)(unsigned)lo;
+}
+__device__ __forceinline__ i64 shfl_i64(i64 v, int src) {
+    int lo = __shfl_sync(0xffffffffu, (int)(v & 0xffffffffLL), src);
+    int hi = __shfl_sync(0xffffffffu, (int)(v >> 32), src);
+    return ((i64)hi << 32) | (u64)(unsigned)lo;
+}
+
+#endif // __CUDACC__
+
+} // namespace apop

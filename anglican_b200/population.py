@@ -1,0 +1,250 @@
+"""Device-resident particle population: the host-side handle over one apop_ctx.
+
+Mirrors the data plane of the reference's particle list: the `:log-weight`
+field of every particle's state map (src/anglican/state.cljc:22-36) and any
+per-particle program values become SoA columns in HBM.
+"""
+import ctypes as C
+import math
+
+import numpy as np
+
+from . import _lib as L
+
+
+class Column:
+    """A device column (f64 or i32, `width` values per particle)."""
+
+    def __init__(self, pop, handle, dtype, width):
+        self.pop, self.handle, self.dtype, self.width = pop, handle, dtype, width
+
+    @property
+    def np_dtype(self):
+        return np.float64 if self.dtype == L.F64 else np.int32
+
+    def upload(self, data):
+        a = np.ascontiguousarray(data, dtype=self.np_dtype)
+        L.check(self.pop.ctx, self.pop.lib.apop_column_upload(
+            self.pop.ctx, self.handle, a.ctypes.data_as(C.c_void_p), a.size))
+        return self
+
+    def download(self, n=None):
+        n = self.pop.n if n is None else n
+        out = np.empty(n * self.width, dtype=self.np_dtype)
+        L.check(self.pop.ctx, self.pop.lib.apop_column_download(
+            self.pop.ctx, self.handle, out.ctypes.data_as(C.c_void_p), out.size))
+        return out.reshape(n, self.width) if self.width > 1 else out
+
+    def fill(self, v):
+        L.check(self.pop.ctx, self.pop.lib.apop_column_fill(self.pop.ctx, self.handle, float(v)))
+        return self
+
+    def free(self):
+        if self.handle is not None:
+            L.check(self.pop.ctx, self.pop.lib.apop_column_free(self.pop.ctx, self.handle))
+            self.handle = None
+
+
+def _arg(v):
+    """scalar or Column -> ApopArg"""
+    if isinstance(v, Column):
+        return L.ApopArg(v.handle, 0.0)
+    return L.ApopArg(-1, float(v))
+
+
+def _dp(a):
+    return None if a is None else a.ctypes.data_as(L.c_double_p)
+
+
+class Population:
+    def __init__(self, n, seed=0xA11CE, device=0, rank=0, world=1, nccl_id=None):
+        self.lib = L.load()
+        self.ctx = C.c_void_p()
+        idbuf = None
+        if nccl_id is not None:
+            idbuf = C.create_string_buffer(bytes(nccl_id), 128)
+        rc = self.lib.apop_create(C.byref(self.ctx), int(n), int(seed), int(device), int(rank),
+                                  int(world), idbuf)
+        if rc != L.APOP_OK:
+            raise L.ApopError(rc, "apop_create failed (no CUDA device? there is no CPU fallback)")
+        self.n = int(n)
+        self.seed = int(seed)
+        self.rank, self.world = rank, world
+
+    # ------------------------------------------------------------ lifecycle
+    def close(self):
+        if self.ctx:
+            self.lib.apop_destroy(self.ctx)
+            self.ctx = C.c_void_p()
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def synchronize(self):
+        L.check(self.ctx, self.lib.apop_synchronize(self.ctx))
+
+    @property
+    def launches(self):
+        return int(self.lib.apop_launch_count(self.ctx))
+
+    def set_step(self, t):
+        L.check(self.ctx, self.lib.apop_set_step(self.ctx, int(t)))
+
+    # timers on the ctx stream
+    def timer_begin(self, tag):
+        L.check(self.ctx, self.lib.apop_timer_begin(self.ctx, tag))
+
+    def timer_end(self, tag):
+        L.check(self.ctx, self.lib.apop_timer_end(self.ctx, tag))
+
+    def timer_ms(self, tag):
+        ms, cnt = C.c_double(), C.c_int64()
+        L.check(self.ctx, self.lib.apop_timer_elapsed_ms(self.ctx, tag, C.byref(ms), C.byref(cnt)))
+        return ms.value, cnt.value
+
+    def timer_reset(self):
+        L.check(self.ctx, self.lib.apop_timer_reset(self.ctx))
+
+    # ------------------------------------------------------------ columns
+    def column(self, dtype=L.F64, width=1, data=None, fill=None):
+        h = C.c_int32()
+        L.check(self.ctx, self.lib.apop_column_alloc(self.ctx, dtype, width, C.byref(h)))
+        col = Column(self, h.value, dtype, width)
+        if data is not None:
+            col.upload(data)
+        elif fill is not None:
+            col.fill(fill)
+        return col
+
+    # ------------------------------------------------------------ weights
+    def normalize(self, logw):
+        m, lm, ess = C.c_double(), C.c_double(), C.c_double()
+        L.check(self.ctx, self.lib.apop_normalize(self.ctx, logw.handle, C.byref(m), C.byref(lm),
+                                                  C.byref(ess)))
+        return m.value, lm.value, ess.value
+
+    def resample(self, logw, u=math.nan, n_new=None, scheme=L.SYSTEMATIC, order=L.ORDER_REFERENCE,
+                 anc=None):
+        n_new = self.n if n_new is None else n_new
+        anc = anc or self.column(L.I32)
+        new_lw, j = C.c_double(), C.c_int64()
+        L.check(self.ctx, self.lib.apop_resample(self.ctx, logw.handle, scheme, float(u), n_new,
+                                                 order, anc.handle, C.byref(new_lw), C.byref(j)))
+        return anc, new_lw.value, j.value
+
+    def resample_weights(self, w, u=math.nan, n_new=None, scheme=L.SYSTEMATIC,
+                         order=L.ORDER_REFERENCE, anc=None):
+        n_new = self.n if n_new is None else n_new
+        anc = anc or self.column(L.I32)
+        total, j = C.c_double(), C.c_int64()
+        L.check(self.ctx, self.lib.apop_resample_weights(self.ctx, w.handle, scheme, float(u),
+                                                         n_new, order, anc.handle,
+                                                         C.byref(total), C.byref(j)))
+        return anc, total.value, j.value
+
+    def resample_multinomial_u(self, w, uniforms, n_new=None, anc=None):
+        n_new = self.n if n_new is None else n_new
+        anc = anc or self.column(L.I32)
+        L.check(self.ctx, self.lib.apop_resample_multinomial_u(self.ctx, w.handle, uniforms.handle,
+                                                               n_new, anc.handle))
+        return anc
+
+    def gather(self, anc, cols, n_new=None):
+        n_new = self.n if n_new is None else n_new
+        arr = (C.c_int32 * len(cols))(*[c.handle for c in cols])
+        L.check(self.ctx, self.lib.apop_gather(self.ctx, anc.handle, n_new, arr, len(cols)))
+
+    # ------------------------------------------------------------ distributions
+    def sample_normal(self, mean, sd, out, draw=0):
+        L.check(self.ctx, self.lib.apop_sample_normal(self.ctx, _arg(mean), _arg(sd), draw, out.handle))
+
+    def observe_normal(self, mean, sd, value, logw):
+        L.check(self.ctx, self.lib.apop_observe_normal(self.ctx, _arg(mean), _arg(sd), _arg(value),
+                                                       logw.handle))
+
+    def sample_gamma(self, shape, rate, out, draw=0):
+        L.check(self.ctx, self.lib.apop_sample_gamma(self.ctx, _arg(shape), _arg(rate), draw, out.handle))
+
+    def observe_gamma(self, shape, rate, value, logw):
+        L.check(self.ctx, self.lib.apop_observe_gamma(self.ctx, _arg(shape), _arg(rate), _arg(value),
+                                                      logw.handle))
+
+    def sample_beta(self, a, b, out, draw=0):
+        L.check(self.ctx, self.lib.apop_sample_beta(self.ctx, _arg(a), _arg(b), draw, out.handle))
+
+    def observe_beta(self, a, b, value, logw):
+        L.check(self.ctx, self.lib.apop_observe_beta(self.ctx, _arg(a), _arg(b), _arg(value),
+                                                     logw.handle))
+
+    def sample_uniform(self, lo, hi, out, draw=0):
+        L.check(self.ctx, self.lib.apop_sample_uniform(self.ctx, _arg(lo), _arg(hi), draw, out.handle))
+
+    def observe_uniform(self, lo, hi, value, logw):
+        L.check(self.ctx, self.lib.apop_observe_uniform(self.ctx, _arg(lo), _arg(hi), _arg(value),
+                                                        logw.handle))
+
+    def sample_discrete(self, weights, out, draw=0):
+        if isinstance(weights, Column):
+            L.check(self.ctx, self.lib.apop_sample_discrete(self.ctx, None, weights.width,
+                                                            weights.handle, draw, out.handle))
+        else:
+            w = np.ascontiguousarray(weights, dtype=np.float64)
+            L.check(self.ctx, self.lib.apop_sample_discrete(self.ctx, _dp(w), w.size, -1, draw,
+                                                            out.handle))
+
+    def observe_discrete(self, weights, value, logw):
+        vcol, vs = (value.handle, 0) if isinstance(value, Column) else (-1, int(value))
+        if isinstance(weights, Column):
+            L.check(self.ctx, self.lib.apop_observe_discrete(self.ctx, None, weights.width,
+                                                             weights.handle, vcol, vs, logw.handle))
+        else:
+            w = np.ascontiguousarray(weights, dtype=np.float64)
+            L.check(self.ctx, self.lib.apop_observe_discrete(self.ctx, _dp(w), w.size, -1, vcol, vs,
+                                                             logw.handle))
+
+    def sample_dirichlet(self, alpha, out, draw=0):
+        a = np.ascontiguousarray(alpha, dtype=np.float64)
+        L.check(self.ctx, self.lib.apop_sample_dirichlet(self.ctx, _dp(a), a.size, draw, out.handle))
+
+    def observe_dirichlet(self, alpha, value, logw):
+        a = np.ascontiguousarray(alpha, dtype=np.float64)
+        L.check(self.ctx, self.lib.apop_observe_dirichlet(self.ctx, _dp(a), a.size, value.handle,
+                                                          logw.handle))
+
+    def sample_mvn(self, mean, cov, out, draw=0):
+        cov = np.ascontiguousarray(cov, dtype=np.float64)
+        d = cov.shape[0]
+        if isinstance(mean, Column):
+            L.check(self.ctx, self.lib.apop_sample_mvn(self.ctx, None, mean.handle, _dp(cov), d,
+                                                       draw, out.handle))
+        else:
+            m = np.ascontiguousarray(mean, dtype=np.float64)
+            L.check(self.ctx, self.lib.apop_sample_mvn(self.ctx, _dp(m), -1, _dp(cov), d, draw,
+                                                       out.handle))
+
+    def observe_mvn(self, mean, cov, value, logw):
+        cov = np.ascontiguousarray(cov, dtype=np.float64)
+        d = cov.shape[0]
+        mh, mp, vh, vp = -1, None, -1, None
+        keep = []
+        if isinstance(mean, Column):
+            mh = mean.handle
+        else:
+            keep.append(np.ascontiguousarray(mean, dtype=np.float64))
+            mp = _dp(keep[-1])
+        if isinstance(value, Column):
+            vh = value.handle
+        else:
+            keep.append(np.ascontiguousarray(value, dtype=np.float64))
+            vp = _dp(keep[-1])
+        L.check(self.ctx, self.lib.apop_observe_mvn(self.ctx, mp, mh, _dp(cov), d, vp, vh,
+                                                    logw.handle))

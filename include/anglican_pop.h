@@ -1,0 +1,218 @@
+/*
+ * anglican_pop.h — C ABI of libanglican_pop.so, the B200-native particle-
+ * population engine that sits behind Anglican's `infer` multimethod
+ * (reference src/anglican/inference.cljc:25-28) for :smc / :pimh / :pgibbs /
+ * :ipmcmc, and behind the `anglican.runtime` distribution protocol
+ * (`sample*` / `observe*`, src/anglican/runtime.cljc:119-124).
+ *
+ * Conventions
+ *  - extern "C", plain pointers and sizes, no C++/torch types.
+ *  - every function returns an int status (APOP_OK == 0, errors < 0) and never
+ *    throws; apop_last_error(ctx) gives the message of the last failure.
+ *  - an apop_ctx owns one CUDA stream, (optionally) one NCCL communicator and
+ *    all device memory of one particle population shard.  One ctx per host
+ *    thread; ctxs are independent (IPMCMC: one ctx per node).
+ *  - particle data live in device-resident columns addressed by integer
+ *    handles (SoA; f64 or i32; `width` values per particle, row-major).
+ *  - host scalars in/out are caller-owned; an output pointer may be NULL when
+ *    the value is not wanted (then the call does not synchronise).
+ *  - there is NO CPU fallback: without a CUDA device every compute entry point
+ *    fails with APOP_ERR_CUDA.
+ *
+ * The reference is pure Clojure and has no FFI; INTEGRATION.md shows the
+ * JNI/Panama binding a maintainer would add (clj/anglican/gpu.clj sketch).
+ */
+#ifndef ANGLICAN_POP_H
+#define ANGLICAN_POP_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct apop_ctx apop_ctx;
+typedef int32_t apop_col;
+
+enum {
+    APOP_OK = 0,
+    APOP_ERR_INVALID = -1,      /* bad argument / handle */
+    APOP_ERR_CUDA = -2,         /* CUDA runtime failure or no device */
+    APOP_ERR_NAN_WEIGHT = -3,   /* a log-weight is NaN (reference: resample never terminates) */
+    APOP_ERR_ZERO_WEIGHT = -4,  /* total weight not > 0 or not finite */
+    APOP_ERR_NCCL = -5,
+    APOP_ERR_OOM = -6,
+    APOP_ERR_UNSUPPORTED = -7,
+    APOP_ERR_INTERNAL = -8,     /* internal consistency check failed */
+    APOP_ERR_NOT_GLOBAL = -9    /* "some `observe' directives are not global" smc.cljc:48-51 */
+};
+
+enum { APOP_F64 = 0, APOP_I32 = 1 };
+
+/* resampling schemes: systematic = smc.cljc:86-137; multinomial = n_new
+ * independent `discrete` draws (runtime.cljc:277-287, inference.cljc:144-147) */
+enum { APOP_SYSTEMATIC = 0, APOP_MULTINOMIAL = 1 };
+
+/* output order of ancestor indices.
+ * REFERENCE: the list returned by smc.cljc resample (offspring prepended:
+ * emission order reversed).  SORTED: the engine's physical order (ancestors
+ * monotone non-decreasing: second-lap emissions first, then first-lap). */
+enum { APOP_ORDER_REFERENCE = 0, APOP_ORDER_SORTED = 1, APOP_ORDER_EMISSION = 2 };
+
+/* A distribution parameter / observed value: per-particle column or scalar
+ * broadcast to all particles (col < 0 => scalar). */
+typedef struct {
+    apop_col col;
+    double scalar;
+} apop_arg;
+
+/* ---- lifecycle --------------------------------------------------------- */
+int apop_version(void);
+int apop_device_count(void);
+/* nccl_id: 128-byte ncclUniqueId shared by all ranks, or NULL when world==1 */
+int apop_create(apop_ctx** out, int64_t n_particles_local, uint64_t seed, int device,
+                int rank, int world, const void* nccl_id);
+int apop_destroy(apop_ctx* ctx);
+const char* apop_last_error(apop_ctx* ctx);
+int apop_get_unique_id(void* out_128_bytes);
+int apop_synchronize(apop_ctx* ctx);
+int64_t apop_num_particles(apop_ctx* ctx);
+/* number of kernels this ctx has launched so far (bench `gpu_launches`) */
+int64_t apop_launch_count(apop_ctx* ctx);
+/* raw CUDA stream (cudaStream_t) so callers can record events on it */
+void* apop_stream(apop_ctx* ctx);
+/* elapsed device ms of the last timed region for tag (see apop_timer_*) */
+int apop_timer_begin(apop_ctx* ctx, int tag);
+int apop_timer_end(apop_ctx* ctx, int tag);
+int apop_timer_elapsed_ms(apop_ctx* ctx, int tag, double* total_ms, int64_t* count);
+int apop_timer_reset(apop_ctx* ctx);
+
+/* ---- columns (state.cljc:9-36: the :log-weight field becomes a column) -- */
+int apop_column_alloc(apop_ctx* ctx, int dtype, int width, apop_col* out);
+int apop_column_free(apop_ctx* ctx, apop_col col);
+int apop_column_upload(apop_ctx* ctx, apop_col col, const void* host, int64_t n_values);
+int apop_column_download(apop_ctx* ctx, apop_col col, void* host, int64_t n_values);
+int apop_column_fill(apop_ctx* ctx, apop_col col, double value);
+int apop_column_device_ptr(apop_ctx* ctx, apop_col col, void** out);
+
+/* ---- runtime distributions (runtime.cljc) ------------------------------
+ * sample:  out[k] <- draw            (inference.cljc:46-47)
+ * observe: logw[k] += log p(value)   (smc.cljc:23-27, state.cljc:27-31)
+ * `draw_id` distinguishes successive sample statements of one program step
+ * (counter-based RNG: key = seed, counter = (slot, step, stream, draw)). */
+int apop_set_step(apop_ctx* ctx, uint32_t step);
+int apop_sample_normal(apop_ctx* ctx, apop_arg mean, apop_arg sd, uint32_t draw_id, apop_col out);
+int apop_observe_normal(apop_ctx* ctx, apop_arg mean, apop_arg sd, apop_arg value, apop_col logw);
+int apop_sample_gamma(apop_ctx* ctx, apop_arg shape, apop_arg rate, uint32_t draw_id, apop_col out);
+int apop_observe_gamma(apop_ctx* ctx, apop_arg shape, apop_arg rate, apop_arg value, apop_col logw);
+int apop_sample_beta(apop_ctx* ctx, apop_arg alpha, apop_arg beta, uint32_t draw_id, apop_col out);
+int apop_observe_beta(apop_ctx* ctx, apop_arg alpha, apop_arg beta, apop_arg value, apop_col logw);
+int apop_sample_uniform(apop_ctx* ctx, apop_arg lo, apop_arg hi, uint32_t draw_id, apop_col out);
+int apop_observe_uniform(apop_ctx* ctx, apop_arg lo, apop_arg hi, apop_arg value, apop_col logw);
+/* discrete / categorical: weights either shared (host array of k doubles,
+ * weights_col < 0) or per particle (f64 column of width k).  Values are i32
+ * indices; out-of-range / -1 observe gives -inf (runtime.cljc:266-290). */
+int apop_sample_discrete(apop_ctx* ctx, const double* weights, int k, apop_col weights_col,
+                         uint32_t draw_id, apop_col out_i32);
+int apop_observe_discrete(apop_ctx* ctx, const double* weights, int k, apop_col weights_col,
+                          apop_col value_i32, int32_t value_scalar, apop_col logw);
+/* dirichlet (runtime.cljc:292-306): alpha shared (host, k); values are f64
+ * columns of width k */
+int apop_sample_dirichlet(apop_ctx* ctx, const double* alpha, int k, uint32_t draw_id, apop_col out);
+int apop_observe_dirichlet(apop_ctx* ctx, const double* alpha, int k, apop_col value, apop_col logw);
+/* mvn (runtime.cljc:349-368): cov is d*d row-major on the host (upper
+ * triangle read); mean/value: shared host vector (col < 0) or f64 column of
+ * width d. */
+int apop_sample_mvn(apop_ctx* ctx, const double* mean, apop_col mean_col, const double* cov,
+                    int d, uint32_t draw_id, apop_col out);
+int apop_observe_mvn(apop_ctx* ctx, const double* mean, apop_col mean_col, const double* cov,
+                     int d, const double* value, apop_col value_col, apop_col logw);
+
+/* ---- weights: particle-weights / log-sum-exp / ESS ---------------------
+ * smc.cljc:70-84, runtime.cljc:130-138, inference.cljc:181-186,
+ * test/anglican/dist_test.cljc:83-94.
+ *   max_lw      = max_k logw[k]
+ *   log_mean_w  = log(sum_k exp(logw[k]-max)/N) + max   (== log-marginal)
+ *   ess         = (sum w)^2 / sum w^2 */
+int apop_normalize(apop_ctx* ctx, apop_col logw, double* max_lw, double* log_mean_w, double* ess);
+
+/* ---- resample (smc.cljc:86-137) ----------------------------------------
+ * u: the uniform of `(rand total-weight)` (inference.cljc:124-129); NaN =>
+ *    drawn from the ctx stream for the current step.
+ * n_new: number of offspring (N, or N-1 for conditional SMC, pgibbs.cljc:92-99)
+ * anc_out: i32 column, receives n_new indices in `order`.
+ * new_logw: log(step)+max, or -inf when max is not finite (smc.cljc:98-103).
+ * n_first_lap: #offspring emitted before the wheel wrapped (defines the
+ *    closed-form permutation between the three orders).
+ * Ancestors are bit-identical to the reference's sequential fp64 wheel on the
+ * same weights and uniform. */
+int apop_resample(apop_ctx* ctx, apop_col logw, int scheme, double u, int64_t n_new, int order,
+                  apop_col anc_out, double* new_logw, int64_t* n_first_lap);
+/* same on explicit fp64 weights (already max-normalised or not) */
+int apop_resample_weights(apop_ctx* ctx, apop_col weights, int scheme, double u, int64_t n_new,
+                          int order, apop_col anc_out, double* total, int64_t* n_first_lap);
+/* multinomial with one supplied uniform per offspring (f64 column) */
+int apop_resample_multinomial_u(apop_ctx* ctx, apop_col weights, apop_col uniforms,
+                                int64_t n_new, apop_col anc_out);
+/* x_new[k] = x[anc[k]] for each listed column (in place; uses ctx scratch) */
+int apop_gather(apop_ctx* ctx, apop_col anc, int64_t n_new, const apop_col* cols, int ncols);
+
+/* ---- fused state-space sweeps (the benchmark fast path) -----------------
+ * One call = one `sweep` (smc.cljc:35-51 / pgibbs.cljc:76-110 /
+ * ipmcmc.cljc:34-83) of a program of the shape
+ *   x0 <- sample; for y_t: x_t <- sample(.|x_{t-1}); observe(.|x_t) y_t
+ * with every particle at the same global observe (smc.cljc:41-51). */
+enum { APOP_SSM_LGSSM1D = 1, APOP_SSM_SV = 2, APOP_SSM_HMM = 3, APOP_SSM_LGMVN = 4 };
+
+typedef struct {
+    int32_t kind;
+    int32_t dim;               /* state dimension; K for HMM */
+    double m0, s0, a, b, q;    /* x0~N(m0,s0); x' = a x + b + q e */
+    double c, d, r, beta;      /* LGSSM1D: y~N(c x+d, r);  SV: y~N(0, beta exp(x/2)) */
+    const double* hmm_init;    /* [K] */
+    const double* hmm_trans;   /* [K*K] row major */
+    const double* hmm_mu;      /* [K] */
+    const double* hmm_sd;      /* [K] */
+    const double* A;           /* [d*d] */
+    const double* Lq;          /* [d*d] lower factor of process cov */
+    const double* R;           /* [d*d] observation cov */
+} apop_ssm;
+
+typedef struct {
+    int32_t csmc;              /* conditional sweep: retained particle in slot 0 */
+    int32_t n_cond_steps;      /* observes using the conditional resample */
+    int32_t reset_weights;     /* pgibbs.cljc:88 */
+    int32_t keep_history;      /* keep ancestors (+ states) for lineage tracing */
+    int32_t use_graph;         /* capture the step loop in a CUDA graph */
+    int32_t want_final;        /* gather final states into x_final */
+} apop_sweep_opts;
+
+typedef struct {
+    double log_z;              /* sum of per-step log-mean-weights */
+    double* log_mean_w;        /* [T] or NULL */
+    double* ess;               /* [T] or NULL */
+    double* filt_mean;         /* [T*dim] or NULL */
+    double* x_final;           /* [n*dim] host or NULL */
+} apop_sweep_result;
+
+int apop_smc_sweep(apop_ctx* ctx, const apop_ssm* model, const double* y, int32_t T,
+                   const double* retained, const apop_sweep_opts* opts,
+                   apop_sweep_result* result);
+/* lineage (x_0..x_T) of final slot `slot` of the last keep_history sweep */
+int apop_trace_lineage(apop_ctx* ctx, int64_t slot, double* out_traj);
+/* device pointer of the final state column of the last sweep (n*dim f64) */
+int apop_sweep_final_device(apop_ctx* ctx, void** out);
+
+/* ---- PIMH / IPMCMC scalars (host arithmetic, restated on the host side) -
+ * accept?: lmh.cljc:146-151; gibbs-update-csmc-indices: ipmcmc.cljc:106-146
+ * with the intended sampling rule; exchange: the only data
+ * that crosses nodes, ipmcmc.cljc:183-187. */
+int apop_pimh_accept(double next_log_z, double prev_log_z, double uniform);
+int apop_ipmcmc_gibbs(const double* log_zs, int m, int p, const double* uniforms,
+                      int32_t* csmc_idx, double* zeta_sums);
+int apop_ipmcmc_exchange_logz(apop_ctx* ctx, const double* local, int n_local, double* out_all);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

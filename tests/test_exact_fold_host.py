@@ -1,0 +1,70 @@
+"""CPU check of anglican_b200/csrc/exact_fold.cuh (the arithmetic the CUDA
+resampler is built on) against the oracle's literal wheel, via the sequential
+emulation in tests/host/exact_fold_host.cpp."""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+from oracle import pyoracle as orc
+from tests.weights_cases import U_VALUES, families
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+SRC = os.path.join(HERE, "host", "exact_fold_host.cpp")
+OUT = os.path.join(HERE, "host", "_build", "libexact_fold_host.so")
+HDR = os.path.join(HERE, "..", "anglican_b200", "csrc", "exact_fold.cuh")
+dp, ip, lp = C.POINTER(C.c_double), C.POINTER(C.c_int32), C.POINTER(C.c_int64)
+
+
+@pytest.fixture(scope="module")
+def host():
+    os.makedirs(os.path.dirname(OUT), exist_ok=True)
+    if (not os.path.exists(OUT) or os.path.getmtime(OUT) < max(os.path.getmtime(SRC),
+                                                               os.path.getmtime(HDR))):
+        subprocess.check_call(["g++", "-O2", "-std=c++17", "-ffp-contract=off", "-fPIC", "-shared",
+                               "-x", "c++", SRC, "-o", OUT])
+    lib = C.CDLL(OUT)
+    lib.host_exact_resample.argtypes = [dp, C.c_int64, C.c_int64, C.c_double, C.c_int, ip, ip, dp, lp]
+    lib.host_comb_values.argtypes = [C.c_double, C.c_double, C.c_int64, dp]
+    return lib
+
+
+def _run(lib, w, n_new, u, tile):
+    w = np.ascontiguousarray(w, dtype=np.float64)
+    em = np.full(n_new, -1, np.int32)
+    lap = np.full(n_new, -1, np.int32)
+    tot = C.c_double()
+    st = (C.c_int64 * 4)()
+    rc = lib.host_exact_resample(w.ctypes.data_as(dp), w.size, n_new, u, tile,
+                                 em.ctypes.data_as(ip), lap.ctypes.data_as(ip), C.byref(tot), st)
+    return rc, em, lap, tot.value
+
+
+@pytest.mark.parametrize("n", [1, 2, 3, 17, 256, 257, 4097, 30011])
+def test_exact_fold_emulation_bit_exact(host, n):
+    rng = np.random.default_rng(n)
+    for name, w in families(n, rng).items():
+        for u in U_VALUES:
+            for n_new in sorted({n, max(1, n - 1), 7}):
+                for tile in (256, 4096):
+                    ref = orc.resample_weights(w, n_new, u)
+                    rc, em, lap, tot = _run(host, w, n_new, u, tile)
+                    assert rc == 0, (name, u, n_new, rc)
+                    assert tot == ref["total"]
+                    assert np.array_equal(em, ref["emission"]), (name, u, n_new, tile)
+                    assert np.array_equal(lap, ref["lap"])
+
+
+def test_comb_closed_form_equals_repeated_addition(host):
+    for tot, u, n in [(1234.567, 0.3, 100000), (1.0, 0.0, 1000), (7.3e5, 1 - 2 ** -53, 300000),
+                      (3.0, 1e-300, 1000), (2.0 ** 20, 0.5, 2 ** 20), (0.1, 0.999, 77777)]:
+        out = np.empty(n)
+        host.host_comb_values(tot, u, n, out.ctypes.data_as(dp))
+        step, x = tot / float(n), tot * u
+        ref = np.empty(n)
+        for j in range(n):
+            ref[j] = x
+            x = x + step
+        assert np.array_equal(out, ref), (tot, u, n)
