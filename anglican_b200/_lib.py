@@ -64,6 +64,7 @@ _SIGS = [
     ("apop_get_unique_id", C.c_int, [_vp]),
     ("apop_synchronize", C.c_int, [_vp]),
     ("apop_num_particles", C.c_int64, [_vp]),
+    ("apop_set_seed", C.c_int, [_vp, C.c_uint64]),
     ("apop_launch_count", C.c_int64, [_vp]),
     ("apop_stream", _vp, [_vp]),
     ("apop_timer_begin", C.c_int, [_vp, C.c_int]),
@@ -104,6 +105,7 @@ _SIGS = [
     ("apop_smc_sweep", C.c_int, [_vp, C.POINTER(ApopSSM), c_double_p, C.c_int32, c_double_p,
                                  C.POINTER(ApopSweepOpts), C.POINTER(ApopSweepResult)]),
     ("apop_trace_lineage", C.c_int, [_vp, C.c_int64, c_double_p]),
+    ("apop_sweep_download_history", C.c_int, [_vp, c_int32_p, c_double_p]),
     ("apop_sweep_final_device", C.c_int, [_vp, C.POINTER(_vp)]),
     ("apop_pimh_accept", C.c_int, [C.c_double, C.c_double, C.c_double]),
     ("apop_ipmcmc_gibbs", C.c_int, [c_double_p, C.c_int, C.c_int, c_double_p, c_int32_p,

@@ -176,6 +176,12 @@ int64_t apop_num_particles(apop_ctx* c) { return c ? c->n : 0; }
 int64_t apop_launch_count(apop_ctx* c) { return c ? c->launches : 0; }
 void* apop_stream(apop_ctx* c) { return c ? (void*)c->stream : nullptr; }
 
+int apop_set_seed(apop_ctx* c, uint64_t seed) {
+    CHECK_CTX(c);
+    c->seed = seed;
+    return APOP_OK;
+}
+
 int apop_set_step(apop_ctx* c, uint32_t step) {
     CHECK_CTX(c);
     c->step = step;

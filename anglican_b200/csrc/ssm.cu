@@ -1,11 +1,522 @@
-// ssm.cu — fused state-space sweeps (stub while the resampler is validated)
+// ssm.cu — fused sweeps over state-space programs: one call = one `sweep`
+// (reference src/anglican/smc.cljc:35-51; conditional variant
+// pgibbs.cljc:76-110 / ipmcmc.cljc:34-83) of a program of the shape
+//     x0 <- sample;  for y_t:  x_t <- sample(. | x_{t-1});  observe(. | x_t) y_t
+//
+// Per step t the stream sees
+//   K1  k_propagate   x_t[k] = f(x_{t-1}[a_{t-1}[k]], noise(t, slot k))   (sample*,
+//                     inference.cljc:46-47), lw[k] = base + log p(y_t | x_t[k])
+//                     (observe*, smc.cljc:23-27) and the per-tile
+//                     (max, sum exp, sum exp^2, sum exp*x) partials — the
+//                     ancestor gather of the previous resample is folded into
+//                     the read of x_{t-1} (K5 never materialises).
+//   K2..K4            resample_enqueue (resample.cu), ancestors in sorted order
+//       k_step_stats  log-mean-weight, ESS, filtering mean, next base weight
+#include <math.h>
+#include <string.h>
+
 #include "apop_internal.cuh"
-namespace apop { void sweep_free(apop_ctx*) {} }
+#include "rng.cuh"
+
+namespace apop {
+
+// ------------------------------------------------------------------ state
+struct SweepDev {           // device-resident scalars of a sweep
+    double base;            // common accumulated log-weight (state.cljc:27-31)
+    double log_z;           // sum_t log-mean-weight (ipmcmc.cljc:67-74)
+    int err;
+    int pad;
+};
+
+struct ModelDev {           // model parameters in device memory
+    int kind, dim;
+    double m0, s0, a, b, q, c, d, r, beta;
+    double obs_const;       // log(r) + 0.5 log(2 pi)   |  log(beta) + 0.5 log(2 pi)
+    double hmm_init[16], hmm_trans[256], hmm_mu[16], hmm_sd[16], hmm_const[16];
+};
+
+} // namespace apop
+
+struct SweepState {
+    int64_t n = 0;
+    int T = 0, dim = 1, kind = 0;
+    bool history = false;
+    double *xa = nullptr, *xb = nullptr, *lw = nullptr;
+    int32_t* anc = nullptr;
+    double* x_hist = nullptr;      // [(T+1) * n * dim]
+    int32_t* anc_hist = nullptr;   // [T * n]
+    double *y = nullptr, *retained = nullptr;
+    double *log_mean_w = nullptr, *ess = nullptr, *filt = nullptr;   // device [T]
+    double* tsx = nullptr;         // per-tile sum exp(lw - tmax) * x
+    double* x_final = nullptr;     // [n * dim]
+    apop::SweepDev* sd = nullptr;
+    apop::ModelDev* model = nullptr;
+    double* traj = nullptr;
+    size_t cap_n = 0, cap_T = 0, cap_hist = 0;
+    const double* last_x = nullptr;    // pre-resample states of the last step
+    const int32_t* last_anc = nullptr;
+};
+
+namespace apop {
+
+void sweep_free(apop_ctx* c) {
+    SweepState* s = c->sweep;
+    if (!s) return;
+    void* ptrs[] = {s->xa, s->xb, s->lw, s->anc, s->x_hist, s->anc_hist, s->y, s->retained,
+                    s->log_mean_w, s->ess, s->filt, s->tsx, s->x_final, s->sd, s->model, s->traj};
+    for (void* p : ptrs)
+        if (p) cudaFree(p);
+    delete s;
+    c->sweep = nullptr;
+}
+
+// ------------------------------------------------------------------ kernels
+constexpr double kHalfLog2Pi_ = 0.91893853320467274178;
+
+template <int KIND>
+__device__ __forceinline__ double obs_logpdf(const ModelDev& M, double x, double y) {
+    if (KIND == APOP_SSM_LGSSM1D) {
+        // NormalDistribution.logDensity, runtime.cljc:403-409
+        double x1 = (y - (M.c * x + M.d)) / M.r;
+        return -0.5 * x1 * x1 - M.obs_const;
+    } else if (KIND == APOP_SSM_SV) {
+        // (normal 0 (* beta (exp (/ x 2)))):  log(sd) = log(beta) + x/2
+        double sd = M.beta * exp(x / 2.0);
+        double x1 = y / sd;
+        return -0.5 * x1 * x1 - (0.5 * x + M.obs_const);
+    } else {
+        int s = (int)x;
+        double x1 = (y - M.hmm_mu[s]) / M.hmm_sd[s];
+        return -0.5 * x1 * x1 - M.hmm_const[s];
+    }
+}
+
+__device__ __forceinline__ int discrete_draw(const double* w, int K, double u) {
+    double total = 0.0;
+    for (int i = 0; i < K; ++i) total = total + w[i];      // runtime.cljc:279
+    double x = u * total, acc = 0.0;
+    for (int i = 0; i < K; ++i) {
+        acc = acc + w[i];
+        if (x < acc) return i;                              // runtime.cljc:285
+    }
+    return K - 1;
+}
+
+template <int KIND>
+__global__ void __launch_bounds__(TB) k_init(const ModelDev* __restrict__ Mp, double* x,
+                                             int64_t n, int64_t g0, uint64_t seed,
+                                             const double* retained) {
+    const ModelDev& M = *Mp;
+    const int64_t k0 = ((int64_t)blockIdx.x * TB + threadIdx.x) * 2;
+    if (k0 >= n) return;
+    double v0, v1;
+    if (KIND == APOP_SSM_HMM) {
+        v0 = discrete_draw(M.hmm_init, M.dim, uniform_at(seed, (uint64_t)(g0 + k0), 0, STREAM_INIT, 0));
+        v1 = discrete_draw(M.hmm_init, M.dim, uniform_at(seed, (uint64_t)(g0 + k0 + 1), 0, STREAM_INIT, 0));
+    } else {
+        double z0, z1;
+        normal_pair_at(seed, (uint64_t)(g0 + k0) >> 1, 0, STREAM_INIT, 0, z0, z1);
+        v0 = M.m0 + M.s0 * z0;
+        v1 = M.m0 + M.s0 * z1;
+    }
+    if (retained && g0 + k0 == 0) v0 = retained[0];        // pgibbs.cljc:78-81
+    x[k0] = v0;
+    if (k0 + 1 < n) x[k0 + 1] = v1;
+}
+
+// K1: propagate + reweight + tile partials (scalar-state models)
+template <int KIND>
+__global__ void __launch_bounds__(TB) k_propagate(const ModelDev* __restrict__ Mp,
+                                                  const double* __restrict__ xp,
+                                                  const int32_t* __restrict__ anc, int first_step,
+                                                  double* __restrict__ xn, double* __restrict__ lw,
+                                                  const double* __restrict__ yt,
+                                                  const double* __restrict__ retained_t,
+                                                  const SweepDev* __restrict__ sd, int64_t n,
+                                                  int64_t g0, uint64_t seed, uint32_t t,
+                                                  double* __restrict__ tmax,
+                                                  double* __restrict__ tsum,
+                                                  double* __restrict__ tsum2,
+                                                  double* __restrict__ tsx, int* errflag) {
+    __shared__ double red[NWARP], red2[NWARP], red3[NWARP];
+    const ModelDev& M = *Mp;
+    const int64_t base = (int64_t)blockIdx.x * TILE;
+    const int64_t i0 = base + (int64_t)threadIdx.x * IPT;
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    const double y = yt[0];
+    const double wbase = sd->base;
+    double x[IPT], l[IPT];
+    // ---- parents (gather folded into the read)
+    int32_t par[IPT];
+    if (first_step) {
+#pragma unroll
+        for (int j = 0; j < IPT; ++j) par[j] = (int32_t)(i0 + j);
+    } else if (i0 + IPT <= n) {
+        const int4* q = reinterpret_cast<const int4*>(anc + i0);
+        int4 a = __ldg(q), b = __ldg(q + 1);
+        par[0] = a.x; par[1] = a.y; par[2] = a.z; par[3] = a.w;
+        par[4] = b.x; par[5] = b.y; par[6] = b.z; par[7] = b.w;
+    } else {
+#pragma unroll
+        for (int j = 0; j < IPT; ++j) par[j] = (i0 + j < n) ? anc[i0 + j] : 0;
+    }
+    double xo[IPT];
+#pragma unroll
+    for (int j = 0; j < IPT; ++j) xo[j] = (i0 + j < n) ? __ldg(xp + par[j]) : 0.0;
+    // ---- sample* (inference.cljc:46-47) and observe* (smc.cljc:23-27)
+    if (KIND == APOP_SSM_HMM) {
+#pragma unroll
+        for (int j = 0; j < IPT; ++j) {
+            double u = uniform_at(seed, (uint64_t)(g0 + i0 + j), t, STREAM_TRANSITION, 0);
+            x[j] = (double)discrete_draw(M.hmm_trans + (int)xo[j] * M.dim, M.dim, u);
+        }
+    } else {
+#pragma unroll
+        for (int j = 0; j < IPT; j += 2) {
+            double z0, z1;
+            normal_pair_at(seed, (uint64_t)(g0 + i0 + j) >> 1, t, STREAM_TRANSITION, 0, z0, z1);
+            x[j] = (M.a * xo[j] + M.b) + M.q * z0;             // sd*z + mean
+            x[j + 1] = (M.a * xo[j + 1] + M.b) + M.q * z1;
+        }
+    }
+    if (retained_t && g0 + i0 == 0) x[0] = retained_t[0];      // conditional SMC: slot 0
+    double mx = -INFINITY;
+    bool nan = false;
+#pragma unroll
+    for (int j = 0; j < IPT; ++j) {
+        l[j] = wbase + obs_logpdf<KIND>(M, x[j], y);           // add-log-weight, state.cljc:27-31
+        if (i0 + j < n) { nan |= (l[j] != l[j]); mx = fmax(mx, l[j]); }
+    }
+    if (nan) atomicOr(errflag, EB_NAN);
+    // ---- store
+    if (i0 + IPT <= n) {
+        double2* qx = reinterpret_cast<double2*>(xn + i0);
+        double2* ql = reinterpret_cast<double2*>(lw + i0);
+#pragma unroll
+        for (int j = 0; j < IPT / 2; ++j) {
+            qx[j] = make_double2(x[2 * j], x[2 * j + 1]);
+            ql[j] = make_double2(l[2 * j], l[2 * j + 1]);
+        }
+    } else {
+#pragma unroll
+        for (int j = 0; j < IPT; ++j)
+            if (i0 + j < n) { xn[i0 + j] = x[j]; lw[i0 + j] = l[j]; }
+    }
+    // ---- tile partials of particle-weights (smc.cljc:70-84)
+    mx = warp_max(mx);
+    if (lane == 0) red[wid] = mx;
+    __syncthreads();
+    mx = red[0];
+#pragma unroll
+    for (int i = 1; i < NWARP; ++i) mx = fmax(mx, red[i]);
+    __syncthreads();
+    double s = 0.0, s2 = 0.0, sx = 0.0;
+#pragma unroll
+    for (int j = 0; j < IPT; ++j) {
+        if (i0 + j < n) {
+            double wv = (l[j] == mx) ? 1.0 : ((l[j] > -INFINITY) ? exp(l[j] - mx) : 0.0);
+            s += wv; s2 += wv * wv; sx += wv * x[j];
+        }
+    }
+    s = warp_sum(s); s2 = warp_sum(s2); sx = warp_sum(sx);
+    if (lane == 0) { red[wid] = s; red2[wid] = s2; red3[wid] = sx; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double a = 0, b = 0, cc = 0;
+        for (int i = 0; i < NWARP; ++i) { a += red[i]; b += red2[i]; cc += red3[i]; }
+        tmax[blockIdx.x] = mx; tsum[blockIdx.x] = a; tsum2[blockIdx.x] = b; tsx[blockIdx.x] = cc;
+    }
+}
+
+// after the resample of step t (1-based): per-step outputs and next base
+__global__ void k_step_stats(SweepDev* sd, ResampleInfo* I, const double* __restrict__ tmax,
+                             const double* __restrict__ tsx, int64_t nt, int t, int reset,
+                             int cond, int32_t* anc, double* log_mean_w, double* ess,
+                             double* filt) {
+    __shared__ double red[32];
+    double acc = 0.0;
+    const double m = I->m;
+    for (int64_t i = threadIdx.x; i < nt; i += blockDim.x) {
+        double tm = tmax[i];
+        double fac = (tm == m) ? 1.0 : exp(tm - m);
+        acc += tsx[i] * fac;
+    }
+    acc = warp_sum(acc);
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = acc;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double tot = 0.0;
+        for (int i = 0; i < (int)(blockDim.x >> 5); ++i) tot += red[i];
+        const double nl = I->new_lw;
+        const double inc = nl - sd->base;
+        log_mean_w[t - 1] = inc;
+        ess[t - 1] = I->ess;
+        filt[t - 1] = tot / I->atot;
+        sd->log_z += inc;
+        sd->base = reset ? 0.0 : nl;                 // pgibbs.cljc:88 / smc.cljc:98-103
+        sd->err |= I->err;
+        I->err = 0;
+        if (cond) anc[0] = 0;                        // retained particle back at position 0
+    }
+}
+
+__global__ void k_sweep_reset(SweepDev* sd, ResampleInfo* I) {
+    sd->base = 0.0; sd->log_z = 0.0; sd->err = 0;
+    I->err = 0;
+}
+
+__global__ void k_trace(const int32_t* __restrict__ anc_hist, const double* __restrict__ x_hist,
+                        int64_t n, int T, int d, int64_t slot, double* traj) {
+    int64_t k = slot;
+    for (int t = T; t >= 1; --t) {
+        k = anc_hist[(int64_t)(t - 1) * n + k];
+        for (int i = threadIdx.x; i < d; i += blockDim.x)
+            traj[(int64_t)t * d + i] = x_hist[((int64_t)t * n + k) * d + i];
+    }
+    for (int i = threadIdx.x; i < d; i += blockDim.x) traj[i] = x_hist[k * d + i];
+}
+
+__global__ void k_gather_rows(const double* __restrict__ src, double* __restrict__ dst,
+                              const int32_t* __restrict__ anc, int64_t n, int d) {
+    const int64_t total = n * (int64_t)d;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+         i += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t k = i / d;
+        dst[i] = src[(int64_t)anc[k] * d + (i - k * d)];
+    }
+}
+
+// ------------------------------------------------------------------ host
+static int dev_alloc(apop_ctx* c, void** p, size_t bytes) {
+    if (cudaMalloc(p, bytes) != cudaSuccess) {
+        *p = nullptr;
+        return set_err(c, APOP_ERR_OOM, "sweep: device allocation of %zu bytes failed", bytes);
+    }
+    return APOP_OK;
+}
+
+static int sweep_prepare(apop_ctx* c, int T, int dim, bool history) {
+    SweepState* s = c->sweep;
+    if (!s) { s = new SweepState(); c->sweep = s; }
+    const size_t n = (size_t)c->n;
+    if (s->cap_n < n || s->dim != dim) {
+        void* ptrs[] = {s->xa, s->xb, s->lw, s->anc, s->tsx, s->x_final};
+        for (void* p : ptrs) if (p) cudaFree(p);
+        APOP_TRY(dev_alloc(c, (void**)&s->xa, (n + 8) * dim * 8));
+        APOP_TRY(dev_alloc(c, (void**)&s->xb, (n + 8) * dim * 8));
+        APOP_TRY(dev_alloc(c, (void**)&s->lw, (n + 8) * 8));
+        APOP_TRY(dev_alloc(c, (void**)&s->anc, (n + 8) * 4));
+        APOP_TRY(dev_alloc(c, (void**)&s->tsx, ((n + TILE - 1) / TILE + 1) * 8 * (size_t)dim));
+        APOP_TRY(dev_alloc(c, (void**)&s->x_final, (n + 8) * dim * 8));
+        s->cap_n = n;
+    }
+    if (!s->sd) {
+        APOP_TRY(dev_alloc(c, (void**)&s->sd, sizeof(SweepDev)));
+        APOP_TRY(dev_alloc(c, (void**)&s->model, sizeof(ModelDev)));
+    }
+    if (s->cap_T < (size_t)T || s->dim != dim) {
+        void* ptrs[] = {s->y, s->retained, s->log_mean_w, s->ess, s->filt, s->traj};
+        for (void* p : ptrs) if (p) cudaFree(p);
+        APOP_TRY(dev_alloc(c, (void**)&s->y, (size_t)(T + 1) * dim * 8));
+        APOP_TRY(dev_alloc(c, (void**)&s->retained, (size_t)(T + 1) * dim * 8));
+        APOP_TRY(dev_alloc(c, (void**)&s->log_mean_w, (size_t)(T + 1) * 8));
+        APOP_TRY(dev_alloc(c, (void**)&s->ess, (size_t)(T + 1) * 8));
+        APOP_TRY(dev_alloc(c, (void**)&s->filt, (size_t)(T + 1) * dim * 8));
+        APOP_TRY(dev_alloc(c, (void**)&s->traj, (size_t)(T + 1) * dim * 8));
+        s->cap_T = (size_t)T;
+    }
+    if (history) {
+        const size_t need = (size_t)(T + 1) * n;
+        if (s->cap_hist < need || s->dim != dim) {
+            if (s->x_hist) cudaFree(s->x_hist);
+            if (s->anc_hist) cudaFree(s->anc_hist);
+            s->x_hist = nullptr; s->anc_hist = nullptr; s->cap_hist = 0;
+            APOP_TRY(dev_alloc(c, (void**)&s->x_hist, need * dim * 8));
+            APOP_TRY(dev_alloc(c, (void**)&s->anc_hist, need * 4));
+            s->cap_hist = need;
+        }
+    }
+    s->n = c->n; s->T = T; s->dim = dim; s->history = history;
+    return APOP_OK;
+}
+
+static int upload_model(apop_ctx* c, const apop_ssm* m) {
+    ModelDev h;
+    memset(&h, 0, sizeof h);
+    h.kind = m->kind; h.dim = m->dim;
+    h.m0 = m->m0; h.s0 = m->s0; h.a = m->a; h.b = m->b; h.q = m->q;
+    h.c = m->c; h.d = m->d; h.r = m->r; h.beta = m->beta;
+    if (m->kind == APOP_SSM_LGSSM1D) h.obs_const = log(m->r) + kHalfLog2Pi_;
+    if (m->kind == APOP_SSM_SV) h.obs_const = log(m->beta) + kHalfLog2Pi_;
+    if (m->kind == APOP_SSM_HMM) {
+        const int K = m->dim;
+        if (K < 1 || K > 16 || !m->hmm_init || !m->hmm_trans || !m->hmm_mu || !m->hmm_sd)
+            return set_err(c, APOP_ERR_INVALID, "hmm: need 1 <= K <= 16 and all tables");
+        memcpy(h.hmm_init, m->hmm_init, sizeof(double) * K);
+        memcpy(h.hmm_trans, m->hmm_trans, sizeof(double) * K * K);
+        memcpy(h.hmm_mu, m->hmm_mu, sizeof(double) * K);
+        memcpy(h.hmm_sd, m->hmm_sd, sizeof(double) * K);
+        for (int i = 0; i < K; ++i) h.hmm_const[i] = log(m->hmm_sd[i]) + kHalfLog2Pi_;
+    }
+    void* staged = nullptr;
+    APOP_TRY(param_upload(c, &h, sizeof h, &staged));
+    APOP_CUDA(c, cudaMemcpyAsync(c->sweep->model, staged, sizeof h, cudaMemcpyDeviceToDevice,
+                                 c->stream));
+    return APOP_OK;
+}
+
+template <int KIND>
+static int run_scalar_sweep(apop_ctx* c, const apop_ssm* model, const double* y, int T,
+                            const double* retained, const apop_sweep_opts* o) {
+    SweepState* s = c->sweep;
+    const int64_t n = c->n;
+    const int nt = (int)((n + TILE - 1) / TILE);
+    APOP_TRY(ensure_resample_ws(c));
+    ResampleWS& ws = c->ws;
+    const bool csmc = o->csmc && retained;
+    void* staged = nullptr;
+    APOP_TRY(param_upload(c, y, sizeof(double) * (size_t)T, &staged));
+    APOP_CUDA(c, cudaMemcpyAsync(s->y, staged, sizeof(double) * (size_t)T,
+                                 cudaMemcpyDeviceToDevice, c->stream));
+    if (csmc) {
+        APOP_TRY(param_upload(c, retained, sizeof(double) * (size_t)(T + 1), &staged));
+        APOP_CUDA(c, cudaMemcpyAsync(s->retained, staged, sizeof(double) * (size_t)(T + 1),
+                                     cudaMemcpyDeviceToDevice, c->stream));
+    }
+    k_sweep_reset<<<1, 1, 0, c->stream>>>(s->sd, ws.info);
+    double* x_prev = s->history ? s->x_hist : s->xa;
+    {
+        const int64_t pairs = (n + 1) / 2;
+        k_init<KIND><<<(int)((pairs + TB - 1) / TB), TB, 0, c->stream>>>(
+            s->model, x_prev, n, c->g0, c->seed, csmc ? s->retained : nullptr);
+    }
+    c->launches += 2;
+    int32_t* anc_prev = s->anc;
+    for (int t = 1; t <= T; ++t) {
+        double* x_new = s->history ? s->x_hist + (size_t)t * n : ((t & 1) ? s->xb : s->xa);
+        int32_t* anc_new = s->history ? s->anc_hist + (size_t)(t - 1) * n : s->anc;
+        k_propagate<KIND><<<nt, TB, 0, c->stream>>>(
+            s->model, x_prev, anc_prev, t == 1, x_new, s->lw, s->y + (t - 1),
+            csmc ? s->retained + t : nullptr, s->sd, n, c->g0, c->seed, (uint32_t)t, ws.tmax,
+            ws.tsum, ws.tsum2, s->tsx, &ws.info->err);
+        c->launches += 1;
+        const bool cond = csmc && t <= o->n_cond_steps;
+        c->step = (uint32_t)t;
+        ResampleArgs a{};
+        a.lw = s->lw; a.w = nullptr; a.n = n; a.n_new = cond ? n - 1 : n;
+        a.u = NAN; a.order = APOP_ORDER_SORTED;
+        a.anc_out = anc_new; a.out_offset = cond ? 1 : 0; a.have_partials = true;
+        APOP_TRY(resample_enqueue(c, a));
+        k_step_stats<<<1, 256, 0, c->stream>>>(s->sd, ws.info, ws.tmax, s->tsx, nt, t,
+                                               o->reset_weights, cond ? 1 : 0, anc_new,
+                                               s->log_mean_w, s->ess, s->filt);
+        c->launches += 1;
+        x_prev = x_new;
+        anc_prev = anc_new;
+    }
+    s->last_x = x_prev;
+    s->last_anc = anc_prev;
+    APOP_CUDA(c, cudaGetLastError());
+    return APOP_OK;
+}
+
+} // namespace apop
+
+using namespace apop;
+
 extern "C" {
-int apop_smc_sweep(apop_ctx* c, const apop_ssm*, const double*, int32_t, const double*,
-                   const apop_sweep_opts*, apop_sweep_result*) {
-    return apop::set_err(c, APOP_ERR_UNSUPPORTED, "sweep not built yet");
+
+int apop_smc_sweep(apop_ctx* c, const apop_ssm* model, const double* y, int32_t T,
+                   const double* retained, const apop_sweep_opts* opts,
+                   apop_sweep_result* result) {
+    if (!c) return APOP_ERR_INVALID;
+    if (!model || !y || T < 1 || !opts || !result)
+        return set_err(c, APOP_ERR_INVALID, "smc_sweep: bad arguments");
+    if (c->world > 1) return set_err(c, APOP_ERR_UNSUPPORTED, "sharded sweep: see apop_smc_sweep_sharded");
+    if (opts->csmc && c->n < 2)
+        return set_err(c, APOP_ERR_INVALID, "conditional sweep needs >= 2 particles");
+    cudaSetDevice(c->device);
+    const int dim = (model->kind == APOP_SSM_LGMVN) ? model->dim : 1;
+    APOP_TRY(sweep_prepare(c, T, dim, opts->keep_history != 0));
+    APOP_TRY(upload_model(c, model));
+    switch (model->kind) {
+    case APOP_SSM_LGSSM1D:
+        APOP_TRY(run_scalar_sweep<APOP_SSM_LGSSM1D>(c, model, y, T, retained, opts)); break;
+    case APOP_SSM_SV:
+        APOP_TRY(run_scalar_sweep<APOP_SSM_SV>(c, model, y, T, retained, opts)); break;
+    case APOP_SSM_HMM:
+        APOP_TRY(run_scalar_sweep<APOP_SSM_HMM>(c, model, y, T, retained, opts)); break;
+    default:
+        return set_err(c, APOP_ERR_UNSUPPORTED, "model kind %d not supported by the fused sweep",
+                       model->kind);
+    }
+    SweepState* s = c->sweep;
+    const int64_t n = c->n;
+    if (opts->want_final || result->x_final) {
+        int blocks = (int)((n * dim + 255) / 256);
+        if (blocks > 148 * 32) blocks = 148 * 32;
+        k_gather_rows<<<blocks, 256, 0, c->stream>>>(s->last_x, s->x_final, s->last_anc, n, dim);
+        c->launches += 1;
+    }
+    // results: one small D2H per requested array, then a single sync
+    SweepDev hsd;
+    APOP_CUDA(c, cudaMemcpyAsync(&hsd, s->sd, sizeof hsd, cudaMemcpyDeviceToHost, c->stream));
+    if (result->log_mean_w)
+        APOP_CUDA(c, cudaMemcpyAsync(result->log_mean_w, s->log_mean_w, sizeof(double) * T,
+                                     cudaMemcpyDeviceToHost, c->stream));
+    if (result->ess)
+        APOP_CUDA(c, cudaMemcpyAsync(result->ess, s->ess, sizeof(double) * T,
+                                     cudaMemcpyDeviceToHost, c->stream));
+    if (result->filt_mean)
+        APOP_CUDA(c, cudaMemcpyAsync(result->filt_mean, s->filt, sizeof(double) * T * dim,
+                                     cudaMemcpyDeviceToHost, c->stream));
+    if (result->x_final)
+        APOP_CUDA(c, cudaMemcpyAsync(result->x_final, s->x_final, sizeof(double) * n * dim,
+                                     cudaMemcpyDeviceToHost, c->stream));
+    APOP_CUDA(c, cudaStreamSynchronize(c->stream));
+    ResampleInfo I{};
+    I.err = hsd.err;
+    APOP_TRY(info_to_status(c, I));
+    // :smc keeps the accumulated weight on the particles: final weight == log Z-hat
+    result->log_z = opts->reset_weights ? hsd.log_z : hsd.base;
+    return APOP_OK;
 }
-int apop_trace_lineage(apop_ctx* c, int64_t, double*) { return apop::set_err(c, APOP_ERR_UNSUPPORTED, "n/a"); }
-int apop_sweep_final_device(apop_ctx* c, void**) { return apop::set_err(c, APOP_ERR_UNSUPPORTED, "n/a"); }
+
+int apop_trace_lineage(apop_ctx* c, int64_t slot, double* out_traj) {
+    if (!c) return APOP_ERR_INVALID;
+    SweepState* s = c->sweep;
+    if (!s || !s->history || !out_traj)
+        return set_err(c, APOP_ERR_INVALID, "trace_lineage: no keep_history sweep available");
+    if (slot < 0 || slot >= s->n) return set_err(c, APOP_ERR_INVALID, "trace_lineage: bad slot");
+    k_trace<<<1, 32, 0, c->stream>>>(s->anc_hist, s->x_hist, s->n, s->T, s->dim, slot, s->traj);
+    c->launches += 1;
+    APOP_CUDA(c, cudaMemcpyAsync(out_traj, s->traj, sizeof(double) * (size_t)(s->T + 1) * s->dim,
+                                 cudaMemcpyDeviceToHost, c->stream));
+    APOP_CUDA(c, cudaStreamSynchronize(c->stream));
+    return APOP_OK;
 }
+
+int apop_sweep_download_history(apop_ctx* c, int32_t* anc, double* x) {
+    if (!c) return APOP_ERR_INVALID;
+    SweepState* s = c->sweep;
+    if (!s || !s->history)
+        return set_err(c, APOP_ERR_INVALID, "download_history: no keep_history sweep available");
+    const size_t n = (size_t)s->n;
+    if (anc)
+        APOP_CUDA(c, cudaMemcpyAsync(anc, s->anc_hist, sizeof(int32_t) * n * s->T,
+                                     cudaMemcpyDeviceToHost, c->stream));
+    if (x)
+        APOP_CUDA(c, cudaMemcpyAsync(x, s->x_hist, sizeof(double) * n * (s->T + 1) * s->dim,
+                                     cudaMemcpyDeviceToHost, c->stream));
+    APOP_CUDA(c, cudaStreamSynchronize(c->stream));
+    return APOP_OK;
+}
+
+int apop_sweep_final_device(apop_ctx* c, void** out) {
+    if (!c || !out) return APOP_ERR_INVALID;
+    if (!c->sweep || !c->sweep->x_final) return set_err(c, APOP_ERR_INVALID, "no sweep yet");
+    *out = c->sweep->x_final;
+    return APOP_OK;
+}
+
+} // extern "C"

@@ -1,0 +1,210 @@
+"""Host-side mirror of `anglican.inference/infer` for the particle algorithms.
+
+    infer(:smc | :pimh | :pgibbs | :ipmcmc, model, observations, **options)
+
+keeps the reference's keywords, defaults and assertions
+(smc.cljc:53-57, pimh.cljc:41-45, pgibbs.cljc:112-116, ipmcmc.cljc:148-171) and
+its return contract: a lazy (generator) sequence of states carrying
+`log_weight`, `result`, `predicts` (stripdown, inference.cljc:114-117).  The
+control flow below (MH accept, retained-trajectory bookkeeping, node index
+Gibbs) is the part that stays on the JVM in the real integration; every sweep
+over the particle population runs in libanglican_pop.so.
+"""
+import math
+from dataclasses import dataclass, field
+
+import numpy as np
+
+from . import _lib as L
+from .population import Population
+
+
+@dataclass
+class State:
+    """the stripped-down state map {:log-weight :result :predicts}"""
+    log_weight: float
+    result: object
+    predicts: list = field(default_factory=list)
+
+
+class _SeedSeq:
+    """one RNG key per sweep; host-side draws (accept, rand-nth, index Gibbs)
+    come from a numpy generator (the reference uses its unseeded runtime RNG:
+    only distributional parity applies, runtime.cljc:142-147)."""
+
+    def __init__(self, seed):
+        self.base = int(seed)
+        self.k = 0
+        self.rng = np.random.default_rng(self.base ^ 0x5EED)
+
+    def next_key(self):
+        self.k += 1
+        return (self.base + 0x9E3779B97F4A7C15 * self.k) & 0xFFFFFFFFFFFFFFFF
+
+
+def _result_of(out, k, trajectories):
+    if trajectories is not None:
+        r = trajectories[k]
+        return r[:, 0].copy() if r.shape[1] == 1 else r.copy()
+    return out.x_final[k].copy() if np.ndim(out.x_final[k]) else float(out.x_final[k])
+
+
+def _states(out, log_weight, with_paths):
+    traj = out.trajectories() if with_paths else None
+    for k in range(out.pop.n):
+        yield State(log_weight, _result_of(out, k, traj))
+
+
+# ---------------------------------------------------------------- :smc
+def _infer_smc(model, y, number_of_particles=1, seed=0xA11CE, device=0, paths=False, pop=None):
+    assert number_of_particles >= 1, ":number-of-particles must be at least 1"   # smc.cljc:56-57
+    own = pop is None
+    pop = pop or Population(number_of_particles, seed=seed, device=device)
+    seeds = _SeedSeq(seed)
+    try:
+        while True:                                   # (sample-seq), smc.cljc:58-63
+            pop.set_seed(seeds.next_key())
+            out = pop.sweep(model, y, keep_history=paths)
+            yield from _states(out, out.log_z, paths)
+    finally:
+        if own:
+            pop.close()
+
+
+# ---------------------------------------------------------------- :pimh
+def _infer_pimh(model, y, number_of_particles=1, seed=0xA11CE, device=0, paths=False):
+    assert number_of_particles >= 1, ":number-of-particles must be at least 1"   # pimh.cljc:44-45
+    n = number_of_particles
+    pop = Population(n, seed=seed, device=device)
+    seeds = _SeedSeq(seed)
+    lib = L.load()
+
+    def run():
+        pop.set_seed(seeds.next_key())
+        out = pop.sweep(model, y, keep_history=paths)
+        traj = out.trajectories() if paths else None
+        res = [_result_of(out, k, traj) for k in range(n)]
+        # get-log-Z, pimh.cljc:48-50: all final weights equal => log(N) + log Z-hat
+        log_z = math.log(float(n)) + out.log_z if math.isfinite(out.log_z) else out.log_z
+        return res, log_z
+
+    try:
+        cur, log_z = run()
+        while True:
+            nxt, nxt_log_z = run()
+            u = seeds.rng.random()
+            if lib.apop_pimh_accept(nxt_log_z, log_z, u):           # lmh.cljc:146-151
+                cur, log_z = nxt, nxt_log_z
+            for r in cur:                                           # pimh.cljc:53-55
+                yield State(0.0, r)
+    finally:
+        pop.close()
+
+
+# ---------------------------------------------------------------- :pgibbs
+def _infer_pgibbs(model, y, number_of_particles=2, seed=0xA11CE, device=0, paths=False):
+    assert number_of_particles >= 2, ":number-of-particles must be at least 2"   # pgibbs.cljc:115-116
+    n = number_of_particles
+    pop = Population(n, seed=seed, device=device)
+    seeds = _SeedSeq(seed)
+    T = len(y) // model.state_dim
+    retained = None
+    try:
+        while True:
+            pop.set_seed(seeds.next_key())
+            # the retained particle runs out of stored samples before the last
+            # observe, so that resample is unconditional (pgibbs.cljc:89)
+            out = pop.sweep(model, y, retained=retained, csmc=retained is not None,
+                            n_cond_steps=T - 1, reset_weights=True, keep_history=True)
+            b = int(seeds.rng.random() * n)                         # rand-nth, pgibbs.cljc:122-123
+            retained = out.trace(b)
+            yield from _states(out, 0.0 if math.isfinite(out.log_z) else -math.inf, paths)
+    finally:
+        pop.close()
+
+
+# ---------------------------------------------------------------- :ipmcmc
+def _infer_ipmcmc(model, y, number_of_particles=2, number_of_nodes=32,
+                  number_of_csmc_nodes=None, all_particles=True, pool=None, seed=0xA11CE,
+                  device=0, paths=False, exchange=None):
+    assert number_of_particles > 1, ":number-of-particles must be larger than 1"
+    assert number_of_nodes > 1, ":number-of-nodes must be larger 1"
+    M, n = number_of_nodes, number_of_particles
+    P = number_of_csmc_nodes or int(M / 2)                          # ipmcmc.cljc:162-165
+    assert P < M, ":number-of-csmc-nodes must be smaller than :number-of-nodes"
+    pop = Population(n, seed=seed, device=device)
+    seeds = _SeedSeq(seed)
+    lib = L.load()
+    T = len(y) // model.state_dim
+    retained = [None] * P
+    try:
+        while True:
+            results, cand, log_zs = [], [], np.empty(M)
+            for j in range(M):                                      # cp/pmap over nodes, 176-182
+                ret = retained[j] if j < P else None
+                pop.set_seed(seeds.next_key())
+                out = pop.sweep(model, y, retained=ret, csmc=ret is not None, n_cond_steps=T,
+                                reset_weights=True, keep_history=True)
+                log_zs[j] = out.log_z
+                traj = out.trajectories() if paths else None
+                results.append([_result_of(out, k, traj) for k in range(n)])
+                # candidate next retained path of this node, drawn now so the
+                # ancestry need not outlive the sweep (rand-nth, ipmcmc.cljc:189)
+                cand.append(out.trace(int(seeds.rng.random() * n)))
+            if exchange is not None:
+                log_zs = exchange(log_zs)                           # only log-Zs cross nodes, 183-187
+            u = seeds.rng.random(P)
+            cs = np.empty(P, dtype=np.int32)
+            zs = np.empty(M)
+            rc = lib.apop_ipmcmc_gibbs(log_zs.ctypes.data_as(L.c_double_p), M, P,
+                                       u.ctypes.data_as(L.c_double_p),
+                                       cs.ctypes.data_as(L.c_int32_p),
+                                       zs.ctypes.data_as(L.c_double_p))
+            assert rc == 0
+            retained = [cand[int(c)] for c in cs]
+            for j in range(M):                                      # ipmcmc.cljc:193-203
+                with np.errstate(divide="ignore"):
+                    lw = float(np.log(zs[j] / n))
+                if all_particles:
+                    for r in results[j]:
+                        yield State(lw, r)
+                else:
+                    yield State(lw, results[j][int(seeds.rng.random() * n)])
+    finally:
+        pop.close()
+
+
+_ALGORITHMS = {"smc": _infer_smc, "pimh": _infer_pimh, "pgibbs": _infer_pgibbs,
+               "ipmcmc": _infer_ipmcmc}
+
+
+def infer(algorithm, model, observations, **options):
+    """(infer algorithm prog value & options) — inference.cljc:25-28.
+
+    `algorithm`: "smc" / ":smc" / "pimh" / "pgibbs" / "ipmcmc".  Options use the
+    reference's names with `-` -> `_` (number_of_particles, number_of_nodes,
+    number_of_csmc_nodes, all_particles, pool)."""
+    key = str(algorithm).lstrip(":")
+    if key not in _ALGORITHMS:
+        raise ValueError(f"no particle engine behind algorithm :{key}")   # core.cljc:15-26
+    y = np.ascontiguousarray(observations, dtype=np.float64).ravel()
+    return _ALGORITHMS[key](model, y, **options)
+
+
+def doquery(algorithm, model, observations, drop_invalid=True, **options):
+    """doquery (core.cljc:223-252): infer, then drop states with log-weight
+    -inf unless :drop-invalid false (inference.cljc:151-157)."""
+    for s in infer(algorithm, model, observations, **options):
+        if drop_invalid and not (s.log_weight > -math.inf):
+            continue
+        yield s
+
+
+def log_marginal(states):
+    """inference.cljc:181-186 on a finite collection of states"""
+    lw = np.sort(np.array([s.log_weight for s in states], dtype=np.float64))
+    acc = lw[0]
+    for v in lw[1:]:
+        mx = max(acc, v)
+        acc = mx + math.log(math.exp(acc - mx) + math.exp(v - mx)) if math.isfinite(mx) else mx
+    return acc - math.log(len(lw))

@@ -248,3 +248,79 @@ class Population:
             vp = _dp(keep[-1])
         L.check(self.ctx, self.lib.apop_observe_mvn(self.ctx, mp, mh, _dp(cov), d, vp, vh,
                                                     logw.handle))
+
+    # ------------------------------------------------------------ fused sweeps
+    def set_seed(self, seed):
+        L.check(self.ctx, self.lib.apop_set_seed(self.ctx, int(seed)))
+        self.seed = int(seed)
+
+    def sweep(self, model, y, retained=None, csmc=False, n_cond_steps=0, reset_weights=False,
+              keep_history=False, want_final=True, want_stats=True):
+        """One `sweep` (smc.cljc:35-51; conditional: pgibbs.cljc:76-110,
+        ipmcmc.cljc:34-83).  Returns a SweepOutput."""
+        y = np.ascontiguousarray(y, dtype=np.float64)
+        d = model.state_dim
+        T = y.size // d
+        opts = L.ApopSweepOpts(int(csmc), int(n_cond_steps), int(reset_weights),
+                               int(keep_history), 0, int(want_final))
+        res = L.ApopSweepResult()
+        out = SweepOutput(self, T, d)
+        if want_stats:
+            out.log_mean_w = np.empty(T)
+            out.ess = np.empty(T)
+            res.log_mean_w, res.ess = _dp(out.log_mean_w), _dp(out.ess)
+            if d == 1:
+                out.filt_mean = np.empty(T)
+                res.filt_mean = _dp(out.filt_mean)
+        if want_final:
+            out.x_final = np.empty((self.n, d)) if d > 1 else np.empty(self.n)
+            res.x_final = _dp(out.x_final)
+        ret = None
+        if retained is not None:
+            ret = np.ascontiguousarray(retained, dtype=np.float64)
+        L.check(self.ctx, self.lib.apop_smc_sweep(self.ctx, C.byref(model.c), _dp(y), T, _dp(ret),
+                                                  C.byref(opts), C.byref(res)))
+        out.log_z = res.log_z
+        out.has_history = bool(keep_history)
+        return out
+
+
+class SweepOutput:
+    """Result of one sweep; ancestry stays on the device until asked for."""
+
+    def __init__(self, pop, T, d):
+        self.pop, self.T, self.d = pop, T, d
+        self.log_z = None
+        self.log_mean_w = self.ess = self.filt_mean = self.x_final = None
+        self.has_history = False
+        self._hist = None
+
+    def trace(self, slot):
+        """x_0..x_T of the final particle in `slot` (its `::past-samples`,
+        pgibbs.cljc:31-35)."""
+        out = np.empty((self.T + 1) * self.d)
+        L.check(self.pop.ctx, self.pop.lib.apop_trace_lineage(self.pop.ctx, int(slot), _dp(out)))
+        return out.reshape(self.T + 1, self.d) if self.d > 1 else out
+
+    def history(self):
+        if self._hist is None:
+            n = self.pop.n
+            anc = np.empty((self.T, n), dtype=np.int32)
+            x = np.empty((self.T + 1, n, self.d))
+            L.check(self.pop.ctx, self.pop.lib.apop_sweep_download_history(
+                self.pop.ctx, anc.ctypes.data_as(L.c_int32_p), _dp(x)))
+            self._hist = (anc, x)
+        return self._hist
+
+    def trajectories(self):
+        """[n, T+1, d] state sequences of all final particles (host-side
+        materialisation of every particle's `:result`)."""
+        anc, x = self.history()
+        n = self.pop.n
+        out = np.empty((n, self.T + 1, self.d))
+        k = np.arange(n)
+        for t in range(self.T, 0, -1):
+            k = anc[t - 1][k]
+            out[:, t, :] = x[t][k]
+        out[:, 0, :] = x[0][k]
+        return out

@@ -77,6 +77,8 @@ const char* apop_last_error(apop_ctx* ctx);
 int apop_get_unique_id(void* out_128_bytes);
 int apop_synchronize(apop_ctx* ctx);
 int64_t apop_num_particles(apop_ctx* ctx);
+/* re-key the counter-based RNG (one key per sweep makes sweeps independent) */
+int apop_set_seed(apop_ctx* ctx, uint64_t seed);
 /* number of kernels this ctx has launched so far (bench `gpu_launches`) */
 int64_t apop_launch_count(apop_ctx* ctx);
 /* raw CUDA stream (cudaStream_t) so callers can record events on it */
@@ -200,6 +202,11 @@ int apop_smc_sweep(apop_ctx* ctx, const apop_ssm* model, const double* y, int32_
                    apop_sweep_result* result);
 /* lineage (x_0..x_T) of final slot `slot` of the last keep_history sweep */
 int apop_trace_lineage(apop_ctx* ctx, int64_t slot, double* out_traj);
+/* whole ancestry of the last keep_history sweep, for host-side result
+ * materialisation (the `:result` / `:predicts` of every particle stay on the
+ * host side): anc [T*n] i32 physical ancestors, x [(T+1)*n*dim] f64 states
+ * before each resample.  Either pointer may be NULL. */
+int apop_sweep_download_history(apop_ctx* ctx, int32_t* anc, double* x);
 /* device pointer of the final state column of the last sweep (n*dim f64) */
 int apop_sweep_final_device(apop_ctx* ctx, void** out);
 

@@ -1,0 +1,196 @@
+"""Fused sweeps through the C ABI vs the oracle's sweep (same counter-based
+noise, literal resampling wheel) and vs exact Kalman / HMM truths.
+Tolerances: per-step log-mean-weights and log Z 1e-9 relative (north_star)."""
+import json
+import math
+import os
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+G = json.load(open(os.path.join(os.path.dirname(__file__), "golden", "reference_goldens.json")))
+
+
+@pytest.fixture(scope="module")
+def orc():
+    from oracle import pyoracle
+    return pyoracle
+
+
+def _rel(a, b):
+    a, b = np.asarray(a, float), np.asarray(b, float)
+    return float(np.max(np.abs(a - b) / np.maximum(1.0, np.abs(b))))
+
+
+def _lgssm_data(T, seed=20240601):
+    rng = np.random.default_rng(seed)
+    x, ys = rng.normal(), []
+    for _ in range(T):
+        x = 0.9 * x + rng.normal()
+        ys.append(x + rng.normal())
+    return np.array(ys)
+
+
+def _sv_data(T, seed=20240602, phi=0.98, sigma=0.16, beta=0.65):
+    rng = np.random.default_rng(seed)
+    x = rng.normal() * sigma / math.sqrt(1 - phi * phi)
+    ys = []
+    for _ in range(T):
+        x = phi * x + sigma * rng.normal()
+        ys.append(beta * math.exp(x / 2) * rng.normal())
+    return np.array(ys)
+
+
+@pytest.mark.parametrize("n", [2, 1000, 4097, 100000])
+def test_lgssm_sweep_matches_oracle(orc, n):
+    from anglican_b200 import Population
+    from anglican_b200.models import LinearGaussian1D
+    y = _lgssm_data(40)
+    m = LinearGaussian1D()
+    om = orc.Model(orc.SSM_LGSSM1D, **m.params)
+    with Population(n, seed=4242) as pop:
+        out = pop.sweep(m, y)
+    ref = orc.smc_sweep(om, y, n, seed=4242)
+    assert _rel(out.log_mean_w, ref["log_mean_w"]) < 1e-9
+    assert _rel(out.log_z, ref["log_z"]) < 1e-9
+    assert _rel(out.ess, ref["ess"]) < 1e-9
+    assert _rel(out.filt_mean, ref["filt_mean"][:, 0]) < 1e-9
+    assert _rel(out.x_final, ref["x_final"][:, 0]) < 1e-9
+
+
+@pytest.mark.parametrize("n", [1000, 65536])
+def test_sv_sweep_matches_oracle(orc, n):
+    from anglican_b200 import Population
+    from anglican_b200.models import StochasticVolatility
+    y = _sv_data(60)
+    m = StochasticVolatility()
+    om = orc.Model(orc.SSM_SV, m0=0.0, s0=m.c.s0, a=m.c.a, b=0.0, q=m.c.q, beta=m.c.beta)
+    with Population(n, seed=99) as pop:
+        out = pop.sweep(m, y)
+    ref = orc.smc_sweep(om, y, n, seed=99)
+    assert _rel(out.log_mean_w, ref["log_mean_w"]) < 1e-9
+    assert _rel(out.log_z, ref["log_z"]) < 1e-9
+    assert _rel(out.x_final, ref["x_final"][:, 0]) < 1e-9
+
+
+def _hmm(orc=None):
+    from anglican_b200.models import GaussianHMM
+    h = G["hmm"]
+    m = GaussianHMM(h["init"], h["trans"], h["mu"], h["sd"])
+    om = None
+    if orc is not None:
+        om = orc.Model(orc.SSM_HMM, dim=3, hmm_init=h["init"], hmm_trans=h["trans"],
+                       hmm_mu=h["mu"], hmm_sd=h["sd"])
+    return m, om, np.array(h["observations"], float), h
+
+
+def test_hmm_config1_matches_oracle_and_exact(orc):
+    """BASELINE config 1: Anglican HMM example, 3 states, 16 obs, 1000 particles."""
+    from anglican_b200 import Population
+    m, om, y, h = _hmm(orc)
+    n = 1000
+    lzs = []
+    with Population(n, seed=7) as pop:
+        for s in range(30):
+            pop.set_seed(1000 + s)
+            out = pop.sweep(m, y, keep_history=True)
+            ref = orc.smc_sweep(om, y, n, seed=1000 + s, keep_history=True)
+            assert _rel(out.log_mean_w, ref["log_mean_w"]) < 1e-9
+            assert np.array_equal(out.x_final, ref["x_final"][:, 0])
+            anc, x = out.history()
+            assert np.array_equal(anc, ref["anc_hist"])          # bit-exact ancestry
+            assert np.array_equal(x[:, :, 0], ref["x_hist"][:, :, 0])
+            for slot in (0, 17, n - 1):
+                assert np.array_equal(out.trace(slot), orc.trace_lineage(ref, slot)[:, 0])
+            lzs.append(out.log_z)
+    # unbiased normalising-constant estimate vs the exact forward algorithm
+    assert abs(math.log(np.mean(np.exp(np.array(lzs) - h["exact_log_z"])))) < 0.1
+
+
+@pytest.mark.parametrize("alg,opts", [
+    ("smc", dict(number_of_particles=100)),
+    ("pimh", dict(number_of_particles=100)),
+    ("pgibbs", dict(number_of_particles=100)),
+    ("ipmcmc", dict(number_of_particles=100, number_of_nodes=10)),
+])
+def test_hmm_posterior_table_per_algorithm(alg, opts):
+    """algorithm_test.cljc:102-151, 265-301: RMS-L2 of the 17x3 smoothing table
+    < 0.1 with the reference's own per-algorithm options (10 000 samples)."""
+    from anglican_b200.inference import infer
+    m, _, y, h = _hmm()
+    acc, wsum = np.zeros((17, 3)), 0.0
+    it = infer(alg, m, y, paths=True, seed=31337, **opts)
+    for i, s in enumerate(it):
+        if i >= 10000:
+            break
+        w = math.exp(s.log_weight) if alg == "ipmcmc" else 1.0
+        acc[np.arange(17), np.asarray(s.result).astype(int)] += w
+        wsum += w
+    it.close()
+    acc /= wsum
+    rms = math.sqrt(((acc - np.array(h["posterior"])) ** 2).sum() / (3 * 16))
+    assert rms < h["rms_threshold"], (alg, rms)
+
+
+def test_config2_log_marginal_vs_kalman(orc):
+    """BASELINE config 2: 1-D LGSSM, T=1000, 2^20 particles; log-marginal and
+    filtering means vs the exact Kalman filter."""
+    from anglican_b200 import Population
+    from anglican_b200.models import LinearGaussian1D
+    y = _lgssm_data(1000)
+    m = LinearGaussian1D()
+    exact, fm = orc.kalman1d(orc.Model(orc.SSM_LGSSM1D, **m.params), y)
+    with Population(1 << 20, seed=0xA11CE) as pop:
+        out = pop.sweep(m, y)
+    assert abs(out.log_z - exact) < 0.25, (out.log_z, exact)
+    assert np.abs(out.filt_mean - fm).max() < 0.02
+    assert abs(out.log_z - out.log_mean_w.sum()) < 1e-9 * abs(out.log_z)
+    assert out.ess.min() > 1000
+
+
+def test_csmc_sweep_matches_oracle(orc):
+    """conditional sweep: retained particle in slot 0, N-1 resampled
+    (pgibbs.cljc:89-104, ipmcmc.cljc:55-66)."""
+    from anglican_b200 import Population
+    from anglican_b200.models import LinearGaussian1D
+    T, n = 25, 5000
+    y = _lgssm_data(T, seed=5)
+    m = LinearGaussian1D()
+    om = orc.Model(orc.SSM_LGSSM1D, **m.params)
+    rng = np.random.default_rng(8)
+    ret = rng.normal(size=T + 1)
+    for n_cond in (T, T - 1):
+        with Population(n, seed=321) as pop:
+            out = pop.sweep(m, y, retained=ret, csmc=True, n_cond_steps=n_cond,
+                            reset_weights=True, keep_history=True)
+            ref = orc.smc_sweep(om, y, n, seed=321, retained=ret, csmc=True, n_cond_steps=n_cond,
+                                reset_weights=True, keep_history=True)
+            assert _rel(out.log_mean_w, ref["log_mean_w"]) < 1e-9
+            assert _rel(out.log_z, ref["log_z"]) < 1e-9
+            anc, x = out.history()
+            assert np.array_equal(anc, ref["anc_hist"])
+            if n_cond == T:
+                assert np.allclose(out.trace(0), ret)             # retained lineage survives
+            assert _rel(out.trace(n // 2), orc.trace_lineage(ref, n // 2)[:, 0]) < 1e-9
+
+
+def test_gaussian_benchmark_posterior():
+    """algorithm_test.cljc:71-94: unknown mean, KL to N(7.25, sqrt(1/1.2)) < 0.10.
+    As a state-space program: x0 ~ normal(mu0, sigma0), x' = x (a=1, q=0)."""
+    from anglican_b200.inference import infer
+    from anglican_b200.models import LinearGaussian1D
+    g = G["gaussian"]
+    m = LinearGaussian1D(m0=g["mu0"], s0=g["sigma0"], a=1.0, b=0.0, q=0.0, c=1.0, d=0.0,
+                         r=g["sigma"])
+    xs = []
+    it = infer("smc", m, g["observations"], number_of_particles=100, seed=5)
+    for i, s in enumerate(it):
+        if i >= 10000:
+            break
+        xs.append(s.result)
+    it.close()
+    mu, sd = np.mean(xs), np.std(xs)
+    q_mu, q_sd = g["post_mean"], g["post_sd"]
+    kl = math.log(q_sd / sd) + (sd ** 2 + (mu - q_mu) ** 2) / (2 * q_sd ** 2) - 0.5
+    assert kl < g["kl_threshold"], (mu, sd, kl)
