@@ -71,6 +71,7 @@ _SIGS = [
     ("apop_timer_end", C.c_int, [_vp, C.c_int]),
     ("apop_timer_elapsed_ms", C.c_int, [_vp, C.c_int, c_double_p, c_int64_p]),
     ("apop_timer_reset", C.c_int, [_vp]),
+    ("apop_enable_kernel_timers", C.c_int, [_vp, C.c_int]),
     ("apop_column_alloc", C.c_int, [_vp, C.c_int, C.c_int, c_int32_p]),
     ("apop_column_free", C.c_int, [_vp, C.c_int32]),
     ("apop_column_upload", C.c_int, [_vp, C.c_int32, _vp, C.c_int64]),

@@ -99,6 +99,7 @@ struct apop_ctx {
     apop::Timer timers[16];
     void* nccl = nullptr;         // ncclComm_t
     apop::ParamArena arena;       // staged distribution parameters
+    bool ktimers = false;         // per-kernel CUDA-event timers (bench roofline)
     // last fused sweep
     struct SweepState* sweep = nullptr;
 };
@@ -118,6 +119,12 @@ int set_err(apop_ctx* c, int code, const char* fmt, ...);
         int rc__ = (expr);           \
         if (rc__ != APOP_OK) return rc__; \
     } while (0)
+
+// kernel-class timer tags (apop_timer_elapsed_ms)
+enum { KT_SWEEP = 0, KT_PROPAGATE = 1, KT_TILE_LSE = 2, KT_FINALIZE = 3, KT_FOLD_AGG = 4,
+       KT_RESOLVE = 5, KT_ANCESTORS = 6, KT_STATS = 7, KT_GATHER = 8, KT_MIGRATE = 9 };
+void kt_begin(apop_ctx* c, int tag);
+void kt_end(apop_ctx* c, int tag);
 
 Column* get_col(apop_ctx* c, apop_col h, int dtype, int width);
 int ensure_scratch(apop_ctx* c, size_t bytes);

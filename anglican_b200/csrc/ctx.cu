@@ -20,6 +20,26 @@ int set_err(apop_ctx* c, int code, const char* fmt, ...) {
     return code;
 }
 
+void kt_begin(apop_ctx* c, int tag) {
+    if (!c->ktimers) return;
+    Timer& t = c->timers[tag];
+    if (t.open) return;
+    if (cudaEventCreate(&t.a) != cudaSuccess) return;
+    cudaEventRecord(t.a, c->stream);
+    t.open = true;
+}
+void kt_end(apop_ctx* c, int tag) {
+    if (!c->ktimers) return;
+    Timer& t = c->timers[tag];
+    if (!t.open) return;
+    cudaEvent_t b;
+    if (cudaEventCreate(&b) != cudaSuccess) return;
+    cudaEventRecord(b, c->stream);
+    t.pending.push_back({t.a, b});
+    t.a = nullptr;
+    t.open = false;
+}
+
 Column* get_col(apop_ctx* c, apop_col h, int dtype, int width) {
     if (h < 0 || (size_t)h >= c->cols.size() || !c->cols[h].used) {
         set_err(c, APOP_ERR_INVALID, "bad column handle %d", (int)h);
@@ -175,6 +195,12 @@ int apop_synchronize(apop_ctx* c) {
 int64_t apop_num_particles(apop_ctx* c) { return c ? c->n : 0; }
 int64_t apop_launch_count(apop_ctx* c) { return c ? c->launches : 0; }
 void* apop_stream(apop_ctx* c) { return c ? (void*)c->stream : nullptr; }
+
+int apop_enable_kernel_timers(apop_ctx* c, int on) {
+    CHECK_CTX(c);
+    c->ktimers = on != 0;
+    return APOP_OK;
+}
 
 int apop_set_seed(apop_ctx* c, uint64_t seed) {
     CHECK_CTX(c);

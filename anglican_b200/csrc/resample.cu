@@ -733,16 +733,26 @@ int resample_enqueue(apop_ctx* c, const ResampleArgs& a) {
     const int wm = a.w ? 1 : 0;
     if (!a.have_partials) {
         k_info_reset<<<1, 1, 0, c->stream>>>(v.info);
+        kt_begin(c, KT_TILE_LSE);
         k_tile_lse<<<nt, TB, 0, c->stream>>>(a.lw, a.w, a.n, v);
+        kt_end(c, KT_TILE_LSE);
         c->launches += 2;
     }
+    kt_begin(c, KT_FINALIZE);
     k_finalize<<<1, FB, 0, c->stream>>>(v, a.n, a.n_new, a.u, c->seed, c->step, wm);
+    kt_end(c, KT_FINALIZE);
+    kt_begin(c, KT_FOLD_AGG);
     k_fold_agg<<<nt, TB, 0, c->stream>>>(a.lw, a.w, a.n, v);
+    kt_end(c, KT_FOLD_AGG);
+    kt_begin(c, KT_RESOLVE);
     k_resolve<<<1, TB, 0, c->stream>>>(a.lw, a.w, a.n, v);
+    kt_end(c, KT_RESOLVE);
     c->launches += 3;
     if (a.anc_out) {
+        kt_begin(c, KT_ANCESTORS);
         k_ancestors<<<nt, TB, 0, c->stream>>>(a.lw, a.w, a.n, c->g0, v, a.order, a.anc_out,
                                               a.out_offset);
+        kt_end(c, KT_ANCESTORS);
         c->launches += 1;
     }
     APOP_CUDA(c, cudaGetLastError());
@@ -795,12 +805,14 @@ int gather_enqueue(apop_ctx* c, const int32_t* anc, int64_t n_new, Column* col) 
     const int64_t total = n_new * col->width;
     int blocks = (int)((total + 255) / 256);
     if (blocks > 148 * 32) blocks = 148 * 32;
+    kt_begin(c, KT_GATHER);
     if (col->dtype == APOP_F64)
         k_gather_f64<<<blocks, 256, 0, c->stream>>>((const double*)col->ptr, (double*)c->scratch,
                                                     anc, n_new, col->width);
     else
         k_gather_i32<<<blocks, 256, 0, c->stream>>>((const int32_t*)col->ptr,
                                                     (int32_t*)c->scratch, anc, n_new, col->width);
+    kt_end(c, KT_GATHER);
     c->launches += 1;
     APOP_CUDA(c, cudaGetLastError());
     APOP_CUDA(c, cudaMemcpyAsync(col->ptr, c->scratch, (size_t)n_new * col->width * esz,

@@ -383,6 +383,13 @@ static int run_scalar_sweep(apop_ctx* c, const apop_ssm* model, const double* y,
         APOP_CUDA(c, cudaMemcpyAsync(s->retained, staged, sizeof(double) * (size_t)(T + 1),
                                      cudaMemcpyDeviceToDevice, c->stream));
     }
+    {
+        Timer& tm = c->timers[KT_SWEEP];
+        if (!tm.open && cudaEventCreate(&tm.a) == cudaSuccess) {
+            cudaEventRecord(tm.a, c->stream);
+            tm.open = true;
+        }
+    }
     k_sweep_reset<<<1, 1, 0, c->stream>>>(s->sd, ws.info);
     double* x_prev = s->history ? s->x_hist : s->xa;
     {
@@ -395,10 +402,12 @@ static int run_scalar_sweep(apop_ctx* c, const apop_ssm* model, const double* y,
     for (int t = 1; t <= T; ++t) {
         double* x_new = s->history ? s->x_hist + (size_t)t * n : ((t & 1) ? s->xb : s->xa);
         int32_t* anc_new = s->history ? s->anc_hist + (size_t)(t - 1) * n : s->anc;
+        kt_begin(c, KT_PROPAGATE);
         k_propagate<KIND><<<nt, TB, 0, c->stream>>>(
             s->model, x_prev, anc_prev, t == 1, x_new, s->lw, s->y + (t - 1),
             csmc ? s->retained + t : nullptr, s->sd, n, c->g0, c->seed, (uint32_t)t, ws.tmax,
             ws.tsum, ws.tsum2, s->tsx, &ws.info->err);
+        kt_end(c, KT_PROPAGATE);
         c->launches += 1;
         const bool cond = csmc && t <= o->n_cond_steps;
         c->step = (uint32_t)t;
@@ -407,9 +416,11 @@ static int run_scalar_sweep(apop_ctx* c, const apop_ssm* model, const double* y,
         a.u = NAN; a.order = APOP_ORDER_SORTED;
         a.anc_out = anc_new; a.out_offset = cond ? 1 : 0; a.have_partials = true;
         APOP_TRY(resample_enqueue(c, a));
+        kt_begin(c, KT_STATS);
         k_step_stats<<<1, 256, 0, c->stream>>>(s->sd, ws.info, ws.tmax, s->tsx, nt, t,
                                                o->reset_weights, cond ? 1 : 0, anc_new,
                                                s->log_mean_w, s->ess, s->filt);
+        kt_end(c, KT_STATS);
         c->launches += 1;
         x_prev = x_new;
         anc_prev = anc_new;
@@ -455,8 +466,20 @@ int apop_smc_sweep(apop_ctx* c, const apop_ssm* model, const double* y, int32_t 
     if (opts->want_final || result->x_final) {
         int blocks = (int)((n * dim + 255) / 256);
         if (blocks > 148 * 32) blocks = 148 * 32;
+        kt_begin(c, KT_GATHER);
         k_gather_rows<<<blocks, 256, 0, c->stream>>>(s->last_x, s->x_final, s->last_anc, n, dim);
+        kt_end(c, KT_GATHER);
         c->launches += 1;
+    }
+    {
+        Timer& tm = c->timers[KT_SWEEP];
+        cudaEvent_t b;
+        if (tm.open && cudaEventCreate(&b) == cudaSuccess) {
+            cudaEventRecord(b, c->stream);
+            tm.pending.push_back({tm.a, b});
+            tm.a = nullptr;
+            tm.open = false;
+        }
     }
     // results: one small D2H per requested array, then a single sync
     SweepDev hsd;

@@ -111,6 +111,9 @@ class Population:
         L.check(self.ctx, self.lib.apop_timer_elapsed_ms(self.ctx, tag, C.byref(ms), C.byref(cnt)))
         return ms.value, cnt.value
 
+    def enable_kernel_timers(self, on=True):
+        L.check(self.ctx, self.lib.apop_enable_kernel_timers(self.ctx, int(on)))
+
     def timer_reset(self):
         L.check(self.ctx, self.lib.apop_timer_reset(self.ctx))
 

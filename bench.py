@@ -1,0 +1,321 @@
+#!/usr/bin/env python
+"""bench.py — SMC particle-steps/s of the particle-population hot path.
+
+    python bench.py --gpus N --steps K --warmup W          (our arm)
+    python bench.py --impl reference --gpus N --steps K --warmup W
+
+One "step" = one full `sweep` (smc.cljc:35-51) of BASELINE config 3: the
+stochastic-volatility SSM, T=2000 observations, 2^27 particles in total,
+sharded contiguously over the N ranks (strong scaling, north_star).  `value` is
+whole-job particle-steps/s timed on the device (CUDA events on the engine's
+stream, max over ranks) with inputs resident in HBM; `e2e` is the same metric
+through the public call (host observations in, log-marginal + per-step stats +
+final particle states out, host<->device copies inside the timed region).
+"""
+import argparse
+import json
+import math
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "smc_particle_steps_per_sec"
+UNIT = "particle-steps/s"
+KT_NAMES = {1: "k_propagate", 2: "k_tile_lse", 3: "k_finalize", 4: "k_fold_agg", 5: "k_resolve",
+            6: "k_ancestors", 7: "k_step_stats", 8: "k_gather", 9: "migrate"}
+# algorithmic bytes per particle per launch (d = 1):
+#   k_propagate does K1 propagate+reweight (16d+8) + K2 normalise partials (8)
+#               + K5 ancestor gather (16d+4)                       = 52
+#   k_fold_agg  weight scan, first pass (reads the log-weights)     =  8
+#   k_ancestors K3+K4 scan + ancestor search (R 8 + W 4)            = 12
+ALGO_BYTES = {"k_propagate": 52.0, "k_fold_agg": 8.0, "k_ancestors": 12.0, "k_tile_lse": 8.0,
+              "k_gather": 20.0}
+STEP_BYTES = 64.0          # whole particle-step: 32d + 32
+
+
+def sv_observations(T, seed=20240602, phi=0.98, sigma=0.16, beta=0.65):
+    rng = np.random.default_rng(seed)
+    x = rng.normal() * sigma / math.sqrt(1 - phi * phi)
+    ys = np.empty(T)
+    for t in range(T):
+        x = phi * x + sigma * rng.normal()
+        ys[t] = beta * math.exp(x / 2) * rng.normal()
+    return ys
+
+
+def measured_peak():
+    try:
+        pk = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        return float(pk["hbm_gbs"]), "measured"
+    except Exception:
+        return 6650.0, "fallback"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons during the timed region"""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        self.gpu = gpu_index
+        self.rows = []
+        self.proc = None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", "-i", str(self.gpu), f"--query-gpu={self.Q}",
+                 "--format=csv,noheader,nounits", "-lms", "200"],
+                stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if self.proc:
+            self.proc.terminate()
+            try:
+                self.proc.wait(timeout=5)
+            except Exception:
+                pass
+        sm, mx, reasons = [], [], set()
+        for r in self.rows:
+            try:
+                sm.append(float(r[1]))
+                mx.append(float(r[2]))
+                for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown",
+                                    "sw_power_cap"), r[4:8]):
+                    if v.lower().startswith("active"):
+                        reasons.add(name)
+            except Exception:
+                pass
+        if not sm:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        busy = sorted(sm)[len(sm) // 2:]
+        return {"sm_mhz": float(np.median(busy)), "sm_max_mhz": max(mx),
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def dist_env():
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    return rank, world, local
+
+
+# --------------------------------------------------------------------- reference arm
+def run_reference(args):
+    """The reference's CPU path for the same workload.  The Clojure reference
+    cannot run here (no JVM, SURVEY header), so this times the oracle port of
+    smc.cljc on the host cores — the one place besides cpu_baseline where bench
+    executes oracle/."""
+    rank, world, _ = dist_env()
+    if rank != 0:
+        return
+    from oracle import pyoracle as orc
+    T = args.T
+    cores = os.cpu_count() or 1
+    n_s, T_s = 1 << 17, min(T, 200)
+    y = sv_observations(T)[:T_s]
+    phi, sigma, beta = 0.98, 0.16, 0.65
+    m = orc.Model(orc.SSM_SV, m0=0.0, s0=sigma / math.sqrt(1 - phi * phi), a=phi, b=0.0, q=sigma,
+                  beta=beta)
+    times = []
+    for i in range(args.warmup + args.steps):
+        t0 = time.perf_counter()
+        orc.smc_sweep(m, y, n_s, seed=100 + i, threads=cores, want_final=True)
+        dt = time.perf_counter() - t0
+        if i >= args.warmup:
+            times.append(dt)
+    total = sum(times)
+    v = n_s * T_s * len(times) / total
+    sample = (f"SV sweep, {n_s} particles x {T_s} of {T} steps per bench step (bounded sample of "
+              f"the 2^{int(math.log2(args.particles))}-particle workload; per-particle-step cost is "
+              "size-independent on the CPU)")
+    line = {"impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * total / len(times),
+            "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64",
+            "data": "synthetic",
+            "config": {"workload": args.workload_name, "particles_total": args.particles,
+                       "T": T, "note": "reference JVM path unavailable on this box (no JVM); "
+                                       "oracle C port of smc.cljc timed instead"},
+            "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": "port",
+                             "sample": sample},
+            "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line), flush=True)
+
+
+# --------------------------------------------------------------------- our arm
+def run_ours(args):
+    rank, world, local = dist_env()
+    import torch
+    import torch.distributed as dist
+    from anglican_b200 import Population
+    from anglican_b200.models import StochasticVolatility
+
+    if world != args.gpus and world > 1:
+        raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={world}")
+    torch.cuda.set_device(local)
+    nccl_id = None
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+        from anglican_b200 import _lib as L
+        import ctypes as C
+        buf = torch.zeros(128, dtype=torch.uint8, device="cuda")
+        if rank == 0:
+            raw = C.create_string_buffer(128)
+            assert L.load().apop_get_unique_id(raw) == 0
+            buf.copy_(torch.frombuffer(bytearray(raw.raw), dtype=torch.uint8))
+        dist.broadcast(buf, 0)
+        nccl_id = bytes(buf.cpu().numpy().tobytes())
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    n_total, T = args.particles, args.T
+    assert n_total % world == 0
+    n_local = n_total // world
+    y = sv_observations(T)
+    model = StochasticVolatility()
+    pop = Population(n_local, seed=0xA11CE, device=local, rank=rank, world=world, nccl_id=nccl_id)
+
+    # ---- warm-up (>= 3 sweeps): device-resident path
+    for i in range(args.warmup):
+        pop.set_seed(1000 + i)
+        pop.sweep(model, y, want_final=False, want_stats=False)
+    pop.timer_reset()
+    pop.enable_kernel_timers(True)
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    launches0 = pop.launches
+    barrier()
+    wall0 = time.perf_counter()
+    log_zs = []
+    for i in range(args.steps):
+        pop.set_seed(2000 + i)
+        out = pop.sweep(model, y, want_final=False, want_stats=False)
+        log_zs.append(out.log_z)
+    barrier()
+    wall = time.perf_counter() - wall0
+    launches = pop.launches - launches0
+    dev_ms, cnt = pop.timer_ms(0)            # kernels of the sweeps, CUDA events on the engine stream
+    kt = {}
+    for tag, name in KT_NAMES.items():
+        ms, c = pop.timer_ms(tag)
+        if c:
+            kt[name] = (ms, c)
+    clocks = sampler.stop() if rank == 0 else None
+    pop.enable_kernel_timers(False)
+
+    # ---- e2e: public call, host buffers in/out, copies inside the timed region
+    x_host_bytes = n_local * 8
+    barrier()
+    e0 = time.perf_counter()
+    for i in range(args.steps):
+        pop.set_seed(3000 + i)
+        out = pop.sweep(model, y, want_final=True, want_stats=True)
+    barrier()
+    e2e_s = time.perf_counter() - e0
+
+    t_dev = torch.tensor([dev_ms / 1e3, e2e_s, wall], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(t_dev, op=dist.ReduceOp.MAX)
+    dev_s, e2e_s, wall = [float(v) for v in t_dev.cpu()]
+    work = float(n_total) * T * args.steps
+
+    if rank == 0:
+        peak, peak_kind = measured_peak()
+        dom = max(((n, v) for n, v in kt.items() if n in ALGO_BYTES), key=lambda kv: kv[1][0],
+                  default=None)
+        roof = None
+        if dom:
+            name, (ms, c) = dom
+            avg_s = ms / 1e3 / c
+            achieved = ALGO_BYTES[name] * n_local / avg_s / 1e9
+            roof = {"kernel": name, "bound": "hbm", "achieved": achieved, "peak": peak,
+                    "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+                    "peak_source": f"{peak_kind} (MEASURED_PEAKS.json hbm_gbs)",
+                    "avg_launch_us": avg_s * 1e6, "launches_timed": c,
+                    "algorithmic_bytes_per_particle": ALGO_BYTES[name]}
+        ksum_ms = sum(v[0] for v in kt.values())
+        path = {"bytes_per_particle_step": STEP_BYTES,
+                "achieved_gbs": STEP_BYTES * n_local * T * args.steps / (dev_s) / 1e9,
+                "frac": STEP_BYTES * n_local * T * args.steps / dev_s / 1e9 / peak,
+                "kernel_share": {n: v[0] / ksum_ms for n, v in kt.items()} if ksum_ms else {},
+                "kernel_avg_us": {n: 1e3 * v[0] / v[1] for n, v in kt.items()}}
+        line = {"metric": METRIC, "value": work / dev_s, "unit": UNIT, "n_gpus": world,
+                "steps": args.steps, "warmup": args.warmup,
+                "ms_per_step": 1e3 * dev_s / args.steps, "higher_is_better": True,
+                "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+                "config": {"workload": args.workload_name, "particles_total": n_total,
+                           "particles_per_gpu": n_local, "T": T, "model": "stochastic volatility "
+                           "phi=0.98 sigma=0.16 beta=0.65", "resampling": "systematic, every step",
+                           "l2": "inputs exceed L2 (columns of %d MiB per GPU)" % (n_local * 8 >> 20),
+                           "timing": "CUDA events on the engine stream, max over ranks"},
+                "e2e": {"value": work / e2e_s, "unit": UNIT,
+                        "h2d_bytes_per_step": int(T * 8 + 4096),
+                        "d2h_bytes_per_step": int(x_host_bytes + 2 * T * 8 + 64)},
+                "gpu_launches": int(launches), "clocks": clocks, "roofline": roof,
+                "path_roofline": path, "wall_ms_per_step": 1e3 * wall / args.steps,
+                "log_z_mean": float(np.mean(log_zs))}
+        if world == 1 and not args.no_cpu_baseline:
+            line["cpu_baseline"] = cpu_baseline(args)
+        print(json.dumps(line), flush=True)
+    pop.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def cpu_baseline(args):
+    """oracle port of smc.cljc, 1 core (the reference's `infer :smc` is single
+    threaded), on a bounded sample of the same workload."""
+    from oracle import pyoracle as orc
+    n_s, T_s = 1 << 17, min(args.T, 300)
+    y = sv_observations(args.T)[:T_s]
+    phi, sigma, beta = 0.98, 0.16, 0.65
+    m = orc.Model(orc.SSM_SV, m0=0.0, s0=sigma / math.sqrt(1 - phi * phi), a=phi, b=0.0, q=sigma,
+                  beta=beta)
+    t0 = time.perf_counter()
+    orc.smc_sweep(m, y, n_s, seed=1, threads=1, want_final=True)
+    dt = time.perf_counter() - t0
+    return {"value": n_s * T_s / dt, "unit": UNIT, "cores": 1, "kind": "port",
+            "sample": f"SV sweep of {n_s} particles x {T_s} steps ({dt:.1f} s), oracle C port of "
+                      "smc.cljc; reference JVM path unavailable on this box (no JVM)"}
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=2)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--particles", type=int, default=1 << 27)
+    ap.add_argument("--T", type=int, default=2000)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    args.workload_name = ("configs[2]: stochastic-volatility SSM, T=%d, %d particles :smc sharded "
+                          "over %d B200" % (args.T, args.particles, args.gpus))
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

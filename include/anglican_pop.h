@@ -88,6 +88,10 @@ int apop_timer_begin(apop_ctx* ctx, int tag);
 int apop_timer_end(apop_ctx* ctx, int tag);
 int apop_timer_elapsed_ms(apop_ctx* ctx, int tag, double* total_ms, int64_t* count);
 int apop_timer_reset(apop_ctx* ctx);
+/* bracket every kernel class of the sweep / resample pipeline with CUDA events
+ * on the ctx stream.  tags: 0 sweep, 1 propagate, 2 tile_lse, 3 finalize,
+ * 4 fold_agg, 5 resolve, 6 ancestors, 7 step_stats, 8 gather, 9 migrate */
+int apop_enable_kernel_timers(apop_ctx* ctx, int on);
 
 /* ---- columns (state.cljc:9-36: the :log-weight field becomes a column) -- */
 int apop_column_alloc(apop_ctx* ctx, int dtype, int width, apop_col* out);

@@ -183,14 +183,18 @@ def test_gaussian_benchmark_posterior():
     g = G["gaussian"]
     m = LinearGaussian1D(m0=g["mu0"], s0=g["sigma0"], a=1.0, b=0.0, q=0.0, c=1.0, d=0.0,
                          r=g["sigma"])
-    xs = []
+    xs, lws = [], []
     it = infer("smc", m, g["observations"], number_of_particles=100, seed=5)
     for i, s in enumerate(it):
         if i >= 10000:
             break
         xs.append(s.result)
+        lws.append(s.log_weight)
     it.close()
-    mu, sd = np.mean(xs), np.std(xs)
+    # stat/empirical-mean / -std weight every state by its :log-weight (stat.cljc:7-103)
+    xs, w = np.array(xs), np.exp(np.array(lws) - max(lws))
+    mu = float((w * xs).sum() / w.sum())
+    sd = math.sqrt(float((w * (xs - mu) ** 2).sum() / w.sum()))
     q_mu, q_sd = g["post_mean"], g["post_sd"]
     kl = math.log(q_sd / sd) + (sd ** 2 + (mu - q_mu) ** 2) / (2 * q_sd ** 2) - 0.5
     assert kl < g["kl_threshold"], (mu, sd, kl)
