@@ -46,6 +46,23 @@ struct ResampleInfo {
     int pad;
 };
 
+struct SweepDev {           // device-resident scalars of a fused sweep
+    double base;            // common accumulated log-weight (state.cljc:27-31)
+    double log_z;           // sum_t log-mean-weight (ipmcmc.cljc:67-74)
+    int err;
+    int pad;
+};
+
+// per-step outputs of a fused sweep, written by the tail of k_resolve
+struct StepOut {
+    SweepDev* sd;           // nullptr outside sweeps
+    double* log_mean_w;
+    double* ess;
+    double* filt;
+    int32_t* anc;
+    int t, reset, cond;
+};
+
 struct Column {
     void* ptr = nullptr;
     int dtype = 0;
@@ -70,7 +87,8 @@ struct ParamArena {
 struct ResampleWS {
     int64_t nt = 0;
     double *tmax = nullptr, *tsum = nullptr, *tsum2 = nullptr, *ain = nullptr;
-    int *cls0 = nullptr, *cls1 = nullptr, *hard0 = nullptr, *hard1 = nullptr;
+    int *cls0 = nullptr, *cls1 = nullptr;
+    double *tacc = nullptr, *tacc2 = nullptr;   // accurate per-tile sum w, sum w^2
     Xd *agg0 = nullptr, *agg1 = nullptr;
     double *sin0 = nullptr, *sin1 = nullptr;
     Comb* comb = nullptr;
@@ -142,6 +160,8 @@ struct ResampleArgs {
     int32_t* anc_out;        // n_new entries
     int64_t out_offset;      // added to every written slot (CSMC keeps slot 0)
     bool have_partials;      // tile partials (tmax/tsum/tsum2) already in ws
+    const double* tsx;       // optional per-tile sum exp(lw-tmax)*x (filtering mean)
+    StepOut step;            // optional per-step outputs (sd == nullptr: none)
 };
 int resample_enqueue(apop_ctx* c, const ResampleArgs& a);
 int resample_fetch_info(apop_ctx* c, ResampleInfo* out);   // syncs

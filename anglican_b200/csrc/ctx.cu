@@ -166,7 +166,7 @@ int apop_destroy(apop_ctx* c) {
     for (auto& col : c->cols)
         if (col.used && col.ptr) cudaFree(col.ptr);
     ResampleWS& w = c->ws;
-    void* ptrs[] = {w.tmax, w.tsum, w.tsum2, w.ain, w.cls0, w.cls1, w.hard0, w.hard1, w.agg0,
+    void* ptrs[] = {w.tmax, w.tsum, w.tsum2, w.ain, w.cls0, w.cls1, w.tacc, w.tacc2, w.agg0,
                     w.agg1, w.sin0, w.sin1, w.comb, w.info, w.edges};
     for (void* p : ptrs)
         if (p) cudaFree(p);

@@ -118,6 +118,26 @@ APOP_HD void quantize(double w, int e, i64& f, int& up, int& tie) {
     tie = rem == half;
 }
 
+// Same result as quantize() for grids 2^e with -1000 <= e <= 0, using fp64
+// arithmetic instead of 64-bit shifts: scaled = w * 2^-e is exact (power of
+// two, no underflow because 2^-e >= 1); adding 2^52 rounds it to an integer
+// (nearest-even) whose value sits in the low mantissa bits.
+//   non-tie: f = RN(scaled), up = 0      tie: f = floor(scaled), up = 0
+// inv_u = 2^-e.  Must be compiled without FMA contraction.
+APOP_HD void quantize_fast(double w, double inv_u, i64& f, int& tie) {
+    const double scaled = w * inv_u;
+    tie = 0;
+    if (!(scaled < 4503599627370496.0)) { f = kSat; return; }     // >= 2^52 (or inf/NaN)
+    const double t = scaled + 4503599627370496.0;
+    const double rn = t - 4503599627370496.0;
+    const double diff = scaled - rn;                               // exact, in [-0.5, 0.5]
+    i64 irn = (i64)(dbits(t) - 0x4330000000000000ULL);
+    if (diff == 0.5) { tie = 1; }
+    else if (diff == -0.5) { tie = 1; irn -= 1; }
+    f = irn;
+}
+APOP_HD bool ctx_fast_ok(int e) { return e >= -1000 && e <= 0; }
+
 // ---- parity transducer: (a0, a1) = total increment for even / odd input ----
 struct Xd {
     i64 a0, a1;

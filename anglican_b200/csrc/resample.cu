@@ -4,16 +4,22 @@
 //
 // Pipeline (all on ctx->stream, no host round trip):
 //   K2  k_tile_lse      per-tile (max, sum exp, sum exp^2) of the log-weights
-//       k_finalize      global max m, approximate tile prefix, ESS, per-tile
-//                       binade classification for both laps of the wheel
-//   K3a k_fold_agg      per-tile parity-transducer aggregate of the exact fold
+//                       (inside a fused sweep k_propagate produces these)
+//       k_finalize      global max m, approximate tile prefix, per-tile binade
+//                       classification for both laps of the wheel
+//   K3a k_fold_agg      per-tile aggregate of the exact fold (integer units of
+//                       the tile's binade) + accurate sum w, sum w^2
 //       k_resolve       chains the aggregates -> exact running sum at every
-//                       tile boundary, exact total, pointer-comb table, J
-//   K3b/K4 k_ancestors  per-element exact edges, pointer counting, writes the
-//                       ancestor index array
+//                       tile boundary, exact total, pointer-comb table, J,
+//                       ESS / log-mean-weight, per-step sweep outputs
+//   K3b/K4 k_ancestors  per-element exact edges merged against the pointer
+//                       comb, writes the ancestor index array
 //   K5  k_gather        x_new[k] = x[a[k]]
 // The arithmetic (why this reproduces a sequential fold exactly) is in
-// exact_fold.cuh.
+// exact_fold.cuh.  "Easy" tiles (the fold provably stays in one binade, no
+// exact ties) take a fast path: fp64 magic-number quantisation, plain int64
+// prefix sums, and a merge of edges and pointers in integer units.  Everything
+// else takes the general parity-transducer path.
 #include <limits.h>
 #include <math.h>
 #include <stddef.h>
@@ -26,7 +32,8 @@ namespace apop {
 struct WSView {
     int64_t nt;
     double *tmax, *tsum, *tsum2, *ain;
-    int *cls0, *cls1, *hard0, *hard1;
+    int *cls0, *cls1;
+    double *tacc, *tacc2;
     Xd *agg0, *agg1;
     double *sin0, *sin1;
     Comb* comb;
@@ -36,7 +43,7 @@ struct WSView {
 static WSView view_of(const ResampleWS& w) {
     WSView v;
     v.nt = w.nt; v.tmax = w.tmax; v.tsum = w.tsum; v.tsum2 = w.tsum2; v.ain = w.ain;
-    v.cls0 = w.cls0; v.cls1 = w.cls1; v.hard0 = w.hard0; v.hard1 = w.hard1;
+    v.cls0 = w.cls0; v.cls1 = w.cls1; v.tacc = w.tacc; v.tacc2 = w.tacc2;
     v.agg0 = w.agg0; v.agg1 = w.agg1; v.sin0 = w.sin0; v.sin1 = w.sin1;
     v.comb = w.comb; v.info = w.info;
     return v;
@@ -44,8 +51,10 @@ static WSView view_of(const ResampleWS& w) {
 
 struct FoldSmem {
     Xd warp_tot[NWARP];
+    i64 wsum[NWARP];
     double bcast_S;
     int cross;
+    int imin;
     double last_edge[TB];
 };
 
@@ -78,12 +87,17 @@ __device__ __forceinline__ Xd cta_total_xd(const Xd* warp_tot) {
     return tot;
 }
 
-// Exact sequential fold of one tile (IPT consecutive elements per thread) that
-// starts from the exact running sum S_in.  Returns the exact sum after the
-// tile; edge[j] receives the exact inclusive running sum after element j.
-// Iterates once per binade crossing inside the tile (usually zero).
-__device__ double cta_tile_fold(double S_in, const double (&w)[IPT], int nvalid,
-                                double (&edge)[IPT], FoldSmem& sm) {
+__device__ __forceinline__ void quantize_ctx(double w, int e, bool fast, double inv_u, i64& f,
+                                             int& up, int& tie) {
+    if (fast) { up = 0; quantize_fast(w, inv_u, f, tie); }
+    else quantize(w, e, f, up, tie);
+}
+
+// General exact fold of one tile (IPT consecutive elements per thread) starting
+// from the exact running sum S_in: parity-transducer scan, one iteration per
+// binade crossing inside the tile.  edge[j] = exact inclusive running sum.
+__device__ __noinline__ double cta_tile_fold(double S_in, const double (&w)[IPT], int nvalid,
+                                             double (&edge)[IPT], FoldSmem& sm) {
     if (nvalid <= 0) return S_in;
     int pos = 0;
     double S = S_in;
@@ -91,6 +105,8 @@ __device__ double cta_tile_fold(double S_in, const double (&w)[IPT], int nvalid,
     for (;;) {
         const int e = ctx_of(S);
         const i64 s_in = units_of(S);
+        const bool fast = ctx_fast_ok(e);
+        const double inv_u = fast ? pow2(-e) : 0.0;
         i64 qf[IPT];
         int qfl[IPT];
         Xd t = xd_identity();
@@ -101,7 +117,7 @@ __device__ double cta_tile_fold(double S_in, const double (&w)[IPT], int nvalid,
             qf[j] = 0;
             if (idx >= pos && idx < nvalid) {
                 i64 f; int up, tie;
-                quantize(w[j], e, f, up, tie);
+                quantize_ctx(w[j], e, fast, inv_u, f, up, tie);
                 qf[j] = f;
                 qfl[j] = up | (tie << 1) | 4;
                 xd_push(t, f, up, tie);
@@ -147,6 +163,36 @@ __device__ double cta_tile_fold(double S_in, const double (&w)[IPT], int nvalid,
         pos = cross + 1;
         if (pos >= nvalid) return S;
     }
+}
+
+// Fast scan of an easy tile in context e: inc[j] = exact integer increment of
+// element j (no ties), s_start = exact integer state before this thread's
+// first element.  Returns false (uniformly) if any element ties or saturates.
+__device__ __forceinline__ bool tile_scan_easy(double S_in, int e, const double (&w)[IPT],
+                                               i64 (&inc)[IPT], i64& s_start, FoldSmem& sm) {
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    const double inv_u = pow2(-e);
+    i64 sum = 0;
+    int bad = 0;
+#pragma unroll
+    for (int j = 0; j < IPT; ++j) {
+        int tie;
+        quantize_fast(w[j], inv_u, inc[j], tie);
+        bad |= tie | (inc[j] >= kSat);
+        sum += inc[j];
+    }
+    i64 incl = sum;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        i64 o = shfl_up_i64(incl, d);
+        if (lane >= d) incl += o;
+    }
+    if (lane == 31) sm.wsum[wid] = incl;
+    if (__syncthreads_or(bad)) return false;
+    i64 pre = 0;
+    for (int i = 0; i < wid; ++i) pre += sm.wsum[i];
+    s_start = units_of(S_in) + pre + (incl - sum);
+    return true;
 }
 
 __device__ __forceinline__ void load_weights(const double* __restrict__ lw,
@@ -225,6 +271,7 @@ __global__ void __launch_bounds__(TB) k_tile_lse(const double* __restrict__ lw,
 
 // ------------------------------------------------------------------ finalize
 constexpr int FB = 1024;
+constexpr int FCH = 4;                 // values per thread per scan chunk
 
 __device__ __forceinline__ double block_excl_scan_f64(double v, double* sm /*[33]*/,
                                                       double& total) {
@@ -255,84 +302,89 @@ __device__ __forceinline__ double block_excl_scan_f64(double v, double* sm /*[33
     return r;
 }
 
-__device__ __forceinline__ int block_excl_scan_i32(int v, int* sm /*[33]*/, int& total) {
-    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-    int inc = v;
-#pragma unroll
-    for (int d = 1; d < 32; d <<= 1) {
-        int o = __shfl_up_sync(0xffffffffu, inc, d);
-        if (lane >= d) inc += o;
-    }
-    if (lane == 31) sm[wid] = inc;
+__device__ __forceinline__ double block_sum_f64(double v, double* sm /*[33]*/) {
+    v = warp_sum(v);
+    if ((threadIdx.x & 31) == 0) sm[threadIdx.x >> 5] = v;
     __syncthreads();
-    if (wid == 0) {
-        int ws = (lane < (int)(blockDim.x >> 5)) ? sm[lane] : 0;
-        int winc = ws;
-#pragma unroll
-        for (int d = 1; d < 32; d <<= 1) {
-            int o = __shfl_up_sync(0xffffffffu, winc, d);
-            if (lane >= d) winc += o;
-        }
-        sm[lane] = winc - ws;
-        if (lane == 31) sm[32] = winc;
+    double r = 0.0;
+    if (threadIdx.x < 32) {
+        r = (threadIdx.x < (blockDim.x >> 5)) ? sm[threadIdx.x] : 0.0;
+        r = warp_sum(r);
+        if (threadIdx.x == 0) sm[32] = r;
     }
     __syncthreads();
-    int r = sm[wid] + (inc - v);
-    total = sm[32];
+    r = sm[32];
     __syncthreads();
     return r;
 }
 
+// single CTA; every global access is coalesced (tiles are walked striped)
 __global__ void __launch_bounds__(FB) k_finalize(WSView v, int64_t n, int64_t n_new, double u_in,
-                                                 uint64_t seed, uint32_t step, int weights_mode) {
+                                                 uint64_t seed, uint32_t step, int weights_mode,
+                                                 const double* __restrict__ tsx) {
+    __shared__ double buf[FB * FCH];
     __shared__ double smd[33];
-    __shared__ int smi[33];
-    __shared__ double sh_m;
     __shared__ int sh_skip;
     const int64_t nt = v.nt;
     const int tid = threadIdx.x;
-    const int64_t per = (nt + FB - 1) / FB;
-    const int64_t t0 = (int64_t)tid * per;
-    const int64_t t1 = (t0 + per < nt) ? t0 + per : nt;
 
     // ---- global max (smc.cljc:75)
     double m = 0.0;
     if (!weights_mode) {
         double mx = -INFINITY;
-        for (int64_t t = t0; t < t1; ++t) mx = fmax(mx, v.tmax[t]);
+        for (int64_t t = tid; t < nt; t += FB) mx = fmax(mx, v.tmax[t]);
         mx = warp_max(mx);
         if ((tid & 31) == 0) smd[tid >> 5] = mx;
         __syncthreads();
-        if (tid == 0) {
-            double a = smd[0];
-            for (int i = 1; i < FB / 32; ++i) a = fmax(a, smd[i]);
-            sh_m = a;
-        }
-        __syncthreads();
-        m = sh_m;
+        double a = smd[0];
+        for (int i = 1; i < FB / 32; ++i) a = fmax(a, smd[i]);
+        m = a;
         __syncthreads();
     }
-    auto asum = [&](int64_t t) -> double {
-        if (weights_mode) return v.tsum[t];
-        double tm = v.tmax[t];
-        double fac = (tm == m) ? 1.0 : exp(tm - m);
-        return v.tsum[t] * fac;
-    };
-    auto asq = [&](int64_t t) -> double {
-        if (weights_mode) return v.tsum2[t];
-        double tm = v.tmax[t];
-        double fac = (tm == m) ? 1.0 : exp(2.0 * (tm - m));
-        return v.tsum2[t] * fac;
-    };
-    // ---- approximate exclusive prefix of tile sums
-    double loc = 0.0, loc2 = 0.0;
-    for (int64_t t = t0; t < t1; ++t) { loc += asum(t); loc2 += asq(t); }
-    double atot, asqtot;
-    double run = block_excl_scan_f64(loc, smd, atot);
-    (void)block_excl_scan_f64(loc2, smd, asqtot);
-    for (int64_t t = t0; t < t1; ++t) { v.ain[t] = run; run += asum(t); }
-    if (t1 == nt && t0 < nt) v.ain[nt] = run;
-    if (nt == 0 && tid == 0) v.ain[0] = 0.0;
+    // ---- rescale the tile partials to the global max (in place)
+    double locq = 0.0, locx = 0.0;
+    for (int64_t t = tid; t < nt; t += FB) {
+        double fac = 1.0;
+        if (!weights_mode) {
+            const double tm = v.tmax[t];
+            fac = (tm == m) ? 1.0 : exp(tm - m);
+        }
+        const double a = v.tsum[t] * fac;
+        const double q = v.tsum2[t] * fac * fac;
+        v.tsum[t] = a;
+        v.tsum2[t] = q;
+        locq += q;
+        if (tsx) locx += tsx[t] * fac;
+    }
+    const double asqtot = block_sum_f64(locq, smd);
+    const double wxtot = block_sum_f64(locx, smd);
+    // ---- approximate exclusive prefix of tile sums: ain[t]
+    double carry = 0.0;
+    for (int64_t base = 0; base < nt; base += FB * FCH) {
+#pragma unroll
+        for (int k = 0; k < FCH; ++k) {
+            const int64_t idx = base + k * FB + tid;
+            buf[k * FB + tid] = (idx < nt) ? v.tsum[idx] : 0.0;
+        }
+        __syncthreads();
+        double a[FCH], loc = 0.0;
+#pragma unroll
+        for (int k = 0; k < FCH; ++k) { a[k] = buf[tid * FCH + k]; loc += a[k]; }
+        double chunk_total;
+        double run = carry + block_excl_scan_f64(loc, smd, chunk_total);
+#pragma unroll
+        for (int k = 0; k < FCH; ++k) { buf[tid * FCH + k] = run; run += a[k]; }
+        __syncthreads();
+#pragma unroll
+        for (int k = 0; k < FCH; ++k) {
+            const int64_t idx = base + k * FB + tid;
+            if (idx < nt) v.ain[idx] = buf[k * FB + tid];
+        }
+        carry += chunk_total;
+        __syncthreads();
+    }
+    const double atot = carry;
+    if (tid == 0) { v.ain[nt] = atot; sh_skip = (nt < INT_MAX) ? (int)nt : INT_MAX; }
     __syncthreads();
 
     const double u = (u_in != u_in) ? uniform_at(seed, 0, step, STREAM_RESAMPLE, 0) : u_in;
@@ -341,14 +393,11 @@ __global__ void __launch_bounds__(FB) k_finalize(WSView v, int64_t n, int64_t n_
     const double xlast_ub = atot * (u + 1.0) * (1.0 + 4.0 * eps_tot);
 
     // ---- classification of every tile for both laps
-    if (tid == 0) sh_skip = (nt < INT_MAX) ? (int)nt : INT_MAX;
-    __syncthreads();
     int nh0 = 0, nh1 = 0;
-    for (int64_t t = t0; t < t1; ++t) {
+    for (int64_t t = tid; t < nt; t += FB) {
         const int64_t hi = ((t + 1) * TILE < n) ? (t + 1) * TILE : n;
-        const double a_in = v.ain[t];
-        const double ao = a_in + asum(t);
-        int c0 = classify_tile(a_in, ao, hi);
+        const double a_in = v.ain[t], ao = v.ain[t + 1];
+        const int c0 = classify_tile(a_in, ao, hi);
         v.cls0[t] = c0;
         nh0 += (c0 == kCtxHard);
         int c1;
@@ -362,14 +411,8 @@ __global__ void __launch_bounds__(FB) k_finalize(WSView v, int64_t n, int64_t n_
         v.cls1[t] = c1;
         nh1 += (c1 == kCtxHard);
     }
-    __syncthreads();
-    int tot0, tot1;
-    int o0 = block_excl_scan_i32(nh0, smi, tot0);
-    int o1 = block_excl_scan_i32(nh1, smi, tot1);
-    for (int64_t t = t0; t < t1; ++t) {
-        if (v.cls0[t] == kCtxHard) v.hard0[o0++] = (int)t;
-        if (v.cls1[t] == kCtxHard) v.hard1[o1++] = (int)t;
-    }
+    const double h0 = block_sum_f64((double)nh0, smd);
+    const double h1 = block_sum_f64((double)nh1, smd);
     if (tid == 0) {
         ResampleInfo* I = v.info;
         I->m = m;
@@ -378,10 +421,11 @@ __global__ void __launch_bounds__(FB) k_finalize(WSView v, int64_t n, int64_t n_
         I->ess = (asqtot > 0.0) ? atot * atot / asqtot : 0.0;
         I->log_mean_approx = (m > -INFINITY && m < INFINITY) ? log(atot / (double)n) + m
                                                                : -INFINITY;
+        I->wx_sum[0] = wxtot;
         I->u = u;
         I->n_new = n_new;
-        I->nh0 = tot0;
-        I->nh1 = tot1;
+        I->nh0 = (int)h0;
+        I->nh1 = (int)h1;
         I->first_skip1 = sh_skip;
         I->weights_mode = weights_mode;
         if (!weights_mode && m != m) I->err |= EB_NAN;
@@ -389,17 +433,57 @@ __global__ void __launch_bounds__(FB) k_finalize(WSView v, int64_t n, int64_t n_
 }
 
 // ------------------------------------------------------------------ K3a
-__global__ void __launch_bounds__(TB) k_fold_agg(const double* __restrict__ lw,
-                                                 const double* __restrict__ win, int64_t n,
-                                                 WSView v) {
+__global__ void __launch_bounds__(TB, 3) k_fold_agg(const double* __restrict__ lw,
+                                                    const double* __restrict__ win, int64_t n,
+                                                    WSView v) {
     __shared__ Xd warp_tot[NWARP];
+    __shared__ i64 ws0[NWARP], ws1[NWARP];
+    __shared__ double wa[NWARP], wb[NWARP];
     const int t = blockIdx.x;
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     const int c0 = v.cls0[t], c1 = v.cls1[t];
     const bool do0 = (c0 != kCtxHard), do1 = (c1 != kCtxHard && c1 != kCtxSkip);
-    if (!do0 && !do1) return;
     const int64_t base = (int64_t)t * TILE;
     double w[IPT];
     load_weights(lw, win, base, n, v.info->m, w);
+    // accurate sum w, sum w^2 of the tile (ESS, log-mean-weight)
+    double s = 0.0, s2 = 0.0;
+#pragma unroll
+    for (int j = 0; j < IPT; ++j) { s += w[j]; s2 += w[j] * w[j]; }
+    // fast integer aggregates (valid when no element ties / saturates)
+    const bool f0 = do0 && ctx_fast_ok(c0), f1 = do1 && ctx_fast_ok(c1);
+    const double inv0 = f0 ? pow2(-c0) : 0.0, inv1 = f1 ? pow2(-c1) : 0.0;
+    i64 sum0 = 0, sum1 = 0;
+    int bad = (do0 && !f0) | (do1 && !f1);
+#pragma unroll
+    for (int j = 0; j < IPT; ++j) {
+        i64 f; int tie;
+        if (f0) { quantize_fast(w[j], inv0, f, tie); sum0 += f; bad |= tie | (f >= kSat); }
+        if (f1) { quantize_fast(w[j], inv1, f, tie); sum1 += f; bad |= tie | (f >= kSat); }
+    }
+    s = warp_sum(s); s2 = warp_sum(s2);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        sum0 += shfl_i64(sum0, lane ^ o);
+        sum1 += shfl_i64(sum1, lane ^ o);
+    }
+    if (lane == 0) { wa[wid] = s; wb[wid] = s2; ws0[wid] = sum0; ws1[wid] = sum1; }
+    const int any_bad = __syncthreads_or(bad);
+    if (threadIdx.x == 0) {
+        double a = 0.0, b = 0.0;
+        i64 t0 = 0, t1 = 0;
+        for (int i = 0; i < NWARP; ++i) { a += wa[i]; b += wb[i]; t0 += ws0[i]; t1 += ws1[i]; }
+        v.tacc[t] = a;
+        v.tacc2[t] = b;
+        if (!any_bad) {
+            Xd x0; x0.a0 = t0; x0.a1 = t0;
+            Xd x1; x1.a0 = t1; x1.a1 = t1;
+            if (do0) v.agg0[t] = x0;
+            if (do1) v.agg1[t] = x1;
+        }
+    }
+    if (!any_bad) return;
+    // ---- general path: parity transducers (ties) / bit-level quantisation
     Xd a = xd_identity(), b = xd_identity();
 #pragma unroll
     for (int j = 0; j < IPT; ++j) {
@@ -407,7 +491,6 @@ __global__ void __launch_bounds__(TB) k_fold_agg(const double* __restrict__ lw,
         if (do0) { quantize(w[j], c0, f, up, tie); xd_push(a, f, up, tie); }
         if (do1) { quantize(w[j], c1, f, up, tie); xd_push(b, f, up, tie); }
     }
-    // (out-of-range elements have w = 0: identity)
     if (do0) {
         (void)cta_excl_scan_xd(a, warp_tot);
         if (threadIdx.x == 0) v.agg0[t] = cta_total_xd(warp_tot);
@@ -420,81 +503,106 @@ __global__ void __launch_bounds__(TB) k_fold_agg(const double* __restrict__ lw,
 }
 
 // ------------------------------------------------------------------ resolve
-constexpr int RI = 4;   // tiles per thread per pass when scanning easy runs
+constexpr int RI = 8;   // tiles per thread per pass when scanning easy runs
 
-// scans the aggregates of the easy tiles [r0, r1) starting from exact S;
-// writes the exact incoming sum of each tile and returns the outgoing sum.
-__device__ double resolve_run(int64_t r0, int64_t r1, double S, const Xd* agg, const int* cls,
-                              double* sin, FoldSmem& sm, int* err) {
-    for (int64_t base = r0; base < r1; base += (int64_t)TB * RI) {
+// One lap of the chain over tiles [0, stop): scans the aggregates of easy tiles
+// and folds hard tiles element by element.  sin[t] receives the exact running
+// sum entering tile t.  Stops early once S exceeds `limit` (second lap).
+// Returns the exact sum entering tile *t_end.
+__device__ double resolve_lap(const Xd* __restrict__ agg, const int* __restrict__ cls,
+                              double* __restrict__ sin, double S, int64_t stop, double limit,
+                              int64_t* t_end, const double* __restrict__ lw,
+                              const double* __restrict__ win, int64_t n, double m, FoldSmem& sm,
+                              int* err) {
+    int64_t t = 0;
+    double w[IPT], edge[IPT];
+    while (t < stop && !(S > limit)) {
+        const int64_t cend = (t + (int64_t)TB * RI < stop) ? t + (int64_t)TB * RI : stop;
         const int e = ctx_of(S);
         const i64 s_in = units_of(S);
         Xd a[RI];
-        Xd loc = xd_identity();
-        int bad = 0;
+        int hardmin = INT_MAX;
+        unsigned badmask = 0;          // bit k: tile k of this thread is in another binade
+        if (threadIdx.x == 0) sm.imin = INT_MAX;
 #pragma unroll
         for (int k = 0; k < RI; ++k) {
-            const int64_t t = base + (int64_t)threadIdx.x * RI + k;
+            const int64_t tt = t + (int64_t)threadIdx.x * RI + k;
             a[k] = xd_identity();
-            if (t < r1) {
-                a[k] = agg[t];
-                bad |= (cls[t] != e);
-                loc = xd_compose(loc, a[k]);
+            if (tt < cend) {
+                const int c = cls[tt];
+                if (c == kCtxHard) { if (hardmin == INT_MAX) hardmin = (int)(tt - t); }
+                else if (hardmin == INT_MAX) { a[k] = agg[tt]; badmask |= (unsigned)(c != e) << k; }
             }
         }
-        Xd ex = cta_excl_scan_xd(loc, sm.warp_tot);
-        i64 s = xd_apply(s_in, ex);
+        __syncthreads();
+        if (hardmin != INT_MAX) atomicMin(&sm.imin, hardmin);
+        __syncthreads();
+        const int hm = sm.imin;
+        const int64_t r1 = (hm == INT_MAX) ? cend : t + hm;      // first hard tile (or chunk end)
+        // tiles at or beyond r1 do not take part in this scan
+        Xd loc = xd_identity();
+        int mybad = 0;
 #pragma unroll
         for (int k = 0; k < RI; ++k) {
-            const int64_t t = base + (int64_t)threadIdx.x * RI + k;
-            if (t < r1) {
-                bad |= (s >= kTwo53);
-                sin[t] = from_units(s, e);
-                s = xd_apply(s, a[k]);
+            const int64_t tt = t + (int64_t)threadIdx.x * RI + k;
+            if (tt < r1) { loc = xd_compose(loc, a[k]); mybad |= (badmask >> k) & 1; }
+            else a[k] = xd_identity();
+        }
+        if (r1 > t) {
+            Xd ex = cta_excl_scan_xd(loc, sm.warp_tot);
+            i64 s = xd_apply(s_in, ex);
+#pragma unroll
+            for (int k = 0; k < RI; ++k) {
+                const int64_t tt = t + (int64_t)threadIdx.x * RI + k;
+                if (tt < r1) {
+                    mybad |= (s >= kTwo53);
+                    sin[tt] = from_units(s, e);
+                    s = xd_apply(s, a[k]);
+                }
             }
+            if (mybad) atomicOr(err, EB_CTX);
+            if (threadIdx.x == 0) {
+                i64 st = xd_apply(s_in, cta_total_xd(sm.warp_tot));
+                if (st >= kTwo53) atomicOr(err, EB_CTX);
+                sm.bcast_S = from_units(st, e);
+            }
+            __syncthreads();
+            S = sm.bcast_S;
+            __syncthreads();
         }
-        if (bad) atomicOr(err, EB_CTX);
-        if (threadIdx.x == 0) {
-            i64 st = xd_apply(s_in, cta_total_xd(sm.warp_tot));
-            if (st >= kTwo53) atomicOr(err, EB_CTX);
-            sm.bcast_S = from_units(st, e);
+        t = r1;
+        if (r1 < cend && !(S > limit)) {        // hard tile r1: fold it element by element
+            if (threadIdx.x == 0) sin[r1] = S;
+            const int64_t base = r1 * TILE;
+            const int nvalid = (int)((n - base < TILE) ? (n - base) : TILE);
+            load_weights(lw, win, base, n, m, w);
+            S = cta_tile_fold(S, w, nvalid, edge, sm);
+            __syncthreads();
+            t = r1 + 1;
         }
-        __syncthreads();
-        S = sm.bcast_S;
-        __syncthreads();
     }
+    *t_end = t;
     return S;
 }
 
 __global__ void __launch_bounds__(TB) k_resolve(const double* __restrict__ lw,
                                                 const double* __restrict__ win, int64_t n,
-                                                WSView v) {
+                                                int64_t n_total, WSView v, StepOut so) {
     __shared__ FoldSmem sm;
+    __shared__ double smd[33];
     const int64_t nt = v.nt;
     ResampleInfo* I = v.info;
     const double m = I->m;
-    double w[IPT], edge[IPT];
 
     // ---------------- lap 0: exact total (smc.cljc:94)
-    double S = 0.0;
-    {
-        const int nh = I->nh0;
-        int64_t r0 = 0;
-        for (int h = 0; h <= nh; ++h) {
-            const int64_t hend = (h < nh) ? (int64_t)v.hard0[h] : nt;
-            if (hend > r0) S = resolve_run(r0, hend, S, v.agg0, v.cls0, v.sin0, sm, &I->err);
-            if (h < nh) {
-                if (threadIdx.x == 0) v.sin0[hend] = S;
-                const int64_t base = hend * TILE;
-                const int nvalid = (int)((n - base < TILE) ? (n - base) : TILE);
-                load_weights(lw, win, base, n, m, w);
-                S = cta_tile_fold(S, w, nvalid, edge, sm);
-                __syncthreads();
-            }
-            r0 = hend + 1;
-        }
-    }
-    const double total = S;
+    int64_t tend;
+    const double total = resolve_lap(v.agg0, v.cls0, v.sin0, 0.0, nt, INFINITY, &tend, lw, win, n,
+                                     m, sm, &I->err);
+    // accurate sum w / sum w^2 (ESS = (sum w)^2 / sum w^2, dist_test.cljc:83-94)
+    double la = 0.0, lb = 0.0;
+    for (int64_t t = threadIdx.x; t < nt; t += TB) { la += v.tacc[t]; lb += v.tacc2[t]; }
+    const double acc = block_sum_f64(la, smd);
+    const double acc2 = block_sum_f64(lb, smd);
     if (threadIdx.x == 0) {
         v.sin0[nt] = total;
         const i64 n_new = I->n_new;
@@ -509,10 +617,25 @@ __global__ void __launch_bounds__(TB) k_resolve(const double* __restrict__ lw,
         }
         int hint = 0;
         I->total = total;
-        I->step = total / (double)n_new;
+        I->step = total / (double)n_new;                                  // smc.cljc:95
         I->J = err ? 0 : comb_count_below(c, total, hint);
-        I->new_lw = (m > -INFINITY && m < INFINITY) ? (log(I->step) + m) : -INFINITY;
+        const bool mfin = (m > -INFINITY && m < INFINITY);
+        I->new_lw = mfin ? (log(I->step) + m) : -INFINITY;                // smc.cljc:98-103
+        I->ess = (acc2 > 0.0) ? acc * acc / acc2 : 0.0;
+        I->log_mean_approx = mfin ? log(acc / (double)n_total) + m : -INFINITY;
         if (err) atomicOr(&I->err, err);
+        if (so.sd) {                       // per-step outputs of a fused sweep
+            SweepDev* sd = so.sd;
+            const double nl = I->new_lw;
+            const double inc = nl - sd->base;
+            so.log_mean_w[so.t - 1] = inc;
+            so.ess[so.t - 1] = I->ess;
+            so.filt[so.t - 1] = I->wx_sum[0] / I->atot;
+            sd->log_z += inc;
+            sd->base = so.reset ? 0.0 : nl;      // pgibbs.cljc:88 / smc.cljc:98-103
+            sd->err |= I->err | err;
+            if (so.cond) so.anc[0] = 0;          // retained particle back at position 0
+        }
     }
     __syncthreads();
     if (I->err & (EB_ZERO | EB_COMB | EB_NAN)) {
@@ -522,34 +645,16 @@ __global__ void __launch_bounds__(TB) k_resolve(const double* __restrict__ lw,
     const double xlast = v.comb->xlast;
 
     // ---------------- lap 1: the wheel wraps with acc NOT reset (smc.cljc:133-136)
-    // After the loop S is the exact running sum entering tile `stop`; tiles at or
-    // beyond `stop` cannot receive a pointer of the second lap.
-    S = total;
     int64_t stop = I->first_skip1;
     if (stop > nt) stop = nt;
-    {
-        const int nh = I->nh1;
-        int h = 0;
-        int64_t r0 = 0;
-        while (r0 < stop) {
-            int64_t hend = (h < nh) ? (int64_t)v.hard1[h] : stop;
-            if (hend > stop) hend = stop;
-            if (hend > r0) S = resolve_run(r0, hend, S, v.agg1, v.cls1, v.sin1, sm, &I->err);
-            if (hend < stop) {
-                if (S > xlast) { stop = hend; break; }
-                if (threadIdx.x == 0) v.sin1[hend] = S;
-                const int64_t base = hend * TILE;
-                const int nvalid = (int)((n - base < TILE) ? (n - base) : TILE);
-                load_weights(lw, win, base, n, m, w);
-                S = cta_tile_fold(S, w, nvalid, edge, sm);
-                __syncthreads();
-                ++h;
-            }
-            r0 = hend + 1;
-        }
+    const double S = resolve_lap(v.agg1, v.cls1, v.sin1, total, stop, xlast, &tend, lw, win, n, m,
+                                 sm, &I->err);
+    // tend = first tile that cannot receive a pointer of the second lap
+    if (tend < nt && !(S > xlast) && threadIdx.x == 0) {
+        atomicOr(&I->err, EB_CTX);
+        if (so.sd) so.sd->err |= EB_CTX;
     }
-    if (stop < nt && !(S > xlast) && threadIdx.x == 0) atomicOr(&I->err, EB_CTX);
-    for (int64_t t = stop + threadIdx.x; t <= nt; t += TB) v.sin1[t] = (t == stop) ? S : INFINITY;
+    for (int64_t t = tend + threadIdx.x; t <= nt; t += TB) v.sin1[t] = (t == tend) ? S : INFINITY;
 }
 
 // ------------------------------------------------------------------ K3b/K4
@@ -559,10 +664,132 @@ __device__ __forceinline__ int64_t slot_of(i64 k, int lap, int order, i64 J, i64
     return lap == 0 ? k + (n_new - J) : k - J;                    // sorted physical order
 }
 
-__global__ void __launch_bounds__(TB) k_ancestors(const double* __restrict__ lw,
-                                                  const double* __restrict__ win, int64_t n,
-                                                  int64_t g0, WSView v, int order,
-                                                  int32_t* __restrict__ anc, int64_t out_offset) {
+struct EmitCtx {
+    int32_t* anc;
+    int64_t out_offset;
+    i64 J, n_new;
+    int order, lap;
+    __device__ __forceinline__ void put(i64 k, int32_t val) const {
+        anc[out_offset + slot_of(k, lap, order, J, n_new)] = val;
+    }
+};
+
+// smallest i >= 0 with i*q >= num  (num > 0, q > 0)
+__device__ __forceinline__ i64 ceil_div_est(i64 num, i64 q) {
+    i64 i = (i64)((double)num / (double)q);
+    while (i * q < num) ++i;
+    while (i > 0 && (i - 1) * q >= num) --i;
+    return i;
+}
+
+// fast path of one lap of an easy tile: merge this thread's exact edges (integer
+// units of context e) against the pointer comb.
+__device__ __forceinline__ void merge_emit(const Comb& comb, int e, i64 s, const i64 (&inc)[IPT],
+                                           int nmine, int32_t val0, const EmitCtx& E) {
+    const int lane = threadIdx.x & 31;
+    i64 c = E.n_new;              // next pointer index not yet emitted
+    int gi = 0;
+    int mode = 3;                 // 0 merge, 1 locate, 3 done
+    i64 p = 0, q = 0, cend = 0;
+    // heavy element (many offspring): filled cooperatively by the warp afterwards
+    i64 hs = 0, he = 0;
+    int32_t hv = 0;
+    if (nmine > 0) {
+        int hint = comb.nseg - 1;
+        c = comb_count_below(comb, from_units(s, e), hint);
+        gi = (c == 0) ? 0 : hint;
+        mode = (c < E.n_new) ? 1 : 3;
+    }
+#pragma unroll
+    for (int j = 0; j < IPT; ++j) {
+        if (j < nmine && mode != 3) {
+            s += inc[j];
+            const int32_t val = val0 + j;
+            for (;;) {
+                if (mode == 0) {
+                    if (!(p < s)) break;
+                    if (q > 0 && s - p > 32 * q && he == hs) {
+                        // heavy: this element owns ceil((s-p)/q) pointers of the segment
+                        i64 cnt = ceil_div_est(s - p, q);
+                        if (cnt > cend - c) cnt = cend - c;
+                        hs = c; he = c + cnt; hv = val;
+                        c += cnt; p += cnt * q;
+                    } else {
+                        E.put(c, val);
+                        ++c; p += q;
+                    }
+                    if (c == cend) mode = 1;
+                    continue;
+                }
+                // locate the segment of pointer c
+                if (c >= E.n_new) { mode = 3; break; }
+                while (c >= comb.seg[gi].j0 + comb.seg[gi].len) ++gi;
+                const CombSeg& g = comb.seg[gi];
+                if (g.e == e) {
+                    q = g.q; p = g.X0 + (c - g.j0) * q; cend = g.j0 + g.len; mode = 0;
+                    continue;
+                }
+                if (g.e > e) { mode = 3; break; }      // all further pointers lie above this binade
+                // (unreachable for pointers >= the running sum) generic count
+                int h2 = gi;
+                const i64 cnt = comb_count_below(comb, from_units(s, e), h2);
+                for (i64 k = c; k < cnt; ++k) E.put(k, val);
+                if (cnt <= c) break;
+                c = cnt;
+            }
+        }
+    }
+    unsigned hmask = __ballot_sync(0xffffffffu, he > hs);
+    while (hmask) {
+        const int src = __ffs(hmask) - 1;
+        hmask &= hmask - 1;
+        const i64 a = shfl_i64(hs, src), b = shfl_i64(he, src);
+        const int32_t vv = __shfl_sync(0xffffffffu, hv, src);
+        for (i64 k = a + lane; k < b; k += 32) E.put(k, vv);
+    }
+}
+
+// general path of one lap: exact edges as doubles, one count per element
+__device__ __noinline__ void generic_emit(const Comb& comb, double Sin, const double (&w)[IPT],
+                                          int nvalid, int32_t val0, const EmitCtx& E,
+                                          FoldSmem& sm) {
+    const int lane = threadIdx.x & 31;
+    const int i0 = threadIdx.x * IPT;
+    double edge[IPT];
+    (void)cta_tile_fold(Sin, w, nvalid, edge, sm);
+    sm.last_edge[threadIdx.x] = edge[IPT - 1];
+    __syncthreads();
+    const double pred = (threadIdx.x == 0) ? Sin : sm.last_edge[threadIdx.x - 1];
+    int hint = comb.nseg - 1;
+    i64 c_prev = (i0 < nvalid) ? comb_count_below(comb, pred, hint) : 0;
+#pragma unroll
+    for (int j = 0; j < IPT; ++j) {
+        const bool valid = (i0 + j < nvalid);
+        i64 c = c_prev;
+        if (valid) c = comb_count_below(comb, edge[j], hint);
+        const i64 cnt = c - c_prev;
+        const int32_t val = val0 + j;
+        const bool heavy = cnt > 8;
+        if (!heavy)
+            for (i64 k = c_prev; k < c; ++k) E.put(k, val);
+        unsigned hm = __ballot_sync(0xffffffffu, heavy);
+        while (hm) {
+            const int src = __ffs(hm) - 1;
+            hm &= hm - 1;
+            const i64 hs = shfl_i64(c_prev, src), he = shfl_i64(c, src);
+            const int32_t hv = __shfl_sync(0xffffffffu, val, src);
+            for (i64 k = hs + lane; k < he; k += 32) E.put(k, hv);
+        }
+        c_prev = c;
+    }
+    __syncthreads();
+}
+
+__global__ void __launch_bounds__(TB, 2) k_ancestors(const double* __restrict__ lw,
+                                                     const double* __restrict__ win, int64_t n,
+                                                     int64_t g0, WSView v, int order,
+                                                     int32_t* __restrict__ anc,
+                                                     int64_t out_offset) {
     __shared__ FoldSmem sm;
     __shared__ Comb comb;
     const ResampleInfo* I = v.info;
@@ -574,58 +801,41 @@ __global__ void __launch_bounds__(TB) k_ancestors(const double* __restrict__ lw,
     const bool need0 = (so0 > x0) && !(si0 > xlast);
     const bool need1 = !(si1 > xlast);
     if (!need0 && !need1) return;
-    // copy the comb table (header + used segments)
-    {
+    {   // copy the comb table (header + used segments)
         const Comb* g = v.comb;
         const int nseg = g->nseg;
-        const int hdr_words = (int)(offsetof(Comb, seg) / 8);
-        const int words = hdr_words + nseg * (int)(sizeof(CombSeg) / 8);
+        const int words = (int)(offsetof(Comb, seg) / 8) + nseg * (int)(sizeof(CombSeg) / 8);
         const uint64_t* src = reinterpret_cast<const uint64_t*>(g);
         uint64_t* dst = reinterpret_cast<uint64_t*>(&comb);
         for (int i = threadIdx.x; i < words; i += TB) dst[i] = src[i];
     }
     const int64_t base = (int64_t)t * TILE;
     const int nvalid = (int)((n - base < TILE) ? (n - base) : TILE);
-    double w[IPT], edge[IPT];
+    const int i0 = threadIdx.x * IPT;
+    const int nmine = (nvalid - i0 > IPT) ? IPT : (nvalid - i0 > 0 ? nvalid - i0 : 0);
+    double w[IPT];
     load_weights(lw, win, base, n, I->m, w);
     __syncthreads();
-    const i64 J = I->J, n_new = I->n_new;
-    const int lane = threadIdx.x & 31;
-    const int i0 = threadIdx.x * IPT;
+    EmitCtx E;
+    E.anc = anc; E.out_offset = out_offset; E.J = I->J; E.n_new = I->n_new; E.order = order;
+    const int32_t val0 = (int32_t)(g0 + base + i0);
     for (int lap = 0; lap < 2; ++lap) {
         if (lap == 0 ? !need0 : !need1) continue;
+        E.lap = lap;
         const double Sin = lap ? si1 : si0;
-        (void)cta_tile_fold(Sin, w, nvalid, edge, sm);
-        sm.last_edge[threadIdx.x] = edge[IPT - 1];
-        __syncthreads();
-        const double pred = (threadIdx.x == 0) ? Sin : sm.last_edge[threadIdx.x - 1];
-        int hint = comb.nseg - 1;
-        i64 c_prev = (i0 < nvalid) ? comb_count_below(comb, pred, hint) : 0;
-#pragma unroll
-        for (int j = 0; j < IPT; ++j) {
-            const bool valid = (i0 + j < nvalid);
-            i64 c = c_prev;
-            if (valid) c = comb_count_below(comb, edge[j], hint);
-            const i64 cnt = c - c_prev;
-            const int32_t val = (int32_t)(g0 + base + i0 + j);
-            const bool heavy = cnt > 8;
-            if (!heavy) {
-                for (i64 k = c_prev; k < c; ++k)
-                    anc[out_offset + slot_of(k, lap, order, J, n_new)] = val;
-            }
-            unsigned hm = __ballot_sync(0xffffffffu, heavy);
-            while (hm) {
-                const int src = __ffs(hm) - 1;
-                hm &= hm - 1;
-                const i64 hs = shfl_i64(c_prev, src);
-                const i64 he = shfl_i64(c, src);
-                const int32_t hv = __shfl_sync(0xffffffffu, val, src);
-                for (i64 k = hs + lane; k < he; k += 32)
-                    anc[out_offset + slot_of(k, lap, order, J, n_new)] = hv;
-            }
-            c_prev = c;
+        const int cls = lap ? v.cls1[t] : v.cls0[t];
+        bool fast = (cls != kCtxHard) && (cls != kCtxSkip) && ctx_fast_ok(cls) &&
+                    (ctx_of(Sin) == cls);
+        i64 inc[IPT];
+        i64 s_start = 0;
+        if (fast) fast = tile_scan_easy(Sin, cls, w, inc, s_start, sm);
+        if (fast) {
+            merge_emit(comb, cls, s_start, inc, nmine, val0, E);
+            __syncthreads();
+        } else {
+            __syncthreads();
+            generic_emit(comb, Sin, w, nvalid, val0, E, sm);
         }
-        __syncthreads();
     }
 }
 
@@ -709,8 +919,8 @@ int ensure_resample_ws(apop_ctx* c) {
     APOP_CUDA(c, cudaMalloc(&w.ain, nd * 8));
     APOP_CUDA(c, cudaMalloc(&w.cls0, nd * 4));
     APOP_CUDA(c, cudaMalloc(&w.cls1, nd * 4));
-    APOP_CUDA(c, cudaMalloc(&w.hard0, nd * 4));
-    APOP_CUDA(c, cudaMalloc(&w.hard1, nd * 4));
+    APOP_CUDA(c, cudaMalloc(&w.tacc, nd * 8));
+    APOP_CUDA(c, cudaMalloc(&w.tacc2, nd * 8));
     APOP_CUDA(c, cudaMalloc(&w.agg0, nd * sizeof(Xd)));
     APOP_CUDA(c, cudaMalloc(&w.agg1, nd * sizeof(Xd)));
     APOP_CUDA(c, cudaMalloc(&w.sin0, nd * 8));
@@ -739,13 +949,13 @@ int resample_enqueue(apop_ctx* c, const ResampleArgs& a) {
         c->launches += 2;
     }
     kt_begin(c, KT_FINALIZE);
-    k_finalize<<<1, FB, 0, c->stream>>>(v, a.n, a.n_new, a.u, c->seed, c->step, wm);
+    k_finalize<<<1, FB, 0, c->stream>>>(v, a.n, a.n_new, a.u, c->seed, c->step, wm, a.tsx);
     kt_end(c, KT_FINALIZE);
     kt_begin(c, KT_FOLD_AGG);
     k_fold_agg<<<nt, TB, 0, c->stream>>>(a.lw, a.w, a.n, v);
     kt_end(c, KT_FOLD_AGG);
     kt_begin(c, KT_RESOLVE);
-    k_resolve<<<1, TB, 0, c->stream>>>(a.lw, a.w, a.n, v);
+    k_resolve<<<1, TB, 0, c->stream>>>(a.lw, a.w, a.n, c->n_global, v, a.step);
     kt_end(c, KT_RESOLVE);
     c->launches += 3;
     if (a.anc_out) {

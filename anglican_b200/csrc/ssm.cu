@@ -21,13 +21,6 @@
 namespace apop {
 
 // ------------------------------------------------------------------ state
-struct SweepDev {           // device-resident scalars of a sweep
-    double base;            // common accumulated log-weight (state.cljc:27-31)
-    double log_z;           // sum_t log-mean-weight (ipmcmc.cljc:67-74)
-    int err;
-    int pad;
-};
-
 struct ModelDev {           // model parameters in device memory
     int kind, dim;
     double m0, s0, a, b, q, c, d, r, beta;
@@ -126,7 +119,7 @@ __global__ void __launch_bounds__(TB) k_init(const ModelDev* __restrict__ Mp, do
 
 // K1: propagate + reweight + tile partials (scalar-state models)
 template <int KIND>
-__global__ void __launch_bounds__(TB) k_propagate(const ModelDev* __restrict__ Mp,
+__global__ void __launch_bounds__(TB, 2) k_propagate(const ModelDev* __restrict__ Mp,
                                                   const double* __restrict__ xp,
                                                   const int32_t* __restrict__ anc, int first_step,
                                                   double* __restrict__ xn, double* __restrict__ lw,
@@ -225,38 +218,6 @@ __global__ void __launch_bounds__(TB) k_propagate(const ModelDev* __restrict__ M
         double a = 0, b = 0, cc = 0;
         for (int i = 0; i < NWARP; ++i) { a += red[i]; b += red2[i]; cc += red3[i]; }
         tmax[blockIdx.x] = mx; tsum[blockIdx.x] = a; tsum2[blockIdx.x] = b; tsx[blockIdx.x] = cc;
-    }
-}
-
-// after the resample of step t (1-based): per-step outputs and next base
-__global__ void k_step_stats(SweepDev* sd, ResampleInfo* I, const double* __restrict__ tmax,
-                             const double* __restrict__ tsx, int64_t nt, int t, int reset,
-                             int cond, int32_t* anc, double* log_mean_w, double* ess,
-                             double* filt) {
-    __shared__ double red[32];
-    double acc = 0.0;
-    const double m = I->m;
-    for (int64_t i = threadIdx.x; i < nt; i += blockDim.x) {
-        double tm = tmax[i];
-        double fac = (tm == m) ? 1.0 : exp(tm - m);
-        acc += tsx[i] * fac;
-    }
-    acc = warp_sum(acc);
-    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = acc;
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        double tot = 0.0;
-        for (int i = 0; i < (int)(blockDim.x >> 5); ++i) tot += red[i];
-        const double nl = I->new_lw;
-        const double inc = nl - sd->base;
-        log_mean_w[t - 1] = inc;
-        ess[t - 1] = I->ess;
-        filt[t - 1] = tot / I->atot;
-        sd->log_z += inc;
-        sd->base = reset ? 0.0 : nl;                 // pgibbs.cljc:88 / smc.cljc:98-103
-        sd->err |= I->err;
-        I->err = 0;
-        if (cond) anc[0] = 0;                        // retained particle back at position 0
     }
 }
 
@@ -415,13 +376,11 @@ static int run_scalar_sweep(apop_ctx* c, const apop_ssm* model, const double* y,
         a.lw = s->lw; a.w = nullptr; a.n = n; a.n_new = cond ? n - 1 : n;
         a.u = NAN; a.order = APOP_ORDER_SORTED;
         a.anc_out = anc_new; a.out_offset = cond ? 1 : 0; a.have_partials = true;
+        a.tsx = s->tsx;
+        a.step.sd = s->sd; a.step.log_mean_w = s->log_mean_w; a.step.ess = s->ess;
+        a.step.filt = s->filt; a.step.anc = anc_new; a.step.t = t;
+        a.step.reset = o->reset_weights; a.step.cond = cond ? 1 : 0;
         APOP_TRY(resample_enqueue(c, a));
-        kt_begin(c, KT_STATS);
-        k_step_stats<<<1, 256, 0, c->stream>>>(s->sd, ws.info, ws.tmax, s->tsx, nt, t,
-                                               o->reset_weights, cond ? 1 : 0, anc_new,
-                                               s->log_mean_w, s->ess, s->filt);
-        kt_end(c, KT_STATS);
-        c->launches += 1;
         x_prev = x_new;
         anc_prev = anc_new;
     }
