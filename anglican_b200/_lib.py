@@ -39,7 +39,8 @@ class ApopSSM(C.Structure):
 
 class ApopSweepOpts(C.Structure):
     _fields_ = [("csmc", C.c_int32), ("n_cond_steps", C.c_int32), ("reset_weights", C.c_int32),
-                ("keep_history", C.c_int32), ("use_graph", C.c_int32), ("want_final", C.c_int32)]
+                ("keep_history", C.c_int32), ("use_graph", C.c_int32), ("want_final", C.c_int32),
+                ("want_filt", C.c_int32), ("reserved", C.c_int32)]
 
 
 class ApopSweepResult(C.Structure):
@@ -96,6 +97,7 @@ _SIGS = [
                                   C.c_int32]),
     ("apop_observe_mvn", C.c_int, [_vp, c_double_p, C.c_int32, c_double_p, C.c_int, c_double_p,
                                    C.c_int32, C.c_int32]),
+    ("apop_selftest_math", C.c_int, [_vp, C.c_int, C.c_int32, C.c_int32]),
     ("apop_normalize", C.c_int, [_vp, C.c_int32, c_double_p, c_double_p, c_double_p]),
     ("apop_resample", C.c_int, [_vp, C.c_int32, C.c_int, C.c_double, C.c_int64, C.c_int, C.c_int32,
                                 c_double_p, c_int64_p]),

@@ -60,7 +60,7 @@ struct StepOut {
     double* ess;
     double* filt;
     int32_t* anc;
-    int t, reset, cond;
+    int t, reset, cond, has_x;
 };
 
 struct Column {
@@ -86,7 +86,7 @@ struct ParamArena {
 
 struct ResampleWS {
     int64_t nt = 0;
-    double *tmax = nullptr, *tsum = nullptr, *tsum2 = nullptr, *ain = nullptr;
+    double *tmax = nullptr, *tsum = nullptr, *tsum2 = nullptr, *ain = nullptr;  // tsum2: sum w x
     int *cls0 = nullptr, *cls1 = nullptr;
     double *tacc = nullptr, *tacc2 = nullptr;   // accurate per-tile sum w, sum w^2
     Xd *agg0 = nullptr, *agg1 = nullptr;
@@ -160,7 +160,8 @@ struct ResampleArgs {
     int32_t* anc_out;        // n_new entries
     int64_t out_offset;      // added to every written slot (CSMC keeps slot 0)
     bool have_partials;      // tile partials (tmax/tsum/tsum2) already in ws
-    const double* tsx;       // optional per-tile sum exp(lw-tmax)*x (filtering mean)
+    const double* xfilt;     // optional state column: per-step filtering mean sum w x / sum w
+    double rel_eps;          // accuracy of the supplied tile partials (0: fp64 partials)
     StepOut step;            // optional per-step outputs (sd == nullptr: none)
 };
 int resample_enqueue(apop_ctx* c, const ResampleArgs& a);
@@ -172,12 +173,15 @@ int gather_enqueue(apop_ctx* c, const int32_t* anc, int64_t n_new, Column* col);
 
 // ---------------------------------------------------------------- device
 #if defined(__CUDACC__)
+} // namespace apop
+#include "fastmath.cuh"
+namespace apop {
 
 __device__ __forceinline__ double weight_from_lw(double lw, double m) {
     // smc.cljc:78-82
     if (lw == m) return 1.0;
     if (!(lw > -INFINITY)) return 0.0;
-    return exp(lw - m);
+    return fm::exp_any(lw - m);
 }
 
 // blocked load of IPT consecutive doubles per thread; out-of-range -> fill

@@ -217,6 +217,23 @@ __global__ void k_sample_mvn(const double* __restrict__ L, int d, const double* 
     }
 }
 
+__global__ void k_selftest_math(int fn, const double* __restrict__ in, double* __restrict__ out,
+                                int64_t n) {
+    GRID_STRIDE(k, n) {
+        const double x = in[k];
+        double s, c, r = 0.0;
+        switch (fn) {
+        case 0: r = fm::exp_any(x); break;
+        case 1: r = fm::log_core(x); break;
+        case 2: r = fm::sqrt_fast(x); break;
+        case 3: fm::sincospi_core(x, s, c); r = s; break;
+        case 4: fm::sincospi_core(x, s, c); r = c; break;
+        default: r = fm::div_fast(1.0, x); break;
+        }
+        out[k] = r;
+    }
+}
+
 // ------------------------------------------------------------------ host
 static int grid_for(int64_t n, int tb) {
     int64_t b = (n + tb - 1) / tb;
@@ -243,6 +260,17 @@ using namespace apop;
 #define LAUNCH_DONE(c) do { (c)->launches += 1; APOP_CUDA(c, cudaGetLastError()); } while (0)
 
 extern "C" {
+
+int apop_selftest_math(apop_ctx* c, int fn, apop_col in, apop_col out) {
+    CHECK_CTX(c);
+    Column* i = get_col(c, in, APOP_F64, 1);
+    Column* o = get_col(c, out, APOP_F64, 1);
+    if (!i || !o) return APOP_ERR_INVALID;
+    k_selftest_math<<<grid_for(c->n, 256), 256, 0, c->stream>>>(fn, (const double*)i->ptr,
+                                                                 (double*)o->ptr, c->n);
+    LAUNCH_DONE(c);
+    return APOP_OK;
+}
 
 int apop_sample_normal(apop_ctx* c, apop_arg mean, apop_arg sd, uint32_t draw, apop_col out) {
     CHECK_CTX(c);

@@ -298,9 +298,11 @@ APOP_HD i64 comb_count_below(const Comb& c, double S, int& hint) {
 static constexpr int kCtxHard = -100000;
 static constexpr int kCtxSkip = -100001;
 
-APOP_HD int classify_tile(double a_in, double a_out, i64 idx_out) {
+// rel_eps: extra relative slack when the approximation itself is only accurate
+// to rel_eps (fp32 tile partials of the fused propagate kernel).
+APOP_HD int classify_tile(double a_in, double a_out, i64 idx_out, double rel_eps = 0.0) {
     if (!(a_in > 0.0) || !(a_out < 1.0e300)) return kCtxHard;
-    double eps = ((double)idx_out + 4096.0) * 4.44089209850062616e-16; // 2^-51
+    double eps = ((double)idx_out + 4096.0) * 4.44089209850062616e-16 + rel_eps; // 2^-51
     double lo = a_in * (1.0 - eps);
     double hi = a_out * (1.0 + eps);
     int e_lo = ctx_of(lo);

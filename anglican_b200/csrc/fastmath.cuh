@@ -1,0 +1,126 @@
+// fastmath.cuh — fp64 exp / log / sincospi / sqrt / reciprocal for the sweep
+// kernels.  Same accuracy class as the CUDA math library (<= 2 ulp), but:
+//   * every polynomial coefficient is an operand in the constant bank
+//     (DFMA R, R, c[3][..], R) instead of a UMOV pair per constant — the
+//     library versions spend ~40% of their issue slots on those moves;
+//   * no special-case branches on the hot path (callers guarantee the range;
+//     out-of-range arguments fall back to the library function).
+// The reference evaluates these through java.lang.Math / commons-math FastMath
+// (<= 1 ulp, runtime.cljc:403-409 `normal`, smc.cljc:82 `exp`); parity bars are
+// 1e-9 relative on log-densities / log-marginals (tests/).
+#pragma once
+#include <math.h>
+
+#include "fastmath_coef.inc"
+
+namespace apop {
+namespace fm {
+
+// [0, NE) exp | [NE, NE+NQ) log Q(z) | sin(pi r)/r | cos(pi r) | misc scalars
+enum { OFF_E = 0, OFF_Q = FM_NE, OFF_S = FM_NE + FM_NQ, OFF_C = FM_NE + FM_NQ + FM_NS,
+       OFF_M = FM_NE + FM_NQ + FM_NS + FM_NC };
+enum { M_L2E = OFF_M, M_MAGIC, M_LN2HI, M_LN2LO, M_ONE, M_HALF, M_TWO, M_NEG2, M_COUNT };
+
+static __constant__ double kC[] = {
+    FM_TABLE,
+    0x1.71547652b82fep+0,      // log2(e)
+    6755399441055744.0,        // 1.5 * 2^52 (round-to-integer magic)
+    0x1.62e42fefa39efp-1,      // ln2 hi
+    0x1.abc9e3b39803fp-56,     // ln2 lo
+    1.0, 0.5, 2.0, -2.0
+};
+
+__device__ __forceinline__ double rcp_approx(double d) {
+    double y;
+    asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(d));
+    return y;
+}
+__device__ __forceinline__ double rsqrt_approx(double d) {
+    double y;
+    asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(d));
+    return y;
+}
+
+// a / d for normal, finite d (|d| in [2^-500, 2^500]) and finite a: Newton on
+// the MUFU seed, one correction step.  <= 1 ulp.
+__device__ __forceinline__ double div_fast(double a, double d) {
+    double y = rcp_approx(d);
+    double e = fma(-d, y, kC[M_ONE]);
+    y = fma(y, e, y);
+    e = fma(-d, y, kC[M_ONE]);
+    y = fma(y, e, y);
+    double q = a * y;
+    double r = fma(-d, q, a);
+    return fma(r, y, q);
+}
+
+// sqrt(a) for normal a > 0 (Goldschmidt on the MUFU seed + one correction)
+__device__ __forceinline__ double sqrt_fast(double a) {
+    double y = rsqrt_approx(a);
+    double g = a * y, h = kC[M_HALF] * y;
+    double r = fma(-h, g, kC[M_HALF]);
+    g = fma(g, r, g); h = fma(h, r, h);
+    r = fma(-h, g, kC[M_HALF]);
+    g = fma(g, r, g); h = fma(h, r, h);
+    double d = fma(-g, g, a);
+    return fma(d, h, g);
+}
+
+// exp(x) for |x| < 708 (no overflow / subnormal results)
+__device__ __forceinline__ double exp_core(double x) {
+    const double t = fma(x, kC[M_L2E], kC[M_MAGIC]);
+    const double n = t - kC[M_MAGIC];
+    const int ni = __double2loint(t);
+    double r = fma(n, -kC[M_LN2HI], x);
+    r = fma(n, -kC[M_LN2LO], r);
+    double p = kC[OFF_E + FM_NE - 1];
+#pragma unroll
+    for (int k = FM_NE - 2; k >= 0; --k) p = fma(p, r, kC[OFF_E + k]);
+    return __hiloint2double(__double2hiint(p) + (ni << 20), __double2loint(p));
+}
+// exp(x), any x: library fallback outside the fast range (rare, warp-divergent)
+__device__ __forceinline__ double exp_any(double x) {
+    if (!(fabs(x) < 708.0)) return exp(x);
+    return exp_core(x);
+}
+
+// log(u) for normal u > 0
+__device__ __forceinline__ double log_core(double u) {
+    int hi = __double2hiint(u);
+    const int lo = __double2loint(u);
+    int e = (hi >> 20) - 1023;
+    hi = (hi & 0x000fffff) | 0x3ff00000;
+    if (hi > 0x3ff6a09e) { hi -= 0x00100000; e += 1; }          // m in [0.7071, 1.4142)
+    const double m = __hiloint2double(hi, lo);
+    const double f = m - kC[M_ONE];
+    const double s = div_fast(f, kC[M_TWO] + f);
+    const double z = s * s;
+    double q = kC[OFF_Q + FM_NQ - 1];
+#pragma unroll
+    for (int k = FM_NQ - 2; k >= 0; --k) q = fma(q, z, kC[OFF_Q + k]);
+    const double ed = (double)e;
+    const double lm = fma(s * z, q, fma(ed, kC[M_LN2LO], s + s));
+    return fma(ed, kC[M_LN2HI], lm);
+}
+
+// sin(pi t), cos(pi t) for t in [0, 2]
+__device__ __forceinline__ void sincospi_core(double t, double& sn, double& cs) {
+    const double kk = fma(t, kC[M_TWO], kC[M_MAGIC]);
+    const int qi = __double2loint(kk);
+    const double kd = kk - kC[M_MAGIC];
+    const double r = fma(kd, -kC[M_HALF], t);                    // exact, |r| <= 1/4
+    const double z = r * r;
+    double sp = kC[OFF_S + FM_NS - 1], cp = kC[OFF_C + FM_NC - 1];
+#pragma unroll
+    for (int k = FM_NS - 2; k >= 0; --k) sp = fma(sp, z, kC[OFF_S + k]);
+#pragma unroll
+    for (int k = FM_NC - 2; k >= 0; --k) cp = fma(cp, z, kC[OFF_C + k]);
+    sp = sp * r;
+    const double a = (qi & 1) ? cp : sp;
+    const double b = (qi & 1) ? sp : cp;
+    sn = (qi & 2) ? -a : a;
+    cs = ((qi + 1) & 2) ? -b : b;
+}
+
+} // namespace fm
+} // namespace apop

@@ -165,36 +165,6 @@ __device__ __noinline__ double cta_tile_fold(double S_in, const double (&w)[IPT]
     }
 }
 
-// Fast scan of an easy tile in context e: inc[j] = exact integer increment of
-// element j (no ties), s_start = exact integer state before this thread's
-// first element.  Returns false (uniformly) if any element ties or saturates.
-__device__ __forceinline__ bool tile_scan_easy(double S_in, int e, const double (&w)[IPT],
-                                               i64 (&inc)[IPT], i64& s_start, FoldSmem& sm) {
-    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-    const double inv_u = pow2(-e);
-    i64 sum = 0;
-    int bad = 0;
-#pragma unroll
-    for (int j = 0; j < IPT; ++j) {
-        int tie;
-        quantize_fast(w[j], inv_u, inc[j], tie);
-        bad |= tie | (inc[j] >= kSat);
-        sum += inc[j];
-    }
-    i64 incl = sum;
-#pragma unroll
-    for (int d = 1; d < 32; d <<= 1) {
-        i64 o = shfl_up_i64(incl, d);
-        if (lane >= d) incl += o;
-    }
-    if (lane == 31) sm.wsum[wid] = incl;
-    if (__syncthreads_or(bad)) return false;
-    i64 pre = 0;
-    for (int i = 0; i < wid; ++i) pre += sm.wsum[i];
-    s_start = units_of(S_in) + pre + (incl - sum);
-    return true;
-}
-
 __device__ __forceinline__ void load_weights(const double* __restrict__ lw,
                                              const double* __restrict__ win, int64_t base,
                                              int64_t n, double m, double (&w)[IPT]) {
@@ -233,7 +203,7 @@ __global__ void __launch_bounds__(TB) k_tile_lse(const double* __restrict__ lw,
         if (threadIdx.x == 0) {
             double a = 0, b = 0;
             for (int i = 0; i < NWARP; ++i) { a += red[i]; b += red2[i]; }
-            v.tmax[blockIdx.x] = 0.0; v.tsum[blockIdx.x] = a; v.tsum2[blockIdx.x] = b;
+            v.tmax[blockIdx.x] = 0.0; v.tsum[blockIdx.x] = a; (void)b;
         }
         return;
     }
@@ -265,7 +235,7 @@ __global__ void __launch_bounds__(TB) k_tile_lse(const double* __restrict__ lw,
     if (threadIdx.x == 0) {
         double a = 0, b = 0;
         for (int i = 0; i < NWARP; ++i) { a += red[i]; b += red2[i]; }
-        v.tmax[blockIdx.x] = mx; v.tsum[blockIdx.x] = a; v.tsum2[blockIdx.x] = b;
+        v.tmax[blockIdx.x] = mx; v.tsum[blockIdx.x] = a; (void)b;
     }
 }
 
@@ -321,7 +291,7 @@ __device__ __forceinline__ double block_sum_f64(double v, double* sm /*[33]*/) {
 // single CTA; every global access is coalesced (tiles are walked striped)
 __global__ void __launch_bounds__(FB) k_finalize(WSView v, int64_t n, int64_t n_new, double u_in,
                                                  uint64_t seed, uint32_t step, int weights_mode,
-                                                 const double* __restrict__ tsx) {
+                                                 double rel_eps) {
     __shared__ double buf[FB * FCH];
     __shared__ double smd[33];
     __shared__ int sh_skip;
@@ -342,22 +312,13 @@ __global__ void __launch_bounds__(FB) k_finalize(WSView v, int64_t n, int64_t n_
         __syncthreads();
     }
     // ---- rescale the tile partials to the global max (in place)
-    double locq = 0.0, locx = 0.0;
-    for (int64_t t = tid; t < nt; t += FB) {
-        double fac = 1.0;
-        if (!weights_mode) {
+    if (!weights_mode) {
+        for (int64_t t = tid; t < nt; t += FB) {
             const double tm = v.tmax[t];
-            fac = (tm == m) ? 1.0 : exp(tm - m);
+            const double fac = (tm == m) ? 1.0 : fm::exp_any(tm - m);
+            v.tsum[t] = v.tsum[t] * fac;
         }
-        const double a = v.tsum[t] * fac;
-        const double q = v.tsum2[t] * fac * fac;
-        v.tsum[t] = a;
-        v.tsum2[t] = q;
-        locq += q;
-        if (tsx) locx += tsx[t] * fac;
     }
-    const double asqtot = block_sum_f64(locq, smd);
-    const double wxtot = block_sum_f64(locx, smd);
     // ---- approximate exclusive prefix of tile sums: ain[t]
     double carry = 0.0;
     for (int64_t base = 0; base < nt; base += FB * FCH) {
@@ -389,7 +350,7 @@ __global__ void __launch_bounds__(FB) k_finalize(WSView v, int64_t n, int64_t n_
 
     const double u = (u_in != u_in) ? uniform_at(seed, 0, step, STREAM_RESAMPLE, 0) : u_in;
     // x_last < x_0 + total <= total*(u+1): generous upper bound for the skip test
-    const double eps_tot = ((double)(2 * n) + 8192.0) * 4.44089209850062616e-16;
+    const double eps_tot = ((double)(2 * n) + 8192.0) * 4.44089209850062616e-16 + rel_eps;
     const double xlast_ub = atot * (u + 1.0) * (1.0 + 4.0 * eps_tot);
 
     // ---- classification of every tile for both laps
@@ -397,16 +358,16 @@ __global__ void __launch_bounds__(FB) k_finalize(WSView v, int64_t n, int64_t n_
     for (int64_t t = tid; t < nt; t += FB) {
         const int64_t hi = ((t + 1) * TILE < n) ? (t + 1) * TILE : n;
         const double a_in = v.ain[t], ao = v.ain[t + 1];
-        const int c0 = classify_tile(a_in, ao, hi);
+        const int c0 = classify_tile(a_in, ao, hi, rel_eps);
         v.cls0[t] = c0;
         nh0 += (c0 == kCtxHard);
         int c1;
-        const double eps1 = ((double)(n + hi) + 4096.0) * 4.44089209850062616e-16;
+        const double eps1 = ((double)(n + hi) + 4096.0) * 4.44089209850062616e-16 + rel_eps;
         if ((atot + a_in) * (1.0 - eps1) > xlast_ub) {
             c1 = kCtxSkip;
             atomicMin(&sh_skip, (int)t);
         } else {
-            c1 = classify_tile(atot + a_in, atot + ao, n + hi);
+            c1 = classify_tile(atot + a_in, atot + ao, n + hi, rel_eps);
         }
         v.cls1[t] = c1;
         nh1 += (c1 == kCtxHard);
@@ -417,11 +378,10 @@ __global__ void __launch_bounds__(FB) k_finalize(WSView v, int64_t n, int64_t n_
         ResampleInfo* I = v.info;
         I->m = m;
         I->atot = atot;
-        I->asq = asqtot;
-        I->ess = (asqtot > 0.0) ? atot * atot / asqtot : 0.0;
+        I->asq = 0.0;
+        I->ess = 0.0;
         I->log_mean_approx = (m > -INFINITY && m < INFINITY) ? log(atot / (double)n) + m
                                                                : -INFINITY;
-        I->wx_sum[0] = wxtot;
         I->u = u;
         I->n_new = n_new;
         I->nh0 = (int)h0;
@@ -435,7 +395,7 @@ __global__ void __launch_bounds__(FB) k_finalize(WSView v, int64_t n, int64_t n_
 // ------------------------------------------------------------------ K3a
 __global__ void __launch_bounds__(TB, 3) k_fold_agg(const double* __restrict__ lw,
                                                     const double* __restrict__ win, int64_t n,
-                                                    WSView v) {
+                                                    WSView v, const double* __restrict__ xf) {
     __shared__ Xd warp_tot[NWARP];
     __shared__ i64 ws0[NWARP], ws1[NWARP];
     __shared__ double wa[NWARP], wb[NWARP];
@@ -450,6 +410,21 @@ __global__ void __launch_bounds__(TB, 3) k_fold_agg(const double* __restrict__ l
     double s = 0.0, s2 = 0.0;
 #pragma unroll
     for (int j = 0; j < IPT; ++j) { s += w[j]; s2 += w[j] * w[j]; }
+    if (xf) {                  // filtering-mean numerator sum w x (uniform branch)
+        __shared__ double wx[NWARP];
+        double xv[IPT], sx = 0.0;
+        load_blocked(xf, base, n, xv, 0.0);
+#pragma unroll
+        for (int j = 0; j < IPT; ++j) sx += w[j] * xv[j];
+        sx = warp_sum(sx);
+        if (lane == 0) wx[wid] = sx;
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            double a = 0.0;
+            for (int i = 0; i < NWARP; ++i) a += wx[i];
+            v.tsum2[t] = a;
+        }
+    }
     // fast integer aggregates (valid when no element ties / saturates)
     const bool f0 = do0 && ctx_fast_ok(c0), f1 = do1 && ctx_fast_ok(c1);
     const double inv0 = f0 ? pow2(-c0) : 0.0, inv1 = f1 ? pow2(-c1) : 0.0;
@@ -599,10 +574,13 @@ __global__ void __launch_bounds__(TB) k_resolve(const double* __restrict__ lw,
     const double total = resolve_lap(v.agg0, v.cls0, v.sin0, 0.0, nt, INFINITY, &tend, lw, win, n,
                                      m, sm, &I->err);
     // accurate sum w / sum w^2 (ESS = (sum w)^2 / sum w^2, dist_test.cljc:83-94)
-    double la = 0.0, lb = 0.0;
+    double la = 0.0, lb = 0.0, lx = 0.0;
     for (int64_t t = threadIdx.x; t < nt; t += TB) { la += v.tacc[t]; lb += v.tacc2[t]; }
+    if (so.sd && so.has_x)
+        for (int64_t t = threadIdx.x; t < nt; t += TB) lx += v.tsum2[t];
     const double acc = block_sum_f64(la, smd);
     const double acc2 = block_sum_f64(lb, smd);
+    const double accx = block_sum_f64(lx, smd);
     if (threadIdx.x == 0) {
         v.sin0[nt] = total;
         const i64 n_new = I->n_new;
@@ -630,7 +608,7 @@ __global__ void __launch_bounds__(TB) k_resolve(const double* __restrict__ lw,
             const double inc = nl - sd->base;
             so.log_mean_w[so.t - 1] = inc;
             so.ess[so.t - 1] = I->ess;
-            so.filt[so.t - 1] = I->wx_sum[0] / I->atot;
+            if (so.has_x) so.filt[so.t - 1] = accx / acc;
             sd->log_z += inc;
             sd->base = so.reset ? 0.0 : nl;      // pgibbs.cljc:88 / smc.cljc:98-103
             sd->err |= I->err | err;
@@ -674,79 +652,198 @@ struct EmitCtx {
     }
 };
 
-// smallest i >= 0 with i*q >= num  (num > 0, q > 0)
-__device__ __forceinline__ i64 ceil_div_est(i64 num, i64 q) {
-    i64 i = (i64)((double)num / (double)q);
-    while (i * q < num) ++i;
-    while (i > 0 && (i - 1) * q >= num) --i;
-    return i;
+// ---- fast path of one lap of an easy tile ---------------------------------
+// Every edge of the tile and every pointer that can fall below them live in one
+// binade (context e) and in ONE comb segment g, strictly inside it
+// (C0 > g.j0, C1 < g.j0 + g.len).  Then, in integer units of 2^e,
+//   pointer k of the segment = X0 + k q,      edge_j = s_j,
+//   #pointers below edge_j   = ceil((s_j - X0) / q)            (strict <, smc.cljc:122)
+// and (s_j - X0) is an integer below 2^53, so the whole computation runs in
+// fp64 on integer-valued doubles, exactly: est = RN(sD * (1/q)) is within 1/2
+// of the true ratio, r = fma(-est, q, sD) is the exact remainder, and
+// ceil = est + (r > 0).  Offspring are staged in shared memory as "head" marks
+// (element j writes j+1 at its first slot), a max-scan fills the runs, and the
+// window is copied out with coalesced stores.
+constexpr int STAGE_CAP = 8192;            // staged slots per window (int32)
+
+struct StageSmem {
+    int buf[STAGE_CAP];
+    int wmax[NWARP];
+    double dsum[NWARP];
+    i64 C0, C1;
+    int gi, ok;
+};
+
+// exclusive block scan of integer-valued doubles (exact below 2^53)
+__device__ __forceinline__ double cta_excl_scan_f64(double v, double* wsum, double& total) {
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    double inc = v;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        double o = __shfl_up_sync(0xffffffffu, inc, d);
+        if (lane >= d) inc += o;
+    }
+    if (lane == 31) wsum[wid] = inc;
+    __syncthreads();
+    double pre = 0.0, tot = 0.0;
+#pragma unroll
+    for (int i = 0; i < NWARP; ++i) {
+        const double x = wsum[i];
+        if (i < wid) pre += x;
+        tot += x;
+    }
+    total = tot;
+    __syncthreads();
+    return pre + (inc - v);
 }
 
-// fast path of one lap of an easy tile: merge this thread's exact edges (integer
-// units of context e) against the pointer comb.
-__device__ __forceinline__ void merge_emit(const Comb& comb, int e, i64 s, const i64 (&inc)[IPT],
-                                           int nmine, int32_t val0, const EmitCtx& E) {
-    const int lane = threadIdx.x & 31;
-    i64 c = E.n_new;              // next pointer index not yet emitted
-    int gi = 0;
-    int mode = 3;                 // 0 merge, 1 locate, 3 done
-    i64 p = 0, q = 0, cend = 0;
-    // heavy element (many offspring): filled cooperatively by the warp afterwards
-    i64 hs = 0, he = 0;
-    int32_t hv = 0;
-    if (nmine > 0) {
-        int hint = comb.nseg - 1;
-        c = comb_count_below(comb, from_units(s, e), hint);
-        gi = (c == 0) ? 0 : hint;
-        mode = (c < E.n_new) ? 1 : 3;
-    }
+// Quantise the tile in context e with the fp64 magic-number trick; incD[j] is
+// the exact integer increment of element j as a double.  Returns (uniformly)
+// false if any element ties or saturates.
+__device__ __forceinline__ bool tile_quantize_f64(int e, const double (&w)[IPT],
+                                                  double (&incD)[IPT]) {
+    const double inv_u = pow2(-e);
+    int bad = 0;
 #pragma unroll
     for (int j = 0; j < IPT; ++j) {
-        if (j < nmine && mode != 3) {
-            s += inc[j];
-            const int32_t val = val0 + j;
-            for (;;) {
-                if (mode == 0) {
-                    if (!(p < s)) break;
-                    if (q > 0 && s - p > 32 * q && he == hs) {
-                        // heavy: this element owns ceil((s-p)/q) pointers of the segment
-                        i64 cnt = ceil_div_est(s - p, q);
-                        if (cnt > cend - c) cnt = cend - c;
-                        hs = c; he = c + cnt; hv = val;
-                        c += cnt; p += cnt * q;
-                    } else {
-                        E.put(c, val);
-                        ++c; p += q;
-                    }
-                    if (c == cend) mode = 1;
-                    continue;
-                }
-                // locate the segment of pointer c
-                if (c >= E.n_new) { mode = 3; break; }
-                while (c >= comb.seg[gi].j0 + comb.seg[gi].len) ++gi;
-                const CombSeg& g = comb.seg[gi];
-                if (g.e == e) {
-                    q = g.q; p = g.X0 + (c - g.j0) * q; cend = g.j0 + g.len; mode = 0;
-                    continue;
-                }
-                if (g.e > e) { mode = 3; break; }      // all further pointers lie above this binade
-                // (unreachable for pointers >= the running sum) generic count
-                int h2 = gi;
-                const i64 cnt = comb_count_below(comb, from_units(s, e), h2);
-                for (i64 k = c; k < cnt; ++k) E.put(k, val);
-                if (cnt <= c) break;
-                c = cnt;
-            }
+        const double scaled = w[j] * inv_u;
+        const double t = scaled + 4503599627370496.0;
+        const double rn = t - 4503599627370496.0;
+        const double diff = scaled - rn;                          // exact
+        bad |= !(scaled < 4503599627370496.0) | (fabs(diff) == 0.5);
+        incD[j] = rn;
+    }
+    return !__syncthreads_or(bad);
+}
+
+__device__ __forceinline__ int find_seg_of_index(const Comb& c, i64 k) {
+    int lo = 0, hi = c.nseg - 1;
+    while (lo < hi) {
+        const int mid = (lo + hi + 1) >> 1;
+        if (c.seg[mid].j0 <= k) lo = mid; else hi = mid - 1;
+    }
+    return lo;
+}
+
+// returns false (uniformly, nothing written) when the tile does not qualify
+__device__ __forceinline__ bool staged_emit(const Comb& comb, int e, double Sin,
+                                            const double (&incD)[IPT], int32_t val_tile0,
+                                            int32_t* __restrict__ anc, int64_t out_offset, i64 J,
+                                            i64 n_new, int order, int lap, StageSmem& st) {
+    // tile totals and the window [C0, C1) of pointer indices
+    double loc = 0.0;
+#pragma unroll
+    for (int j = 0; j < IPT; ++j) loc += incD[j];
+    double tile_units;
+    const double pre = cta_excl_scan_f64(loc, st.dsum, tile_units);
+    const i64 s_in = units_of(Sin);
+    const i64 s_out = s_in + (i64)tile_units;
+    if (s_out >= kTwo53) return false;
+    if (threadIdx.x == 0) {
+        int h0 = comb.nseg - 1, h1 = comb.nseg - 1;
+        const i64 c0 = comb_count_below(comb, Sin, h0);
+        const i64 c1 = comb_count_below(comb, from_units(s_out, e), h1);
+        const int gsel = find_seg_of_index(comb, c0);
+        const CombSeg& gs = comb.seg[gsel];
+        st.C0 = c0; st.C1 = c1; st.gi = gsel;
+        st.ok = (c1 == c0) ? 2
+              : (gs.e == e && gs.q > 0 && c0 > gs.j0 && c1 < gs.j0 + gs.len) ? 1 : 0;
+    }
+    __syncthreads();
+    const int ok = st.ok;
+    if (ok != 1) { __syncthreads(); return ok == 2; }            // 2: no offspring in this lap
+    const i64 C0 = st.C0, C1 = st.C1;
+    const CombSeg& g = comb.seg[st.gi];
+    const double qD = (double)g.q;
+    const double invq = fm::div_fast(1.0, qD);
+    const double magic = 6755399441055744.0;                      // 1.5 * 2^52
+    // relative pointer index k(s) = ceil((s - X0)/q); k0 = k(S_in) = C0 - g.j0
+    const int k0 = (int)(C0 - g.j0);
+    double sD = (double)(s_in - g.X0) + pre;                      // exact
+    int kprev;
+    {
+        const double tm = sD * invq + magic;
+        const double est = tm - magic;
+        const double r = fma(-est, qD, sD);
+        kprev = __double2loint(tm) + (r > 0.0 ? 1 : 0);
+    }
+    int ks[IPT], kst[IPT];
+#pragma unroll
+    for (int j = 0; j < IPT; ++j) {
+        sD += incD[j];
+        const double tm = sD * invq + magic;
+        const double est = tm - magic;
+        const double r = fma(-est, qD, sD);
+        const int k = __double2loint(tm) + (r > 0.0 ? 1 : 0);
+        kst[j] = kprev - k0;                                      // first slot (window relative)
+        ks[j] = k - k0;                                           // one past the last slot
+        kprev = k;
+    }
+    const int W = (int)(C1 - C0);
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    for (int wb = 0; wb < W; wb += STAGE_CAP) {
+        const int wn = (W - wb < STAGE_CAP) ? (W - wb) : STAGE_CAP;
+        const int wn8 = (wn + 7) & ~7;
+        for (int i = tid * 4; i < wn8; i += TB * 4)
+            *reinterpret_cast<int4*>(&st.buf[i]) = make_int4(0, 0, 0, 0);
+        __syncthreads();
+#pragma unroll
+        for (int j = 0; j < IPT; ++j) {
+            const int a = kst[j] > wb ? kst[j] : wb;
+            const int b = ks[j] < wb + wn ? ks[j] : wb + wn;
+            if (a < b) st.buf[a - wb] = tid * IPT + j + 1;
         }
+        __syncthreads();
+        // max-scan over the window, 8 consecutive entries per thread per round
+        int carry = 0;
+        for (int rb = 0; rb < wn8; rb += TB * 8) {
+            const int i = rb + tid * 8;
+            int v[8];
+            if (i < wn8) {
+                const int4 a = *reinterpret_cast<const int4*>(&st.buf[i]);
+                const int4 b = *reinterpret_cast<const int4*>(&st.buf[i + 4]);
+                v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w;
+                v[4] = b.x; v[5] = b.y; v[6] = b.z; v[7] = b.w;
+            } else {
+#pragma unroll
+                for (int q = 0; q < 8; ++q) v[q] = 0;
+            }
+#pragma unroll
+            for (int q = 1; q < 8; ++q) v[q] = max(v[q], v[q - 1]);
+            int inc = v[7];
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) {
+                const int o = __shfl_up_sync(0xffffffffu, inc, d);
+                if (lane >= d) inc = max(inc, o);
+            }
+            int ex = __shfl_up_sync(0xffffffffu, inc, 1);
+            if (lane == 0) ex = 0;
+            if (lane == 31) st.wmax[wid] = inc;
+            __syncthreads();
+            int pre_w = carry, all = carry;
+#pragma unroll
+            for (int q = 0; q < NWARP; ++q) {
+                const int x = st.wmax[q];
+                if (q < wid) pre_w = max(pre_w, x);
+                all = max(all, x);
+            }
+            ex = max(ex, pre_w);
+            if (i < wn8) {
+#pragma unroll
+                for (int q = 0; q < 8; ++q) v[q] = max(v[q], ex) - 1 + val_tile0;
+                *reinterpret_cast<int4*>(&st.buf[i]) = make_int4(v[0], v[1], v[2], v[3]);
+                *reinterpret_cast<int4*>(&st.buf[i + 4]) = make_int4(v[4], v[5], v[6], v[7]);
+            }
+            carry = all;
+            __syncthreads();
+        }
+        // coalesced copy-out
+        const i64 kbase = C0 + wb;
+        for (int i = tid; i < wn; i += TB)
+            anc[out_offset + slot_of(kbase + i, lap, order, J, n_new)] = st.buf[i];
+        __syncthreads();
     }
-    unsigned hmask = __ballot_sync(0xffffffffu, he > hs);
-    while (hmask) {
-        const int src = __ffs(hmask) - 1;
-        hmask &= hmask - 1;
-        const i64 a = shfl_i64(hs, src), b = shfl_i64(he, src);
-        const int32_t vv = __shfl_sync(0xffffffffu, hv, src);
-        for (i64 k = a + lane; k < b; k += 32) E.put(k, vv);
-    }
+    return true;
 }
 
 // general path of one lap: exact edges as doubles, one count per element
@@ -785,12 +882,17 @@ __device__ __noinline__ void generic_emit(const Comb& comb, double Sin, const do
     __syncthreads();
 }
 
+union AncSmem {
+    FoldSmem fold;
+    StageSmem stage;
+};
+
 __global__ void __launch_bounds__(TB, 2) k_ancestors(const double* __restrict__ lw,
                                                      const double* __restrict__ win, int64_t n,
                                                      int64_t g0, WSView v, int order,
                                                      int32_t* __restrict__ anc,
                                                      int64_t out_offset) {
-    __shared__ FoldSmem sm;
+    __shared__ AncSmem sm;
     __shared__ Comb comb;
     const ResampleInfo* I = v.info;
     if (I->err) return;
@@ -812,29 +914,34 @@ __global__ void __launch_bounds__(TB, 2) k_ancestors(const double* __restrict__ 
     const int64_t base = (int64_t)t * TILE;
     const int nvalid = (int)((n - base < TILE) ? (n - base) : TILE);
     const int i0 = threadIdx.x * IPT;
-    const int nmine = (nvalid - i0 > IPT) ? IPT : (nvalid - i0 > 0 ? nvalid - i0 : 0);
-    double w[IPT];
-    load_weights(lw, win, base, n, I->m, w);
+    const double m = I->m;
     __syncthreads();
-    EmitCtx E;
-    E.anc = anc; E.out_offset = out_offset; E.J = I->J; E.n_new = I->n_new; E.order = order;
-    const int32_t val0 = (int32_t)(g0 + base + i0);
+    const i64 J = I->J, n_new = I->n_new;
     for (int lap = 0; lap < 2; ++lap) {
         if (lap == 0 ? !need0 : !need1) continue;
-        E.lap = lap;
         const double Sin = lap ? si1 : si0;
         const int cls = lap ? v.cls1[t] : v.cls0[t];
         bool fast = (cls != kCtxHard) && (cls != kCtxSkip) && ctx_fast_ok(cls) &&
                     (ctx_of(Sin) == cls);
-        i64 inc[IPT];
-        i64 s_start = 0;
-        if (fast) fast = tile_scan_easy(Sin, cls, w, inc, s_start, sm);
         if (fast) {
-            merge_emit(comb, cls, s_start, inc, nmine, val0, E);
+            double incD[IPT];
+            {
+                double w[IPT];
+                load_weights(lw, win, base, n, m, w);
+                fast = tile_quantize_f64(cls, w, incD);
+            }
+            if (fast)
+                fast = staged_emit(comb, cls, Sin, incD, (int32_t)(g0 + base), anc, out_offset,
+                                   J, n_new, order, lap, sm.stage);
+        }
+        if (!fast) {
+            EmitCtx E;
+            E.anc = anc; E.out_offset = out_offset; E.J = J; E.n_new = n_new; E.order = order;
+            E.lap = lap;
+            double w[IPT];
+            load_weights(lw, win, base, n, m, w);      // rare path: reload instead of keeping w live
             __syncthreads();
-        } else {
-            __syncthreads();
-            generic_emit(comb, Sin, w, nvalid, val0, E, sm);
+            generic_emit(comb, Sin, w, nvalid, (int32_t)(g0 + base + i0), E, sm.fold);
         }
     }
 }
@@ -949,10 +1056,10 @@ int resample_enqueue(apop_ctx* c, const ResampleArgs& a) {
         c->launches += 2;
     }
     kt_begin(c, KT_FINALIZE);
-    k_finalize<<<1, FB, 0, c->stream>>>(v, a.n, a.n_new, a.u, c->seed, c->step, wm, a.tsx);
+    k_finalize<<<1, FB, 0, c->stream>>>(v, a.n, a.n_new, a.u, c->seed, c->step, wm, a.rel_eps);
     kt_end(c, KT_FINALIZE);
     kt_begin(c, KT_FOLD_AGG);
-    k_fold_agg<<<nt, TB, 0, c->stream>>>(a.lw, a.w, a.n, v);
+    k_fold_agg<<<nt, TB, 0, c->stream>>>(a.lw, a.w, a.n, v, a.xfilt);
     kt_end(c, KT_FOLD_AGG);
     kt_begin(c, KT_RESOLVE);
     k_resolve<<<1, TB, 0, c->stream>>>(a.lw, a.w, a.n, c->n_global, v, a.step);

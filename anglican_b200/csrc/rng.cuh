@@ -57,6 +57,9 @@ __host__ __device__ __forceinline__ double uniform_at(uint64_t seed, uint64_t sl
 }
 
 #if defined(__CUDACC__)
+} // namespace apop
+#include "fastmath.cuh"
+namespace apop {
 // Box-Muller pair for the slot pair (2p, 2p+1): z0 -> even slot, z1 -> odd.
 __device__ __forceinline__ void normal_pair_at(uint64_t seed, uint64_t pair, uint32_t t,
                                                uint32_t stream, uint32_t draw, double& z0,
@@ -65,9 +68,9 @@ __device__ __forceinline__ void normal_pair_at(uint64_t seed, uint64_t pair, uin
                          (uint32_t)seed, (uint32_t)(seed >> 32));
     double u1 = u01_open(o.x, o.y);
     double u2 = u01_half(o.z, o.w);
-    double r = sqrt(-2.0 * log(u1));
+    double r = fm::sqrt_fast(-2.0 * fm::log_core(u1));     // u1 in [2^-54, 1): normal, < 1
     double s, c;
-    sincospi(2.0 * u2, &s, &c);
+    fm::sincospi_core(u2 + u2, s, c);
     z0 = r * c;
     z1 = r * s;
 }

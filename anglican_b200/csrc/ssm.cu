@@ -16,6 +16,7 @@
 #include <string.h>
 
 #include "apop_internal.cuh"
+#include "fastmath.cuh"
 #include "rng.cuh"
 
 namespace apop {
@@ -117,7 +118,17 @@ __global__ void __launch_bounds__(TB) k_init(const ModelDev* __restrict__ Mp, do
     if (k0 + 1 < n) x[k0 + 1] = v1;
 }
 
-// K1: propagate + reweight + tile partials (scalar-state models)
+// K1: propagate + reweight + tile partials (scalar-state models).
+// The tile partials (max, approximate sum of exp(lw - max)) only steer the
+// binade classification of k_finalize, so the exponentials are fp32 MUFU.EX2
+// against a per-warp reference; the exact sums (ESS, log-mean-weight) come
+// from k_fold_agg.
+__device__ __forceinline__ float ex2_approx(float x) {
+    float y;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
+
 template <int KIND>
 __global__ void __launch_bounds__(TB, 2) k_propagate(const ModelDev* __restrict__ Mp,
                                                   const double* __restrict__ xp,
@@ -128,10 +139,9 @@ __global__ void __launch_bounds__(TB, 2) k_propagate(const ModelDev* __restrict_
                                                   const SweepDev* __restrict__ sd, int64_t n,
                                                   int64_t g0, uint64_t seed, uint32_t t,
                                                   double* __restrict__ tmax,
-                                                  double* __restrict__ tsum,
-                                                  double* __restrict__ tsum2,
-                                                  double* __restrict__ tsx, int* errflag) {
-    __shared__ double red[NWARP], red2[NWARP], red3[NWARP];
+                                                  double* __restrict__ tsum, int* errflag) {
+    __shared__ double red_mx[NWARP];
+    __shared__ float red_ref[NWARP], red_s[NWARP];
     const ModelDev& M = *Mp;
     const int64_t base = (int64_t)blockIdx.x * TILE;
     const int64_t i0 = base + (int64_t)threadIdx.x * IPT;
@@ -154,9 +164,14 @@ __global__ void __launch_bounds__(TB, 2) k_propagate(const ModelDev* __restrict_
         for (int j = 0; j < IPT; ++j) par[j] = (i0 + j < n) ? anc[i0 + j] : 0;
     }
     double xo[IPT];
+    if (i0 + IPT <= n) {
 #pragma unroll
-    for (int j = 0; j < IPT; ++j) xo[j] = (i0 + j < n) ? __ldg(xp + par[j]) : 0.0;
-    // ---- sample* (inference.cljc:46-47) and observe* (smc.cljc:23-27)
+        for (int j = 0; j < IPT; ++j) xo[j] = __ldg(xp + par[j]);
+    } else {
+#pragma unroll
+        for (int j = 0; j < IPT; ++j) xo[j] = (i0 + j < n) ? __ldg(xp + par[j]) : 0.0;
+    }
+    // ---- sample* (inference.cljc:46-47)
     if (KIND == APOP_SSM_HMM) {
 #pragma unroll
         for (int j = 0; j < IPT; ++j) {
@@ -173,12 +188,36 @@ __global__ void __launch_bounds__(TB, 2) k_propagate(const ModelDev* __restrict_
         }
     }
     if (retained_t && g0 + i0 == 0) x[0] = retained_t[0];      // conditional SMC: slot 0
+    // ---- observe* (smc.cljc:23-27) + add-log-weight (state.cljc:27-31)
     double mx = -INFINITY;
     bool nan = false;
+    if (KIND == APOP_SSM_LGSSM1D) {
+        const double rinv = fm::div_fast(1.0, M.r);
+#pragma unroll
+        for (int j = 0; j < IPT; ++j) {
+            const double x1 = (y - (M.c * x[j] + M.d)) * rinv;
+            l[j] = wbase + (-0.5 * x1 * x1 - M.obs_const);
+        }
+    } else if (KIND == APOP_SSM_SV) {
+        // (normal 0 (* beta (exp (/ x 2)))): y/sd = (y/beta) exp(-x/2), log sd = log beta + x/2
+        const double yb = fm::div_fast(y, M.beta);
+#pragma unroll
+        for (int j = 0; j < IPT; ++j) {
+            const double x1 = yb * fm::exp_any(-0.5 * x[j]);
+            l[j] = wbase + (-0.5 * x1 * x1 - (0.5 * x[j] + M.obs_const));
+        }
+    } else {
+#pragma unroll
+        for (int j = 0; j < IPT; ++j) l[j] = wbase + obs_logpdf<KIND>(M, x[j], y);
+    }
+    float mxf = -INFINITY;
 #pragma unroll
     for (int j = 0; j < IPT; ++j) {
-        l[j] = wbase + obs_logpdf<KIND>(M, x[j], y);           // add-log-weight, state.cljc:27-31
-        if (i0 + j < n) { nan |= (l[j] != l[j]); mx = fmax(mx, l[j]); }
+        if (i0 + j < n) {
+            nan |= (l[j] != l[j]) | (l[j] == INFINITY);
+            mx = fmax(mx, l[j]);
+            mxf = fmaxf(mxf, __double2float_rn(l[j]));
+        }
     }
     if (nan) atomicOr(errflag, EB_NAN);
     // ---- store
@@ -195,29 +234,36 @@ __global__ void __launch_bounds__(TB, 2) k_propagate(const ModelDev* __restrict_
         for (int j = 0; j < IPT; ++j)
             if (i0 + j < n) { xn[i0 + j] = x[j]; lw[i0 + j] = l[j]; }
     }
-    // ---- tile partials of particle-weights (smc.cljc:70-84)
-    mx = warp_max(mx);
-    if (lane == 0) red[wid] = mx;
-    __syncthreads();
-    mx = red[0];
+    // ---- tile partials of particle-weights (smc.cljc:70-84), fp32 against a warp reference
 #pragma unroll
-    for (int i = 1; i < NWARP; ++i) mx = fmax(mx, red[i]);
-    __syncthreads();
-    double s = 0.0, s2 = 0.0, sx = 0.0;
+    for (int o = 16; o > 0; o >>= 1) mxf = fmaxf(mxf, __shfl_xor_sync(0xffffffffu, mxf, o));
+    const float reff = (mxf > -INFINITY) ? mxf : 0.0f;
+    const double refd = (double)reff;
+    float s = 0.0f;
 #pragma unroll
     for (int j = 0; j < IPT; ++j) {
         if (i0 + j < n) {
-            double wv = (l[j] == mx) ? 1.0 : ((l[j] > -INFINITY) ? exp(l[j] - mx) : 0.0);
-            s += wv; s2 += wv * wv; sx += wv * x[j];
+            const float df = __double2float_rn(l[j] - refd);
+            s += ex2_approx(df * 1.4426950408889634f);
         }
     }
-    s = warp_sum(s); s2 = warp_sum(s2); sx = warp_sum(sx);
-    if (lane == 0) { red[wid] = s; red2[wid] = s2; red3[wid] = sx; }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+    mx = warp_max(mx);
+    if (lane == 0) { red_mx[wid] = mx; red_ref[wid] = reff; red_s[wid] = s; }
     __syncthreads();
-    if (threadIdx.x == 0) {
-        double a = 0, b = 0, cc = 0;
-        for (int i = 0; i < NWARP; ++i) { a += red[i]; b += red2[i]; cc += red3[i]; }
-        tmax[blockIdx.x] = mx; tsum[blockIdx.x] = a; tsum2[blockIdx.x] = b; tsx[blockIdx.x] = cc;
+    if (wid == 0) {
+        double m = (lane < NWARP) ? red_mx[lane] : -INFINITY;
+        m = warp_max(m);
+        double a = 0.0;
+        if (lane < NWARP && m > -INFINITY) {
+            const double d = (double)red_ref[lane] - m;
+            a = (double)red_s[lane] * ((d > -700.0) ? fm::exp_core(d) : 0.0);
+        }
+        a = warp_sum(a);
+        // all log-weights -inf: every weight is 1 (smc.cljc:80)
+        if (!(m > -INFINITY)) a = (double)((n - base < TILE) ? (n - base) : TILE);
+        if (lane == 0) { tmax[blockIdx.x] = m; tsum[blockIdx.x] = a; }
     }
 }
 
@@ -367,7 +413,7 @@ static int run_scalar_sweep(apop_ctx* c, const apop_ssm* model, const double* y,
         k_propagate<KIND><<<nt, TB, 0, c->stream>>>(
             s->model, x_prev, anc_prev, t == 1, x_new, s->lw, s->y + (t - 1),
             csmc ? s->retained + t : nullptr, s->sd, n, c->g0, c->seed, (uint32_t)t, ws.tmax,
-            ws.tsum, ws.tsum2, s->tsx, &ws.info->err);
+            ws.tsum, &ws.info->err);
         kt_end(c, KT_PROPAGATE);
         c->launches += 1;
         const bool cond = csmc && t <= o->n_cond_steps;
@@ -376,10 +422,12 @@ static int run_scalar_sweep(apop_ctx* c, const apop_ssm* model, const double* y,
         a.lw = s->lw; a.w = nullptr; a.n = n; a.n_new = cond ? n - 1 : n;
         a.u = NAN; a.order = APOP_ORDER_SORTED;
         a.anc_out = anc_new; a.out_offset = cond ? 1 : 0; a.have_partials = true;
-        a.tsx = s->tsx;
+        a.xfilt = o->want_filt ? x_new : nullptr;
+        a.rel_eps = 2e-5;            // fp32 tile partials of k_propagate
         a.step.sd = s->sd; a.step.log_mean_w = s->log_mean_w; a.step.ess = s->ess;
         a.step.filt = s->filt; a.step.anc = anc_new; a.step.t = t;
         a.step.reset = o->reset_weights; a.step.cond = cond ? 1 : 0;
+        a.step.has_x = o->want_filt ? 1 : 0;
         APOP_TRY(resample_enqueue(c, a));
         x_prev = x_new;
         anc_prev = anc_new;

@@ -258,23 +258,25 @@ class Population:
         self.seed = int(seed)
 
     def sweep(self, model, y, retained=None, csmc=False, n_cond_steps=0, reset_weights=False,
-              keep_history=False, want_final=True, want_stats=True):
+              keep_history=False, want_final=True, want_stats=True, want_filt=None):
         """One `sweep` (smc.cljc:35-51; conditional: pgibbs.cljc:76-110,
         ipmcmc.cljc:34-83).  Returns a SweepOutput."""
         y = np.ascontiguousarray(y, dtype=np.float64)
         d = model.state_dim
         T = y.size // d
+        if want_filt is None:
+            want_filt = want_stats and d == 1
         opts = L.ApopSweepOpts(int(csmc), int(n_cond_steps), int(reset_weights),
-                               int(keep_history), 0, int(want_final))
+                               int(keep_history), 0, int(want_final), int(bool(want_filt)), 0)
         res = L.ApopSweepResult()
         out = SweepOutput(self, T, d)
         if want_stats:
             out.log_mean_w = np.empty(T)
             out.ess = np.empty(T)
             res.log_mean_w, res.ess = _dp(out.log_mean_w), _dp(out.ess)
-            if d == 1:
-                out.filt_mean = np.empty(T)
-                res.filt_mean = _dp(out.filt_mean)
+        if want_filt:
+            out.filt_mean = np.empty(T * d)
+            res.filt_mean = _dp(out.filt_mean)
         if want_final:
             out.x_final = np.empty((self.n, d)) if d > 1 else np.empty(self.n)
             res.x_final = _dp(out.x_final)

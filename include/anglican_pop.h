@@ -134,6 +134,11 @@ int apop_sample_mvn(apop_ctx* ctx, const double* mean, apop_col mean_col, const 
 int apop_observe_mvn(apop_ctx* ctx, const double* mean, apop_col mean_col, const double* cov,
                      int d, const double* value, apop_col value_col, apop_col logw);
 
+/* self-test hook for the engine's own fp64 math (csrc/fastmath.cuh), used by
+ * tests/test_dists_gpu.py: out[k] = f(in[k]) with fn 0 exp, 1 log, 2 sqrt,
+ * 3 sin(pi x), 4 cos(pi x), 5 1/x. */
+int apop_selftest_math(apop_ctx* ctx, int fn, apop_col in, apop_col out);
+
 /* ---- weights: particle-weights / log-sum-exp / ESS ---------------------
  * smc.cljc:70-84, runtime.cljc:130-138, inference.cljc:181-186,
  * test/anglican/dist_test.cljc:83-94.
@@ -191,6 +196,8 @@ typedef struct {
     int32_t keep_history;      /* keep ancestors (+ states) for lineage tracing */
     int32_t use_graph;         /* capture the step loop in a CUDA graph */
     int32_t want_final;        /* gather final states into x_final */
+    int32_t want_filt;         /* per-step filtering means sum w x / sum w (reads x once more) */
+    int32_t reserved;
 } apop_sweep_opts;
 
 typedef struct {

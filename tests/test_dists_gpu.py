@@ -165,3 +165,40 @@ def test_samplers_distributional(pop):
     M = mout.download()
     assert np.abs(M.mean(0) - [0.5, -0.2]).max() < 0.03
     assert np.abs(np.cov(M.T) - cov).max() < 0.05
+
+
+def test_fastmath_accuracy(pop):
+    """csrc/fastmath.cuh (constant-bank polynomial exp/log/sqrt/sincospi/rcp) against
+    numpy: <= 2 ulp (sin/cos: 2 ulp of 1.0 absolute, as for any reduced-argument form)."""
+    from anglican_b200 import _lib as L
+    import ctypes as C
+    n = pop.n
+    rng = np.random.default_rng(99)
+    cin, cout = pop.column(L.F64), pop.column(L.F64)
+
+    def run(fn, x):
+        cin.upload(x)
+        L.check(pop.ctx, pop.lib.apop_selftest_math(pop.ctx, fn, cin.handle, cout.handle))
+        return cout.download()
+
+    def ulps(a, b):
+        return np.abs(a - b) / np.spacing(np.abs(b))
+
+    x = np.concatenate([rng.uniform(-707, 707, n // 2), rng.normal(0, 3, n - n // 2)])
+    x[:4] = [0.0, -0.0, -745.2, 709.0]                     # library fallback range too
+    assert ulps(run(0, x), np.exp(x)).max() <= 2.0
+    u = np.concatenate([rng.random(n // 2), 2.0 ** rng.uniform(-54, 0, n - n // 2)])
+    u[u <= 0] = 0.5
+    assert ulps(run(1, u), np.log(u)).max() <= 2.0
+    a = 2.0 ** rng.uniform(-60, 8, n) * rng.uniform(1, 2, n)
+    assert ulps(run(2, a), np.sqrt(a)).max() <= 1.0
+    assert ulps(run(5, a), 1.0 / a).max() <= 1.0
+    t = rng.uniform(0, 2, n)
+    t[:5] = [0.0, 0.5, 1.0, 1.5, 2.0 - 2.0 ** -52]
+    import mpmath as mp
+    mp.mp.dps = 40
+    sn, cs = run(3, t), run(4, t)
+    for k in list(range(5)) + list(rng.integers(0, n, 3000)):
+        tk = mp.mpf(float(t[k]))
+        assert abs(mp.mpf(float(sn[k])) - mp.sinpi(tk)) <= 2.3e-16, (k, t[k])
+        assert abs(mp.mpf(float(cs[k])) - mp.cospi(tk)) <= 2.3e-16, (k, t[k])
