@@ -172,10 +172,22 @@ __device__ __forceinline__ void load_weights(const double* __restrict__ lw,
         load_blocked(win, base, n, w, 0.0);
     } else {
         double v[IPT];
-        load_blocked(lw, base, n, v, -INFINITY);
-        const int64_t i0 = base + (int64_t)threadIdx.x * IPT;
+        load_blocked(lw, base, n, v, -INFINITY);     // out of range: -inf -> weight 0
+        if (m > -INFINITY) {
+            double a[4], b[4];
 #pragma unroll
-        for (int j = 0; j < IPT; ++j) w[j] = (i0 + j < n) ? weight_from_lw(v[j], m) : 0.0;
+            for (int h = 0; h < IPT; h += 4) {
+#pragma unroll
+                for (int j = 0; j < 4; ++j) a[j] = v[h + j];
+                fm::weights_v<4>(a, m, b);
+#pragma unroll
+                for (int j = 0; j < 4; ++j) w[h + j] = b[j];
+            }
+        } else {                                       // all -inf: every weight is 1 (smc.cljc:80)
+            const int64_t i0 = base + (int64_t)threadIdx.x * IPT;
+#pragma unroll
+            for (int j = 0; j < IPT; ++j) w[j] = (i0 + j < n) ? weight_from_lw(v[j], m) : 0.0;
+        }
     }
 }
 
@@ -428,21 +440,32 @@ __global__ void __launch_bounds__(TB, 3) k_fold_agg(const double* __restrict__ l
     // fast integer aggregates (valid when no element ties / saturates)
     const bool f0 = do0 && ctx_fast_ok(c0), f1 = do1 && ctx_fast_ok(c1);
     const double inv0 = f0 ? pow2(-c0) : 0.0, inv1 = f1 ? pow2(-c1) : 0.0;
-    i64 sum0 = 0, sum1 = 0;
+    // integer-valued doubles: RN(w / ulp) by the 2^52 magic add; exact sums below 2^53
+    double sum0 = 0.0, sum1 = 0.0;
     int bad = (do0 && !f0) | (do1 && !f1);
+    const double k52 = 4503599627370496.0;
+    if (f0) {
 #pragma unroll
-    for (int j = 0; j < IPT; ++j) {
-        i64 f; int tie;
-        if (f0) { quantize_fast(w[j], inv0, f, tie); sum0 += f; bad |= tie | (f >= kSat); }
-        if (f1) { quantize_fast(w[j], inv1, f, tie); sum1 += f; bad |= tie | (f >= kSat); }
+        for (int j = 0; j < IPT; ++j) {
+            const double scaled = w[j] * inv0;
+            const double rn = (scaled + k52) - k52;
+            bad |= !(scaled < k52) | (fabs(scaled - rn) == 0.5);
+            sum0 += rn;
+        }
+    }
+    if (f1) {
+#pragma unroll
+        for (int j = 0; j < IPT; ++j) {
+            const double scaled = w[j] * inv1;
+            const double rn = (scaled + k52) - k52;
+            bad |= !(scaled < k52) | (fabs(scaled - rn) == 0.5);
+            sum1 += rn;
+        }
     }
     s = warp_sum(s); s2 = warp_sum(s2);
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) {
-        sum0 += shfl_i64(sum0, lane ^ o);
-        sum1 += shfl_i64(sum1, lane ^ o);
-    }
-    if (lane == 0) { wa[wid] = s; wb[wid] = s2; ws0[wid] = sum0; ws1[wid] = sum1; }
+    sum0 = warp_sum(sum0); sum1 = warp_sum(sum1);
+    bad |= !(sum0 < 9007199254740992.0) | !(sum1 < 9007199254740992.0);
+    if (lane == 0) { wa[wid] = s; wb[wid] = s2; ws0[wid] = (i64)sum0; ws1[wid] = (i64)sum1; }
     const int any_bad = __syncthreads_or(bad);
     if (threadIdx.x == 0) {
         double a = 0.0, b = 0.0;
@@ -685,14 +708,16 @@ __device__ __forceinline__ double cta_excl_scan_f64(double v, double* wsum, doub
     }
     if (lane == 31) wsum[wid] = inc;
     __syncthreads();
-    double pre = 0.0, tot = 0.0;
+    // every warp scans the NWARP (= 16) warp totals with shuffles
+    double ws = (lane < NWARP) ? wsum[lane] : 0.0;
 #pragma unroll
-    for (int i = 0; i < NWARP; ++i) {
-        const double x = wsum[i];
-        if (i < wid) pre += x;
-        tot += x;
+    for (int d = 1; d < NWARP; d <<= 1) {
+        double o = __shfl_up_sync(0xffffffffu, ws, d);
+        if (lane >= d) ws += o;
     }
-    total = tot;
+    total = __shfl_sync(0xffffffffu, ws, NWARP - 1);
+    double pre = __shfl_sync(0xffffffffu, ws, (wid > 0) ? wid - 1 : 0);
+    if (wid == 0) pre = 0.0;
     __syncthreads();
     return pre + (inc - v);
 }
@@ -787,11 +812,17 @@ __device__ __forceinline__ bool staged_emit(const Comb& comb, int e, double Sin,
         for (int i = tid * 4; i < wn8; i += TB * 4)
             *reinterpret_cast<int4*>(&st.buf[i]) = make_int4(0, 0, 0, 0);
         __syncthreads();
+        if (W <= STAGE_CAP) {
 #pragma unroll
-        for (int j = 0; j < IPT; ++j) {
-            const int a = kst[j] > wb ? kst[j] : wb;
-            const int b = ks[j] < wb + wn ? ks[j] : wb + wn;
-            if (a < b) st.buf[a - wb] = tid * IPT + j + 1;
+            for (int j = 0; j < IPT; ++j)
+                if (kst[j] < ks[j]) st.buf[kst[j]] = tid * IPT + j + 1;
+        } else {
+#pragma unroll
+            for (int j = 0; j < IPT; ++j) {
+                const int a = kst[j] > wb ? kst[j] : wb;
+                const int b = ks[j] < wb + wn ? ks[j] : wb + wn;
+                if (a < b) st.buf[a - wb] = tid * IPT + j + 1;
+            }
         }
         __syncthreads();
         // max-scan over the window, 8 consecutive entries per thread per round
@@ -820,13 +851,15 @@ __device__ __forceinline__ bool staged_emit(const Comb& comb, int e, double Sin,
             if (lane == 0) ex = 0;
             if (lane == 31) st.wmax[wid] = inc;
             __syncthreads();
-            int pre_w = carry, all = carry;
+            int wm = (lane < NWARP) ? st.wmax[lane] : 0;
 #pragma unroll
-            for (int q = 0; q < NWARP; ++q) {
-                const int x = st.wmax[q];
-                if (q < wid) pre_w = max(pre_w, x);
-                all = max(all, x);
+            for (int d = 1; d < NWARP; d <<= 1) {
+                const int o = __shfl_up_sync(0xffffffffu, wm, d);
+                if (lane >= d) wm = max(wm, o);
             }
+            const int all = max(carry, __shfl_sync(0xffffffffu, wm, NWARP - 1));
+            int pre_w = __shfl_sync(0xffffffffu, wm, (wid > 0) ? wid - 1 : 0);
+            pre_w = (wid > 0) ? max(pre_w, carry) : carry;
             ex = max(ex, pre_w);
             if (i < wn8) {
 #pragma unroll
@@ -837,10 +870,13 @@ __device__ __forceinline__ bool staged_emit(const Comb& comb, int e, double Sin,
             carry = all;
             __syncthreads();
         }
-        // coalesced copy-out
-        const i64 kbase = C0 + wb;
-        for (int i = tid; i < wn; i += TB)
-            anc[out_offset + slot_of(kbase + i, lap, order, J, n_new)] = st.buf[i];
+        // coalesced copy-out (the three orders are contiguous runs, ascending or descending)
+        int32_t* dst = anc + out_offset + slot_of(C0 + wb, lap, order, J, n_new);
+        if (order == APOP_ORDER_REFERENCE) {
+            for (int i = tid; i < wn; i += TB) dst[-i] = st.buf[i];
+        } else {
+            for (int i = tid; i < wn; i += TB) dst[i] = st.buf[i];
+        }
         __syncthreads();
     }
     return true;
@@ -893,7 +929,7 @@ __global__ void __launch_bounds__(TB, 2) k_ancestors(const double* __restrict__ 
                                                      int32_t* __restrict__ anc,
                                                      int64_t out_offset) {
     __shared__ AncSmem sm;
-    __shared__ Comb comb;
+    const Comb& comb = *v.comb;          // global (L1/L2 resident); the fast path reads one segment
     const ResampleInfo* I = v.info;
     if (I->err) return;
     const int t = blockIdx.x;
@@ -903,14 +939,6 @@ __global__ void __launch_bounds__(TB, 2) k_ancestors(const double* __restrict__ 
     const bool need0 = (so0 > x0) && !(si0 > xlast);
     const bool need1 = !(si1 > xlast);
     if (!need0 && !need1) return;
-    {   // copy the comb table (header + used segments)
-        const Comb* g = v.comb;
-        const int nseg = g->nseg;
-        const int words = (int)(offsetof(Comb, seg) / 8) + nseg * (int)(sizeof(CombSeg) / 8);
-        const uint64_t* src = reinterpret_cast<const uint64_t*>(g);
-        uint64_t* dst = reinterpret_cast<uint64_t*>(&comb);
-        for (int i = threadIdx.x; i < words; i += TB) dst[i] = src[i];
-    }
     const int64_t base = (int64_t)t * TILE;
     const int nvalid = (int)((n - base < TILE) ? (n - base) : TILE);
     const int i0 = threadIdx.x * IPT;

@@ -74,6 +74,22 @@ __device__ __forceinline__ void normal_pair_at(uint64_t seed, uint64_t pair, uin
     z0 = r * c;
     z1 = r * s;
 }
+// four consecutive pairs (slots 8p .. 8p+7 when pair0 = 4p): vectorised Box-Muller
+template <int NP>
+__device__ __forceinline__ void normal_pairs_at(uint64_t seed, uint64_t pair0, uint32_t t,
+                                                uint32_t stream, uint32_t draw,
+                                                double (&z0)[NP], double (&z1)[NP]) {
+    double u1[NP], u2[NP];
+#pragma unroll
+    for (int i = 0; i < NP; ++i) {
+        const uint64_t pair = pair0 + i;
+        U4 o = philox4x32_10((uint32_t)pair, (uint32_t)(pair >> 32), t, ctr3(stream, 0, draw),
+                             (uint32_t)seed, (uint32_t)(seed >> 32));
+        u1[i] = u01_open(o.x, o.y);
+        u2[i] = u01_half(o.z, o.w);
+    }
+    fm::box_muller_v<NP>(u1, u2, z0, z1);
+}
 __device__ __forceinline__ double normal_at(uint64_t seed, uint64_t slot, uint32_t t,
                                             uint32_t stream, uint32_t draw) {
     double z0, z1;

@@ -129,128 +129,145 @@ __device__ __forceinline__ float ex2_approx(float x) {
     return y;
 }
 
-template <int KIND>
-__global__ void __launch_bounds__(TB, 2) k_propagate(const ModelDev* __restrict__ Mp,
-                                                  const double* __restrict__ xp,
-                                                  const int32_t* __restrict__ anc, int first_step,
-                                                  double* __restrict__ xn, double* __restrict__ lw,
-                                                  const double* __restrict__ yt,
-                                                  const double* __restrict__ retained_t,
-                                                  const SweepDev* __restrict__ sd, int64_t n,
-                                                  int64_t g0, uint64_t seed, uint32_t t,
-                                                  double* __restrict__ tmax,
-                                                  double* __restrict__ tsum, int* errflag) {
+template <int KIND, bool FULL>
+__device__ __forceinline__ void propagate_tile(const ModelDev& M, const double* __restrict__ xp,
+                                               const int32_t* __restrict__ anc, int first_step,
+                                               double* __restrict__ xn, double* __restrict__ lw,
+                                               double y, const double* __restrict__ retained_t,
+                                               double wbase, int64_t n, int64_t g0, uint64_t seed,
+                                               uint32_t t, double* __restrict__ tmax,
+                                               double* __restrict__ tsum, int* errflag) {
     __shared__ double red_mx[NWARP];
     __shared__ float red_ref[NWARP], red_s[NWARP];
-    const ModelDev& M = *Mp;
     const int64_t base = (int64_t)blockIdx.x * TILE;
     const int64_t i0 = base + (int64_t)threadIdx.x * IPT;
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-    const double y = yt[0];
-    const double wbase = sd->base;
-    double x[IPT], l[IPT];
-    // ---- parents (gather folded into the read)
-    int32_t par[IPT];
-    if (first_step) {
-#pragma unroll
-        for (int j = 0; j < IPT; ++j) par[j] = (int32_t)(i0 + j);
-    } else if (i0 + IPT <= n) {
-        const int4* q = reinterpret_cast<const int4*>(anc + i0);
-        int4 a = __ldg(q), b = __ldg(q + 1);
-        par[0] = a.x; par[1] = a.y; par[2] = a.z; par[3] = a.w;
-        par[4] = b.x; par[5] = b.y; par[6] = b.z; par[7] = b.w;
-    } else {
-#pragma unroll
-        for (int j = 0; j < IPT; ++j) par[j] = (i0 + j < n) ? anc[i0 + j] : 0;
-    }
-    double xo[IPT];
-    if (i0 + IPT <= n) {
-#pragma unroll
-        for (int j = 0; j < IPT; ++j) xo[j] = __ldg(xp + par[j]);
-    } else {
-#pragma unroll
-        for (int j = 0; j < IPT; ++j) xo[j] = (i0 + j < n) ? __ldg(xp + par[j]) : 0.0;
-    }
-    // ---- sample* (inference.cljc:46-47)
-    if (KIND == APOP_SSM_HMM) {
-#pragma unroll
-        for (int j = 0; j < IPT; ++j) {
-            double u = uniform_at(seed, (uint64_t)(g0 + i0 + j), t, STREAM_TRANSITION, 0);
-            x[j] = (double)discrete_draw(M.hmm_trans + (int)xo[j] * M.dim, M.dim, u);
-        }
-    } else {
-#pragma unroll
-        for (int j = 0; j < IPT; j += 2) {
-            double z0, z1;
-            normal_pair_at(seed, (uint64_t)(g0 + i0 + j) >> 1, t, STREAM_TRANSITION, 0, z0, z1);
-            x[j] = (M.a * xo[j] + M.b) + M.q * z0;             // sd*z + mean
-            x[j + 1] = (M.a * xo[j + 1] + M.b) + M.q * z1;
-        }
-    }
-    if (retained_t && g0 + i0 == 0) x[0] = retained_t[0];      // conditional SMC: slot 0
-    // ---- observe* (smc.cljc:23-27) + add-log-weight (state.cljc:27-31)
+    constexpr int HW = 4;                         // particles per half-step (register budget)
+    constexpr float kL2E = 1.4426950408889634f;
+    // running per-thread partials: exact max, fp32 (reference, sum of exp) pair
     double mx = -INFINITY;
-    bool nan = false;
-    if (KIND == APOP_SSM_LGSSM1D) {
-        const double rinv = fm::div_fast(1.0, M.r);
+    float ref = -INFINITY, s = 0.0f;
+    bool bad = false;
+    // model constants hoisted out of the half loop
+    double c_obs = 0.0;
+    if (KIND == APOP_SSM_LGSSM1D) c_obs = fm::div_fast(1.0, M.r);
+    if (KIND == APOP_SSM_SV) c_obs = fm::div_fast(y, M.beta);
 #pragma unroll
-        for (int j = 0; j < IPT; ++j) {
-            const double x1 = (y - (M.c * x[j] + M.d)) * rinv;
-            l[j] = wbase + (-0.5 * x1 * x1 - M.obs_const);
+    for (int h = 0; h < IPT; h += HW) {
+        const int64_t ih = i0 + h;
+        const bool inb = FULL || ih + HW <= n;
+#define VALID(j) (FULL || ih + (j) < n)
+        double x[HW], l[HW];
+        // ---- parents (gather folded into the read)
+        {
+            int32_t par[HW];
+            if (first_step) {
+#pragma unroll
+                for (int j = 0; j < HW; ++j) par[j] = (int32_t)(ih + j);
+            } else if (inb) {
+                const int4 a = __ldg(reinterpret_cast<const int4*>(anc + ih));
+                par[0] = a.x; par[1] = a.y; par[2] = a.z; par[3] = a.w;
+            } else {
+#pragma unroll
+                for (int j = 0; j < HW; ++j) par[j] = (ih + j < n) ? anc[ih + j] : 0;
+            }
+#pragma unroll
+            for (int j = 0; j < HW; ++j) x[j] = VALID(j) ? __ldg(xp + par[j]) : 0.0;
         }
-    } else if (KIND == APOP_SSM_SV) {
-        // (normal 0 (* beta (exp (/ x 2)))): y/sd = (y/beta) exp(-x/2), log sd = log beta + x/2
-        const double yb = fm::div_fast(y, M.beta);
+        // ---- sample* (inference.cljc:46-47)
+        if (KIND == APOP_SSM_HMM) {
 #pragma unroll
-        for (int j = 0; j < IPT; ++j) {
-            const double x1 = yb * fm::exp_any(-0.5 * x[j]);
-            l[j] = wbase + (-0.5 * x1 * x1 - (0.5 * x[j] + M.obs_const));
+            for (int j = 0; j < HW; ++j) {
+                double u = uniform_at(seed, (uint64_t)(g0 + ih + j), t, STREAM_TRANSITION, 0);
+                x[j] = (double)discrete_draw(M.hmm_trans + (int)x[j] * M.dim, M.dim, u);
+            }
+        } else {
+            double z0[2], z1[2];
+            normal_pairs_at<2>(seed, (uint64_t)(g0 + ih) >> 1, t, STREAM_TRANSITION, 0, z0, z1);
+#pragma unroll
+            for (int j = 0; j < HW; j += 2) {
+                x[j] = (M.a * x[j] + M.b) + M.q * z0[j >> 1];              // sd*z + mean
+                x[j + 1] = (M.a * x[j + 1] + M.b) + M.q * z1[j >> 1];
+            }
         }
-    } else {
+        if (h == 0 && retained_t && g0 + i0 == 0) x[0] = retained_t[0];    // conditional SMC: slot 0
+        // ---- observe* (smc.cljc:23-27) + add-log-weight (state.cljc:27-31)
+        if (KIND == APOP_SSM_LGSSM1D) {
 #pragma unroll
-        for (int j = 0; j < IPT; ++j) l[j] = wbase + obs_logpdf<KIND>(M, x[j], y);
+            for (int j = 0; j < HW; ++j) {
+                const double x1 = (y - (M.c * x[j] + M.d)) * c_obs;
+                l[j] = wbase + (-0.5 * x1 * x1 - M.obs_const);
+            }
+        } else if (KIND == APOP_SSM_SV) {
+            // (normal 0 (* beta (exp (/ x 2)))): y/sd = (y/beta) exp(-x/2), log sd = log beta + x/2
+            bool slow = false;
+#pragma unroll
+            for (int j = 0; j < HW; ++j) { l[j] = -0.5 * x[j]; slow |= !(fabs(l[j]) < 708.0); }
+            if (slow) {
+#pragma unroll
+                for (int j = 0; j < HW; ++j) l[j] = exp(l[j]);
+            } else {
+                fm::exp_core_v<HW>(l);
+            }
+#pragma unroll
+            for (int j = 0; j < HW; ++j) {
+                const double x1 = c_obs * l[j];
+                l[j] = wbase + (-0.5 * x1 * x1 - (0.5 * x[j] + M.obs_const));
+            }
+        } else {
+#pragma unroll
+            for (int j = 0; j < HW; ++j) l[j] = wbase + obs_logpdf<KIND>(M, x[j], y);
+        }
+        // ---- store
+        if (inb) {
+            double2* qx = reinterpret_cast<double2*>(xn + ih);
+            double2* ql = reinterpret_cast<double2*>(lw + ih);
+#pragma unroll
+            for (int j = 0; j < HW / 2; ++j) {
+                qx[j] = make_double2(x[2 * j], x[2 * j + 1]);
+                ql[j] = make_double2(l[2 * j], l[2 * j + 1]);
+            }
+        } else {
+#pragma unroll
+            for (int j = 0; j < HW; ++j)
+                if (ih + j < n) { xn[ih + j] = x[j]; lw[ih + j] = l[j]; }
+        }
+        // ---- partials of particle-weights (smc.cljc:70-84): exact max; fp32 online
+        //      (reference, sum exp) pair
+        float mh = -INFINITY;
+#pragma unroll
+        for (int j = 0; j < HW; ++j) {
+            if (VALID(j)) {
+                bad |= !(l[j] < INFINITY);                                 // NaN or +inf
+                mx = (l[j] > mx) ? l[j] : mx;
+                mh = fmaxf(mh, __double2float_rn(l[j]));
+            }
+        }
+        const float nref = fmaxf(ref, mh);
+        if (nref > -INFINITY) {
+            s *= ex2_approx((ref - nref) * kL2E);                          // ref = -inf -> 0
+            const double refd = (double)nref;
+#pragma unroll
+            for (int j = 0; j < HW; ++j)
+                if (VALID(j)) s += ex2_approx(__double2float_rn(l[j] - refd) * kL2E);
+            ref = nref;
+        }
+#undef VALID
     }
-    float mxf = -INFINITY;
+    if (bad) atomicOr(errflag, EB_NAN);
+    // ---- warp: common fp32 reference, rescaled sums; exact max
+    float wref = ref;
 #pragma unroll
-    for (int j = 0; j < IPT; ++j) {
-        if (i0 + j < n) {
-            nan |= (l[j] != l[j]) | (l[j] == INFINITY);
-            mx = fmax(mx, l[j]);
-            mxf = fmaxf(mxf, __double2float_rn(l[j]));
-        }
-    }
-    if (nan) atomicOr(errflag, EB_NAN);
-    // ---- store
-    if (i0 + IPT <= n) {
-        double2* qx = reinterpret_cast<double2*>(xn + i0);
-        double2* ql = reinterpret_cast<double2*>(lw + i0);
-#pragma unroll
-        for (int j = 0; j < IPT / 2; ++j) {
-            qx[j] = make_double2(x[2 * j], x[2 * j + 1]);
-            ql[j] = make_double2(l[2 * j], l[2 * j + 1]);
-        }
-    } else {
-#pragma unroll
-        for (int j = 0; j < IPT; ++j)
-            if (i0 + j < n) { xn[i0 + j] = x[j]; lw[i0 + j] = l[j]; }
-    }
-    // ---- tile partials of particle-weights (smc.cljc:70-84), fp32 against a warp reference
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) mxf = fmaxf(mxf, __shfl_xor_sync(0xffffffffu, mxf, o));
-    const float reff = (mxf > -INFINITY) ? mxf : 0.0f;
-    const double refd = (double)reff;
-    float s = 0.0f;
-#pragma unroll
-    for (int j = 0; j < IPT; ++j) {
-        if (i0 + j < n) {
-            const float df = __double2float_rn(l[j] - refd);
-            s += ex2_approx(df * 1.4426950408889634f);
-        }
-    }
+    for (int o = 16; o > 0; o >>= 1) wref = fmaxf(wref, __shfl_xor_sync(0xffffffffu, wref, o));
+    if (wref > -INFINITY) s *= ex2_approx((ref - wref) * kL2E); else s = 0.0f;
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
-    mx = warp_max(mx);
-    if (lane == 0) { red_mx[wid] = mx; red_ref[wid] = reff; red_s[wid] = s; }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        const double v = __shfl_xor_sync(0xffffffffu, mx, o);
+        mx = (v > mx) ? v : mx;
+    }
+    if (lane == 0) { red_mx[wid] = mx; red_ref[wid] = (wref > -INFINITY) ? wref : 0.0f; red_s[wid] = s; }
     __syncthreads();
     if (wid == 0) {
         double m = (lane < NWARP) ? red_mx[lane] : -INFINITY;
@@ -265,6 +282,28 @@ __global__ void __launch_bounds__(TB, 2) k_propagate(const ModelDev* __restrict_
         if (!(m > -INFINITY)) a = (double)((n - base < TILE) ? (n - base) : TILE);
         if (lane == 0) { tmax[blockIdx.x] = m; tsum[blockIdx.x] = a; }
     }
+}
+
+template <int KIND>
+__global__ void __launch_bounds__(TB, 2) k_propagate(const ModelDev* __restrict__ Mp,
+                                                  const double* __restrict__ xp,
+                                                  const int32_t* __restrict__ anc, int first_step,
+                                                  double* __restrict__ xn, double* __restrict__ lw,
+                                                  const double* __restrict__ yt,
+                                                  const double* __restrict__ retained_t,
+                                                  const SweepDev* __restrict__ sd, int64_t n,
+                                                  int64_t g0, uint64_t seed, uint32_t t,
+                                                  double* __restrict__ tmax,
+                                                  double* __restrict__ tsum, int* errflag) {
+    const ModelDev& M = *Mp;
+    const double y = yt[0];
+    const double wbase = sd->base;
+    if ((int64_t)(blockIdx.x + 1) * TILE <= n)
+        propagate_tile<KIND, true>(M, xp, anc, first_step, xn, lw, y, retained_t, wbase, n, g0,
+                                   seed, t, tmax, tsum, errflag);
+    else
+        propagate_tile<KIND, false>(M, xp, anc, first_step, xn, lw, y, retained_t, wbase, n, g0,
+                                    seed, t, tmax, tsum, errflag);
 }
 
 __global__ void k_sweep_reset(SweepDev* sd, ResampleInfo* I) {
