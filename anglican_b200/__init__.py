@@ -4,6 +4,6 @@ distribution protocol.  All particle arithmetic runs in hand-written CUDA
 (sm_100a) inside libanglican_pop.so; this package is the host-side mirror of
 the reference interface.  There is no CPU fallback."""
 from . import _lib
-from .population import Column, Population
+from .population import Column, Population, PopulationGroup
 
-__all__ = ["_lib", "Column", "Population"]
+__all__ = ["_lib", "Column", "Population", "PopulationGroup"]

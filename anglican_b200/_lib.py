@@ -60,6 +60,7 @@ _SIGS = [
     ("apop_version", C.c_int, []),
     ("apop_device_count", C.c_int, []),
     ("apop_create", C.c_int, [C.POINTER(_vp), C.c_int64, C.c_uint64, C.c_int, C.c_int, C.c_int, _vp]),
+    ("apop_link_group", C.c_int, [C.POINTER(_vp), C.c_int32]),
     ("apop_destroy", C.c_int, [_vp]),
     ("apop_last_error", C.c_char_p, [_vp]),
     ("apop_get_unique_id", C.c_int, [_vp]),
@@ -107,6 +108,9 @@ _SIGS = [
     ("apop_gather", C.c_int, [_vp, C.c_int32, C.c_int64, c_int32_p, C.c_int]),
     ("apop_smc_sweep", C.c_int, [_vp, C.POINTER(ApopSSM), c_double_p, C.c_int32, c_double_p,
                                  C.POINTER(ApopSweepOpts), C.POINTER(ApopSweepResult)]),
+    ("apop_smc_sweep_group", C.c_int, [C.POINTER(_vp), C.c_int32, C.POINTER(ApopSSM), c_double_p,
+                                       C.c_int32, C.POINTER(ApopSweepOpts),
+                                       C.POINTER(ApopSweepResult)]),
     ("apop_trace_lineage", C.c_int, [_vp, C.c_int64, c_double_p]),
     ("apop_sweep_download_history", C.c_int, [_vp, c_int32_p, c_double_p]),
     ("apop_sweep_final_device", C.c_int, [_vp, C.POINTER(_vp)]),

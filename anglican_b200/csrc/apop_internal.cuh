@@ -9,6 +9,9 @@
 
 #include "../../include/anglican_pop.h"
 #include "exact_fold.cuh"
+#include "fabric.cuh"
+
+struct apop_ctx;
 
 namespace apop {
 
@@ -23,7 +26,8 @@ enum {
     EB_ZERO = 2,         // total weight not > 0 / not finite
     EB_CTX = 4,          // classification / chain context mismatch (internal)
     EB_COMB = 8,         // comb table overflow / stuck comb
-    EB_COUNT = 16        // emitted offspring count mismatch (internal)
+    EB_COUNT = 16,       // emitted offspring count mismatch (internal)
+    EB_COMM = 32         // a peer rank never arrived at an exchange (spin timeout)
 };
 
 struct ResampleInfo {
@@ -84,6 +88,20 @@ struct ParamArena {
     size_t cap = 0, off = 0;
 };
 
+// host side of the peer-memory fabric (fabric.cuh)
+struct FabricHost {
+    bool linked = false;
+    bool in_process = false;               // all ranks live in this process (apop_link_group)
+    char* heap[kMaxWorld] = {};            // heap[q]: rank q's symmetric heap as mapped here
+    bool ipc_open[kMaxWorld] = {};
+    size_t heap_bytes = 0;
+    size_t off_xa = 0, off_xb = 0, off_anc = 0;
+    size_t cap_n = 0;
+    unsigned long long epoch = 0;          // per-step exchange sequence number
+    unsigned long long bar_epoch = 0;      // barrier sequence number
+    std::vector<apop_ctx*> group;          // in-process group, rank order
+};
+
 struct ResampleWS {
     int64_t nt = 0;
     double *tmax = nullptr, *tsum = nullptr, *tsum2 = nullptr, *ain = nullptr;  // tsum2: sum w x
@@ -118,6 +136,7 @@ struct apop_ctx {
     void* nccl = nullptr;         // ncclComm_t
     apop::ParamArena arena;       // staged distribution parameters
     bool ktimers = false;         // per-kernel CUDA-event timers (bench roofline)
+    apop::FabricHost fab;         // world > 1: peer heaps and mailboxes
     // last fused sweep
     struct SweepState* sweep = nullptr;
 };
@@ -163,6 +182,8 @@ struct ResampleArgs {
     const double* xfilt;     // optional state column: per-step filtering mean sum w x / sum w
     double rel_eps;          // accuracy of the supplied tile partials (0: fp64 partials)
     StepOut step;            // optional per-step outputs (sd == nullptr: none)
+    bool sharded;            // world > 1: exchange through the fabric, offspring stored to peers
+    PeerI32 anc_peer;        // sharded: anc_peer.p[q] = rank q's ancestor array
 };
 int resample_enqueue(apop_ctx* c, const ResampleArgs& a);
 int resample_fetch_info(apop_ctx* c, ResampleInfo* out);   // syncs
@@ -170,6 +191,10 @@ int info_to_status(apop_ctx* c, const ResampleInfo& info);
 int multinomial_enqueue(apop_ctx* c, const double* lw, const double* w, const double* uni,
                         int64_t n_new, int32_t* anc);
 int gather_enqueue(apop_ctx* c, const int32_t* anc, int64_t n_new, Column* col);
+Fabric fabric_view(const apop_ctx* c);                      // by-value kernel argument
+int fabric_barrier_enqueue(apop_ctx* c);                    // all ranks: flags over peer memory
+int fabric_prepare(apop_ctx* c, size_t n_cap);              // (re)allocate + map the heaps (comm.cu)
+void fabric_free(apop_ctx* c);
 
 // ---------------------------------------------------------------- device
 #if defined(__CUDACC__)

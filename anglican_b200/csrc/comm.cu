@@ -12,6 +12,8 @@
 
 namespace apop {
 
+int comm_allgather_dev(apop_ctx* c, const void* send, void* recv, size_t bytes);
+
 typedef struct ncclComm* ncclComm_t;
 typedef struct { char internal[128]; } ncclUniqueId;
 enum { ncclSuccess = 0 };
@@ -116,6 +118,151 @@ int comm_exchange_dev(apop_ctx* c, void* const* send_ptr, const size_t* send_byt
                                      c->stream));
     }
     APOP_NCCL(c, g_nccl.GroupEnd());
+    return APOP_OK;
+}
+
+// ------------------------------------------------------------------ fabric
+Fabric fabric_view(const apop_ctx* c) {
+    Fabric F;
+    memset(&F, 0, sizeof F);
+    F.rank = c->rank;
+    F.world = c->world;
+    F.n_local = c->n;
+    if (c->world > 1 && c->fab.linked)
+        for (int q = 0; q < c->world; ++q) F.mbox[q] = (Mailbox*)c->fab.heap[q];
+    return F;
+}
+
+// every rank raises its flag in every peer's mailbox, then waits for all flags
+__global__ void k_fabric_barrier(Fabric F, unsigned long long seq, int* err) {
+    __threadfence_system();
+    const int q = threadIdx.x;
+    if (q < F.world) {
+        st_release_sys(&F.mbox[q]->bar[F.rank], seq);
+        if (!spin_until(&F.mbox[F.rank]->bar[q], seq) && err) atomicOr(err, EB_COMM);
+    }
+}
+
+void preload_comm_kernels() {
+    cudaFuncAttributes a;
+    cudaFuncGetAttributes(&a, k_fabric_barrier);
+}
+
+int fabric_barrier_enqueue(apop_ctx* c) {
+    if (c->world == 1) return APOP_OK;
+    if (!c->fab.linked) return set_err(c, APOP_ERR_INVALID, "fabric not linked");
+    k_fabric_barrier<<<1, 32, 0, c->stream>>>(fabric_view(c), ++c->fab.bar_epoch,
+                                              c->ws.info ? &c->ws.info->err : nullptr);
+    c->launches += 1;
+    APOP_CUDA(c, cudaGetLastError());
+    return APOP_OK;
+}
+
+static void fabric_unmap(apop_ctx* c) {
+    FabricHost& f = c->fab;
+    for (int q = 0; q < kMaxWorld; ++q) {
+        if (q != c->rank && f.ipc_open[q] && f.heap[q]) cudaIpcCloseMemHandle(f.heap[q]);
+        if (q != c->rank) { f.heap[q] = nullptr; f.ipc_open[q] = false; }
+    }
+    f.linked = false;
+}
+
+void fabric_free(apop_ctx* c) {
+    FabricHost& f = c->fab;
+    fabric_unmap(c);
+    if (f.heap[c->rank]) cudaFree(f.heap[c->rank]);
+    f.heap[c->rank] = nullptr;
+    f.heap_bytes = 0;
+    f.cap_n = 0;
+}
+
+// allocate this rank's symmetric heap for n_cap particles (layout identical on
+// every rank: mailbox | xa | xb | anc)
+static int fabric_alloc_own(apop_ctx* c, size_t n_cap) {
+    FabricHost& f = c->fab;
+    const size_t col = ((n_cap + 8) * 8 + 255) & ~(size_t)255;
+    const size_t acol = ((n_cap + 8) * 4 + 255) & ~(size_t)255;
+    f.off_xa = kMailboxBytes;
+    f.off_xb = f.off_xa + col;
+    f.off_anc = f.off_xb + col;
+    const size_t bytes = f.off_anc + acol;
+    cudaSetDevice(c->device);
+    if (f.heap[c->rank]) {
+        APOP_CUDA(c, cudaStreamSynchronize(c->stream));
+        cudaFree(f.heap[c->rank]);
+        f.heap[c->rank] = nullptr;
+    }
+    if (cudaMalloc((void**)&f.heap[c->rank], bytes) != cudaSuccess)
+        return set_err(c, APOP_ERR_OOM, "fabric: heap allocation of %zu bytes failed", bytes);
+    APOP_CUDA(c, cudaMemset(f.heap[c->rank], 0, kMailboxBytes));
+    APOP_CUDA(c, cudaDeviceSynchronize());       // ctx streams do not order with the NULL stream
+    f.heap_bytes = bytes;
+    f.cap_n = n_cap;
+    return APOP_OK;
+}
+
+// Collective over all ranks (same n_cap everywhere).  Multi-process: IPC handles
+// are exchanged with one NCCL allgather and mapped with cudaIpcOpenMemHandle.
+// In-process group (apop_link_group): pointers are shared directly, with peer
+// access enabled between distinct devices.
+int fabric_prepare(apop_ctx* c, size_t n_cap) {
+    FabricHost& f = c->fab;
+    if (c->world == 1) return APOP_OK;
+    if (c->world > kMaxWorld) return set_err(c, APOP_ERR_UNSUPPORTED, "world > %d", kMaxWorld);
+    if (f.linked && f.cap_n >= n_cap) return APOP_OK;
+    if (f.in_process) {
+        if (c->rank != 0) return APOP_OK;          // rank 0 of the group (re)builds everything
+        for (apop_ctx* g : f.group) {
+            fabric_unmap(g);
+            APOP_TRY(fabric_alloc_own(g, n_cap));
+        }
+        for (apop_ctx* g : f.group) {
+            cudaSetDevice(g->device);
+            for (apop_ctx* h : f.group) {
+                if (h == g) continue;
+                if (h->device != g->device) {
+                    cudaError_t e = cudaDeviceEnablePeerAccess(h->device, 0);
+                    if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled)
+                        return set_err(c, APOP_ERR_CUDA, "peer access %d -> %d: %s", g->device,
+                                       h->device, cudaGetErrorString(e));
+                    cudaGetLastError();
+                }
+                g->fab.heap[h->rank] = h->fab.heap[h->rank];
+            }
+            g->fab.linked = true;
+            APOP_CUDA(g, cudaDeviceSynchronize());
+        }
+        return APOP_OK;
+    }
+    // ---- one process per GPU
+    if (!c->nccl) return set_err(c, APOP_ERR_NCCL, "fabric: no communicator");
+    fabric_unmap(c);
+    APOP_TRY(fabric_alloc_own(c, n_cap));
+    cudaIpcMemHandle_t mine;
+    APOP_CUDA(c, cudaIpcGetMemHandle(&mine, f.heap[c->rank]));
+    const size_t hb = sizeof(cudaIpcMemHandle_t);
+    APOP_TRY(ensure_scratch(c, hb * (size_t)(c->world + 1)));
+    char* base = (char*)c->scratch;
+    APOP_CUDA(c, cudaMemcpyAsync(base, &mine, hb, cudaMemcpyHostToDevice, c->stream));
+    APOP_TRY(comm_allgather_dev(c, base, base + hb, hb));
+    std::vector<cudaIpcMemHandle_t> all((size_t)c->world);
+    APOP_CUDA(c, cudaMemcpyAsync(all.data(), base + hb, hb * (size_t)c->world,
+                                 cudaMemcpyDeviceToHost, c->stream));
+    APOP_CUDA(c, cudaStreamSynchronize(c->stream));
+    for (int q = 0; q < c->world; ++q) {
+        if (q == c->rank) continue;
+        void* p = nullptr;
+        cudaError_t e = cudaIpcOpenMemHandle(&p, all[(size_t)q], cudaIpcMemLazyEnablePeerAccess);
+        if (e != cudaSuccess)
+            return set_err(c, APOP_ERR_CUDA, "cudaIpcOpenMemHandle(rank %d): %s", q,
+                           cudaGetErrorString(e));
+        f.heap[q] = (char*)p;
+        f.ipc_open[q] = true;
+    }
+    f.linked = true;
+    // nobody may touch a peer heap before every rank has mapped and zeroed its own
+    APOP_TRY(comm_allgather_dev(c, base, base + hb, hb));
+    APOP_CUDA(c, cudaStreamSynchronize(c->stream));
     return APOP_OK;
 }
 

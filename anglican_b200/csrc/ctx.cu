@@ -145,7 +145,7 @@ int apop_create(apop_ctx** out, int64_t n_local, uint64_t seed, int device, int 
         delete c;
         return APOP_ERR_CUDA;
     }
-    if (world > 1) {
+    if (world > 1 && nccl_id) {
         int rc = comm_init(c, nccl_id);
         if (rc != APOP_OK) {
             cudaStreamDestroy(c->stream);
@@ -153,7 +153,28 @@ int apop_create(apop_ctx** out, int64_t n_local, uint64_t seed, int device, int 
             return rc;
         }
     }
+    // world > 1 without an NCCL id: a rank of an in-process group, to be wired
+    // with apop_link_group before its first sweep
     *out = c;
+    return APOP_OK;
+}
+
+int apop_link_group(apop_ctx* const* ctxs, int32_t world) {
+    if (!ctxs || world < 2 || world > kMaxWorld) return APOP_ERR_INVALID;
+    for (int i = 0; i < world; ++i) {
+        apop_ctx* c = ctxs[i];
+        if (!c) return APOP_ERR_INVALID;
+        if (c->world != world || c->rank != i || c->n != ctxs[0]->n || c->nccl)
+            return set_err(ctxs[0], APOP_ERR_INVALID,
+                           "link_group: need ranks 0..world-1 of equal size, created without an "
+                           "NCCL id, in rank order");
+    }
+    for (int i = 0; i < world; ++i) {
+        FabricHost& f = ctxs[i]->fab;
+        f.in_process = true;
+        f.linked = false;
+        f.group.assign(ctxs, ctxs + world);
+    }
     return APOP_OK;
 }
 
@@ -162,6 +183,7 @@ int apop_destroy(apop_ctx* c) {
     cudaSetDevice(c->device);
     cudaStreamSynchronize(c->stream);
     sweep_free(c);
+    fabric_free(c);
     comm_free(c);
     for (auto& col : c->cols)
         if (col.used && col.ptr) cudaFree(col.ptr);

@@ -303,10 +303,13 @@ __device__ __forceinline__ double block_sum_f64(double v, double* sm /*[33]*/) {
 // single CTA; every global access is coalesced (tiles are walked striped)
 __global__ void __launch_bounds__(FB) k_finalize(WSView v, int64_t n, int64_t n_new, double u_in,
                                                  uint64_t seed, uint32_t step, int weights_mode,
-                                                 double rel_eps) {
+                                                 double rel_eps, Fabric F, unsigned long long seq,
+                                                 int64_t g0, int64_t n_global) {
     __shared__ double buf[FB * FCH];
     __shared__ double smd[33];
     __shared__ int sh_skip;
+    __shared__ double pm[kMaxWorld], ps[kMaxWorld];
+    __shared__ int perr[kMaxWorld];
     const int64_t nt = v.nt;
     const int tid = threadIdx.x;
 
@@ -323,7 +326,7 @@ __global__ void __launch_bounds__(FB) k_finalize(WSView v, int64_t n, int64_t n_
         m = a;
         __syncthreads();
     }
-    // ---- rescale the tile partials to the global max (in place)
+    // ---- rescale the tile partials to the (local) max (in place)
     if (!weights_mode) {
         for (int64_t t = tid; t < nt; t += FB) {
             const double tm = v.tmax[t];
@@ -331,13 +334,46 @@ __global__ void __launch_bounds__(FB) k_finalize(WSView v, int64_t n, int64_t n_
             v.tsum[t] = v.tsum[t] * fac;
         }
     }
+    // ---- sharded: exchange (local max, local sum, error bits) with every peer
+    //      through the mailboxes; afterwards m is the global max, `offset` the
+    //      approximate weight of all lower ranks and gtot the global total.
+    double gfac = 1.0, offset = 0.0, gtot = 0.0;
+    if (F.world > 1) {
+        double ls = 0.0;
+        for (int64_t t = tid; t < nt; t += FB) ls += v.tsum[t];
+        __syncthreads();
+        const double lsum = block_sum_f64(ls, smd);
+        const int par = (int)(seq & 1);
+        if (tid < F.world) {
+            mail_send(&F.mbox[tid]->fin[par][F.rank], m, lsum, (double)v.info->err, seq);
+            double o[3];
+            const bool ok = mail_wait(&F.mbox[F.rank]->fin[par][tid], seq, o);
+            pm[tid] = o[0]; ps[tid] = o[1]; perr[tid] = (int)o[2] | (ok ? 0 : EB_COMM);
+        }
+        __syncthreads();
+        const double m_loc = m;
+        double gm = pm[0];
+        int gerr = 0;
+        for (int q = 1; q < F.world; ++q) gm = fmax(gm, pm[q]);
+        if (weights_mode) gm = 0.0;
+        for (int q = 0; q < F.world; ++q) {
+            const double sq = ps[q] * ((pm[q] == gm || weights_mode) ? 1.0 : fm::exp_any(pm[q] - gm));
+            if (q < F.rank) offset += sq;
+            gtot += sq;
+            gerr |= perr[q];
+        }
+        m = gm;
+        gfac = (m_loc == gm || weights_mode) ? 1.0 : fm::exp_any(m_loc - gm);
+        if (tid == 0 && gerr) atomicOr(&v.info->err, gerr);
+        __syncthreads();
+    }
     // ---- approximate exclusive prefix of tile sums: ain[t]
-    double carry = 0.0;
+    double carry = offset;
     for (int64_t base = 0; base < nt; base += FB * FCH) {
 #pragma unroll
         for (int k = 0; k < FCH; ++k) {
             const int64_t idx = base + k * FB + tid;
-            buf[k * FB + tid] = (idx < nt) ? v.tsum[idx] : 0.0;
+            buf[k * FB + tid] = (idx < nt) ? v.tsum[idx] * gfac : 0.0;
         }
         __syncthreads();
         double a[FCH], loc = 0.0;
@@ -356,13 +392,13 @@ __global__ void __launch_bounds__(FB) k_finalize(WSView v, int64_t n, int64_t n_
         carry += chunk_total;
         __syncthreads();
     }
-    const double atot = carry;
-    if (tid == 0) { v.ain[nt] = atot; sh_skip = (nt < INT_MAX) ? (int)nt : INT_MAX; }
+    const double atot = (F.world > 1) ? gtot : carry;
+    if (tid == 0) { v.ain[nt] = carry; sh_skip = (nt < INT_MAX) ? (int)nt : INT_MAX; }
     __syncthreads();
 
     const double u = (u_in != u_in) ? uniform_at(seed, 0, step, STREAM_RESAMPLE, 0) : u_in;
     // x_last < x_0 + total <= total*(u+1): generous upper bound for the skip test
-    const double eps_tot = ((double)(2 * n) + 8192.0) * 4.44089209850062616e-16 + rel_eps;
+    const double eps_tot = ((double)(2 * n_global) + 8192.0) * 4.44089209850062616e-16 + rel_eps;
     const double xlast_ub = atot * (u + 1.0) * (1.0 + 4.0 * eps_tot);
 
     // ---- classification of every tile for both laps
@@ -370,16 +406,16 @@ __global__ void __launch_bounds__(FB) k_finalize(WSView v, int64_t n, int64_t n_
     for (int64_t t = tid; t < nt; t += FB) {
         const int64_t hi = ((t + 1) * TILE < n) ? (t + 1) * TILE : n;
         const double a_in = v.ain[t], ao = v.ain[t + 1];
-        const int c0 = classify_tile(a_in, ao, hi, rel_eps);
+        const int c0 = classify_tile(a_in, ao, g0 + hi, rel_eps);
         v.cls0[t] = c0;
         nh0 += (c0 == kCtxHard);
         int c1;
-        const double eps1 = ((double)(n + hi) + 4096.0) * 4.44089209850062616e-16 + rel_eps;
+        const double eps1 = ((double)(n_global + g0 + hi) + 4096.0) * 4.44089209850062616e-16 + rel_eps;
         if ((atot + a_in) * (1.0 - eps1) > xlast_ub) {
             c1 = kCtxSkip;
             atomicMin(&sh_skip, (int)t);
         } else {
-            c1 = classify_tile(atot + a_in, atot + ao, n + hi, rel_eps);
+            c1 = classify_tile(atot + a_in, atot + ao, n_global + g0 + hi, rel_eps);
         }
         v.cls1[t] = c1;
         nh1 += (c1 == kCtxHard);
@@ -392,7 +428,7 @@ __global__ void __launch_bounds__(FB) k_finalize(WSView v, int64_t n, int64_t n_
         I->atot = atot;
         I->asq = 0.0;
         I->ess = 0.0;
-        I->log_mean_approx = (m > -INFINITY && m < INFINITY) ? log(atot / (double)n) + m
+        I->log_mean_approx = (m > -INFINITY && m < INFINITY) ? log(atot / (double)n_global) + m
                                                                : -INFINITY;
         I->u = u;
         I->n_new = n_new;
@@ -585,32 +621,80 @@ __device__ double resolve_lap(const Xd* __restrict__ agg, const int* __restrict_
 
 __global__ void __launch_bounds__(TB) k_resolve(const double* __restrict__ lw,
                                                 const double* __restrict__ win, int64_t n,
-                                                int64_t n_total, WSView v, StepOut so) {
+                                                int64_t n_total, WSView v, StepOut so, Fabric F,
+                                                unsigned long long seq) {
     __shared__ FoldSmem sm;
     __shared__ double smd[33];
+    __shared__ double sh_in;
+    __shared__ double pa[kMaxWorld], pb[kMaxWorld], px[kMaxWorld];
+    __shared__ int sh_comm;
     const int64_t nt = v.nt;
     ResampleInfo* I = v.info;
     const double m = I->m;
+    const bool sharded = F.world > 1;
+    const bool last_rank = F.rank == F.world - 1;
+    const int par = (int)(seq & 1);
+    if (threadIdx.x == 0) sh_comm = 0;
 
-    // ---------------- lap 0: exact total (smc.cljc:94)
+    // ---------------- lap 0: exact total (smc.cljc:94).  Sharded: the sequential
+    // fold runs through the ranks in order; the exact running sum entering this
+    // shard arrives from the previous rank.
+    double S0 = 0.0;
+    if (sharded && F.rank > 0) {
+        if (threadIdx.x == 0) {
+            double o[3];
+            if (!mail_wait(&F.mbox[F.rank]->s0[par], seq, o)) sh_comm = 1;
+            sh_in = o[0];
+        }
+        __syncthreads();
+        S0 = sh_in;
+    }
     int64_t tend;
-    const double total = resolve_lap(v.agg0, v.cls0, v.sin0, 0.0, nt, INFINITY, &tend, lw, win, n,
+    const double Send0 = resolve_lap(v.agg0, v.cls0, v.sin0, S0, nt, INFINITY, &tend, lw, win, n,
                                      m, sm, &I->err);
+    if (sharded && threadIdx.x == 0) {
+        if (!last_rank) {
+            mail_send(&F.mbox[F.rank + 1]->s0[par], Send0, 0.0, 0.0, seq);
+        } else {
+            for (int q = 0; q < F.world - 1; ++q)
+                mail_send(&F.mbox[q]->tot[par], Send0, 0.0, 0.0, seq);
+        }
+    }
     // accurate sum w / sum w^2 (ESS = (sum w)^2 / sum w^2, dist_test.cljc:83-94)
     double la = 0.0, lb = 0.0, lx = 0.0;
     for (int64_t t = threadIdx.x; t < nt; t += TB) { la += v.tacc[t]; lb += v.tacc2[t]; }
     if (so.sd && so.has_x)
         for (int64_t t = threadIdx.x; t < nt; t += TB) lx += v.tsum2[t];
-    const double acc = block_sum_f64(la, smd);
-    const double acc2 = block_sum_f64(lb, smd);
-    const double accx = block_sum_f64(lx, smd);
+    double acc = block_sum_f64(la, smd);
+    double acc2 = block_sum_f64(lb, smd);
+    double accx = block_sum_f64(lx, smd);
+    double total = Send0;
+    if (sharded) {
+        if (threadIdx.x < F.world) {
+            const int q = threadIdx.x;
+            mail_send(&F.mbox[q]->acc[par][F.rank], acc, acc2, accx, seq);
+            double o[3];
+            if (!mail_wait(&F.mbox[F.rank]->acc[par][q], seq, o)) sh_comm = 1;
+            pa[q] = o[0]; pb[q] = o[1]; px[q] = o[2];
+        }
+        if (threadIdx.x == 0 && !last_rank) {
+            double o[3];
+            if (!mail_wait(&F.mbox[F.rank]->tot[par], seq, o)) sh_comm = 1;
+            sh_in = o[0];
+        }
+        __syncthreads();
+        acc = 0.0; acc2 = 0.0; accx = 0.0;
+        for (int q = 0; q < F.world; ++q) { acc += pa[q]; acc2 += pb[q]; accx += px[q]; }
+        if (!last_rank) total = sh_in;
+        __syncthreads();
+    }
     if (threadIdx.x == 0) {
-        v.sin0[nt] = total;
+        v.sin0[nt] = Send0;
         const i64 n_new = I->n_new;
-        int err = 0;
+        int err = sh_comm ? EB_COMM : 0;
         if (!(total > 0.0) || !(total < INFINITY)) err |= EB_ZERO;
         Comb& c = *v.comb;
-        if (!err) {
+        if (!(err & EB_ZERO)) {
             comb_build(c, total, I->u, n_new);
             if (c.err) err |= EB_COMB;
         } else {
@@ -619,7 +703,7 @@ __global__ void __launch_bounds__(TB) k_resolve(const double* __restrict__ lw,
         int hint = 0;
         I->total = total;
         I->step = total / (double)n_new;                                  // smc.cljc:95
-        I->J = err ? 0 : comb_count_below(c, total, hint);
+        I->J = (err & (EB_ZERO | EB_COMB)) ? 0 : comb_count_below(c, total, hint);
         const bool mfin = (m > -INFINITY && m < INFINITY);
         I->new_lw = mfin ? (log(I->step) + m) : -INFINITY;                // smc.cljc:98-103
         I->ess = (acc2 > 0.0) ? acc * acc / acc2 : 0.0;
@@ -641,15 +725,33 @@ __global__ void __launch_bounds__(TB) k_resolve(const double* __restrict__ lw,
     __syncthreads();
     if (I->err & (EB_ZERO | EB_COMB | EB_NAN)) {
         for (int64_t t = threadIdx.x; t <= nt; t += TB) v.sin1[t] = INFINITY;
+        // keep the chain moving so that no peer waits for this rank
+        if (sharded && !last_rank && threadIdx.x == 0)
+            mail_send(&F.mbox[F.rank + 1]->s1[par], INFINITY, 0.0, 0.0, seq);
         return;
     }
     const double xlast = v.comb->xlast;
 
     // ---------------- lap 1: the wheel wraps with acc NOT reset (smc.cljc:133-136)
+    double S1 = total;
+    if (sharded && F.rank > 0) {
+        if (threadIdx.x == 0) {
+            double o[3];
+            if (!mail_wait(&F.mbox[F.rank]->s1[par], seq, o)) {
+                atomicOr(&I->err, EB_COMM);
+                if (so.sd) so.sd->err |= EB_COMM;
+            }
+            sh_in = o[0];
+        }
+        __syncthreads();
+        S1 = sh_in;
+    }
     int64_t stop = I->first_skip1;
     if (stop > nt) stop = nt;
-    const double S = resolve_lap(v.agg1, v.cls1, v.sin1, total, stop, xlast, &tend, lw, win, n, m,
+    const double S = resolve_lap(v.agg1, v.cls1, v.sin1, S1, stop, xlast, &tend, lw, win, n, m,
                                  sm, &I->err);
+    if (sharded && !last_rank && threadIdx.x == 0)
+        mail_send(&F.mbox[F.rank + 1]->s1[par], S, 0.0, 0.0, seq);
     // tend = first tile that cannot receive a pointer of the second lap
     if (tend < nt && !(S > xlast) && threadIdx.x == 0) {
         atomicOr(&I->err, EB_CTX);
@@ -665,13 +767,27 @@ __device__ __forceinline__ int64_t slot_of(i64 k, int lap, int order, i64 J, i64
     return lap == 0 ? k + (n_new - J) : k - J;                    // sorted physical order
 }
 
+// where offspring indices go: the local ancestor array, or (sharded) the array
+// of whichever rank owns the output slot, written through peer memory
+struct AncOut {
+    int32_t* local;
+    PeerI32 peer;
+    int world;
+    i64 nl;                      // particles per rank
+    __device__ __forceinline__ int32_t* at(i64 slot) const {
+        if (world == 1) return local + slot;
+        const int q = (int)(slot / nl);
+        return peer.p[q] + (slot - (i64)q * nl);
+    }
+};
+
 struct EmitCtx {
-    int32_t* anc;
+    AncOut out;
     int64_t out_offset;
     i64 J, n_new;
     int order, lap;
     __device__ __forceinline__ void put(i64 k, int32_t val) const {
-        anc[out_offset + slot_of(k, lap, order, J, n_new)] = val;
+        *out.at(out_offset + slot_of(k, lap, order, J, n_new)) = val;
     }
 };
 
@@ -753,7 +869,7 @@ __device__ __forceinline__ int find_seg_of_index(const Comb& c, i64 k) {
 // returns false (uniformly, nothing written) when the tile does not qualify
 __device__ __forceinline__ bool staged_emit(const Comb& comb, int e, double Sin,
                                             const double (&incD)[IPT], int32_t val_tile0,
-                                            int32_t* __restrict__ anc, int64_t out_offset, i64 J,
+                                            const AncOut& A, int64_t out_offset, i64 J,
                                             i64 n_new, int order, int lap, StageSmem& st) {
     // tile totals and the window [C0, C1) of pointer indices
     double loc = 0.0;
@@ -871,11 +987,27 @@ __device__ __forceinline__ bool staged_emit(const Comb& comb, int e, double Sin,
             __syncthreads();
         }
         // coalesced copy-out (the three orders are contiguous runs, ascending or descending)
-        int32_t* dst = anc + out_offset + slot_of(C0 + wb, lap, order, J, n_new);
-        if (order == APOP_ORDER_REFERENCE) {
-            for (int i = tid; i < wn; i += TB) dst[-i] = st.buf[i];
+        const i64 slot0 = out_offset + slot_of(C0 + wb, lap, order, J, n_new);
+        if (A.world == 1) {
+            int32_t* dst = A.local + slot0;
+            if (order == APOP_ORDER_REFERENCE) {
+                for (int i = tid; i < wn; i += TB) dst[-i] = st.buf[i];
+            } else {
+                for (int i = tid; i < wn; i += TB) dst[i] = st.buf[i];
+            }
         } else {
-            for (int i = tid; i < wn; i += TB) dst[i] = st.buf[i];
+            // the window may straddle shard boundaries: the part beyond this
+            // rank's slots is stored into the owner's array over NVLink
+            const int dir = (order == APOP_ORDER_REFERENCE) ? -1 : 1;
+            const i64 lo = (dir > 0) ? slot0 : slot0 - (wn - 1);
+            const int q_lo = (int)(lo / A.nl);
+            const i64 off_lo = lo - (i64)q_lo * A.nl;
+            for (int i = tid; i < wn; i += TB) {
+                i64 li = off_lo + ((dir > 0) ? i : (wn - 1 - i));
+                int q = q_lo;
+                while (li >= A.nl) { li -= A.nl; ++q; }
+                A.peer.p[q][li] = st.buf[i];
+            }
         }
         __syncthreads();
     }
@@ -927,7 +1059,7 @@ __global__ void __launch_bounds__(TB, 2) k_ancestors(const double* __restrict__ 
                                                      const double* __restrict__ win, int64_t n,
                                                      int64_t g0, WSView v, int order,
                                                      int32_t* __restrict__ anc,
-                                                     int64_t out_offset) {
+                                                     int64_t out_offset, PeerI32 ancp, int world) {
     __shared__ AncSmem sm;
     const Comb& comb = *v.comb;          // global (L1/L2 resident); the fast path reads one segment
     const ResampleInfo* I = v.info;
@@ -945,6 +1077,8 @@ __global__ void __launch_bounds__(TB, 2) k_ancestors(const double* __restrict__ 
     const double m = I->m;
     __syncthreads();
     const i64 J = I->J, n_new = I->n_new;
+    AncOut A;
+    A.local = anc; A.peer = ancp; A.world = world; A.nl = n;
     for (int lap = 0; lap < 2; ++lap) {
         if (lap == 0 ? !need0 : !need1) continue;
         const double Sin = lap ? si1 : si0;
@@ -959,12 +1093,12 @@ __global__ void __launch_bounds__(TB, 2) k_ancestors(const double* __restrict__ 
                 fast = tile_quantize_f64(cls, w, incD);
             }
             if (fast)
-                fast = staged_emit(comb, cls, Sin, incD, (int32_t)(g0 + base), anc, out_offset,
+                fast = staged_emit(comb, cls, Sin, incD, (int32_t)(g0 + base), A, out_offset,
                                    J, n_new, order, lap, sm.stage);
         }
         if (!fast) {
             EmitCtx E;
-            E.anc = anc; E.out_offset = out_offset; E.J = J; E.n_new = n_new; E.order = order;
+            E.out = A; E.out_offset = out_offset; E.J = J; E.n_new = n_new; E.order = order;
             E.lap = lap;
             double w[IPT];
             load_weights(lw, win, base, n, m, w);      // rare path: reload instead of keeping w live
@@ -1042,6 +1176,16 @@ __global__ void k_info_reset(ResampleInfo* I) {
 }
 
 // ------------------------------------------------------------------ host side
+void preload_resample_kernels() {
+    cudaFuncAttributes a;
+    cudaFuncGetAttributes(&a, k_tile_lse);
+    cudaFuncGetAttributes(&a, k_finalize);
+    cudaFuncGetAttributes(&a, k_fold_agg);
+    cudaFuncGetAttributes(&a, k_resolve);
+    cudaFuncGetAttributes(&a, k_ancestors);
+    cudaFuncGetAttributes(&a, k_info_reset);
+}
+
 int ensure_resample_ws(apop_ctx* c) {
     ResampleWS& w = c->ws;
     if (w.info) return APOP_OK;
@@ -1083,20 +1227,26 @@ int resample_enqueue(apop_ctx* c, const ResampleArgs& a) {
         kt_end(c, KT_TILE_LSE);
         c->launches += 2;
     }
+    Fabric F = fabric_view(c);
+    if (!a.sharded) { F.world = 1; F.rank = 0; }
+    const int64_t g0 = a.sharded ? c->g0 : 0;
+    const int64_t n_glob = a.sharded ? c->n_global : a.n;
+    const unsigned long long seq = a.sharded ? ++c->fab.epoch : 0ULL;
     kt_begin(c, KT_FINALIZE);
-    k_finalize<<<1, FB, 0, c->stream>>>(v, a.n, a.n_new, a.u, c->seed, c->step, wm, a.rel_eps);
+    k_finalize<<<1, FB, 0, c->stream>>>(v, a.n, a.n_new, a.u, c->seed, c->step, wm, a.rel_eps, F,
+                                        seq, g0, n_glob);
     kt_end(c, KT_FINALIZE);
     kt_begin(c, KT_FOLD_AGG);
     k_fold_agg<<<nt, TB, 0, c->stream>>>(a.lw, a.w, a.n, v, a.xfilt);
     kt_end(c, KT_FOLD_AGG);
     kt_begin(c, KT_RESOLVE);
-    k_resolve<<<1, TB, 0, c->stream>>>(a.lw, a.w, a.n, c->n_global, v, a.step);
+    k_resolve<<<1, TB, 0, c->stream>>>(a.lw, a.w, a.n, n_glob, v, a.step, F, seq);
     kt_end(c, KT_RESOLVE);
     c->launches += 3;
     if (a.anc_out) {
         kt_begin(c, KT_ANCESTORS);
-        k_ancestors<<<nt, TB, 0, c->stream>>>(a.lw, a.w, a.n, c->g0, v, a.order, a.anc_out,
-                                              a.out_offset);
+        k_ancestors<<<nt, TB, 0, c->stream>>>(a.lw, a.w, a.n, g0, v, a.order, a.anc_out,
+                                              a.out_offset, a.anc_peer, F.world);
         kt_end(c, KT_ANCESTORS);
         c->launches += 1;
     }
@@ -1118,6 +1268,9 @@ int info_to_status(apop_ctx* c, const ResampleInfo& I) {
                        "NaN (or negative) weight: the reference's resample would not terminate");
     if (I.err & EB_ZERO)
         return set_err(c, APOP_ERR_ZERO_WEIGHT, "total weight is not a positive finite number");
+    if (I.err & EB_COMM)
+        return set_err(c, APOP_ERR_NCCL, "a peer rank never arrived at a fabric exchange "
+                                         "(spin timeout): results of this sweep are invalid");
     if (I.err & (EB_CTX | EB_COMB | EB_COUNT))
         return set_err(c, APOP_ERR_INTERNAL, "exact-fold consistency check failed (bits %d)",
                        I.err);

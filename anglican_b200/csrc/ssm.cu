@@ -35,6 +35,7 @@ struct SweepState {
     int64_t n = 0;
     int T = 0, dim = 1, kind = 0;
     bool history = false;
+    bool heap_backed = false;      // xa/xb/anc live in the fabric heap (world > 1)
     double *xa = nullptr, *xb = nullptr, *lw = nullptr;
     int32_t* anc = nullptr;
     double* x_hist = nullptr;      // [(T+1) * n * dim]
@@ -56,6 +57,7 @@ namespace apop {
 void sweep_free(apop_ctx* c) {
     SweepState* s = c->sweep;
     if (!s) return;
+    if (s->heap_backed) { s->xa = nullptr; s->xb = nullptr; s->anc = nullptr; }
     void* ptrs[] = {s->xa, s->xb, s->lw, s->anc, s->x_hist, s->anc_hist, s->y, s->retained,
                     s->log_mean_w, s->ess, s->filt, s->tsx, s->x_final, s->sd, s->model, s->traj};
     for (void* p : ptrs)
@@ -129,8 +131,9 @@ __device__ __forceinline__ float ex2_approx(float x) {
     return y;
 }
 
-template <int KIND, bool FULL>
-__device__ __forceinline__ void propagate_tile(const ModelDev& M, const double* __restrict__ xp,
+template <int KIND, bool FULL, bool SHARD>
+__device__ __forceinline__ void propagate_tile(const PeerF64& xpeer,
+                                               const ModelDev& M, const double* __restrict__ xp,
                                                const int32_t* __restrict__ anc, int first_step,
                                                double* __restrict__ xn, double* __restrict__ lw,
                                                double y, const double* __restrict__ retained_t,
@@ -171,8 +174,26 @@ __device__ __forceinline__ void propagate_tile(const ModelDev& M, const double* 
 #pragma unroll
                 for (int j = 0; j < HW; ++j) par[j] = (ih + j < n) ? anc[ih + j] : 0;
             }
+            if (!SHARD || first_step) {
 #pragma unroll
-            for (int j = 0; j < HW; ++j) x[j] = VALID(j) ? __ldg(xp + par[j]) : 0.0;
+                for (int j = 0; j < HW; ++j) x[j] = VALID(j) ? __ldg(xp + par[j]) : 0.0;
+            } else {
+                // parents are global ids: almost all live in this shard; the sliver
+                // that migrated is read from its owner's heap over NVLink
+#pragma unroll
+                for (int j = 0; j < HW; ++j) {
+                    x[j] = 0.0;
+                    if (VALID(j)) {
+                        const int64_t d = (int64_t)par[j] - g0;
+                        if ((uint64_t)d < (uint64_t)n) {
+                            x[j] = __ldg(xp + d);
+                        } else {
+                            const int q = (int)((int64_t)par[j] / n);
+                            x[j] = __ldcv(xpeer.p[q] + ((int64_t)par[j] - (int64_t)q * n));
+                        }
+                    }
+                }
+            }
         }
         // ---- sample* (inference.cljc:46-47)
         if (KIND == APOP_SSM_HMM) {
@@ -284,7 +305,7 @@ __device__ __forceinline__ void propagate_tile(const ModelDev& M, const double* 
     }
 }
 
-template <int KIND>
+template <int KIND, bool SHARD>
 __global__ void __launch_bounds__(TB, 2) k_propagate(const ModelDev* __restrict__ Mp,
                                                   const double* __restrict__ xp,
                                                   const int32_t* __restrict__ anc, int first_step,
@@ -294,16 +315,17 @@ __global__ void __launch_bounds__(TB, 2) k_propagate(const ModelDev* __restrict_
                                                   const SweepDev* __restrict__ sd, int64_t n,
                                                   int64_t g0, uint64_t seed, uint32_t t,
                                                   double* __restrict__ tmax,
-                                                  double* __restrict__ tsum, int* errflag) {
+                                                  double* __restrict__ tsum, int* errflag,
+                                                  PeerF64 xpeer) {
     const ModelDev& M = *Mp;
     const double y = yt[0];
     const double wbase = sd->base;
     if ((int64_t)(blockIdx.x + 1) * TILE <= n)
-        propagate_tile<KIND, true>(M, xp, anc, first_step, xn, lw, y, retained_t, wbase, n, g0,
-                                   seed, t, tmax, tsum, errflag);
+        propagate_tile<KIND, true, SHARD>(xpeer, M, xp, anc, first_step, xn, lw, y, retained_t,
+                                          wbase, n, g0, seed, t, tmax, tsum, errflag);
     else
-        propagate_tile<KIND, false>(M, xp, anc, first_step, xn, lw, y, retained_t, wbase, n, g0,
-                                    seed, t, tmax, tsum, errflag);
+        propagate_tile<KIND, false, SHARD>(xpeer, M, xp, anc, first_step, xn, lw, y, retained_t,
+                                           wbase, n, g0, seed, t, tmax, tsum, errflag);
 }
 
 __global__ void k_sweep_reset(SweepDev* sd, ResampleInfo* I) {
@@ -332,6 +354,17 @@ __global__ void k_gather_rows(const double* __restrict__ src, double* __restrict
     }
 }
 
+// final states of a sharded sweep: parents are global ids
+__global__ void k_gather_shard(PeerF64 src, double* __restrict__ dst,
+                               const int32_t* __restrict__ anc, int64_t n) {
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n;
+         i += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t a = anc[i];
+        const int q = (int)(a / n);
+        dst[i] = __ldcv(src.p[q] + (a - (int64_t)q * n));
+    }
+}
+
 // ------------------------------------------------------------------ host
 static int dev_alloc(apop_ctx* c, void** p, size_t bytes) {
     if (cudaMalloc(p, bytes) != cudaSuccess) {
@@ -345,16 +378,34 @@ static int sweep_prepare(apop_ctx* c, int T, int dim, bool history) {
     SweepState* s = c->sweep;
     if (!s) { s = new SweepState(); c->sweep = s; }
     const size_t n = (size_t)c->n;
+    if (c->world > 1) {
+        if (dim != 1) return set_err(c, APOP_ERR_UNSUPPORTED, "sharded sweep: scalar states only");
+        APOP_TRY(fabric_prepare(c, n));             // collective: (re)maps the peer heaps
+        if (!c->fab.linked)
+            return set_err(c, APOP_ERR_INVALID, "sharded sweep: ranks are not linked "
+                                                "(apop_link_group / NCCL id)");
+    }
     if (s->cap_n < n || s->dim != dim) {
+        if (s->heap_backed) { s->xa = nullptr; s->xb = nullptr; s->anc = nullptr; }
         void* ptrs[] = {s->xa, s->xb, s->lw, s->anc, s->tsx, s->x_final};
         for (void* p : ptrs) if (p) cudaFree(p);
-        APOP_TRY(dev_alloc(c, (void**)&s->xa, (n + 8) * dim * 8));
-        APOP_TRY(dev_alloc(c, (void**)&s->xb, (n + 8) * dim * 8));
+        s->xa = s->xb = nullptr; s->anc = nullptr;
+        if (c->world == 1) {
+            APOP_TRY(dev_alloc(c, (void**)&s->xa, (n + 8) * dim * 8));
+            APOP_TRY(dev_alloc(c, (void**)&s->xb, (n + 8) * dim * 8));
+            APOP_TRY(dev_alloc(c, (void**)&s->anc, (n + 8) * 4));
+        }
         APOP_TRY(dev_alloc(c, (void**)&s->lw, (n + 8) * 8));
-        APOP_TRY(dev_alloc(c, (void**)&s->anc, (n + 8) * 4));
         APOP_TRY(dev_alloc(c, (void**)&s->tsx, ((n + TILE - 1) / TILE + 1) * 8 * (size_t)dim));
         APOP_TRY(dev_alloc(c, (void**)&s->x_final, (n + 8) * dim * 8));
         s->cap_n = n;
+    }
+    if (c->world > 1) {
+        char* h = c->fab.heap[c->rank];
+        s->xa = (double*)(h + c->fab.off_xa);
+        s->xb = (double*)(h + c->fab.off_xb);
+        s->anc = (int32_t*)(h + c->fab.off_anc);
+        s->heap_backed = true;
     }
     if (!s->sd) {
         APOP_TRY(dev_alloc(c, (void**)&s->sd, sizeof(SweepDev)));
@@ -411,14 +462,31 @@ static int upload_model(apop_ctx* c, const apop_ssm* m) {
     return APOP_OK;
 }
 
-template <int KIND>
-static int run_scalar_sweep(apop_ctx* c, const apop_ssm* model, const double* y, int T,
-                            const double* retained, const apop_sweep_opts* o) {
+// peer views of one heap column (identical offsets on every rank)
+static PeerF64 peer_f64(const apop_ctx* c, size_t off) {
+    PeerF64 P;
+    for (int q = 0; q < kMaxWorld; ++q)
+        P.p[q] = (q < c->world && c->fab.heap[q]) ? (const double*)(c->fab.heap[q] + off) : nullptr;
+    return P;
+}
+static PeerI32 peer_i32(const apop_ctx* c, size_t off) {
+    PeerI32 P;
+    for (int q = 0; q < kMaxWorld; ++q)
+        P.p[q] = (q < c->world && c->fab.heap[q]) ? (int32_t*)(c->fab.heap[q] + off) : nullptr;
+    return P;
+}
+
+// ---- one sweep, split in phases so that an in-process group of ranks can be
+//      driven in lock step from one host thread (begin / step t / end)
+// phase A: allocations and host->device staging.  Everything that may block the
+// host (cudaMalloc, pinned allocations, arena wrap-around) happens here, for ALL
+// ranks of an in-process group, before any kernel that waits on a peer is
+// enqueued — a blocking call issued while a peer's kernel spins would stall it
+// until the spin times out.
+static int sweep_stage(apop_ctx* c, const double* y, int T, const double* retained,
+                       const apop_sweep_opts* o) {
     SweepState* s = c->sweep;
-    const int64_t n = c->n;
-    const int nt = (int)((n + TILE - 1) / TILE);
     APOP_TRY(ensure_resample_ws(c));
-    ResampleWS& ws = c->ws;
     const bool csmc = o->csmc && retained;
     void* staged = nullptr;
     APOP_TRY(param_upload(c, y, sizeof(double) * (size_t)T, &staged));
@@ -429,6 +497,16 @@ static int run_scalar_sweep(apop_ctx* c, const apop_ssm* model, const double* y,
         APOP_CUDA(c, cudaMemcpyAsync(s->retained, staged, sizeof(double) * (size_t)(T + 1),
                                      cudaMemcpyDeviceToDevice, c->stream));
     }
+    return APOP_OK;
+}
+
+// phase B: first kernels of the sweep
+template <int KIND>
+static int sweep_begin(apop_ctx* c, const double* retained, const apop_sweep_opts* o) {
+    SweepState* s = c->sweep;
+    const int64_t n = c->n;
+    ResampleWS& ws = c->ws;
+    const bool csmc = o->csmc && retained;
     {
         Timer& tm = c->timers[KT_SWEEP];
         if (!tm.open && cudaEventCreate(&tm.a) == cudaSuccess) {
@@ -437,83 +515,91 @@ static int run_scalar_sweep(apop_ctx* c, const apop_ssm* model, const double* y,
         }
     }
     k_sweep_reset<<<1, 1, 0, c->stream>>>(s->sd, ws.info);
-    double* x_prev = s->history ? s->x_hist : s->xa;
+    // sharded: peers may still be reading this rank's buffers (final gather of
+    // the previous sweep)
+    APOP_TRY(fabric_barrier_enqueue(c));
+    double* x0 = s->history ? s->x_hist : s->xa;
     {
         const int64_t pairs = (n + 1) / 2;
         k_init<KIND><<<(int)((pairs + TB - 1) / TB), TB, 0, c->stream>>>(
-            s->model, x_prev, n, c->g0, c->seed, csmc ? s->retained : nullptr);
+            s->model, x0, n, c->g0, c->seed, csmc ? s->retained : nullptr);
     }
     c->launches += 2;
-    int32_t* anc_prev = s->anc;
-    for (int t = 1; t <= T; ++t) {
-        double* x_new = s->history ? s->x_hist + (size_t)t * n : ((t & 1) ? s->xb : s->xa);
-        int32_t* anc_new = s->history ? s->anc_hist + (size_t)(t - 1) * n : s->anc;
-        kt_begin(c, KT_PROPAGATE);
-        k_propagate<KIND><<<nt, TB, 0, c->stream>>>(
-            s->model, x_prev, anc_prev, t == 1, x_new, s->lw, s->y + (t - 1),
-            csmc ? s->retained + t : nullptr, s->sd, n, c->g0, c->seed, (uint32_t)t, ws.tmax,
-            ws.tsum, &ws.info->err);
-        kt_end(c, KT_PROPAGATE);
-        c->launches += 1;
-        const bool cond = csmc && t <= o->n_cond_steps;
-        c->step = (uint32_t)t;
-        ResampleArgs a{};
-        a.lw = s->lw; a.w = nullptr; a.n = n; a.n_new = cond ? n - 1 : n;
-        a.u = NAN; a.order = APOP_ORDER_SORTED;
-        a.anc_out = anc_new; a.out_offset = cond ? 1 : 0; a.have_partials = true;
-        a.xfilt = o->want_filt ? x_new : nullptr;
-        a.rel_eps = 2e-5;            // fp32 tile partials of k_propagate
-        a.step.sd = s->sd; a.step.log_mean_w = s->log_mean_w; a.step.ess = s->ess;
-        a.step.filt = s->filt; a.step.anc = anc_new; a.step.t = t;
-        a.step.reset = o->reset_weights; a.step.cond = cond ? 1 : 0;
-        a.step.has_x = o->want_filt ? 1 : 0;
-        APOP_TRY(resample_enqueue(c, a));
-        x_prev = x_new;
-        anc_prev = anc_new;
-    }
-    s->last_x = x_prev;
-    s->last_anc = anc_prev;
-    APOP_CUDA(c, cudaGetLastError());
+    s->last_x = x0;
+    s->last_anc = s->anc;
     return APOP_OK;
 }
 
-} // namespace apop
-
-using namespace apop;
-
-extern "C" {
-
-int apop_smc_sweep(apop_ctx* c, const apop_ssm* model, const double* y, int32_t T,
-                   const double* retained, const apop_sweep_opts* opts,
-                   apop_sweep_result* result) {
-    if (!c) return APOP_ERR_INVALID;
-    if (!model || !y || T < 1 || !opts || !result)
-        return set_err(c, APOP_ERR_INVALID, "smc_sweep: bad arguments");
-    if (c->world > 1) return set_err(c, APOP_ERR_UNSUPPORTED, "sharded sweep: see apop_smc_sweep_sharded");
-    if (opts->csmc && c->n < 2)
-        return set_err(c, APOP_ERR_INVALID, "conditional sweep needs >= 2 particles");
-    cudaSetDevice(c->device);
-    const int dim = (model->kind == APOP_SSM_LGMVN) ? model->dim : 1;
-    APOP_TRY(sweep_prepare(c, T, dim, opts->keep_history != 0));
-    APOP_TRY(upload_model(c, model));
-    switch (model->kind) {
-    case APOP_SSM_LGSSM1D:
-        APOP_TRY(run_scalar_sweep<APOP_SSM_LGSSM1D>(c, model, y, T, retained, opts)); break;
-    case APOP_SSM_SV:
-        APOP_TRY(run_scalar_sweep<APOP_SSM_SV>(c, model, y, T, retained, opts)); break;
-    case APOP_SSM_HMM:
-        APOP_TRY(run_scalar_sweep<APOP_SSM_HMM>(c, model, y, T, retained, opts)); break;
-    default:
-        return set_err(c, APOP_ERR_UNSUPPORTED, "model kind %d not supported by the fused sweep",
-                       model->kind);
-    }
+template <int KIND>
+static int sweep_step(apop_ctx* c, int t, const apop_sweep_opts* o, bool csmc) {
     SweepState* s = c->sweep;
     const int64_t n = c->n;
+    const int nt = (int)((n + TILE - 1) / TILE);
+    ResampleWS& ws = c->ws;
+    const bool shard = c->world > 1;
+    const double* x_prev = s->last_x;
+    const int32_t* anc_prev = s->last_anc;
+    double* x_new = s->history ? s->x_hist + (size_t)t * n : ((t & 1) ? s->xb : s->xa);
+    int32_t* anc_new = s->history ? s->anc_hist + (size_t)(t - 1) * n : s->anc;
+    kt_begin(c, KT_PROPAGATE);
+    if (shard) {
+        const PeerF64 xpeer = peer_f64(c, (t & 1) ? c->fab.off_xa : c->fab.off_xb);   // x_{t-1}
+        k_propagate<KIND, true><<<nt, TB, 0, c->stream>>>(
+            s->model, x_prev, anc_prev, t == 1, x_new, s->lw, s->y + (t - 1), nullptr, s->sd, n,
+            c->g0, c->seed, (uint32_t)t, ws.tmax, ws.tsum, &ws.info->err, xpeer);
+    } else {
+        PeerF64 none;
+        memset(&none, 0, sizeof none);
+        k_propagate<KIND, false><<<nt, TB, 0, c->stream>>>(
+            s->model, x_prev, anc_prev, t == 1, x_new, s->lw, s->y + (t - 1),
+            csmc ? s->retained + t : nullptr, s->sd, n, c->g0, c->seed, (uint32_t)t, ws.tmax,
+            ws.tsum, &ws.info->err, none);
+    }
+    kt_end(c, KT_PROPAGATE);
+    c->launches += 1;
+    const bool cond = csmc && t <= o->n_cond_steps;
+    c->step = (uint32_t)t;
+    ResampleArgs a{};
+    a.lw = s->lw; a.w = nullptr; a.n = n;
+    a.n_new = shard ? c->n_global : (cond ? n - 1 : n);
+    a.u = NAN; a.order = APOP_ORDER_SORTED;
+    a.anc_out = anc_new; a.out_offset = cond ? 1 : 0; a.have_partials = true;
+    a.xfilt = o->want_filt ? x_new : nullptr;
+    a.rel_eps = 2e-5;            // fp32 tile partials of k_propagate
+    a.step.sd = s->sd; a.step.log_mean_w = s->log_mean_w; a.step.ess = s->ess;
+    a.step.filt = s->filt; a.step.anc = anc_new; a.step.t = t;
+    a.step.reset = o->reset_weights; a.step.cond = cond ? 1 : 0;
+    a.step.has_x = o->want_filt ? 1 : 0;
+    a.sharded = shard;
+    if (shard) a.anc_peer = peer_i32(c, c->fab.off_anc);
+    APOP_TRY(resample_enqueue(c, a));
+    // sharded: offspring indices were stored into peers' arrays and the next
+    // propagate reads parents from peers' x_t: all ranks meet here
+    if (shard) {
+        kt_begin(c, KT_MIGRATE);
+        APOP_TRY(fabric_barrier_enqueue(c));
+        kt_end(c, KT_MIGRATE);
+    }
+    s->last_x = x_new;
+    s->last_anc = anc_new;
+    return APOP_OK;
+}
+
+static int sweep_end(apop_ctx* c, int T, const apop_sweep_opts* opts, apop_sweep_result* result) {
+    SweepState* s = c->sweep;
+    const int64_t n = c->n;
+    const int dim = s->dim;
+    APOP_CUDA(c, cudaGetLastError());
     if (opts->want_final || result->x_final) {
         int blocks = (int)((n * dim + 255) / 256);
         if (blocks > 148 * 32) blocks = 148 * 32;
         kt_begin(c, KT_GATHER);
-        k_gather_rows<<<blocks, 256, 0, c->stream>>>(s->last_x, s->x_final, s->last_anc, n, dim);
+        if (c->world > 1) {
+            const PeerF64 src = peer_f64(c, (T & 1) ? c->fab.off_xb : c->fab.off_xa);    // x_T
+            k_gather_shard<<<blocks, 256, 0, c->stream>>>(src, s->x_final, s->last_anc, n);
+        } else {
+            k_gather_rows<<<blocks, 256, 0, c->stream>>>(s->last_x, s->x_final, s->last_anc, n, dim);
+        }
         kt_end(c, KT_GATHER);
         c->launches += 1;
     }
@@ -527,7 +613,14 @@ int apop_smc_sweep(apop_ctx* c, const apop_ssm* model, const double* y, int32_t 
             tm.open = false;
         }
     }
-    // results: one small D2H per requested array, then a single sync
+    return APOP_OK;
+}
+
+// results: one small D2H per requested array, then a single sync
+static int sweep_fetch(apop_ctx* c, int T, const apop_sweep_opts* opts, apop_sweep_result* result) {
+    SweepState* s = c->sweep;
+    const int64_t n = c->n;
+    const int dim = s->dim;
     SweepDev hsd;
     APOP_CUDA(c, cudaMemcpyAsync(&hsd, s->sd, sizeof hsd, cudaMemcpyDeviceToHost, c->stream));
     if (result->log_mean_w)
@@ -549,6 +642,120 @@ int apop_smc_sweep(apop_ctx* c, const apop_ssm* model, const double* y, int32_t 
     // :smc keeps the accumulated weight on the particles: final weight == log Z-hat
     result->log_z = opts->reset_weights ? hsd.log_z : hsd.base;
     return APOP_OK;
+}
+
+template <int KIND>
+static int run_group(apop_ctx* const* g, int ng, const double* y, int T, const double* retained,
+                     const apop_sweep_opts* o, apop_sweep_result* results) {
+    for (int i = 0; i < ng; ++i) {
+        cudaSetDevice(g[i]->device);
+        APOP_TRY(sweep_stage(g[i], y, T, retained, o));
+    }
+    for (int i = 0; i < ng; ++i) {
+        if (ng > 1) cudaSetDevice(g[i]->device);
+        APOP_TRY(sweep_begin<KIND>(g[i], retained, o));
+    }
+    const bool csmc = o->csmc && retained;
+    for (int t = 1; t <= T; ++t)
+        for (int i = 0; i < ng; ++i) {
+            if (ng > 1) cudaSetDevice(g[i]->device);
+            APOP_TRY(sweep_step<KIND>(g[i], t, o, csmc));
+        }
+    for (int i = 0; i < ng; ++i) {
+        if (ng > 1) cudaSetDevice(g[i]->device);
+        APOP_TRY(sweep_end(g[i], T, o, &results[i]));
+    }
+    int rc = APOP_OK;
+    for (int i = 0; i < ng; ++i) {
+        if (ng > 1) cudaSetDevice(g[i]->device);
+        const int r = sweep_fetch(g[i], T, o, &results[i]);
+        if (r != APOP_OK && rc == APOP_OK) rc = r;
+    }
+    return rc;
+}
+
+// CUDA loads kernels lazily at their first launch, and that load waits for the
+// device to go idle: with a peer's kernel spinning on a mailbox it would wait
+// for the spin to time out.  Sharded sweeps therefore resolve every kernel they
+// will launch before the first one is enqueued.
+template <typename K>
+static void preload(K kernel) {
+    cudaFuncAttributes a;
+    cudaFuncGetAttributes(&a, kernel);
+}
+void preload_resample_kernels();     // resample.cu
+void preload_comm_kernels();         // comm.cu
+static void preload_sweep_kernels() {
+    preload(k_init<APOP_SSM_LGSSM1D>); preload(k_init<APOP_SSM_SV>); preload(k_init<APOP_SSM_HMM>);
+    preload(k_propagate<APOP_SSM_LGSSM1D, true>); preload(k_propagate<APOP_SSM_SV, true>);
+    preload(k_propagate<APOP_SSM_HMM, true>);
+    preload(k_sweep_reset); preload(k_gather_shard);
+    preload_resample_kernels();
+    preload_comm_kernels();
+    cudaGetLastError();
+}
+
+static int sweep_group(apop_ctx* const* g, int ng, const apop_ssm* model, const double* y, int T,
+                       const double* retained, const apop_sweep_opts* opts,
+                       apop_sweep_result* results) {
+    apop_ctx* c0 = g[0];
+    if (!model || !y || T < 1 || !opts || !results)
+        return set_err(c0, APOP_ERR_INVALID, "smc_sweep: bad arguments");
+    const int dim = (model->kind == APOP_SSM_LGMVN) ? model->dim : 1;
+    for (int i = 0; i < ng; ++i) {
+        apop_ctx* c = g[i];
+        if (opts->csmc && c->n < 2)
+            return set_err(c, APOP_ERR_INVALID, "conditional sweep needs >= 2 particles");
+        if (c->world > 1 && (opts->csmc || opts->keep_history || opts->want_filt))
+            return set_err(c, APOP_ERR_UNSUPPORTED,
+                           "sharded sweep: conditional sweeps / lineages / filtering means run "
+                           "one population per GPU (IPMCMC nodes), not sharded");
+        if (c->world > 1 && (c->n % 8) != 0)
+            return set_err(c, APOP_ERR_INVALID, "sharded sweep: particles per rank must be a "
+                                                "multiple of 8");
+        cudaSetDevice(c->device);
+        if (c->world > 1) preload_sweep_kernels();
+        APOP_TRY(sweep_prepare(c, T, dim, opts->keep_history != 0));
+        APOP_TRY(upload_model(c, model));
+    }
+    switch (model->kind) {
+    case APOP_SSM_LGSSM1D:
+        return run_group<APOP_SSM_LGSSM1D>(g, ng, y, T, retained, opts, results);
+    case APOP_SSM_SV:
+        return run_group<APOP_SSM_SV>(g, ng, y, T, retained, opts, results);
+    case APOP_SSM_HMM:
+        return run_group<APOP_SSM_HMM>(g, ng, y, T, retained, opts, results);
+    default:
+        return set_err(c0, APOP_ERR_UNSUPPORTED, "model kind %d not supported by the fused sweep",
+                       model->kind);
+    }
+}
+
+} // namespace apop
+
+using namespace apop;
+
+extern "C" {
+
+int apop_smc_sweep(apop_ctx* c, const apop_ssm* model, const double* y, int32_t T,
+                   const double* retained, const apop_sweep_opts* opts,
+                   apop_sweep_result* result) {
+    if (!c) return APOP_ERR_INVALID;
+    if (c->world > 1 && c->fab.in_process)
+        return set_err(c, APOP_ERR_INVALID, "in-process group: call apop_smc_sweep_group");
+    apop_ctx* g[1] = {c};
+    return sweep_group(g, 1, model, y, T, retained, opts, result);
+}
+
+int apop_smc_sweep_group(apop_ctx* const* ctxs, int32_t n_ctx, const apop_ssm* model,
+                         const double* y, int32_t T, const apop_sweep_opts* opts,
+                         apop_sweep_result* results) {
+    if (!ctxs || n_ctx < 1 || n_ctx > kMaxWorld || !ctxs[0]) return APOP_ERR_INVALID;
+    for (int i = 0; i < n_ctx; ++i)
+        if (!ctxs[i] || ctxs[i]->world != n_ctx || ctxs[i]->rank != i || !ctxs[i]->fab.in_process)
+            return set_err(ctxs[0], APOP_ERR_INVALID,
+                           "sweep_group: pass all ranks of one apop_link_group, in rank order");
+    return sweep_group(ctxs, n_ctx, model, y, T, nullptr, opts, results);
 }
 
 int apop_trace_lineage(apop_ctx* c, int64_t slot, double* out_traj) {

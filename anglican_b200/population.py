@@ -329,3 +329,66 @@ class SweepOutput:
             out[:, t, :] = x[t][k]
         out[:, 0, :] = x[0][k]
         return out
+
+
+class PopulationGroup:
+    """`world` shards of ONE population inside this process.
+
+    `devices[r]` is the GPU of rank r (all ranks may share one device: the
+    shards then exchange through the same peer-memory protocol, which is how the
+    sharded path is exercised on a single-GPU box).  One process per GPU needs
+    no group: every rank builds `Population(n_local, rank=r, world=R,
+    nccl_id=...)` and calls `sweep` collectively."""
+
+    def __init__(self, n_local, world, seed=0xA11CE, devices=None):
+        devices = list(devices) if devices is not None else [0] * world
+        assert len(devices) == world and world >= 2
+        self.lib = L.load()
+        self.world, self.n_local, self.n = world, int(n_local), int(n_local) * world
+        self.ranks = [Population(n_local, seed=seed, device=devices[r], rank=r, world=world)
+                      for r in range(world)]
+        self._arr = (C.c_void_p * world)(*[p.ctx for p in self.ranks])
+        rc = self.lib.apop_link_group(self._arr, world)
+        if rc != L.APOP_OK:
+            L.check(self.ranks[0].ctx, rc)
+
+    def close(self):
+        for p in self.ranks:
+            p.close()
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    def set_seed(self, seed):
+        for p in self.ranks:
+            p.set_seed(seed)
+
+    def sweep(self, model, y, want_final=True, want_stats=True):
+        y = np.ascontiguousarray(y, dtype=np.float64)
+        T = y.size
+        opts = L.ApopSweepOpts(0, 0, 0, 0, 0, int(want_final), 0, 0)
+        res = (L.ApopSweepResult * self.world)()
+        outs = []
+        for r, p in enumerate(self.ranks):
+            out = SweepOutput(p, T, 1)
+            if want_stats:
+                out.log_mean_w, out.ess = np.empty(T), np.empty(T)
+                res[r].log_mean_w, res[r].ess = _dp(out.log_mean_w), _dp(out.ess)
+            if want_final:
+                out.x_final = np.empty(self.n_local)
+                res[r].x_final = _dp(out.x_final)
+            outs.append(out)
+        rc = self.lib.apop_smc_sweep_group(self._arr, self.world, C.byref(model.c), _dp(y), T,
+                                           C.byref(opts), res)
+        if rc != L.APOP_OK:
+            for p in self.ranks:
+                msg = self.lib.apop_last_error(p.ctx)
+                if msg:
+                    raise L.ApopError(rc, msg.decode())
+            raise L.ApopError(rc, "")
+        for r, out in enumerate(outs):
+            out.log_z = res[r].log_z
+        return outs

@@ -171,15 +171,8 @@ def run_ours(args):
     nccl_id = None
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
-        from anglican_b200 import _lib as L
-        import ctypes as C
-        buf = torch.zeros(128, dtype=torch.uint8, device="cuda")
-        if rank == 0:
-            raw = C.create_string_buffer(128)
-            assert L.load().apop_get_unique_id(raw) == 0
-            buf.copy_(torch.frombuffer(bytearray(raw.raw), dtype=torch.uint8))
-        dist.broadcast(buf, 0)
-        nccl_id = bytes(buf.cpu().numpy().tobytes())
+        from anglican_b200.distributed import nccl_unique_id
+        nccl_id = nccl_unique_id(rank)
 
     def barrier():
         torch.cuda.synchronize()

@@ -72,6 +72,11 @@ int apop_device_count(void);
 /* nccl_id: 128-byte ncclUniqueId shared by all ranks, or NULL when world==1 */
 int apop_create(apop_ctx** out, int64_t n_particles_local, uint64_t seed, int device,
                 int rank, int world, const void* nccl_id);
+/* In-process group: create `world` contexts with ranks 0..world-1 and
+ * nccl_id == NULL (same or different devices), then link them; their shards
+ * then form ONE population driven through apop_smc_sweep_group.  (The
+ * one-process-per-GPU form needs no link call: the NCCL id is enough.) */
+int apop_link_group(apop_ctx* const* ctxs, int32_t world);
 int apop_destroy(apop_ctx* ctx);
 const char* apop_last_error(apop_ctx* ctx);
 int apop_get_unique_id(void* out_128_bytes);
@@ -211,6 +216,15 @@ typedef struct {
 int apop_smc_sweep(apop_ctx* ctx, const apop_ssm* model, const double* y, int32_t T,
                    const double* retained, const apop_sweep_opts* opts,
                    apop_sweep_result* result);
+/* Sharded population: N = world * n_local particles in
+ * contiguous shards, global id = rank * n_local + local.  One process per GPU:
+ * every rank calls apop_smc_sweep with identical arguments (collective).
+ * In-process group: one call drives all ranks in lock step; results[i] belongs
+ * to ctxs[i] (x_final = that rank's shard of the final particles).  Results
+ * are bit-identical to an unsharded population of N particles. */
+int apop_smc_sweep_group(apop_ctx* const* ctxs, int32_t n_ctx, const apop_ssm* model,
+                         const double* y, int32_t T, const apop_sweep_opts* opts,
+                         apop_sweep_result* results);
 /* lineage (x_0..x_T) of final slot `slot` of the last keep_history sweep */
 int apop_trace_lineage(apop_ctx* ctx, int64_t slot, double* out_traj);
 /* whole ancestry of the last keep_history sweep, for host-side result
