@@ -99,6 +99,8 @@ _SIGS = [
     ("apop_observe_mvn", C.c_int, [_vp, c_double_p, C.c_int32, c_double_p, C.c_int, c_double_p,
                                    C.c_int32, C.c_int32]),
     ("apop_selftest_math", C.c_int, [_vp, C.c_int, C.c_int32, C.c_int32]),
+    ("apop_debug_resolve_phases", C.c_int, [_vp, c_double_p]),
+    ("apop_debug_chain_trace", C.c_int, [_vp, c_double_p]),
     ("apop_normalize", C.c_int, [_vp, C.c_int32, c_double_p, c_double_p, c_double_p]),
     ("apop_resample", C.c_int, [_vp, C.c_int32, C.c_int, C.c_double, C.c_int64, C.c_int, C.c_int32,
                                 c_double_p, c_int64_p]),

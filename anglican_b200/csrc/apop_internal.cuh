@@ -102,13 +102,37 @@ struct FabricHost {
     std::vector<apop_ctx*> group;          // in-process group, rank order
 };
 
+constexpr int SEGB = 512;        // tiles per block of the segmented tile scan (k_seg_scan)
+constexpr int HCAP = 128;        // hard tiles per lap with precomputed prefix / suffix tables
+
+// Device workspace of the resampling pipeline (one slab).  Arrays indexed [lap]:
+// lap 0 = first pass over the wheel, lap 1 = after the wrap (smc.cljc:133-136).
 struct ResampleWS {
-    int64_t nt = 0;
+    void* slab = nullptr;
+    int64_t nt = 0;              // tiles
+    int nb = 0;                  // blocks of SEGB tiles
     double *tmax = nullptr, *tsum = nullptr, *tsum2 = nullptr, *ain = nullptr;  // tsum2: sum w x
-    int *cls0 = nullptr, *cls1 = nullptr;
     double *tacc = nullptr, *tacc2 = nullptr;   // accurate per-tile sum w, sum w^2
-    Xd *agg0 = nullptr, *agg1 = nullptr;
-    double *sin0 = nullptr, *sin1 = nullptr;
+    int* cls[2] = {};            // class of every tile: binade context, kCtxHard or kCtxSkip
+    Xd* agg[2] = {};             // easy tile: transducer of the whole tile in its context
+    Xd* ex[2] = {};              // easy tile: composite of the tiles since the last hard tile /
+                                 //   block start (exclusive)
+    int* hix[2] = {};            // hard tile: its index in hl, else -1
+    int* hp[2] = {};             // easy tile: index of the last hard tile before it in its block, or -1
+    int* hl[2] = {};             // sorted list of hard tiles
+    int* hctx[2] = {};           // per hard tile: context eA of its tables, or kCtxHard (general fold)
+    Xd* bc[2] = {};              // per block: composite from the last hard tile (or block start) to
+                                 //   the block end
+    double* sblk[2] = {};        // exact running sum entering each block
+    double* shin[2] = {};        // exact running sum entering / leaving each hard tile
+    double* shout[2] = {};
+    Xd* hpa[2] = {};             // [HCAP][TILE] per-element inclusive prefix transducers, context eA
+    Xd* hsb[2] = {};             // [HCAP][TILE] per-element suffix transducers, context eA + 1
+    double* hw[2] = {};          // [HCAP][TILE] weights of the hard tiles
+    double *bacc = nullptr, *bacc2 = nullptr, *baccx = nullptr;   // per block: sums of tacc, tacc2, tsum2
+    double* send = nullptr;      // [2] exact running sum at the end of each lap (this rank)
+    double* trace = nullptr;     // [2][256] chain diagnostics: ns per hard-tile event (lap 0 / 1)
+    int hcap = 0;                // table slots allocated per lap (min(HCAP, nt))
     Comb* comb = nullptr;
     ResampleInfo* info = nullptr;      // device
     ResampleInfo* info_host = nullptr; // pinned

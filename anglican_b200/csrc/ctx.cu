@@ -188,10 +188,8 @@ int apop_destroy(apop_ctx* c) {
     for (auto& col : c->cols)
         if (col.used && col.ptr) cudaFree(col.ptr);
     ResampleWS& w = c->ws;
-    void* ptrs[] = {w.tmax, w.tsum, w.tsum2, w.ain, w.cls0, w.cls1, w.tacc, w.tacc2, w.agg0,
-                    w.agg1, w.sin0, w.sin1, w.comb, w.info, w.edges};
-    for (void* p : ptrs)
-        if (p) cudaFree(p);
+    if (w.slab) cudaFree(w.slab);
+    if (w.edges) cudaFree(w.edges);
     if (w.info_host) cudaFreeHost(w.info_host);
     if (c->scratch) cudaFree(c->scratch);
     for (auto& t : c->timers) {
@@ -469,6 +467,25 @@ int apop_resample_multinomial_u(apop_ctx* c, apop_col weights, apop_col uniforms
     ResampleInfo I;
     APOP_TRY(resample_fetch_info(c, &I));
     return info_to_status(c, I);
+}
+
+int apop_debug_chain_trace(apop_ctx* c, double* out512) {
+    CHECK_CTX(c);
+    if (!out512 || !c->ws.trace) return APOP_ERR_INVALID;
+    APOP_CUDA(c, cudaMemcpyAsync(out512, c->ws.trace, 512 * sizeof(double), cudaMemcpyDeviceToHost,
+                                 c->stream));
+    APOP_CUDA(c, cudaStreamSynchronize(c->stream));
+    return APOP_OK;
+}
+
+int apop_debug_resolve_phases(apop_ctx* c, double* out8) {
+    CHECK_CTX(c);
+    if (!out8 || !c->ws.info) return APOP_ERR_INVALID;
+    ResampleInfo I;
+    APOP_TRY(resample_fetch_info(c, &I));
+    for (int i = 0; i < 4; ++i) out8[i] = I.wx_sum[i];
+    out8[4] = I.nh0; out8[5] = I.nh1; out8[6] = I.first_skip1; out8[7] = I.asq;
+    return APOP_OK;
 }
 
 int apop_gather(apop_ctx* c, apop_col anc, int64_t n_new, const apop_col* cols, int ncols) {

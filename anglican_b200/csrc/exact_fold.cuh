@@ -300,15 +300,26 @@ static constexpr int kCtxSkip = -100001;
 
 // rel_eps: extra relative slack when the approximation itself is only accurate
 // to rel_eps (fp32 tile partials of the fused propagate kernel).
-APOP_HD int classify_tile(double a_in, double a_out, i64 idx_out, double rel_eps = 0.0) {
+// e_lo / e_hi (optional): contexts of the lower / upper bound of the running
+// sum over the tile, or kCtxHard when they are unusable.  A hard tile with
+// e_hi == e_lo + 1 crosses (at most) one binade boundary: its fold can be
+// resolved from precomputed prefix tables in e_lo and suffix tables in e_hi.
+APOP_HD int classify_tile2(double a_in, double a_out, i64 idx_out, double rel_eps, int* e_lo_out,
+                           int* e_hi_out) {
+    *e_lo_out = kCtxHard; *e_hi_out = kCtxHard;
     if (!(a_in > 0.0) || !(a_out < 1.0e300)) return kCtxHard;
     double eps = ((double)idx_out + 4096.0) * 4.44089209850062616e-16 + rel_eps; // 2^-51
     double lo = a_in * (1.0 - eps);
     double hi = a_out * (1.0 + eps);
     int e_lo = ctx_of(lo);
     if (e_lo == kCtxSubnormal) return kCtxHard;
+    *e_lo_out = e_lo; *e_hi_out = ctx_of(hi);
     if (ctx_of(hi) != e_lo) return kCtxHard;
     return e_lo;
+}
+APOP_HD int classify_tile(double a_in, double a_out, i64 idx_out, double rel_eps = 0.0) {
+    int a, b;
+    return classify_tile2(a_in, a_out, idx_out, rel_eps, &a, &b);
 }
 
 } // namespace apop

@@ -29,25 +29,8 @@
 
 namespace apop {
 
-struct WSView {
-    int64_t nt;
-    double *tmax, *tsum, *tsum2, *ain;
-    int *cls0, *cls1;
-    double *tacc, *tacc2;
-    Xd *agg0, *agg1;
-    double *sin0, *sin1;
-    Comb* comb;
-    ResampleInfo* info;
-};
-
-static WSView view_of(const ResampleWS& w) {
-    WSView v;
-    v.nt = w.nt; v.tmax = w.tmax; v.tsum = w.tsum; v.tsum2 = w.tsum2; v.ain = w.ain;
-    v.cls0 = w.cls0; v.cls1 = w.cls1; v.tacc = w.tacc; v.tacc2 = w.tacc2;
-    v.agg0 = w.agg0; v.agg1 = w.agg1; v.sin0 = w.sin0; v.sin1 = w.sin1;
-    v.comb = w.comb; v.info = w.info;
-    return v;
-}
+using WSView = ResampleWS;      // passed to kernels by value (device pointers only)
+static WSView view_of(const ResampleWS& w) { return w; }
 
 struct FoldSmem {
     Xd warp_tot[NWARP];
@@ -57,6 +40,12 @@ struct FoldSmem {
     int imin;
     double last_edge[TB];
 };
+
+__device__ __forceinline__ long long gtimer_ns() {
+    long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
 
 // ------------------------------------------------------------------ helpers
 __device__ __forceinline__ Xd cta_excl_scan_xd(Xd t, Xd* warp_tot) {
@@ -87,6 +76,36 @@ __device__ __forceinline__ Xd cta_total_xd(const Xd* warp_tot) {
     return tot;
 }
 
+__device__ __forceinline__ i64 shfl_down_i64(i64 v, int d) {
+    int lo = __shfl_down_sync(0xffffffffu, (int)(v & 0xffffffffLL), d);
+    int hi = __shfl_down_sync(0xffffffffu, (int)(v >> 32), d);
+    return ((i64)hi << 32) | (u64)(unsigned)lo;
+}
+
+// exclusive SUFFIX scan over the CTA: returns the composite of the transducers of
+// all later threads (thread order), identity for the last thread
+__device__ __forceinline__ Xd cta_excl_suffix_scan_xd(Xd t, Xd* warp_tot) {
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    Xd inc = t;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        Xd o;
+        o.a0 = shfl_down_i64(inc.a0, d);
+        o.a1 = shfl_down_i64(inc.a1, d);
+        if (lane + d < 32) inc = xd_compose(inc, o);
+    }
+    Xd ex;
+    ex.a0 = shfl_down_i64(inc.a0, 1);
+    ex.a1 = shfl_down_i64(inc.a1, 1);
+    if (lane == 31) ex = xd_identity();
+    __syncthreads();
+    if (lane == 0) warp_tot[wid] = inc;
+    __syncthreads();
+    Xd post = xd_identity();
+    for (int i = NWARP - 1; i > wid; --i) post = xd_compose(warp_tot[i], post);
+    return xd_compose(ex, post);
+}
+
 __device__ __forceinline__ void quantize_ctx(double w, int e, bool fast, double inv_u, i64& f,
                                              int& up, int& tie) {
     if (fast) { up = 0; quantize_fast(w, inv_u, f, tie); }
@@ -97,9 +116,9 @@ __device__ __forceinline__ void quantize_ctx(double w, int e, bool fast, double 
 // from the exact running sum S_in: parity-transducer scan, one iteration per
 // binade crossing inside the tile.  edge[j] = exact inclusive running sum.
 __device__ __noinline__ double cta_tile_fold(double S_in, const double (&w)[IPT], int nvalid,
-                                             double (&edge)[IPT], FoldSmem& sm) {
-    if (nvalid <= 0) return S_in;
-    int pos = 0;
+                                             double (&edge)[IPT], FoldSmem& sm, int pos_start = 0) {
+    if (nvalid <= pos_start) return S_in;
+    int pos = pos_start;
     double S = S_in;
     const int i0 = threadIdx.x * IPT;
     for (;;) {
@@ -401,13 +420,17 @@ __global__ void __launch_bounds__(FB) k_finalize(WSView v, int64_t n, int64_t n_
     const double eps_tot = ((double)(2 * n_global) + 8192.0) * 4.44089209850062616e-16 + rel_eps;
     const double xlast_ub = atot * (u + 1.0) * (1.0 + 4.0 * eps_tot);
 
-    // ---- classification of every tile for both laps
+    // ---- classification of every tile for both laps; each thread owns a
+    //      contiguous range of tiles so that the hard tiles come out sorted
+    const int64_t per = (nt + FB - 1) / FB;
+    const int64_t tb = (int64_t)tid * per;
+    const int64_t te = (tb + per < nt) ? tb + per : nt;
     int nh0 = 0, nh1 = 0;
-    for (int64_t t = tid; t < nt; t += FB) {
+    for (int64_t t = tb; t < te; ++t) {
         const int64_t hi = ((t + 1) * TILE < n) ? (t + 1) * TILE : n;
         const double a_in = v.ain[t], ao = v.ain[t + 1];
         const int c0 = classify_tile(a_in, ao, g0 + hi, rel_eps);
-        v.cls0[t] = c0;
+        v.cls[0][t] = c0;
         nh0 += (c0 == kCtxHard);
         int c1;
         const double eps1 = ((double)(n_global + g0 + hi) + 4096.0) * 4.44089209850062616e-16 + rel_eps;
@@ -417,11 +440,39 @@ __global__ void __launch_bounds__(FB) k_finalize(WSView v, int64_t n, int64_t n_
         } else {
             c1 = classify_tile(atot + a_in, atot + ao, n_global + g0 + hi, rel_eps);
         }
-        v.cls1[t] = c1;
+        v.cls[1][t] = c1;
         nh1 += (c1 == kCtxHard);
     }
-    const double h0 = block_sum_f64((double)nh0, smd);
-    const double h1 = block_sum_f64((double)nh1, smd);
+    __syncthreads();
+    // sorted hard lists: exclusive scan of the per-thread counts (small integers: exact)
+    double h0tot, h1tot;
+    int o0 = (int)block_excl_scan_f64((double)nh0, smd, h0tot);
+    int o1 = (int)block_excl_scan_f64((double)nh1, smd, h1tot);
+    const int skip1 = sh_skip;
+    for (int64_t t = tb; t < te; ++t) {
+        const int64_t hi = ((t + 1) * TILE < n) ? (t + 1) * TILE : n;
+        const double a_in = v.ain[t], ao = v.ain[t + 1];
+        int ea, eb;
+        const int c0 = v.cls[0][t];
+        int hx0 = -1, hx1 = -1;
+        if (c0 == kCtxHard) {
+            classify_tile2(a_in, ao, g0 + hi, rel_eps, &ea, &eb);
+            hx0 = o0++;
+            v.hl[0][hx0] = (int)t;
+            v.hctx[0][hx0] = (ea != kCtxHard && eb == ea + 1 && ea > -1000 && ea < 900) ? ea : kCtxHard;
+        }
+        const int c1 = v.cls[1][t];
+        if (c1 == kCtxHard) {
+            classify_tile2(atot + a_in, atot + ao, n_global + g0 + hi, rel_eps, &ea, &eb);
+            hx1 = o1++;
+            v.hl[1][hx1] = (int)t;
+            // tiles at or beyond the first skipped tile are never folded in lap 1
+            v.hctx[1][hx1] = (t < skip1 && ea != kCtxHard && eb == ea + 1 && ea > -1000 && ea < 900)
+                                 ? ea : kCtxHard;
+        }
+        v.hix[0][t] = hx0;
+        v.hix[1][t] = hx1;
+    }
     if (tid == 0) {
         ResampleInfo* I = v.info;
         I->m = m;
@@ -432,15 +483,69 @@ __global__ void __launch_bounds__(FB) k_finalize(WSView v, int64_t n, int64_t n_
                                                                : -INFINITY;
         I->u = u;
         I->n_new = n_new;
-        I->nh0 = (int)h0;
-        I->nh1 = (int)h1;
-        I->first_skip1 = sh_skip;
+        I->nh0 = (int)h0tot;
+        I->nh1 = (int)h1tot;
+        I->first_skip1 = skip1;
         I->weights_mode = weights_mode;
         if (!weights_mode && m != m) I->err |= EB_NAN;
     }
 }
 
 // ------------------------------------------------------------------ K3a
+// Tables of one hard tile whose fold crosses (at most) the boundary between the
+// binades eA and eA + 1: per-element inclusive prefix transducers in eA, suffix
+// transducers in eA + 1, and the weights.  With them the chain kernel resolves
+// the tile for ANY exact running sum entering it in O(1) serial steps: find the
+// crossing element in the prefix table, do the crossing add in hardware fp64
+// (smc.cljc:120), finish with one suffix transducer.
+__device__ __noinline__ void hard_tile_tables(const double (&w)[IPT], int eA, Xd* __restrict__ pa,
+                                              Xd* __restrict__ sb, double* __restrict__ hw,
+                                              Xd* warp_tot) {
+    const int i0 = threadIdx.x * IPT;
+    Xd lp[IPT];
+    Xd run = xd_identity();
+#pragma unroll
+    for (int j = 0; j < IPT; ++j) {
+        i64 f; int up, tie;
+        quantize(w[j], eA, f, up, tie);
+        xd_push(run, f, up, tie);
+        lp[j] = run;
+    }
+    const Xd exl = cta_excl_scan_xd(run, warp_tot);
+#pragma unroll
+    for (int j = 0; j < IPT; ++j) pa[i0 + j] = xd_compose(exl, lp[j]);
+    __syncthreads();
+    Xd suf = xd_identity();
+#pragma unroll
+    for (int j = IPT - 1; j >= 0; --j) {
+        i64 f; int up, tie;
+        quantize(w[j], eA + 1, f, up, tie);
+        Xd one = xd_identity();
+        xd_push(one, f, up, tie);
+        suf = xd_compose(one, suf);
+        lp[j] = suf;
+    }
+    const Xd post = cta_excl_suffix_scan_xd(suf, warp_tot);
+#pragma unroll
+    for (int j = 0; j < IPT; ++j) {
+        sb[i0 + j] = xd_compose(lp[j], post);
+        hw[i0 + j] = w[j];
+    }
+    __syncthreads();
+}
+
+// rare path of k_fold_agg, kept out of line (and loading the weights itself) so
+// that it costs the streaming path neither registers nor stack
+__device__ __noinline__ void hard_tile_prework(const double* __restrict__ lw,
+                                               const double* __restrict__ win, int64_t n,
+                                               double m, int t, int eA, Xd* __restrict__ pa,
+                                               Xd* __restrict__ sb, double* __restrict__ hw,
+                                               Xd* warp_tot) {
+    double w[IPT];
+    load_weights(lw, win, (int64_t)t * TILE, n, m, w);
+    hard_tile_tables(w, eA, pa, sb, hw, warp_tot);
+}
+
 __global__ void __launch_bounds__(TB, 3) k_fold_agg(const double* __restrict__ lw,
                                                     const double* __restrict__ win, int64_t n,
                                                     WSView v, const double* __restrict__ xf) {
@@ -449,9 +554,22 @@ __global__ void __launch_bounds__(TB, 3) k_fold_agg(const double* __restrict__ l
     __shared__ double wa[NWARP], wb[NWARP];
     const int t = blockIdx.x;
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-    const int c0 = v.cls0[t], c1 = v.cls1[t];
+    const int c0 = v.cls[0][t], c1 = v.cls[1][t];
     const bool do0 = (c0 != kCtxHard), do1 = (c1 != kCtxHard && c1 != kCtxSkip);
     const int64_t base = (int64_t)t * TILE;
+    if (c0 == kCtxHard || c1 == kCtxHard) {          // rare, uniform per CTA
+#pragma unroll 1
+        for (int lap = 0; lap < 2; ++lap) {
+            if ((lap ? c1 : c0) != kCtxHard) continue;
+            const int h = v.hix[lap][t];
+            if (h < 0 || h >= v.hcap) continue;
+            const int eA = v.hctx[lap][h];
+            if (eA == kCtxHard) continue;
+            hard_tile_prework(lw, win, n, v.info->m, t, eA, v.hpa[lap] + (size_t)h * TILE,
+                              v.hsb[lap] + (size_t)h * TILE, v.hw[lap] + (size_t)h * TILE,
+                              warp_tot);
+        }
+    }
     double w[IPT];
     load_weights(lw, win, base, n, v.info->m, w);
     // accurate sum w, sum w^2 of the tile (ESS, log-mean-weight)
@@ -512,8 +630,8 @@ __global__ void __launch_bounds__(TB, 3) k_fold_agg(const double* __restrict__ l
         if (!any_bad) {
             Xd x0; x0.a0 = t0; x0.a1 = t0;
             Xd x1; x1.a0 = t1; x1.a1 = t1;
-            if (do0) v.agg0[t] = x0;
-            if (do1) v.agg1[t] = x1;
+            if (do0) v.agg[0][t] = x0;
+            if (do1) v.agg[1][t] = x1;
         }
     }
     if (!any_bad) return;
@@ -527,103 +645,344 @@ __global__ void __launch_bounds__(TB, 3) k_fold_agg(const double* __restrict__ l
     }
     if (do0) {
         (void)cta_excl_scan_xd(a, warp_tot);
-        if (threadIdx.x == 0) v.agg0[t] = cta_total_xd(warp_tot);
+        if (threadIdx.x == 0) v.agg[0][t] = cta_total_xd(warp_tot);
         __syncthreads();
     }
     if (do1) {
         (void)cta_excl_scan_xd(b, warp_tot);
-        if (threadIdx.x == 0) v.agg1[t] = cta_total_xd(warp_tot);
+        if (threadIdx.x == 0) v.agg[1][t] = cta_total_xd(warp_tot);
     }
 }
 
-// ------------------------------------------------------------------ resolve
-constexpr int RI = 8;   // tiles per thread per pass when scanning easy runs
-
-// One lap of the chain over tiles [0, stop): scans the aggregates of easy tiles
-// and folds hard tiles element by element.  sin[t] receives the exact running
-// sum entering tile t.  Stops early once S exceeds `limit` (second lap).
-// Returns the exact sum entering tile *t_end.
-__device__ double resolve_lap(const Xd* __restrict__ agg, const int* __restrict__ cls,
-                              double* __restrict__ sin, double S, int64_t stop, double limit,
-                              int64_t* t_end, const double* __restrict__ lw,
-                              const double* __restrict__ win, int64_t n, double m, FoldSmem& sm,
-                              int* err) {
-    int64_t t = 0;
-    double w[IPT], edge[IPT];
-    while (t < stop && !(S > limit)) {
-        const int64_t cend = (t + (int64_t)TB * RI < stop) ? t + (int64_t)TB * RI : stop;
-        const int e = ctx_of(S);
-        const i64 s_in = units_of(S);
-        Xd a[RI];
-        int hardmin = INT_MAX;
-        unsigned badmask = 0;          // bit k: tile k of this thread is in another binade
-        if (threadIdx.x == 0) sm.imin = INT_MAX;
-#pragma unroll
-        for (int k = 0; k < RI; ++k) {
-            const int64_t tt = t + (int64_t)threadIdx.x * RI + k;
-            a[k] = xd_identity();
-            if (tt < cend) {
-                const int c = cls[tt];
-                if (c == kCtxHard) { if (hardmin == INT_MAX) hardmin = (int)(tt - t); }
-                else if (hardmin == INT_MAX) { a[k] = agg[tt]; badmask |= (unsigned)(c != e) << k; }
-            }
-        }
+// ------------------------------------------------------------------ tile scan
+// Segmented scan of the tile transducers, SEGB tiles per CTA.  Hard tiles cut
+// the segments (their fold depends on the exact running sum entering them), so
+//   ex[t]  = composite of the easy tiles between the last hard tile before t in
+//            this block (or the block start) and t, exclusive;
+//   hp[t]  = index (in hl) of that hard tile, or -1;
+//   bc[b]  = composite from the last hard tile of the block (or its start) to
+//            the block end.
+// None of this depends on the running sum, so it runs at full width; the chain
+// kernel then only touches one value per block and per hard tile.
+__global__ void __launch_bounds__(SEGB) k_seg_scan(WSView v, int has_x) {
+    __shared__ Xd wv[SEGB / 32];
+    __shared__ int wf[SEGB / 32], wh[SEGB / 32];
+    __shared__ double ra[SEGB / 32], rb[SEGB / 32], rx[SEGB / 32];
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    const int64_t t = (int64_t)blockIdx.x * SEGB + threadIdx.x;
+    const int64_t nt = v.nt;
+    {   // per-block sums of the accurate tile sums (ESS, log-mean-weight, filtering mean)
+        double a = (t < nt) ? v.tacc[t] : 0.0, b2 = (t < nt) ? v.tacc2[t] : 0.0;
+        double x = (has_x && t < nt) ? v.tsum2[t] : 0.0;
+        a = warp_sum(a); b2 = warp_sum(b2); x = warp_sum(x);
+        if (lane == 0) { ra[wid] = a; rb[wid] = b2; rx[wid] = x; }
         __syncthreads();
-        if (hardmin != INT_MAX) atomicMin(&sm.imin, hardmin);
-        __syncthreads();
-        const int hm = sm.imin;
-        const int64_t r1 = (hm == INT_MAX) ? cend : t + hm;      // first hard tile (or chunk end)
-        // tiles at or beyond r1 do not take part in this scan
-        Xd loc = xd_identity();
-        int mybad = 0;
-#pragma unroll
-        for (int k = 0; k < RI; ++k) {
-            const int64_t tt = t + (int64_t)threadIdx.x * RI + k;
-            if (tt < r1) { loc = xd_compose(loc, a[k]); mybad |= (badmask >> k) & 1; }
-            else a[k] = xd_identity();
-        }
-        if (r1 > t) {
-            Xd ex = cta_excl_scan_xd(loc, sm.warp_tot);
-            i64 s = xd_apply(s_in, ex);
-#pragma unroll
-            for (int k = 0; k < RI; ++k) {
-                const int64_t tt = t + (int64_t)threadIdx.x * RI + k;
-                if (tt < r1) {
-                    mybad |= (s >= kTwo53);
-                    sin[tt] = from_units(s, e);
-                    s = xd_apply(s, a[k]);
-                }
-            }
-            if (mybad) atomicOr(err, EB_CTX);
-            if (threadIdx.x == 0) {
-                i64 st = xd_apply(s_in, cta_total_xd(sm.warp_tot));
-                if (st >= kTwo53) atomicOr(err, EB_CTX);
-                sm.bcast_S = from_units(st, e);
-            }
-            __syncthreads();
-            S = sm.bcast_S;
-            __syncthreads();
-        }
-        t = r1;
-        if (r1 < cend && !(S > limit)) {        // hard tile r1: fold it element by element
-            if (threadIdx.x == 0) sin[r1] = S;
-            const int64_t base = r1 * TILE;
-            const int nvalid = (int)((n - base < TILE) ? (n - base) : TILE);
-            load_weights(lw, win, base, n, m, w);
-            S = cta_tile_fold(S, w, nvalid, edge, sm);
-            __syncthreads();
-            t = r1 + 1;
+        if (threadIdx.x == 0) {
+            double sa = 0.0, sb = 0.0, sx = 0.0;
+            for (int i = 0; i < SEGB / 32; ++i) { sa += ra[i]; sb += rb[i]; sx += rx[i]; }
+            v.bacc[blockIdx.x] = sa; v.bacc2[blockIdx.x] = sb; v.baccx[blockIdx.x] = sx;
         }
     }
-    *t_end = t;
+#pragma unroll 1
+    for (int lap = 0; lap < 2; ++lap) {
+        int64_t stop = nt;
+        if (lap == 1 && v.info->first_skip1 < stop) stop = v.info->first_skip1;
+        const int c = (t < stop) ? v.cls[lap][t] : kCtxSkip;
+        const bool hard = (c == kCtxHard);
+        const bool act = (c != kCtxHard) && (c != kCtxSkip);
+        Xd val = act ? v.agg[lap][t] : xd_identity();
+        int f = hard ? 1 : 0;
+        int hm = hard ? v.hix[lap][t] : -1;
+        // inclusive segmented scan inside the warp
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            Xd o;
+            o.a0 = shfl_up_i64(val.a0, d);
+            o.a1 = shfl_up_i64(val.a1, d);
+            const int of = __shfl_up_sync(0xffffffffu, f, d);
+            const int oh = __shfl_up_sync(0xffffffffu, hm, d);
+            if (lane >= d) {
+                if (!f) val = xd_compose(o, val);
+                f |= of;
+                hm = max(hm, oh);
+            }
+        }
+        if (lane == 31) { wv[wid] = val; wf[wid] = f; wh[wid] = hm; }
+        __syncthreads();
+        // prefix of the preceding warps
+        Xd pv = xd_identity();
+        int pf = 0, ph = -1;
+        for (int i = 0; i < wid; ++i) {
+            pv = wf[i] ? wv[i] : xd_compose(pv, wv[i]);
+            pf |= wf[i];
+            ph = max(ph, wh[i]);
+        }
+        // inclusive value of this tile, then shift by one for the exclusive result
+        Xd inc = f ? val : xd_compose(pv, val);
+        const int ih = max(ph, hm);
+        Xd exv;
+        exv.a0 = shfl_up_i64(inc.a0, 1);
+        exv.a1 = shfl_up_i64(inc.a1, 1);
+        int exh = __shfl_up_sync(0xffffffffu, ih, 1);
+        if (lane == 0) { exv = pv; exh = ph; }
+        if (t < nt) { v.ex[lap][t] = exv; v.hp[lap][t] = exh; }
+        if (threadIdx.x == SEGB - 1) v.bc[lap][blockIdx.x] = inc;
+        __syncthreads();
+    }
+}
+
+// ------------------------------------------------------------------ chain
+constexpr int CH_BC = 1024;      // blocks of the tile scan staged in shared memory per lap
+
+struct ChainSmem {
+    FoldSmem fold;
+    double bcast;
+    int cross, fallback;
+    i64 last[TB];                // running units after each thread's elements (hard-tile search)
+    double head[1024];           // first weights of a fold that starts at zero
+    Xd bc[CH_BC];                // staged per-block composites / class of the block's last tile
+    int cend[CH_BC];
+    int hl[HCAP];                // staged head of the hard list: tile, ex[tile], class of the
+    Xd hex[HCAP];                //   run before it, table context
+    int hcr[HCAP];
+    int hctx[HCAP];
+};
+
+// S' = S + (transducer of a run of easy tiles); the run must live in the binade of S
+__device__ __forceinline__ double apply_run(double S, const Xd& x, int cls_run, int* err) {
+    if ((x.a0 | x.a1) == 0) return S;
+    const int e = ctx_of(S);
+    const i64 s = xd_apply(units_of(S), x);
+    if (s >= kTwo53 || e != cls_run) atomicOr(err, EB_CTX);
+    return from_units(s, e);
+}
+
+// coarse level of the prefix table of one hard tile: the entry after this
+// thread's IPT elements.  Prefetched while the previous event of the chain is
+// still in flight (the tables do not depend on S).
+struct HardPre {
+    Xd c;
+    int h;                       // hard index the entry belongs to, or -1
+};
+
+__device__ __forceinline__ void hard_prefetch(const WSView& v, int lap, int h, int nh, int eA,
+                                              HardPre& P) {
+    P.h = -1;
+    if (h >= nh || h >= v.hcap || eA == kCtxHard) return;
+    P.c = v.hpa[lap][(size_t)h * TILE + threadIdx.x * IPT + (IPT - 1)];
+    P.h = h;
+}
+
+// exact fold of hard tile t (index h of the lap's hard list) from the exact
+// running sum S entering it.  Uniform over the CTA.  eA: context of the tile's
+// tables (kCtxHard: none).  P holds this thread's coarse entry; on return it
+// holds the entry of hard tile h + 1 (context eA_next).
+__device__ __forceinline__ double chain_hard_tile(const WSView& v, int lap, int h, int nh,
+                                                  int64_t t, double S, int eA, int eA_next,
+                                                  HardPre& P, const double* __restrict__ lw,
+                                                  const double* __restrict__ win, int64_t n,
+                                                  double m, ChainSmem& sm) {
+    const int e = ctx_of(S);
+    bool general = true;
+    if (P.h == h && eA != kCtxHard && (e == eA || e == eA + 1)) {
+        const Xd* pa = v.hpa[lap] + (size_t)h * TILE;
+        const Xd* sb = v.hsb[lap] + (size_t)h * TILE;
+        const double* hw = v.hw[lap] + (size_t)h * TILE;
+        const i64 s_in = units_of(S);
+        if (threadIdx.x == 0) { sm.cross = INT_MAX; sm.fallback = 0; }
+        __syncthreads();
+        if (e == eA + 1) {                         // already in the upper binade: one suffix step
+            hard_prefetch(v, lap, h + 1, nh, eA_next, P);
+            if (threadIdx.x == 0) {
+                const i64 s2 = xd_apply(s_in, sb[0]);
+                if (s2 >= kTwo53) sm.fallback = 1;
+                sm.bcast = from_units(s2, e);
+            }
+        } else {
+            // coarse search: first thread whose elements take the sum across 2^53 units
+            const i64 mine = xd_apply(s_in, P.c);
+            sm.last[threadIdx.x] = mine;
+            if (mine >= kTwo53) atomicMin(&sm.cross, (int)threadIdx.x);
+            hard_prefetch(v, lap, h + 1, nh, eA_next, P);
+            __syncthreads();
+            const int cc = sm.cross;
+            if (cc == INT_MAX) {                   // stays in eA over the whole tile
+                if (threadIdx.x == TB - 1) sm.bcast = from_units(mine, eA);
+            } else if ((int)threadIdx.x == cc) {   // fine search inside the chunk, one thread
+                const int i0 = cc * IPT;
+                Xd f[IPT], sf[IPT];
+                double wj[IPT];
+#pragma unroll
+                for (int j = 0; j < IPT; ++j) {
+                    f[j] = pa[i0 + j];
+                    wj[j] = hw[i0 + j];
+                    sf[j] = (i0 + j + 1 < TILE) ? sb[i0 + j + 1] : xd_identity();
+                }
+                i64 run = cc ? sm.last[cc - 1] : s_in, sprev = 0;
+                double wc = 0.0;
+                Xd sfx = xd_identity();
+                bool found = false;
+#pragma unroll
+                for (int j = 0; j < IPT; ++j) {
+                    const i64 nx = xd_apply(s_in, f[j]);
+                    if (!found && nx >= kTwo53) { found = true; sprev = run; wc = wj[j]; sfx = sf[j]; }
+                    run = nx;
+                }
+                const double Sn = from_units(sprev, eA) + wc;          // the crossing add (smc.cljc:120)
+                double out = Sn;
+                if (!found || ctx_of(Sn) != eA + 1) {
+                    sm.fallback = 1;
+                } else {
+                    const i64 s2 = xd_apply(units_of(Sn), sfx);
+                    if (s2 >= kTwo53) sm.fallback = 1;
+                    out = from_units(s2, eA + 1);
+                }
+                sm.bcast = out;
+            }
+        }
+        __syncthreads();
+        general = sm.fallback != 0;
+        const double r = sm.bcast;
+        __syncthreads();
+        if (!general) return r;
+    }
+    P.h = -1;              // not live across the call below; re-fetched afterwards
+    // general path: parity-transducer fold, one iteration per binade crossing
+    if (threadIdx.x == 0) v.info->asq += 1.0;          // diagnostics: general folds in the chain
+    double w[IPT], edge[IPT];
+    const int64_t base = t * TILE;
+    const int nvalid = (int)((n - base < TILE) ? (n - base) : TILE);
+    load_weights(lw, win, base, n, m, w);
+    // A fold that starts near zero crosses a binade at every doubling of the sum
+    // (elements 1, 2, 4, 8, ...): one thread adds the first elements literally,
+    // the parallel fold takes over from there.
+    constexpr int HEAD = 1024;
+    int pos = 0;
+    if (S == 0.0 && nvalid > HEAD) {
+        if (threadIdx.x < HEAD / IPT) {
+#pragma unroll
+            for (int j = 0; j < IPT; ++j) sm.head[threadIdx.x * IPT + j] = w[j];
+        }
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            double acc = S;
+#pragma unroll 8
+            for (int i = 0; i < HEAD; ++i) acc = acc + sm.head[i];              // smc.cljc:94
+            sm.bcast = acc;
+        }
+        __syncthreads();
+        S = sm.bcast;
+        pos = HEAD;
+        __syncthreads();
+    }
+    const double r = cta_tile_fold(S, w, nvalid, edge, sm.fold, pos);
+    __syncthreads();
+    hard_prefetch(v, lap, h + 1, nh, eA_next, P);
+    return r;
+}
+
+// One lap of the exact chain over this rank's tiles [0, stop): walks the blocks
+// of the tile scan and the hard tiles in order.  Records the exact running sum
+// entering every block (sblk) and entering / leaving every hard tile (shin,
+// shout); the running sum entering any other tile follows from ex[] (tile_sin).
+// Stops once S exceeds `limit` (second lap: no pointer lies beyond xlast);
+// everything not reached is marked +inf.  *reached_stop: the walk got to `stop`.
+__device__ double chain_lap(const WSView& v, int lap, double S, int64_t stop, double limit,
+                            int nh, const double* __restrict__ lw, const double* __restrict__ win,
+                            int64_t n, double m, ChainSmem& sm, int* err, bool* reached_stop) {
+    const int nb = v.nb;
+    const int nb_stop = (int)((stop + SEGB - 1) / SEGB);
+    // ---- stage what the walk reads into shared memory (none of it depends on S)
+    __syncthreads();
+    for (int b = threadIdx.x; b < nb_stop && b < CH_BC; b += TB) {
+        const int64_t be = ((int64_t)(b + 1) * SEGB < stop) ? (int64_t)(b + 1) * SEGB : stop;
+        sm.bc[b] = v.bc[lap][b];
+        sm.cend[b] = v.cls[lap][be - 1];
+    }
+    for (int i = threadIdx.x; i < nh && i < HCAP; i += TB) {
+        const int t = v.hl[lap][i];
+        sm.hl[i] = t;
+        sm.hex[i] = v.ex[lap][t];
+        sm.hcr[i] = (t > 0) ? v.cls[lap][t - 1] : kCtxHard;
+        sm.hctx[i] = (i < v.hcap) ? v.hctx[lap][i] : kCtxHard;
+    }
+    __syncthreads();
+    auto hctx_of = [&](int i) { return (i < nh && i < HCAP) ? sm.hctx[i] : kCtxHard; };
+    HardPre P;
+    hard_prefetch(v, lap, 0, nh, hctx_of(0), P);
+    int h = 0, b = 0;
+    int shin_done = 0;             // hard entries whose shin has been written
+    bool over = false;
+    // the running sum as (integer significand, binade): easy runs are integer adds
+    i64 su = units_of(S);
+    int se = ctx_of(S);
+    int bad = 0;
+    auto apply_units = [&](const Xd& x, int cls_run) {
+        if ((x.a0 | x.a1) == 0) return;
+        su = xd_apply(su, x);
+        bad |= (su >= kTwo53) | (se != cls_run);
+    };
+    for (; b < nb_stop; ++b) {
+        S = from_units(su, se);
+        if (S > limit) { over = true; break; }
+        if (threadIdx.x == 0) v.sblk[lap][b] = S;
+        const int64_t blk_end = ((int64_t)(b + 1) * SEGB < stop) ? (int64_t)(b + 1) * SEGB : stop;
+        while (h < nh) {
+            const int64_t t = (h < HCAP) ? sm.hl[h] : v.hl[lap][h];
+            if (t >= blk_end) break;
+            const Xd x = (h < HCAP) ? sm.hex[h] : v.ex[lap][t];
+            const int crun = (h < HCAP) ? sm.hcr[h] : ((t > 0) ? v.cls[lap][t - 1] : kCtxHard);
+            apply_units(x, crun);
+            const double S_at = from_units(su, se);
+            if (threadIdx.x == 0) v.shin[lap][h] = S_at;
+            shin_done = h + 1;
+            if (S_at > limit) { over = true; break; }
+            S = chain_hard_tile(v, lap, h, nh, t, S_at, hctx_of(h), hctx_of(h + 1), P, lw, win, n,
+                                m, sm);
+            su = units_of(S);
+            se = ctx_of(S);
+            if (threadIdx.x == 0) v.shout[lap][h] = S;
+            ++h;
+        }
+        if (over) { ++b; break; }
+        const Xd xb = (b < CH_BC) ? sm.bc[b] : v.bc[lap][b];
+        const int ce = (b < CH_BC) ? sm.cend[b] : v.cls[lap][blk_end - 1];
+        apply_units(xb, ce);
+    }
+    S = from_units(su, se);
+    if (bad && threadIdx.x == 0) atomicOr(err, EB_CTX);
+    *reached_stop = !over;
+    // everything the walk did not reach
+    for (int i = b + threadIdx.x; i <= nb; i += TB) v.sblk[lap][i] = INFINITY;
+    for (int i = h + threadIdx.x; i < nh; i += TB) {
+        if (i >= shin_done) v.shin[lap][i] = INFINITY;
+        v.shout[lap][i] = INFINITY;
+    }
     return S;
 }
 
-__global__ void __launch_bounds__(TB) k_resolve(const double* __restrict__ lw,
+// exact running sum entering tile t in `lap` (t == nt: at the end of the lap)
+__device__ __forceinline__ double tile_sin(const WSView& v, int lap, int64_t t, int* err) {
+    if (t >= v.nt) return v.send[lap];
+    if (lap == 1 && t >= v.info->first_skip1) return INFINITY;
+    const int c = v.cls[lap][t];
+    if (c == kCtxSkip) return INFINITY;
+    if (c == kCtxHard) return v.shin[lap][v.hix[lap][t]];
+    const int h = v.hp[lap][t];
+    const double base = (h >= 0) ? v.shout[lap][h] : v.sblk[lap][t / SEGB];
+    if (!(base < INFINITY)) return INFINITY;
+    const Xd x = v.ex[lap][t];
+    if ((x.a0 | x.a1) == 0) return base;
+    const i64 s = xd_apply(units_of(base), x);
+    if (s >= kTwo53 || ctx_of(base) != c) { atomicOr(err, EB_CTX); return INFINITY; }
+    return from_units(s, c);
+}
+
+__global__ void __launch_bounds__(TB) k_chain(const double* __restrict__ lw,
                                                 const double* __restrict__ win, int64_t n,
                                                 int64_t n_total, WSView v, StepOut so, Fabric F,
                                                 unsigned long long seq) {
-    __shared__ FoldSmem sm;
+    __shared__ ChainSmem sm;
     __shared__ double smd[33];
     __shared__ double sh_in;
     __shared__ double pa[kMaxWorld], pb[kMaxWorld], px[kMaxWorld];
@@ -635,6 +994,8 @@ __global__ void __launch_bounds__(TB) k_resolve(const double* __restrict__ lw,
     const bool last_rank = F.rank == F.world - 1;
     const int par = (int)(seq & 1);
     if (threadIdx.x == 0) sh_comm = 0;
+    long long tg0 = 0, tg1 = 0, tg2 = 0;
+    if (threadIdx.x == 0) tg0 = gtimer_ns();
 
     // ---------------- lap 0: exact total (smc.cljc:94).  Sharded: the sequential
     // fold runs through the ranks in order; the exact running sum entering this
@@ -649,9 +1010,9 @@ __global__ void __launch_bounds__(TB) k_resolve(const double* __restrict__ lw,
         __syncthreads();
         S0 = sh_in;
     }
-    int64_t tend;
-    const double Send0 = resolve_lap(v.agg0, v.cls0, v.sin0, S0, nt, INFINITY, &tend, lw, win, n,
-                                     m, sm, &I->err);
+    bool reached;
+    const double Send0 = chain_lap(v, 0, S0, nt, INFINITY, I->nh0, lw, win, n, m, sm, &I->err,
+                                   &reached);
     if (sharded && threadIdx.x == 0) {
         if (!last_rank) {
             mail_send(&F.mbox[F.rank + 1]->s0[par], Send0, 0.0, 0.0, seq);
@@ -660,11 +1021,10 @@ __global__ void __launch_bounds__(TB) k_resolve(const double* __restrict__ lw,
                 mail_send(&F.mbox[q]->tot[par], Send0, 0.0, 0.0, seq);
         }
     }
+    if (threadIdx.x == 0) tg1 = gtimer_ns();
     // accurate sum w / sum w^2 (ESS = (sum w)^2 / sum w^2, dist_test.cljc:83-94)
     double la = 0.0, lb = 0.0, lx = 0.0;
-    for (int64_t t = threadIdx.x; t < nt; t += TB) { la += v.tacc[t]; lb += v.tacc2[t]; }
-    if (so.sd && so.has_x)
-        for (int64_t t = threadIdx.x; t < nt; t += TB) lx += v.tsum2[t];
+    for (int b = threadIdx.x; b < v.nb; b += TB) { la += v.bacc[b]; lb += v.bacc2[b]; lx += v.baccx[b]; }
     double acc = block_sum_f64(la, smd);
     double acc2 = block_sum_f64(lb, smd);
     double accx = block_sum_f64(lx, smd);
@@ -689,7 +1049,7 @@ __global__ void __launch_bounds__(TB) k_resolve(const double* __restrict__ lw,
         __syncthreads();
     }
     if (threadIdx.x == 0) {
-        v.sin0[nt] = Send0;
+        v.send[0] = Send0;
         const i64 n_new = I->n_new;
         int err = sh_comm ? EB_COMM : 0;
         if (!(total > 0.0) || !(total < INFINITY)) err |= EB_ZERO;
@@ -721,10 +1081,13 @@ __global__ void __launch_bounds__(TB) k_resolve(const double* __restrict__ lw,
             sd->err |= I->err | err;
             if (so.cond) so.anc[0] = 0;          // retained particle back at position 0
         }
+        tg2 = gtimer_ns();
     }
     __syncthreads();
     if (I->err & (EB_ZERO | EB_COMB | EB_NAN)) {
-        for (int64_t t = threadIdx.x; t <= nt; t += TB) v.sin1[t] = INFINITY;
+        for (int i = threadIdx.x; i <= v.nb; i += TB) v.sblk[1][i] = INFINITY;
+        for (int i = threadIdx.x; i < I->nh1; i += TB) { v.shin[1][i] = INFINITY; v.shout[1][i] = INFINITY; }
+        if (threadIdx.x == 0) v.send[1] = INFINITY;
         // keep the chain moving so that no peer waits for this rank
         if (sharded && !last_rank && threadIdx.x == 0)
             mail_send(&F.mbox[F.rank + 1]->s1[par], INFINITY, 0.0, 0.0, seq);
@@ -748,16 +1111,22 @@ __global__ void __launch_bounds__(TB) k_resolve(const double* __restrict__ lw,
     }
     int64_t stop = I->first_skip1;
     if (stop > nt) stop = nt;
-    const double S = resolve_lap(v.agg1, v.cls1, v.sin1, S1, stop, xlast, &tend, lw, win, n, m,
-                                 sm, &I->err);
+    const double S = chain_lap(v, 1, S1, stop, xlast, I->nh1, lw, win, n, m, sm, &I->err, &reached);
     if (sharded && !last_rank && threadIdx.x == 0)
         mail_send(&F.mbox[F.rank + 1]->s1[par], S, 0.0, 0.0, seq);
-    // tend = first tile that cannot receive a pointer of the second lap
-    if (tend < nt && !(S > xlast) && threadIdx.x == 0) {
+    // the walk may only end at a skipped tile if no pointer of the second lap lies beyond
+    if (reached && stop < nt && !(S > xlast) && threadIdx.x == 0) {
         atomicOr(&I->err, EB_CTX);
         if (so.sd) so.sd->err |= EB_CTX;
     }
-    for (int64_t t = tend + threadIdx.x; t <= nt; t += TB) v.sin1[t] = (t == tend) ? S : INFINITY;
+    if (threadIdx.x == 0) v.send[1] = S;
+    if (threadIdx.x == 0) {          // phase durations in ns (apop_debug_resolve_phases)
+        const long long tg3 = gtimer_ns();
+        I->wx_sum[0] = (double)(tg1 - tg0);      // lap 0 (incl. waiting for the previous rank)
+        I->wx_sum[1] = (double)(tg2 - tg1);      // sums, exchange, comb table
+        I->wx_sum[2] = (double)(tg3 - tg2);      // lap 1
+        I->wx_sum[3] = (double)v.comb->nseg;
+    }
 }
 
 // ------------------------------------------------------------------ K3b/K4
@@ -1066,8 +1435,9 @@ __global__ void __launch_bounds__(TB, 2) k_ancestors(const double* __restrict__ 
     if (I->err) return;
     const int t = blockIdx.x;
     const double x0 = v.comb->x0, xlast = v.comb->xlast;
-    const double si0 = v.sin0[t], so0 = v.sin0[t + 1];
-    const double si1 = v.sin1[t];
+    int* errp = &v.info->err;
+    const double si0 = tile_sin(v, 0, t, errp), so0 = tile_sin(v, 0, (int64_t)t + 1, errp);
+    const double si1 = tile_sin(v, 1, t, errp);
     const bool need0 = (so0 > x0) && !(si0 > xlast);
     const bool need1 = !(si1 > xlast);
     if (!need0 && !need1) return;
@@ -1082,7 +1452,7 @@ __global__ void __launch_bounds__(TB, 2) k_ancestors(const double* __restrict__ 
     for (int lap = 0; lap < 2; ++lap) {
         if (lap == 0 ? !need0 : !need1) continue;
         const double Sin = lap ? si1 : si0;
-        const int cls = lap ? v.cls1[t] : v.cls0[t];
+        const int cls = v.cls[lap][t];
         bool fast = (cls != kCtxHard) && (cls != kCtxSkip) && ctx_fast_ok(cls) &&
                     (ctx_of(Sin) == cls);
         if (fast) {
@@ -1141,7 +1511,7 @@ __global__ void __launch_bounds__(TB) k_edges(const double* __restrict__ lw,
     const int nvalid = (int)((n - base < TILE) ? (n - base) : TILE);
     double w[IPT], edge[IPT];
     load_weights(lw, win, base, n, v.info->m, w);
-    (void)cta_tile_fold(v.sin0[t], w, nvalid, edge, sm);
+    (void)cta_tile_fold(tile_sin(v, 0, t, &v.info->err), w, nvalid, edge, sm);
     const int64_t i0 = base + (int64_t)threadIdx.x * IPT;
 #pragma unroll
     for (int j = 0; j < IPT; ++j)
@@ -1181,7 +1551,8 @@ void preload_resample_kernels() {
     cudaFuncGetAttributes(&a, k_tile_lse);
     cudaFuncGetAttributes(&a, k_finalize);
     cudaFuncGetAttributes(&a, k_fold_agg);
-    cudaFuncGetAttributes(&a, k_resolve);
+    cudaFuncGetAttributes(&a, k_seg_scan);
+    cudaFuncGetAttributes(&a, k_chain);
     cudaFuncGetAttributes(&a, k_ancestors);
     cudaFuncGetAttributes(&a, k_info_reset);
 }
@@ -1191,21 +1562,49 @@ int ensure_resample_ws(apop_ctx* c) {
     if (w.info) return APOP_OK;
     const int64_t nt = (c->n + TILE - 1) / TILE;
     w.nt = nt;
-    const size_t nd = (size_t)(nt + 1);
-    APOP_CUDA(c, cudaMalloc(&w.tmax, nd * 8));
-    APOP_CUDA(c, cudaMalloc(&w.tsum, nd * 8));
-    APOP_CUDA(c, cudaMalloc(&w.tsum2, nd * 8));
-    APOP_CUDA(c, cudaMalloc(&w.ain, nd * 8));
-    APOP_CUDA(c, cudaMalloc(&w.cls0, nd * 4));
-    APOP_CUDA(c, cudaMalloc(&w.cls1, nd * 4));
-    APOP_CUDA(c, cudaMalloc(&w.tacc, nd * 8));
-    APOP_CUDA(c, cudaMalloc(&w.tacc2, nd * 8));
-    APOP_CUDA(c, cudaMalloc(&w.agg0, nd * sizeof(Xd)));
-    APOP_CUDA(c, cudaMalloc(&w.agg1, nd * sizeof(Xd)));
-    APOP_CUDA(c, cudaMalloc(&w.sin0, nd * 8));
-    APOP_CUDA(c, cudaMalloc(&w.sin1, nd * 8));
-    APOP_CUDA(c, cudaMalloc(&w.comb, sizeof(Comb)));
-    APOP_CUDA(c, cudaMalloc(&w.info, sizeof(ResampleInfo)));
+    w.nb = (int)((nt + SEGB - 1) / SEGB);
+    w.hcap = (int)((nt < HCAP) ? nt : HCAP);
+    const size_t nd = (size_t)(nt + 1), nbd = (size_t)(w.nb + 1);
+    // one slab, carved in two passes (measure, then assign)
+    char* base = nullptr;
+    size_t off = 0;
+    auto carve = [&](size_t bytes) -> void* {
+        void* p = base ? base + off : nullptr;
+        off += (bytes + 255) & ~(size_t)255;
+        return p;
+    };
+    for (int pass = 0; pass < 2; ++pass) {
+        off = 0;
+        w.tmax = (double*)carve(nd * 8); w.tsum = (double*)carve(nd * 8);
+        w.tsum2 = (double*)carve(nd * 8); w.ain = (double*)carve(nd * 8);
+        w.tacc = (double*)carve(nd * 8); w.tacc2 = (double*)carve(nd * 8);
+        for (int l = 0; l < 2; ++l) {
+            w.cls[l] = (int*)carve(nd * 4); w.agg[l] = (Xd*)carve(nd * sizeof(Xd));
+            w.ex[l] = (Xd*)carve(nd * sizeof(Xd)); w.hix[l] = (int*)carve(nd * 4);
+            w.hp[l] = (int*)carve(nd * 4); w.hl[l] = (int*)carve(nd * 4);
+            w.hctx[l] = (int*)carve(nd * 4); w.bc[l] = (Xd*)carve(nbd * sizeof(Xd));
+            w.sblk[l] = (double*)carve(nbd * 8); w.shin[l] = (double*)carve(nd * 8);
+            w.shout[l] = (double*)carve(nd * 8);
+            w.hpa[l] = (Xd*)carve((size_t)w.hcap * TILE * sizeof(Xd));
+            w.hsb[l] = (Xd*)carve((size_t)w.hcap * TILE * sizeof(Xd));
+            w.hw[l] = (double*)carve((size_t)w.hcap * TILE * 8);
+        }
+        w.bacc = (double*)carve(nbd * 8); w.bacc2 = (double*)carve(nbd * 8);
+        w.baccx = (double*)carve(nbd * 8);
+        w.send = (double*)carve(2 * 8);
+        w.trace = (double*)carve(2 * 256 * 8);
+        w.comb = (Comb*)carve(sizeof(Comb));
+        ResampleInfo* info = (ResampleInfo*)carve(sizeof(ResampleInfo));
+        if (pass == 0) {
+            if (cudaMalloc(&w.slab, off) != cudaSuccess) {
+                w.slab = nullptr;
+                return set_err(c, APOP_ERR_OOM, "resample workspace: %zu bytes", off);
+            }
+            base = (char*)w.slab;
+        } else {
+            w.info = info;
+        }
+    }
     APOP_CUDA(c, cudaMemsetAsync(w.info, 0, sizeof(ResampleInfo), c->stream));
     APOP_CUDA(c, cudaMallocHost(&w.info_host, sizeof(ResampleInfo)));
     return APOP_OK;
@@ -1240,9 +1639,10 @@ int resample_enqueue(apop_ctx* c, const ResampleArgs& a) {
     k_fold_agg<<<nt, TB, 0, c->stream>>>(a.lw, a.w, a.n, v, a.xfilt);
     kt_end(c, KT_FOLD_AGG);
     kt_begin(c, KT_RESOLVE);
-    k_resolve<<<1, TB, 0, c->stream>>>(a.lw, a.w, a.n, n_glob, v, a.step, F, seq);
+    k_seg_scan<<<c->ws.nb, SEGB, 0, c->stream>>>(v, a.xfilt ? 1 : 0);
+    k_chain<<<1, TB, 0, c->stream>>>(a.lw, a.w, a.n, n_glob, v, a.step, F, seq);
     kt_end(c, KT_RESOLVE);
-    c->launches += 3;
+    c->launches += 4;
     if (a.anc_out) {
         kt_begin(c, KT_ANCESTORS);
         k_ancestors<<<nt, TB, 0, c->stream>>>(a.lw, a.w, a.n, g0, v, a.order, a.anc_out,

@@ -622,7 +622,10 @@ static int sweep_fetch(apop_ctx* c, int T, const apop_sweep_opts* opts, apop_swe
     const int64_t n = c->n;
     const int dim = s->dim;
     SweepDev hsd;
+    int info_err = 0;          // errors raised after the chain kernel (k_ancestors consistency checks)
     APOP_CUDA(c, cudaMemcpyAsync(&hsd, s->sd, sizeof hsd, cudaMemcpyDeviceToHost, c->stream));
+    APOP_CUDA(c, cudaMemcpyAsync(&info_err, &c->ws.info->err, sizeof(int), cudaMemcpyDeviceToHost,
+                                 c->stream));
     if (result->log_mean_w)
         APOP_CUDA(c, cudaMemcpyAsync(result->log_mean_w, s->log_mean_w, sizeof(double) * T,
                                      cudaMemcpyDeviceToHost, c->stream));
@@ -637,7 +640,7 @@ static int sweep_fetch(apop_ctx* c, int T, const apop_sweep_opts* opts, apop_swe
                                      cudaMemcpyDeviceToHost, c->stream));
     APOP_CUDA(c, cudaStreamSynchronize(c->stream));
     ResampleInfo I{};
-    I.err = hsd.err;
+    I.err = hsd.err | info_err;
     APOP_TRY(info_to_status(c, I));
     // :smc keeps the accumulated weight on the particles: final weight == log Z-hat
     result->log_z = opts->reset_weights ? hsd.log_z : hsd.base;
@@ -706,10 +709,10 @@ static int sweep_group(apop_ctx* const* g, int ng, const apop_ssm* model, const 
         apop_ctx* c = g[i];
         if (opts->csmc && c->n < 2)
             return set_err(c, APOP_ERR_INVALID, "conditional sweep needs >= 2 particles");
-        if (c->world > 1 && (opts->csmc || opts->keep_history || opts->want_filt))
+        if (c->world > 1 && (opts->csmc || opts->keep_history))
             return set_err(c, APOP_ERR_UNSUPPORTED,
-                           "sharded sweep: conditional sweeps / lineages / filtering means run "
-                           "one population per GPU (IPMCMC nodes), not sharded");
+                           "sharded sweep: conditional sweeps / lineages run one population "
+                           "per GPU (IPMCMC nodes), not sharded");
         if (c->world > 1 && (c->n % 8) != 0)
             return set_err(c, APOP_ERR_INVALID, "sharded sweep: particles per rank must be a "
                                                 "multiple of 8");

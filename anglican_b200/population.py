@@ -366,10 +366,10 @@ class PopulationGroup:
         for p in self.ranks:
             p.set_seed(seed)
 
-    def sweep(self, model, y, want_final=True, want_stats=True):
+    def sweep(self, model, y, want_final=True, want_stats=True, want_filt=False):
         y = np.ascontiguousarray(y, dtype=np.float64)
         T = y.size
-        opts = L.ApopSweepOpts(0, 0, 0, 0, 0, int(want_final), 0, 0)
+        opts = L.ApopSweepOpts(0, 0, 0, 0, 0, int(want_final), int(bool(want_filt)), 0)
         res = (L.ApopSweepResult * self.world)()
         outs = []
         for r, p in enumerate(self.ranks):
@@ -377,6 +377,9 @@ class PopulationGroup:
             if want_stats:
                 out.log_mean_w, out.ess = np.empty(T), np.empty(T)
                 res[r].log_mean_w, res[r].ess = _dp(out.log_mean_w), _dp(out.ess)
+            if want_filt:
+                out.filt_mean = np.empty(T)
+                res[r].filt_mean = _dp(out.filt_mean)
             if want_final:
                 out.x_final = np.empty(self.n_local)
                 res[r].x_final = _dp(out.x_final)

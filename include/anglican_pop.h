@@ -144,6 +144,14 @@ int apop_observe_mvn(apop_ctx* ctx, const double* mean, apop_col mean_col, const
  * 3 sin(pi x), 4 cos(pi x), 5 1/x. */
 int apop_selftest_math(apop_ctx* ctx, int fn, apop_col in, apop_col out);
 
+/* diagnostics of the last resample of this ctx: out8 = {ns in lap 0 of the
+ * exact chain, ns in sums/exchange/comb table, ns in lap 1, comb segments,
+ * hard tiles lap 0, hard tiles lap 1, first skipped tile of lap 1, J} */
+int apop_debug_resolve_phases(apop_ctx* ctx, double* out8);
+/* per hard-tile event of the last chain: out512[lap*256 + 2h] = ns spent folding
+ * hard tile h, out512[lap*256 + 2h + 1] = device timestamp (ns) when it began */
+int apop_debug_chain_trace(apop_ctx* ctx, double* out512);
+
 /* ---- weights: particle-weights / log-sum-exp / ESS ---------------------
  * smc.cljc:70-84, runtime.cljc:130-138, inference.cljc:181-186,
  * test/anglican/dist_test.cljc:83-94.

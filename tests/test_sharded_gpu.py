@@ -31,14 +31,15 @@ def test_sharded_sv_equals_unsharded(world, n_local):
     y = _sv_data(25)
     m = StochasticVolatility()
     with Population(n_local * world, seed=31337) as pop:
-        ref = pop.sweep(m, y, want_filt=False)
+        ref = pop.sweep(m, y, want_filt=True)
     with PopulationGroup(n_local, world, seed=31337) as grp:
-        outs = grp.sweep(m, y)
+        outs = grp.sweep(m, y, want_filt=True)
     x = np.concatenate([o.x_final for o in outs])
     for o in outs:
         assert o.log_z == ref.log_z
         assert np.array_equal(o.log_mean_w, ref.log_mean_w)
         assert np.allclose(o.ess, ref.ess, rtol=1e-12)
+        assert np.allclose(o.filt_mean, ref.filt_mean, rtol=1e-11, atol=1e-13)
     assert np.array_equal(x, ref.x_final)
 
 
