@@ -124,6 +124,7 @@ struct ResampleWS {
     Xd* bc[2] = {};              // per block: composite from the last hard tile (or block start) to
                                  //   the block end
     double* sblk[2] = {};        // exact running sum entering each block
+    double* sin[2] = {};         // exact running sum entering every tile (k_expand), [nt + 1]
     double* shin[2] = {};        // exact running sum entering / leaving each hard tile
     double* shout[2] = {};
     Xd* hpa[2] = {};             // [HCAP][TILE] per-element inclusive prefix transducers, context eA

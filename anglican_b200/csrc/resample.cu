@@ -420,18 +420,20 @@ __global__ void __launch_bounds__(FB) k_finalize(WSView v, int64_t n, int64_t n_
     const double eps_tot = ((double)(2 * n_global) + 8192.0) * 4.44089209850062616e-16 + rel_eps;
     const double xlast_ub = atot * (u + 1.0) * (1.0 + 4.0 * eps_tot);
 
-    // ---- classification of every tile for both laps; each thread owns a
-    //      contiguous range of tiles so that the hard tiles come out sorted
-    const int64_t per = (nt + FB - 1) / FB;
-    const int64_t tb = (int64_t)tid * per;
-    const int64_t te = (tb + per < nt) ? tb + per : nt;
-    int nh0 = 0, nh1 = 0;
-    for (int64_t t = tb; t < te; ++t) {
+    // ---- classification of every tile for both laps (coalesced, tiles striped
+    //      over the threads).  Hard tiles are rare: they are collected in shared
+    //      memory and rank-sorted afterwards; if they overflow the buffer the
+    //      lists are rebuilt by the slow contiguous walk below.
+    constexpr int HB = FB * FCH;                   // ints per lap in the staging buffer
+    int* hbuf = reinterpret_cast<int*>(buf);       // buf is free again: [2][HB]
+    __shared__ int hcnt[2];
+    if (tid < 2) hcnt[tid] = 0;
+    __syncthreads();
+    for (int64_t t = tid; t < nt; t += FB) {
         const int64_t hi = ((t + 1) * TILE < n) ? (t + 1) * TILE : n;
         const double a_in = v.ain[t], ao = v.ain[t + 1];
         const int c0 = classify_tile(a_in, ao, g0 + hi, rel_eps);
         v.cls[0][t] = c0;
-        nh0 += (c0 == kCtxHard);
         int c1;
         const double eps1 = ((double)(n_global + g0 + hi) + 4096.0) * 4.44089209850062616e-16 + rel_eps;
         if ((atot + a_in) * (1.0 - eps1) > xlast_ub) {
@@ -441,37 +443,57 @@ __global__ void __launch_bounds__(FB) k_finalize(WSView v, int64_t n, int64_t n_
             c1 = classify_tile(atot + a_in, atot + ao, n_global + g0 + hi, rel_eps);
         }
         v.cls[1][t] = c1;
-        nh1 += (c1 == kCtxHard);
+        v.hix[0][t] = -1;
+        v.hix[1][t] = -1;
+        if (c0 == kCtxHard) { const int k = atomicAdd(&hcnt[0], 1); if (k < HB) hbuf[k] = (int)t; }
+        if (c1 == kCtxHard) { const int k = atomicAdd(&hcnt[1], 1); if (k < HB) hbuf[HB + k] = (int)t; }
     }
     __syncthreads();
-    // sorted hard lists: exclusive scan of the per-thread counts (small integers: exact)
-    double h0tot, h1tot;
-    int o0 = (int)block_excl_scan_f64((double)nh0, smd, h0tot);
-    int o1 = (int)block_excl_scan_f64((double)nh1, smd, h1tot);
     const int skip1 = sh_skip;
-    for (int64_t t = tb; t < te; ++t) {
+    const int h0tot = hcnt[0], h1tot = hcnt[1];
+    auto emit_hard = [&](int lap, int rank, int64_t t) {
         const int64_t hi = ((t + 1) * TILE < n) ? (t + 1) * TILE : n;
         const double a_in = v.ain[t], ao = v.ain[t + 1];
         int ea, eb;
-        const int c0 = v.cls[0][t];
-        int hx0 = -1, hx1 = -1;
-        if (c0 == kCtxHard) {
-            classify_tile2(a_in, ao, g0 + hi, rel_eps, &ea, &eb);
-            hx0 = o0++;
-            v.hl[0][hx0] = (int)t;
-            v.hctx[0][hx0] = (ea != kCtxHard && eb == ea + 1 && ea > -1000 && ea < 900) ? ea : kCtxHard;
+        if (lap == 0) classify_tile2(a_in, ao, g0 + hi, rel_eps, &ea, &eb);
+        else classify_tile2(atot + a_in, atot + ao, n_global + g0 + hi, rel_eps, &ea, &eb);
+        // tiles at or beyond the first skipped tile are never folded in lap 1
+        const bool usable = (lap == 0 || t < skip1) && ea != kCtxHard && eb == ea + 1 &&
+                            ea > -1000 && ea < 900;
+        v.hl[lap][rank] = (int)t;
+        v.hctx[lap][rank] = usable ? ea : kCtxHard;
+        v.hix[lap][t] = rank;
+    };
+    if (h0tot <= HB && h1tot <= HB) {
+#pragma unroll 1
+        for (int lap = 0; lap < 2; ++lap) {
+            const int cnt = lap ? h1tot : h0tot;
+            const int* list = hbuf + lap * HB;
+            for (int i = tid; i < cnt; i += FB) {
+                const int t = list[i];
+                int rank = 0;
+                for (int k = 0; k < cnt; ++k) rank += (list[k] < t);
+                emit_hard(lap, rank, t);
+            }
         }
-        const int c1 = v.cls[1][t];
-        if (c1 == kCtxHard) {
-            classify_tile2(atot + a_in, atot + ao, n_global + g0 + hi, rel_eps, &ea, &eb);
-            hx1 = o1++;
-            v.hl[1][hx1] = (int)t;
-            // tiles at or beyond the first skipped tile are never folded in lap 1
-            v.hctx[1][hx1] = (t < skip1 && ea != kCtxHard && eb == ea + 1 && ea > -1000 && ea < 900)
-                                 ? ea : kCtxHard;
+    } else {
+        // overflow: contiguous walk, each thread owns a range of tiles
+        const int64_t per = (nt + FB - 1) / FB;
+        const int64_t tb = (int64_t)tid * per;
+        const int64_t te = (tb + per < nt) ? tb + per : nt;
+        int nh0 = 0, nh1 = 0;
+        for (int64_t t = tb; t < te; ++t) {
+            nh0 += (v.cls[0][t] == kCtxHard);
+            nh1 += (v.cls[1][t] == kCtxHard);
         }
-        v.hix[0][t] = hx0;
-        v.hix[1][t] = hx1;
+        double d0, d1;
+        __syncthreads();
+        int o0 = (int)block_excl_scan_f64((double)nh0, smd, d0);
+        int o1 = (int)block_excl_scan_f64((double)nh1, smd, d1);
+        for (int64_t t = tb; t < te; ++t) {
+            if (v.cls[0][t] == kCtxHard) emit_hard(0, o0++, t);
+            if (v.cls[1][t] == kCtxHard) emit_hard(1, o1++, t);
+        }
     }
     if (tid == 0) {
         ResampleInfo* I = v.info;
@@ -483,8 +505,8 @@ __global__ void __launch_bounds__(FB) k_finalize(WSView v, int64_t n, int64_t n_
                                                                : -INFINITY;
         I->u = u;
         I->n_new = n_new;
-        I->nh0 = (int)h0tot;
-        I->nh1 = (int)h1tot;
+        I->nh0 = h0tot;
+        I->nh1 = h1tot;
         I->first_skip1 = skip1;
         I->weights_mode = weights_mode;
         if (!weights_mode && m != m) I->err |= EB_NAN;
@@ -1129,6 +1151,15 @@ __global__ void __launch_bounds__(TB) k_chain(const double* __restrict__ lw,
     }
 }
 
+// exact running sum entering every tile, both laps, from the chain's records
+__global__ void __launch_bounds__(256) k_expand(WSView v) {
+    const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (t > v.nt) return;
+    int* err = &v.info->err;
+    v.sin[0][t] = tile_sin(v, 0, t, err);
+    v.sin[1][t] = tile_sin(v, 1, t, err);
+}
+
 // ------------------------------------------------------------------ K3b/K4
 __device__ __forceinline__ int64_t slot_of(i64 k, int lap, int order, i64 J, i64 n_new) {
     if (order == APOP_ORDER_EMISSION) return k;
@@ -1140,13 +1171,13 @@ __device__ __forceinline__ int64_t slot_of(i64 k, int lap, int order, i64 J, i64
 // of whichever rank owns the output slot, written through peer memory
 struct AncOut {
     int32_t* local;
-    PeerI32 peer;
+    const PeerI32* peerp;        // points at the kernel's __grid_constant__ parameter
     int world;
     i64 nl;                      // particles per rank
     __device__ __forceinline__ int32_t* at(i64 slot) const {
         if (world == 1) return local + slot;
         const int q = (int)(slot / nl);
-        return peer.p[q] + (slot - (i64)q * nl);
+        return peerp->p[q] + (slot - (i64)q * nl);
     }
 };
 
@@ -1375,7 +1406,7 @@ __device__ __forceinline__ bool staged_emit(const Comb& comb, int e, double Sin,
                 i64 li = off_lo + ((dir > 0) ? i : (wn - 1 - i));
                 int q = q_lo;
                 while (li >= A.nl) { li -= A.nl; ++q; }
-                A.peer.p[q][li] = st.buf[i];
+                A.peerp->p[q][li] = st.buf[i];
             }
         }
         __syncthreads();
@@ -1428,16 +1459,17 @@ __global__ void __launch_bounds__(TB, 2) k_ancestors(const double* __restrict__ 
                                                      const double* __restrict__ win, int64_t n,
                                                      int64_t g0, WSView v, int order,
                                                      int32_t* __restrict__ anc,
-                                                     int64_t out_offset, PeerI32 ancp, int world) {
+                                                     int64_t out_offset,
+                                                     const __grid_constant__ PeerI32 ancp,
+                                                     int world) {
     __shared__ AncSmem sm;
     const Comb& comb = *v.comb;          // global (L1/L2 resident); the fast path reads one segment
     const ResampleInfo* I = v.info;
     if (I->err) return;
     const int t = blockIdx.x;
     const double x0 = v.comb->x0, xlast = v.comb->xlast;
-    int* errp = &v.info->err;
-    const double si0 = tile_sin(v, 0, t, errp), so0 = tile_sin(v, 0, (int64_t)t + 1, errp);
-    const double si1 = tile_sin(v, 1, t, errp);
+    const double si0 = v.sin[0][t], so0 = v.sin[0][t + 1];
+    const double si1 = v.sin[1][t];
     const bool need0 = (so0 > x0) && !(si0 > xlast);
     const bool need1 = !(si1 > xlast);
     if (!need0 && !need1) return;
@@ -1448,7 +1480,7 @@ __global__ void __launch_bounds__(TB, 2) k_ancestors(const double* __restrict__ 
     __syncthreads();
     const i64 J = I->J, n_new = I->n_new;
     AncOut A;
-    A.local = anc; A.peer = ancp; A.world = world; A.nl = n;
+    A.local = anc; A.peerp = &ancp; A.world = world; A.nl = n;
     for (int lap = 0; lap < 2; ++lap) {
         if (lap == 0 ? !need0 : !need1) continue;
         const double Sin = lap ? si1 : si0;
@@ -1511,7 +1543,7 @@ __global__ void __launch_bounds__(TB) k_edges(const double* __restrict__ lw,
     const int nvalid = (int)((n - base < TILE) ? (n - base) : TILE);
     double w[IPT], edge[IPT];
     load_weights(lw, win, base, n, v.info->m, w);
-    (void)cta_tile_fold(tile_sin(v, 0, t, &v.info->err), w, nvalid, edge, sm);
+    (void)cta_tile_fold(v.sin[0][t], w, nvalid, edge, sm);
     const int64_t i0 = base + (int64_t)threadIdx.x * IPT;
 #pragma unroll
     for (int j = 0; j < IPT; ++j)
@@ -1553,6 +1585,7 @@ void preload_resample_kernels() {
     cudaFuncGetAttributes(&a, k_fold_agg);
     cudaFuncGetAttributes(&a, k_seg_scan);
     cudaFuncGetAttributes(&a, k_chain);
+    cudaFuncGetAttributes(&a, k_expand);
     cudaFuncGetAttributes(&a, k_ancestors);
     cudaFuncGetAttributes(&a, k_info_reset);
 }
@@ -1584,6 +1617,7 @@ int ensure_resample_ws(apop_ctx* c) {
             w.hp[l] = (int*)carve(nd * 4); w.hl[l] = (int*)carve(nd * 4);
             w.hctx[l] = (int*)carve(nd * 4); w.bc[l] = (Xd*)carve(nbd * sizeof(Xd));
             w.sblk[l] = (double*)carve(nbd * 8); w.shin[l] = (double*)carve(nd * 8);
+            w.sin[l] = (double*)carve(nd * 8);
             w.shout[l] = (double*)carve(nd * 8);
             w.hpa[l] = (Xd*)carve((size_t)w.hcap * TILE * sizeof(Xd));
             w.hsb[l] = (Xd*)carve((size_t)w.hcap * TILE * sizeof(Xd));
@@ -1641,8 +1675,9 @@ int resample_enqueue(apop_ctx* c, const ResampleArgs& a) {
     kt_begin(c, KT_RESOLVE);
     k_seg_scan<<<c->ws.nb, SEGB, 0, c->stream>>>(v, a.xfilt ? 1 : 0);
     k_chain<<<1, TB, 0, c->stream>>>(a.lw, a.w, a.n, n_glob, v, a.step, F, seq);
+    k_expand<<<(int)((v.nt + 1 + 255) / 256), 256, 0, c->stream>>>(v);
     kt_end(c, KT_RESOLVE);
-    c->launches += 4;
+    c->launches += 5;
     if (a.anc_out) {
         kt_begin(c, KT_ANCESTORS);
         k_ancestors<<<nt, TB, 0, c->stream>>>(a.lw, a.w, a.n, g0, v, a.order, a.anc_out,

@@ -316,7 +316,7 @@ __global__ void __launch_bounds__(TB, 2) k_propagate(const ModelDev* __restrict_
                                                   int64_t g0, uint64_t seed, uint32_t t,
                                                   double* __restrict__ tmax,
                                                   double* __restrict__ tsum, int* errflag,
-                                                  PeerF64 xpeer) {
+                                                  const __grid_constant__ PeerF64 xpeer) {
     const ModelDev& M = *Mp;
     const double y = yt[0];
     const double wbase = sd->base;
@@ -355,7 +355,7 @@ __global__ void k_gather_rows(const double* __restrict__ src, double* __restrict
 }
 
 // final states of a sharded sweep: parents are global ids
-__global__ void k_gather_shard(PeerF64 src, double* __restrict__ dst,
+__global__ void k_gather_shard(const __grid_constant__ PeerF64 src, double* __restrict__ dst,
                                const int32_t* __restrict__ anc, int64_t n) {
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n;
          i += (int64_t)gridDim.x * blockDim.x) {
