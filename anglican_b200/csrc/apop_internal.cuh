@@ -125,6 +125,8 @@ struct ResampleWS {
                                  //   the block end
     double* sblk[2] = {};        // exact running sum entering each block
     double* sin[2] = {};         // exact running sum entering every tile (k_expand), [nt + 1]
+    long long* cnt[2] = {};      // pointers of the comb strictly below sin[lap][t], [nt + 1]
+    int* gseg[2] = {};           // comb segment that holds pointer cnt[lap][t]
     double* shin[2] = {};        // exact running sum entering / leaving each hard tile
     double* shout[2] = {};
     Xd* hpa[2] = {};             // [HCAP][TILE] per-element inclusive prefix transducers, context eA

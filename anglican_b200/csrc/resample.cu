@@ -1151,15 +1151,6 @@ __global__ void __launch_bounds__(TB) k_chain(const double* __restrict__ lw,
     }
 }
 
-// exact running sum entering every tile, both laps, from the chain's records
-__global__ void __launch_bounds__(256) k_expand(WSView v) {
-    const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (t > v.nt) return;
-    int* err = &v.info->err;
-    v.sin[0][t] = tile_sin(v, 0, t, err);
-    v.sin[1][t] = tile_sin(v, 1, t, err);
-}
-
 // ------------------------------------------------------------------ K3b/K4
 __device__ __forceinline__ int64_t slot_of(i64 k, int lap, int order, i64 J, i64 n_new) {
     if (order == APOP_ORDER_EMISSION) return k;
@@ -1267,11 +1258,18 @@ __device__ __forceinline__ int find_seg_of_index(const Comb& c, i64 k) {
 }
 
 // returns false (uniformly, nothing written) when the tile does not qualify
-__device__ __forceinline__ bool staged_emit(const Comb& comb, int e, double Sin,
+__device__ __forceinline__ bool staged_emit(const Comb& comb, int e, double Sin, double Sout,
+                                            i64 C0in, i64 C1in, int gsel,
                                             const double (&incD)[IPT], int32_t val_tile0,
                                             const AncOut& A, int64_t out_offset, i64 J,
-                                            i64 n_new, int order, int lap, StageSmem& st) {
-    // tile totals and the window [C0, C1) of pointer indices
+                                            i64 n_new, int order, int lap, StageSmem& st,
+                                            int* err) {
+    // the window [C0, C1) of pointer indices and its comb segment were computed
+    // per tile boundary by k_expand (uniform over the CTA)
+    const CombSeg& gs = comb.seg[gsel];
+    const int ok = (C1in == C0in) ? 2
+                 : (gs.e == e && gs.q > 0 && C0in > gs.j0 && C1in < gs.j0 + gs.len) ? 1 : 0;
+    if (ok != 1) return ok == 2;                                   // 2: no offspring in this lap
     double loc = 0.0;
 #pragma unroll
     for (int j = 0; j < IPT; ++j) loc += incD[j];
@@ -1279,22 +1277,11 @@ __device__ __forceinline__ bool staged_emit(const Comb& comb, int e, double Sin,
     const double pre = cta_excl_scan_f64(loc, st.dsum, tile_units);
     const i64 s_in = units_of(Sin);
     const i64 s_out = s_in + (i64)tile_units;
-    if (s_out >= kTwo53) return false;
-    if (threadIdx.x == 0) {
-        int h0 = comb.nseg - 1, h1 = comb.nseg - 1;
-        const i64 c0 = comb_count_below(comb, Sin, h0);
-        const i64 c1 = comb_count_below(comb, from_units(s_out, e), h1);
-        const int gsel = find_seg_of_index(comb, c0);
-        const CombSeg& gs = comb.seg[gsel];
-        st.C0 = c0; st.C1 = c1; st.gi = gsel;
-        st.ok = (c1 == c0) ? 2
-              : (gs.e == e && gs.q > 0 && c0 > gs.j0 && c1 < gs.j0 + gs.len) ? 1 : 0;
-    }
-    __syncthreads();
-    const int ok = st.ok;
-    if (ok != 1) { __syncthreads(); return ok == 2; }            // 2: no offspring in this lap
-    const i64 C0 = st.C0, C1 = st.C1;
-    const CombSeg& g = comb.seg[st.gi];
+    // consistency: the tile's integer sum must land on the chain's exact edge
+    if ((s_out >= kTwo53 || (Sout < INFINITY && from_units(s_out, e) != Sout)) && threadIdx.x == 0)
+        atomicOr(err, EB_CTX);
+    const i64 C0 = C0in, C1 = C1in;
+    const CombSeg& g = gs;
     const double qD = (double)g.q;
     const double invq = fm::div_fast(1.0, qD);
     const double magic = 6755399441055744.0;                      // 1.5 * 2^52
@@ -1450,6 +1437,25 @@ __device__ __noinline__ void generic_emit(const Comb& comb, double Sin, const do
     __syncthreads();
 }
 
+// exact running sum entering every tile, both laps, from the chain's records
+__global__ void __launch_bounds__(256) k_expand(WSView v) {
+    const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (t > v.nt) return;
+    int* err = &v.info->err;
+    const double s0 = tile_sin(v, 0, t, err), s1 = tile_sin(v, 1, t, err);
+    v.sin[0][t] = s0;
+    v.sin[1][t] = s1;
+    // pointer counts at the tile boundary and the comb segment they fall in: the
+    // emission kernel then needs no serial search per tile
+    const Comb& comb = *v.comb;
+    if (comb.err || comb.nseg <= 0) { v.cnt[0][t] = 0; v.cnt[1][t] = 0; v.gseg[0][t] = 0; v.gseg[1][t] = 0; return; }
+    int h0 = comb.nseg - 1, h1 = comb.nseg - 1;
+    const i64 c0 = comb_count_below(comb, s0, h0), c1 = comb_count_below(comb, s1, h1);
+    v.cnt[0][t] = c0; v.cnt[1][t] = c1;
+    v.gseg[0][t] = find_seg_of_index(comb, c0);
+    v.gseg[1][t] = find_seg_of_index(comb, c1);
+}
+
 union AncSmem {
     FoldSmem fold;
     StageSmem stage;
@@ -1469,7 +1475,7 @@ __global__ void __launch_bounds__(TB, 2) k_ancestors(const double* __restrict__ 
     const int t = blockIdx.x;
     const double x0 = v.comb->x0, xlast = v.comb->xlast;
     const double si0 = v.sin[0][t], so0 = v.sin[0][t + 1];
-    const double si1 = v.sin[1][t];
+    const double si1 = v.sin[1][t], so1 = v.sin[1][t + 1];
     const bool need0 = (so0 > x0) && !(si0 > xlast);
     const bool need1 = !(si1 > xlast);
     if (!need0 && !need1) return;
@@ -1483,6 +1489,7 @@ __global__ void __launch_bounds__(TB, 2) k_ancestors(const double* __restrict__ 
     A.local = anc; A.peerp = &ancp; A.world = world; A.nl = n;
     for (int lap = 0; lap < 2; ++lap) {
         if (lap == 0 ? !need0 : !need1) continue;
+        if (v.cnt[lap][t] == v.cnt[lap][t + 1]) continue;       // no pointer falls into this tile
         const double Sin = lap ? si1 : si0;
         const int cls = v.cls[lap][t];
         bool fast = (cls != kCtxHard) && (cls != kCtxSkip) && ctx_fast_ok(cls) &&
@@ -1495,8 +1502,9 @@ __global__ void __launch_bounds__(TB, 2) k_ancestors(const double* __restrict__ 
                 fast = tile_quantize_f64(cls, w, incD);
             }
             if (fast)
-                fast = staged_emit(comb, cls, Sin, incD, (int32_t)(g0 + base), A, out_offset,
-                                   J, n_new, order, lap, sm.stage);
+                fast = staged_emit(comb, cls, Sin, lap ? so1 : so0, v.cnt[lap][t],
+                                   v.cnt[lap][t + 1], v.gseg[lap][t], incD, (int32_t)(g0 + base),
+                                   A, out_offset, J, n_new, order, lap, sm.stage, &v.info->err);
         }
         if (!fast) {
             EmitCtx E;
@@ -1618,6 +1626,7 @@ int ensure_resample_ws(apop_ctx* c) {
             w.hctx[l] = (int*)carve(nd * 4); w.bc[l] = (Xd*)carve(nbd * sizeof(Xd));
             w.sblk[l] = (double*)carve(nbd * 8); w.shin[l] = (double*)carve(nd * 8);
             w.sin[l] = (double*)carve(nd * 8);
+            w.cnt[l] = (long long*)carve(nd * 8); w.gseg[l] = (int*)carve(nd * 4);
             w.shout[l] = (double*)carve(nd * 8);
             w.hpa[l] = (Xd*)carve((size_t)w.hcap * TILE * sizeof(Xd));
             w.hsb[l] = (Xd*)carve((size_t)w.hcap * TILE * sizeof(Xd));
