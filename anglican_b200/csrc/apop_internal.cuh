@@ -218,6 +218,32 @@ int info_to_status(apop_ctx* c, const ResampleInfo& info);
 int multinomial_enqueue(apop_ctx* c, const double* lw, const double* w, const double* uni,
                         int64_t n_new, int32_t* anc);
 int gather_enqueue(apop_ctx* c, const int32_t* anc, int64_t n_new, Column* col);
+// mvn.cu: fp64 tensor-core (DMMA) kernels
+struct MvnSweepArgs {
+    const double* A;        // [d*d] dense transition
+    const double* Lq;       // [d*d] lower factor of the process covariance
+    const double* iL;       // [d*d] inverse lower factor of the observation covariance
+    double Z;               // 0.5 d log(2 pi) + log det L   (runtime.cljc:355-358)
+    const double* xp;       // parent states [n*d]
+    const int32_t* anc;     // ancestors (sorted physical order), unused on the first step
+    int first_step;
+    double* xn;             // new states [n*d]
+    double* lw;             // log-weights [n]
+    const double* y;        // observation of this step [d] (device)
+    const double* retained; // conditional sweep: state of slot 0 at this step, or NULL
+    const SweepDev* sd;
+    int64_t n, g0;
+    uint64_t seed;
+    uint32_t t;
+};
+
+bool mvn_dim_supported(int d);
+int mvn_propagate_enqueue(apop_ctx* c, int d, const MvnSweepArgs& a);
+int mvn_init_enqueue(apop_ctx* c, double* x, int d, double s0, const double* retained);
+int mvn_observe_dmma_enqueue(apop_ctx* c, int d, const double* iL, double Z, const double* mean,
+                             int ms, const double* val, int vs, double* lw);
+int mvn_prepare_host(const double* cov, int d, std::vector<double>& L, std::vector<double>& iL,
+                     double* Z);
 Fabric fabric_view(const apop_ctx* c);                      // by-value kernel argument
 int fabric_barrier_enqueue(apop_ctx* c);                    // all ranks: flags over peer memory
 int fabric_prepare(apop_ctx* c, size_t n_cap);              // (re)allocate + map the heaps (comm.cu)

@@ -540,6 +540,9 @@ int apop_observe_mvn(apop_ctx* c, const double* mean, apop_col mean_col, const d
         APOP_TRY(param_upload(c, value, sizeof(double) * (size_t)d, &dv));
         vp = (const double*)dv; vs = 0;
     }
+    if (mvn_dim_supported(d))          // batched whitening on the fp64 tensor pipe (mvn.cu)
+        return mvn_observe_dmma_enqueue(c, d, (const double*)diL, Z, mp, ms, vp, vs,
+                                        (double*)l->ptr);
     const int tb = 128, nw = tb / 32;
     k_observe_mvn<<<grid_for(c->n, nw), tb, sizeof(double) * (size_t)d * nw, c->stream>>>(
         (const double*)diL, Z, d, mp, ms, vp, vs, (double*)l->ptr, c->n);

@@ -47,6 +47,8 @@ struct SweepState {
     apop::SweepDev* sd = nullptr;
     apop::ModelDev* model = nullptr;
     double* traj = nullptr;
+    double* mvn_mats = nullptr;    // LGMVN: A | Lq | iL, each [dim*dim]
+    double mvn_Z = 0.0, mvn_s0 = 1.0;
     size_t cap_n = 0, cap_T = 0, cap_hist = 0;
     const double* last_x = nullptr;    // pre-resample states of the last step
     const int32_t* last_anc = nullptr;
@@ -59,7 +61,8 @@ void sweep_free(apop_ctx* c) {
     if (!s) return;
     if (s->heap_backed) { s->xa = nullptr; s->xb = nullptr; s->anc = nullptr; }
     void* ptrs[] = {s->xa, s->xb, s->lw, s->anc, s->x_hist, s->anc_hist, s->y, s->retained,
-                    s->log_mean_w, s->ess, s->filt, s->tsx, s->x_final, s->sd, s->model, s->traj};
+                    s->log_mean_w, s->ess, s->filt, s->tsx, s->x_final, s->sd, s->model, s->traj,
+                    s->mvn_mats};
     for (void* p : ptrs)
         if (p) cudaFree(p);
     delete s;
@@ -455,6 +458,29 @@ static int upload_model(apop_ctx* c, const apop_ssm* m) {
         memcpy(h.hmm_sd, m->hmm_sd, sizeof(double) * K);
         for (int i = 0; i < K; ++i) h.hmm_const[i] = log(m->hmm_sd[i]) + kHalfLog2Pi_;
     }
+    if (m->kind == APOP_SSM_LGMVN) {
+        const int d = m->dim;
+        if (!mvn_dim_supported(d) || !m->A || !m->Lq || !m->R)
+            return set_err(c, APOP_ERR_UNSUPPORTED, "fused mvn sweep: dim must be 8/16/32/64 and "
+                                                    "A, Lq, R given (dim %d)", d);
+        std::vector<double> L, iL;
+        double Z;
+        if (mvn_prepare_host(m->R, d, L, iL, &Z))
+            return set_err(c, APOP_ERR_INVALID, "mvn: observation covariance not PD");
+        SweepState* s = c->sweep;
+        const size_t dd = (size_t)d * d;
+        if (!s->mvn_mats) APOP_TRY(dev_alloc(c, (void**)&s->mvn_mats, sizeof(double) * 3 * 64 * 64));
+        std::vector<double> pack(3 * dd);
+        memcpy(pack.data(), m->A, sizeof(double) * dd);
+        memcpy(pack.data() + dd, m->Lq, sizeof(double) * dd);
+        memcpy(pack.data() + 2 * dd, iL.data(), sizeof(double) * dd);
+        void* st = nullptr;
+        APOP_TRY(param_upload(c, pack.data(), sizeof(double) * 3 * dd, &st));
+        APOP_CUDA(c, cudaMemcpyAsync(s->mvn_mats, st, sizeof(double) * 3 * dd,
+                                     cudaMemcpyDeviceToDevice, c->stream));
+        s->mvn_Z = Z;
+        s->mvn_s0 = m->s0;
+    }
     void* staged = nullptr;
     APOP_TRY(param_upload(c, &h, sizeof h, &staged));
     APOP_CUDA(c, cudaMemcpyAsync(c->sweep->model, staged, sizeof h, cudaMemcpyDeviceToDevice,
@@ -489,12 +515,13 @@ static int sweep_stage(apop_ctx* c, const double* y, int T, const double* retain
     APOP_TRY(ensure_resample_ws(c));
     const bool csmc = o->csmc && retained;
     void* staged = nullptr;
-    APOP_TRY(param_upload(c, y, sizeof(double) * (size_t)T, &staged));
-    APOP_CUDA(c, cudaMemcpyAsync(s->y, staged, sizeof(double) * (size_t)T,
+    const size_t dim = (size_t)s->dim;
+    APOP_TRY(param_upload(c, y, sizeof(double) * (size_t)T * dim, &staged));
+    APOP_CUDA(c, cudaMemcpyAsync(s->y, staged, sizeof(double) * (size_t)T * dim,
                                  cudaMemcpyDeviceToDevice, c->stream));
     if (csmc) {
-        APOP_TRY(param_upload(c, retained, sizeof(double) * (size_t)(T + 1), &staged));
-        APOP_CUDA(c, cudaMemcpyAsync(s->retained, staged, sizeof(double) * (size_t)(T + 1),
+        APOP_TRY(param_upload(c, retained, sizeof(double) * (size_t)(T + 1) * dim, &staged));
+        APOP_CUDA(c, cudaMemcpyAsync(s->retained, staged, sizeof(double) * (size_t)(T + 1) * dim,
                                      cudaMemcpyDeviceToDevice, c->stream));
     }
     return APOP_OK;
@@ -519,9 +546,12 @@ static int sweep_begin(apop_ctx* c, const double* retained, const apop_sweep_opt
     // the previous sweep)
     APOP_TRY(fabric_barrier_enqueue(c));
     double* x0 = s->history ? s->x_hist : s->xa;
-    {
+    if (KIND == APOP_SSM_LGMVN) {
+        APOP_TRY(mvn_init_enqueue(c, x0, s->dim, s->mvn_s0, csmc ? s->retained : nullptr));
+    } else {
         const int64_t pairs = (n + 1) / 2;
-        k_init<KIND><<<(int)((pairs + TB - 1) / TB), TB, 0, c->stream>>>(
+        k_init<(KIND == APOP_SSM_LGMVN) ? APOP_SSM_LGSSM1D : KIND>
+            <<<(int)((pairs + TB - 1) / TB), TB, 0, c->stream>>>(
             s->model, x0, n, c->g0, c->seed, csmc ? s->retained : nullptr);
     }
     c->launches += 2;
@@ -539,18 +569,30 @@ static int sweep_step(apop_ctx* c, int t, const apop_sweep_opts* o, bool csmc) {
     const bool shard = c->world > 1;
     const double* x_prev = s->last_x;
     const int32_t* anc_prev = s->last_anc;
-    double* x_new = s->history ? s->x_hist + (size_t)t * n : ((t & 1) ? s->xb : s->xa);
+    const size_t dim = (size_t)s->dim;
+    double* x_new = s->history ? s->x_hist + (size_t)t * n * dim : ((t & 1) ? s->xb : s->xa);
     int32_t* anc_new = s->history ? s->anc_hist + (size_t)(t - 1) * n : s->anc;
     kt_begin(c, KT_PROPAGATE);
-    if (shard) {
+    if (KIND == APOP_SSM_LGMVN) {
+        MvnSweepArgs ma;
+        const size_t dd = dim * dim;
+        ma.A = s->mvn_mats; ma.Lq = s->mvn_mats + dd; ma.iL = s->mvn_mats + 2 * dd;
+        ma.Z = s->mvn_Z;
+        ma.xp = x_prev; ma.anc = anc_prev; ma.first_step = (t == 1);
+        ma.xn = x_new; ma.lw = s->lw; ma.y = s->y + (size_t)(t - 1) * dim;
+        ma.retained = csmc ? s->retained + (size_t)t * dim : nullptr;
+        ma.sd = s->sd; ma.n = n; ma.g0 = c->g0; ma.seed = c->seed; ma.t = (uint32_t)t;
+        APOP_TRY(mvn_propagate_enqueue(c, s->dim, ma));
+        c->launches -= 1;                 // counted below
+    } else if (shard) {
         const PeerF64 xpeer = peer_f64(c, (t & 1) ? c->fab.off_xa : c->fab.off_xb);   // x_{t-1}
-        k_propagate<KIND, true><<<nt, TB, 0, c->stream>>>(
+        k_propagate<(KIND == APOP_SSM_LGMVN) ? APOP_SSM_LGSSM1D : KIND, true><<<nt, TB, 0, c->stream>>>(
             s->model, x_prev, anc_prev, t == 1, x_new, s->lw, s->y + (t - 1), nullptr, s->sd, n,
             c->g0, c->seed, (uint32_t)t, ws.tmax, ws.tsum, &ws.info->err, xpeer);
     } else {
         PeerF64 none;
         memset(&none, 0, sizeof none);
-        k_propagate<KIND, false><<<nt, TB, 0, c->stream>>>(
+        k_propagate<(KIND == APOP_SSM_LGMVN) ? APOP_SSM_LGSSM1D : KIND, false><<<nt, TB, 0, c->stream>>>(
             s->model, x_prev, anc_prev, t == 1, x_new, s->lw, s->y + (t - 1),
             csmc ? s->retained + t : nullptr, s->sd, n, c->g0, c->seed, (uint32_t)t, ws.tmax,
             ws.tsum, &ws.info->err, none);
@@ -563,13 +605,14 @@ static int sweep_step(apop_ctx* c, int t, const apop_sweep_opts* o, bool csmc) {
     a.lw = s->lw; a.w = nullptr; a.n = n;
     a.n_new = shard ? c->n_global : (cond ? n - 1 : n);
     a.u = NAN; a.order = APOP_ORDER_SORTED;
-    a.anc_out = anc_new; a.out_offset = cond ? 1 : 0; a.have_partials = true;
-    a.xfilt = o->want_filt ? x_new : nullptr;
-    a.rel_eps = 2e-5;            // fp32 tile partials of k_propagate
+    a.anc_out = anc_new; a.out_offset = cond ? 1 : 0;
+    a.have_partials = (KIND != APOP_SSM_LGMVN);      // the mvn kernel leaves K2 to k_tile_lse
+    a.xfilt = (o->want_filt && dim == 1) ? x_new : nullptr;
+    a.rel_eps = (KIND != APOP_SSM_LGMVN) ? 2e-5 : 0.0;   // fp32 tile partials of k_propagate
     a.step.sd = s->sd; a.step.log_mean_w = s->log_mean_w; a.step.ess = s->ess;
     a.step.filt = s->filt; a.step.anc = anc_new; a.step.t = t;
     a.step.reset = o->reset_weights; a.step.cond = cond ? 1 : 0;
-    a.step.has_x = o->want_filt ? 1 : 0;
+    a.step.has_x = (o->want_filt && dim == 1) ? 1 : 0;
     a.sharded = shard;
     if (shard) a.anc_peer = peer_i32(c, c->fab.off_anc);
     APOP_TRY(resample_enqueue(c, a));
@@ -728,6 +771,8 @@ static int sweep_group(apop_ctx* const* g, int ng, const apop_ssm* model, const 
         return run_group<APOP_SSM_SV>(g, ng, y, T, retained, opts, results);
     case APOP_SSM_HMM:
         return run_group<APOP_SSM_HMM>(g, ng, y, T, retained, opts, results);
+    case APOP_SSM_LGMVN:
+        return run_group<APOP_SSM_LGMVN>(g, ng, y, T, retained, opts, results);
     default:
         return set_err(c0, APOP_ERR_UNSUPPORTED, "model kind %d not supported by the fused sweep",
                        model->kind);
