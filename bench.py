@@ -37,6 +37,17 @@ KT_NAMES = {1: "k_propagate", 2: "k_tile_lse", 3: "k_finalize", 4: "k_fold_agg",
 #   k_ancestors K3+K4 scan + ancestor search (R 8 + W 4)            = 12
 ALGO_BYTES = {"k_propagate": 52.0, "k_fold_agg": 8.0, "k_ancestors": 12.0, "k_tile_lse": 8.0,
               "k_gather": 20.0}
+# The fused k_propagate never materialises the gathered state nor re-reads the
+# log-weights for the normalise partials, so the bytes it MUST move are
+# R anc 4 + R x 8 + W x 8 + W lw 8 = 28: the roofline fraction is quoted on those
+# (52 would read as > 100 % of HBM); the unfused figure is kept beside it.
+MOVED_BYTES = {"k_propagate": 28.0, "k_fold_agg": 8.0, "k_ancestors": 12.0, "k_tile_lse": 8.0,
+               "k_gather": 20.0}
+# dram__bytes_read.sum + dram__bytes_write.sum per launch at 2^27 particles from the
+# committed `ncu --set full` capture (profiles/r01g_ncu_full_summary.csv), bytes/particle
+NCU_TRAFFIC_PER_PARTICLE = {"k_propagate": (1.6199e9 + 2.0980e9) / (1 << 27),
+                            "k_fold_agg": (1.0746e9 + 0.0104e9) / (1 << 27),
+                            "k_ancestors": (1.0753e9 + 0.5089e9) / (1 << 27)}
 STEP_BYTES = 64.0          # whole particle-step: 32d + 32
 
 
@@ -240,12 +251,15 @@ def run_ours(args):
         if dom:
             name, (ms, c) = dom
             avg_s = ms / 1e3 / c
-            achieved = ALGO_BYTES[name] * n_local / avg_s / 1e9
+            achieved = MOVED_BYTES[name] * n_local / avg_s / 1e9
+            tr = NCU_TRAFFIC_PER_PARTICLE.get(name)
             roof = {"kernel": name, "bound": "hbm", "achieved": achieved, "peak": peak,
-                    "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+                    "unit": "GB/s", "frac": achieved / peak,
+                    "traffic": tr * n_local if tr else None,
+                    "unfused_algorithmic_bytes_per_particle": ALGO_BYTES[name],
                     "peak_source": f"{peak_kind} (MEASURED_PEAKS.json hbm_gbs)",
                     "avg_launch_us": avg_s * 1e6, "launches_timed": c,
-                    "algorithmic_bytes_per_particle": ALGO_BYTES[name]}
+                    "algorithmic_bytes_per_particle": MOVED_BYTES[name]}
         ksum_ms = sum(v[0] for v in kt.values())
         path = {"bytes_per_particle_step": STEP_BYTES,
                 "achieved_gbs": STEP_BYTES * n_local * T * args.steps / (dev_s) / 1e9,
