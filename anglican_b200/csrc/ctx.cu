@@ -141,7 +141,11 @@ int apop_create(apop_ctx** out, int64_t n_local, uint64_t seed, int device, int 
     c->n_global = n_local * world;
     c->g0 = n_local * rank;
     c->seed = seed;
-    if (cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) != cudaSuccess) {
+    // the engine stream takes the greatest priority so that helper work on
+    // low-priority side streams (noise prefetch, ssm.cu) only fills idle SMs
+    int prio_lo = 0, prio_hi = 0;
+    cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi);
+    if (cudaStreamCreateWithPriority(&c->stream, cudaStreamNonBlocking, prio_hi) != cudaSuccess) {
         delete c;
         return APOP_ERR_CUDA;
     }

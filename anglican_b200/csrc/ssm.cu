@@ -13,6 +13,7 @@
 //   K2..K4            resample_enqueue (resample.cu), ancestors in sorted order
 //       k_step_stats  log-mean-weight, ESS, filtering mean, next base weight
 #include <math.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include "apop_internal.cuh"
@@ -52,6 +53,16 @@ struct SweepState {
     size_t cap_n = 0, cap_T = 0, cap_hist = 0;
     const double* last_x = nullptr;    // pre-resample states of the last step
     const int32_t* last_anc = nullptr;
+    // transition-noise prefetch: the draws of step t+1 do not depend on step t, so
+    // a low-priority side stream generates them for the first z_tiles tiles while
+    // the single-CTA kernels of the resampler (k_finalize, k_chain) leave the
+    // other SMs idle; k_propagate then reads them instead of running Philox +
+    // Box-Muller.  Same device function, same bits.
+    cudaStream_t side = nullptr;
+    cudaEvent_t ev_prop[2] = {nullptr, nullptr}, ev_noise[2] = {nullptr, nullptr};
+    double* zbuf[2] = {nullptr, nullptr};
+    size_t z_cap = 0;                  // particles per buffer
+    int64_t z_tiles = 0;               // tiles prefetched per step of this sweep (0: off)
 };
 
 namespace apop {
@@ -60,9 +71,14 @@ void sweep_free(apop_ctx* c) {
     SweepState* s = c->sweep;
     if (!s) return;
     if (s->heap_backed) { s->xa = nullptr; s->xb = nullptr; s->anc = nullptr; }
+    if (s->side) { cudaStreamSynchronize(s->side); cudaStreamDestroy(s->side); }
+    for (int i = 0; i < 2; ++i) {
+        if (s->ev_prop[i]) cudaEventDestroy(s->ev_prop[i]);
+        if (s->ev_noise[i]) cudaEventDestroy(s->ev_noise[i]);
+    }
     void* ptrs[] = {s->xa, s->xb, s->lw, s->anc, s->x_hist, s->anc_hist, s->y, s->retained,
                     s->log_mean_w, s->ess, s->filt, s->tsx, s->x_final, s->sd, s->model, s->traj,
-                    s->mvn_mats};
+                    s->mvn_mats, s->zbuf[0], s->zbuf[1]};
     for (void* p : ptrs)
         if (p) cudaFree(p);
     delete s;
@@ -142,7 +158,8 @@ __device__ __forceinline__ void propagate_tile(const PeerF64& xpeer,
                                                double y, const double* __restrict__ retained_t,
                                                double wbase, int64_t n, int64_t g0, uint64_t seed,
                                                uint32_t t, double* __restrict__ tmax,
-                                               double* __restrict__ tsum, int* errflag) {
+                                               double* __restrict__ tsum, int* errflag,
+                                               const double* __restrict__ zpre) {
     __shared__ double red_mx[NWARP];
     __shared__ float red_ref[NWARP], red_s[NWARP];
     const int64_t base = (int64_t)blockIdx.x * TILE;
@@ -207,7 +224,14 @@ __device__ __forceinline__ void propagate_tile(const PeerF64& xpeer,
             }
         } else {
             double z0[2], z1[2];
-            normal_pairs_at<2>(seed, (uint64_t)(g0 + ih) >> 1, t, STREAM_TRANSITION, 0, z0, z1);
+            if (FULL && zpre) {
+                // this tile's draws were generated ahead of time by k_noise
+                const double2 za = __ldg(reinterpret_cast<const double2*>(zpre + ih));
+                const double2 zb = __ldg(reinterpret_cast<const double2*>(zpre + ih + 2));
+                z0[0] = za.x; z1[0] = za.y; z0[1] = zb.x; z1[1] = zb.y;
+            } else {
+                normal_pairs_at<2>(seed, (uint64_t)(g0 + ih) >> 1, t, STREAM_TRANSITION, 0, z0, z1);
+            }
 #pragma unroll
             for (int j = 0; j < HW; j += 2) {
                 x[j] = (M.a * x[j] + M.b) + M.q * z0[j >> 1];              // sd*z + mean
@@ -319,16 +343,34 @@ __global__ void __launch_bounds__(TB, 2) k_propagate(const ModelDev* __restrict_
                                                   int64_t g0, uint64_t seed, uint32_t t,
                                                   double* __restrict__ tmax,
                                                   double* __restrict__ tsum, int* errflag,
-                                                  const __grid_constant__ PeerF64 xpeer) {
+                                                  const __grid_constant__ PeerF64 xpeer,
+                                                  const double* __restrict__ zpre, int z_tiles) {
     const ModelDev& M = *Mp;
     const double y = yt[0];
     const double wbase = sd->base;
+    const double* zp = ((int)blockIdx.x < z_tiles) ? zpre : nullptr;     // CTA-uniform
     if ((int64_t)(blockIdx.x + 1) * TILE <= n)
         propagate_tile<KIND, true, SHARD>(xpeer, M, xp, anc, first_step, xn, lw, y, retained_t,
-                                          wbase, n, g0, seed, t, tmax, tsum, errflag);
+                                          wbase, n, g0, seed, t, tmax, tsum, errflag, zp);
     else
         propagate_tile<KIND, false, SHARD>(xpeer, M, xp, anc, first_step, xn, lw, y, retained_t,
-                                           wbase, n, g0, seed, t, tmax, tsum, errflag);
+                                           wbase, n, g0, seed, t, tmax, tsum, errflag, nullptr);
+}
+
+// transition noise of step t for the full tiles [0, gridDim.x): exactly the
+// draws propagate_tile would make (same counters, same Box-Muller code)
+__global__ void __launch_bounds__(TB) k_noise(double* __restrict__ z, int64_t g0, uint64_t seed,
+                                              uint32_t t) {
+    const int64_t i0 = (int64_t)blockIdx.x * TILE + (int64_t)threadIdx.x * IPT;
+#pragma unroll
+    for (int h = 0; h < IPT; h += 4) {
+        const int64_t ih = i0 + h;
+        double z0[2], z1[2];
+        normal_pairs_at<2>(seed, (uint64_t)(g0 + ih) >> 1, t, STREAM_TRANSITION, 0, z0, z1);
+        double2* q = reinterpret_cast<double2*>(z + ih);
+        q[0] = make_double2(z0[0], z1[0]);
+        q[1] = make_double2(z0[1], z1[1]);
+    }
 }
 
 __global__ void k_sweep_reset(SweepDev* sd, ResampleInfo* I) {
@@ -437,6 +479,48 @@ static int sweep_prepare(apop_ctx* c, int T, int dim, bool history) {
         }
     }
     s->n = c->n; s->T = T; s->dim = dim; s->history = history;
+    return APOP_OK;
+}
+
+// Noise prefetch set-up (host-blocking calls: staging phase only).
+// APOP_NOISE_PREFETCH_TILES = tiles per step (default 0 = off).  Measured on one
+// B200 at 2^27 particles (profiles/r01h_noise_prefetch.txt): the extra 16 B per
+// prefetched particle cost more than the idle SM time recovers (k_propagate is
+// already at ~60 % of HBM), so it is off by default.
+static int noise_prepare(apop_ctx* c, int kind, bool history) {
+    SweepState* s = c->sweep;
+    s->z_tiles = 0;
+    if (kind != APOP_SSM_LGSSM1D && kind != APOP_SSM_SV) return APOP_OK;
+    const int64_t full_tiles = c->n / TILE;
+    int64_t want = 0;
+    if (const char* e = getenv("APOP_NOISE_PREFETCH_TILES")) want = atoll(e);
+    if (want > full_tiles) want = full_tiles;
+    if (want <= 0) return APOP_OK;
+    (void)history;
+    if (!s->side) {
+        int lo = 0, hi = 0;
+        cudaDeviceGetStreamPriorityRange(&lo, &hi);          // lo: least priority
+        if (cudaStreamCreateWithPriority(&s->side, cudaStreamNonBlocking, lo) != cudaSuccess)
+            return set_err(c, APOP_ERR_CUDA, "sweep: side stream");
+        for (int i = 0; i < 2; ++i) {
+            if (cudaEventCreateWithFlags(&s->ev_prop[i], cudaEventDisableTiming) != cudaSuccess ||
+                cudaEventCreateWithFlags(&s->ev_noise[i], cudaEventDisableTiming) != cudaSuccess)
+                return set_err(c, APOP_ERR_CUDA, "sweep: events");
+        }
+    }
+    const size_t need = (size_t)want * TILE;
+    if (s->z_cap < need) {
+        cudaStreamSynchronize(s->side);
+        for (int i = 0; i < 2; ++i) {
+            if (s->zbuf[i]) cudaFree(s->zbuf[i]);
+            s->zbuf[i] = nullptr;
+        }
+        s->z_cap = 0;
+        APOP_TRY(dev_alloc(c, (void**)&s->zbuf[0], need * 8));
+        APOP_TRY(dev_alloc(c, (void**)&s->zbuf[1], need * 8));
+        s->z_cap = need;
+    }
+    s->z_tiles = want;
     return APOP_OK;
 }
 
@@ -557,6 +641,10 @@ static int sweep_begin(apop_ctx* c, const double* retained, const apop_sweep_opt
     c->launches += 2;
     s->last_x = x0;
     s->last_anc = s->anc;
+    if (s->z_tiles > 0) {
+        // the noise buffers may still be read by the previous sweep's last steps
+        for (int i = 0; i < 2; ++i) APOP_CUDA(c, cudaEventRecord(s->ev_prop[i], c->stream));
+    }
     return APOP_OK;
 }
 
@@ -572,6 +660,10 @@ static int sweep_step(apop_ctx* c, int t, const apop_sweep_opts* o, bool csmc) {
     const size_t dim = (size_t)s->dim;
     double* x_new = s->history ? s->x_hist + (size_t)t * n * dim : ((t & 1) ? s->xb : s->xa);
     int32_t* anc_new = s->history ? s->anc_hist + (size_t)(t - 1) * n : s->anc;
+    constexpr bool kGauss = (KIND == APOP_SSM_LGSSM1D || KIND == APOP_SSM_SV);
+    const int zt = (kGauss && t >= 2) ? (int)s->z_tiles : 0;      // step 1 draws inline
+    const double* zpre = zt ? s->zbuf[t & 1] : nullptr;
+    if (zt) APOP_CUDA(c, cudaStreamWaitEvent(c->stream, s->ev_noise[t & 1], 0));
     kt_begin(c, KT_PROPAGATE);
     if (KIND == APOP_SSM_LGMVN) {
         MvnSweepArgs ma;
@@ -588,17 +680,30 @@ static int sweep_step(apop_ctx* c, int t, const apop_sweep_opts* o, bool csmc) {
         const PeerF64 xpeer = peer_f64(c, (t & 1) ? c->fab.off_xa : c->fab.off_xb);   // x_{t-1}
         k_propagate<(KIND == APOP_SSM_LGMVN) ? APOP_SSM_LGSSM1D : KIND, true><<<nt, TB, 0, c->stream>>>(
             s->model, x_prev, anc_prev, t == 1, x_new, s->lw, s->y + (t - 1), nullptr, s->sd, n,
-            c->g0, c->seed, (uint32_t)t, ws.tmax, ws.tsum, &ws.info->err, xpeer);
+            c->g0, c->seed, (uint32_t)t, ws.tmax, ws.tsum, &ws.info->err, xpeer, zpre, zt);
     } else {
         PeerF64 none;
         memset(&none, 0, sizeof none);
         k_propagate<(KIND == APOP_SSM_LGMVN) ? APOP_SSM_LGSSM1D : KIND, false><<<nt, TB, 0, c->stream>>>(
             s->model, x_prev, anc_prev, t == 1, x_new, s->lw, s->y + (t - 1),
             csmc ? s->retained + t : nullptr, s->sd, n, c->g0, c->seed, (uint32_t)t, ws.tmax,
-            ws.tsum, &ws.info->err, none);
+            ws.tsum, &ws.info->err, none, zpre, zt);
     }
     kt_end(c, KT_PROPAGATE);
     c->launches += 1;
+    if (kGauss && s->z_tiles > 0) {
+        // propagate(t) has been enqueued: Z[t&1] is busy until it completes.  The
+        // draws of step t+1 go to the other buffer, last read by propagate(t-1).
+        APOP_CUDA(c, cudaEventRecord(s->ev_prop[t & 1], c->stream));
+        if (t < s->T) {
+            const int nb = (t + 1) & 1;
+            APOP_CUDA(c, cudaStreamWaitEvent(s->side, s->ev_prop[nb], 0));
+            k_noise<<<(int)s->z_tiles, TB, 0, s->side>>>(s->zbuf[nb], c->g0, c->seed,
+                                                         (uint32_t)(t + 1));
+            APOP_CUDA(c, cudaEventRecord(s->ev_noise[nb], s->side));
+            c->launches += 1;
+        }
+    }
     const bool cond = csmc && t <= o->n_cond_steps;
     c->step = (uint32_t)t;
     ResampleArgs a{};
@@ -735,7 +840,7 @@ static void preload_sweep_kernels() {
     preload(k_init<APOP_SSM_LGSSM1D>); preload(k_init<APOP_SSM_SV>); preload(k_init<APOP_SSM_HMM>);
     preload(k_propagate<APOP_SSM_LGSSM1D, true>); preload(k_propagate<APOP_SSM_SV, true>);
     preload(k_propagate<APOP_SSM_HMM, true>);
-    preload(k_sweep_reset); preload(k_gather_shard);
+    preload(k_sweep_reset); preload(k_gather_shard); preload(k_noise);
     preload_resample_kernels();
     preload_comm_kernels();
     cudaGetLastError();
@@ -762,6 +867,7 @@ static int sweep_group(apop_ctx* const* g, int ng, const apop_ssm* model, const 
         cudaSetDevice(c->device);
         if (c->world > 1) preload_sweep_kernels();
         APOP_TRY(sweep_prepare(c, T, dim, opts->keep_history != 0));
+        APOP_TRY(noise_prepare(c, model->kind, opts->keep_history != 0));
         APOP_TRY(upload_model(c, model));
     }
     switch (model->kind) {

@@ -80,3 +80,21 @@ def test_sharded_repeat_sweeps_and_seed():
             ref = pop.sweep(m, y, want_filt=False)
             assert outs[0].log_z == ref.log_z == outs[1].log_z
             assert np.array_equal(np.concatenate([o.x_final for o in outs]), ref.x_final)
+
+
+def test_sharded_with_noise_prefetch(monkeypatch):
+    """sharded sweep with the side-stream noise prefetch forced on for every
+    full tile == unsharded sweep with it off"""
+    from anglican_b200 import Population, PopulationGroup
+    from anglican_b200.models import StochasticVolatility
+    y = _sv_data(12)
+    m = StochasticVolatility()
+    monkeypatch.setenv("APOP_NOISE_PREFETCH_TILES", "0")
+    with Population(4 * 3 * 4096, seed=5) as pop:
+        ref = pop.sweep(m, y)
+    monkeypatch.setenv("APOP_NOISE_PREFETCH_TILES", "1000")
+    with PopulationGroup(3 * 4096, 4, seed=5) as grp:
+        outs = grp.sweep(m, y)
+    for o in outs:
+        assert o.log_z == ref.log_z
+    assert np.array_equal(np.concatenate([o.x_final for o in outs]), ref.x_final)

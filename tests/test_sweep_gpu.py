@@ -198,3 +198,32 @@ def test_gaussian_benchmark_posterior():
     q_mu, q_sd = g["post_mean"], g["post_sd"]
     kl = math.log(q_sd / sd) + (sd ** 2 + (mu - q_mu) ** 2) / (2 * q_sd ** 2) - 0.5
     assert kl < g["kl_threshold"], (mu, sd, kl)
+
+
+@pytest.mark.parametrize("kind", ["sv", "lgssm"])
+def test_noise_prefetch_is_bit_identical(kind, monkeypatch):
+    """The transition draws generated ahead of time on the side stream (k_noise)
+    must be the very numbers k_propagate would draw inline: sweeps with the
+    prefetch off, partial and covering every full tile agree bit for bit."""
+    from anglican_b200 import Population
+    from anglican_b200.models import LinearGaussian1D, StochasticVolatility
+    n, T = 9 * 4096 + 777, 9
+    m, y = ((StochasticVolatility(), _sv_data(T)) if kind == "sv"
+            else (LinearGaussian1D(), _lgssm_data(T)))
+    outs = []
+    for tiles in ("0", "4", "100000"):
+        monkeypatch.setenv("APOP_NOISE_PREFETCH_TILES", tiles)
+        with Population(n, seed=99) as pop:
+            launches0 = pop.launches
+            a = pop.sweep(m, y, want_filt=True)
+            b = pop.sweep(m, y, want_filt=True)       # buffers reused by the next sweep
+            outs.append((a, pop.launches - launches0))
+            assert a.log_z == b.log_z and np.array_equal(a.x_final, b.x_final)
+    ref, l0 = outs[0]
+    for o, l in outs[1:]:
+        assert l == l0 + 2 * (T - 1)                  # one k_noise per step after the first
+        assert o.log_z == ref.log_z
+        assert np.array_equal(o.log_mean_w, ref.log_mean_w)
+        assert np.array_equal(o.ess, ref.ess)
+        assert np.array_equal(o.filt_mean, ref.filt_mean)
+        assert np.array_equal(o.x_final, ref.x_final)
