@@ -67,6 +67,8 @@ _SIGS = [
     ("apop_synchronize", C.c_int, [_vp]),
     ("apop_num_particles", C.c_int64, [_vp]),
     ("apop_set_seed", C.c_int, [_vp, C.c_uint64]),
+    ("apop_host_alloc", C.c_int, [_vp, C.POINTER(_vp), C.c_uint64]),
+    ("apop_host_free", C.c_int, [_vp, _vp]),
     ("apop_launch_count", C.c_int64, [_vp]),
     ("apop_stream", _vp, [_vp]),
     ("apop_timer_begin", C.c_int, [_vp, C.c_int]),

@@ -17,7 +17,8 @@ NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = ["-O3", "-std=c++17", "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo",
          "--fmad=false",            # a*b+c must never fuse: exact-fold and parity arithmetic
          "-Xcompiler", "-fPIC", "-Xcompiler", "-fvisibility=default",
-         "--use-local-env" if False else "-Xcudafe", "--diag_suppress=177"]
+         "-Xcudafe", "--diag_suppress=177"]
+FLAGS += os.environ.get("APOP_NVCC_DEFS", "").split()      # tuning experiments (-DAPOP_...=..)
 
 
 def _srcs():

@@ -216,6 +216,25 @@ int apop_synchronize(apop_ctx* c) {
     return APOP_OK;
 }
 
+int apop_host_alloc(apop_ctx* c, void** out, uint64_t bytes) {
+    CHECK_CTX(c);
+    if (!out || bytes == 0) return set_err(c, APOP_ERR_INVALID, "host_alloc: bad arguments");
+    cudaSetDevice(c->device);
+    if (cudaHostAlloc(out, (size_t)bytes, cudaHostAllocDefault) != cudaSuccess) {
+        *out = nullptr;
+        cudaGetLastError();
+        return set_err(c, APOP_ERR_OOM, "host_alloc: %llu pinned bytes unavailable",
+                       (unsigned long long)bytes);
+    }
+    return APOP_OK;
+}
+
+int apop_host_free(apop_ctx* c, void* p) {
+    CHECK_CTX(c);
+    if (p) APOP_CUDA(c, cudaFreeHost(p));
+    return APOP_OK;
+}
+
 int64_t apop_num_particles(apop_ctx* c) { return c ? c->n : 0; }
 int64_t apop_launch_count(apop_ctx* c) { return c ? c->launches : 0; }
 void* apop_stream(apop_ctx* c) { return c ? (void*)c->stream : nullptr; }

@@ -30,6 +30,12 @@
 namespace apop {
 
 using WSView = ResampleWS;      // passed to kernels by value (device pointers only)
+#ifndef APOP_FOLD_CTAS
+#define APOP_FOLD_CTAS 3
+#endif
+#ifndef APOP_ANC_CTAS
+#define APOP_ANC_CTAS 3
+#endif
 static WSView view_of(const ResampleWS& w) { return w; }
 
 struct FoldSmem {
@@ -184,30 +190,41 @@ __device__ __noinline__ double cta_tile_fold(double S_in, const double (&w)[IPT]
     }
 }
 
+// raw tile values: the weights themselves (weights mode) or the log-weights
+__device__ __forceinline__ void load_raw(const double* __restrict__ lw,
+                                         const double* __restrict__ win, int64_t base,
+                                         int64_t n, double (&v)[IPT]) {
+    if (win) load_blocked(win, base, n, v, 0.0);
+    else load_blocked(lw, base, n, v, -INFINITY);      // out of range: -inf -> weight 0
+}
+// particle-weights (smc.cljc:70-84) from the raw tile values
+__device__ __forceinline__ void weights_from_raw(bool is_w, const double (&v)[IPT], int64_t base,
+                                                 int64_t n, double m, double (&w)[IPT]) {
+    if (is_w) {
+#pragma unroll
+        for (int j = 0; j < IPT; ++j) w[j] = v[j];
+    } else if (m > -INFINITY) {
+        double a[4], b[4];
+#pragma unroll
+        for (int h = 0; h < IPT; h += 4) {
+#pragma unroll
+            for (int j = 0; j < 4; ++j) a[j] = v[h + j];
+            fm::weights_v<4>(a, m, b);
+#pragma unroll
+            for (int j = 0; j < 4; ++j) w[h + j] = b[j];
+        }
+    } else {                                           // all -inf: every weight is 1 (smc.cljc:80)
+        const int64_t i0 = base + (int64_t)threadIdx.x * IPT;
+#pragma unroll
+        for (int j = 0; j < IPT; ++j) w[j] = (i0 + j < n) ? weight_from_lw(v[j], m) : 0.0;
+    }
+}
 __device__ __forceinline__ void load_weights(const double* __restrict__ lw,
                                              const double* __restrict__ win, int64_t base,
                                              int64_t n, double m, double (&w)[IPT]) {
-    if (win) {
-        load_blocked(win, base, n, w, 0.0);
-    } else {
-        double v[IPT];
-        load_blocked(lw, base, n, v, -INFINITY);     // out of range: -inf -> weight 0
-        if (m > -INFINITY) {
-            double a[4], b[4];
-#pragma unroll
-            for (int h = 0; h < IPT; h += 4) {
-#pragma unroll
-                for (int j = 0; j < 4; ++j) a[j] = v[h + j];
-                fm::weights_v<4>(a, m, b);
-#pragma unroll
-                for (int j = 0; j < 4; ++j) w[h + j] = b[j];
-            }
-        } else {                                       // all -inf: every weight is 1 (smc.cljc:80)
-            const int64_t i0 = base + (int64_t)threadIdx.x * IPT;
-#pragma unroll
-            for (int j = 0; j < IPT; ++j) w[j] = (i0 + j < n) ? weight_from_lw(v[j], m) : 0.0;
-        }
-    }
+    double v[IPT];
+    load_raw(lw, win, base, n, v);
+    weights_from_raw(win != nullptr, v, base, n, m, w);
 }
 
 // ------------------------------------------------------------------ K2
@@ -568,7 +585,7 @@ __device__ __noinline__ void hard_tile_prework(const double* __restrict__ lw,
     hard_tile_tables(w, eA, pa, sb, hw, warp_tot);
 }
 
-__global__ void __launch_bounds__(TB, 3) k_fold_agg(const double* __restrict__ lw,
+__global__ void __launch_bounds__(TB, APOP_FOLD_CTAS) k_fold_agg(const double* __restrict__ lw,
                                                     const double* __restrict__ win, int64_t n,
                                                     WSView v, const double* __restrict__ xf) {
     __shared__ Xd warp_tot[NWARP];
@@ -576,24 +593,16 @@ __global__ void __launch_bounds__(TB, 3) k_fold_agg(const double* __restrict__ l
     __shared__ double wa[NWARP], wb[NWARP];
     const int t = blockIdx.x;
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-    const int c0 = v.cls[0][t], c1 = v.cls[1][t];
-    const bool do0 = (c0 != kCtxHard), do1 = (c1 != kCtxHard && c1 != kCtxSkip);
     const int64_t base = (int64_t)t * TILE;
-    if (c0 == kCtxHard || c1 == kCtxHard) {          // rare, uniform per CTA
-#pragma unroll 1
-        for (int lap = 0; lap < 2; ++lap) {
-            if ((lap ? c1 : c0) != kCtxHard) continue;
-            const int h = v.hix[lap][t];
-            if (h < 0 || h >= v.hcap) continue;
-            const int eA = v.hctx[lap][h];
-            if (eA == kCtxHard) continue;
-            hard_tile_prework(lw, win, n, v.info->m, t, eA, v.hpa[lap] + (size_t)h * TILE,
-                              v.hsb[lap] + (size_t)h * TILE, v.hw[lap] + (size_t)h * TILE,
-                              warp_tot);
-        }
-    }
+    // every global read of the streaming path is issued up front so that the
+    // tile data, the classes and the max arrive in ONE memory round trip
+    double raw[IPT];
+    load_raw(lw, win, base, n, raw);
+    const int c0 = v.cls[0][t], c1 = v.cls[1][t];
+    const double m_glob = v.info->m;
+    const bool do0 = (c0 != kCtxHard), do1 = (c1 != kCtxHard && c1 != kCtxSkip);
     double w[IPT];
-    load_weights(lw, win, base, n, v.info->m, w);
+    weights_from_raw(win != nullptr, raw, base, n, m_glob, w);
     // accurate sum w, sum w^2 of the tile (ESS, log-mean-weight)
     double s = 0.0, s2 = 0.0;
 #pragma unroll
@@ -656,23 +665,40 @@ __global__ void __launch_bounds__(TB, 3) k_fold_agg(const double* __restrict__ l
             if (do1) v.agg[1][t] = x1;
         }
     }
-    if (!any_bad) return;
-    // ---- general path: parity transducers (ties) / bit-level quantisation
-    Xd a = xd_identity(), b = xd_identity();
+    if (any_bad) {
+        // ---- general path: parity transducers (ties) / bit-level quantisation
+        Xd a = xd_identity(), b = xd_identity();
 #pragma unroll
-    for (int j = 0; j < IPT; ++j) {
-        i64 f; int up, tie;
-        if (do0) { quantize(w[j], c0, f, up, tie); xd_push(a, f, up, tie); }
-        if (do1) { quantize(w[j], c1, f, up, tie); xd_push(b, f, up, tie); }
+        for (int j = 0; j < IPT; ++j) {
+            i64 f; int up, tie;
+            if (do0) { quantize(w[j], c0, f, up, tie); xd_push(a, f, up, tie); }
+            if (do1) { quantize(w[j], c1, f, up, tie); xd_push(b, f, up, tie); }
+        }
+        if (do0) {
+            (void)cta_excl_scan_xd(a, warp_tot);
+            if (threadIdx.x == 0) v.agg[0][t] = cta_total_xd(warp_tot);
+            __syncthreads();
+        }
+        if (do1) {
+            (void)cta_excl_scan_xd(b, warp_tot);
+            if (threadIdx.x == 0) v.agg[1][t] = cta_total_xd(warp_tot);
+        }
     }
-    if (do0) {
-        (void)cta_excl_scan_xd(a, warp_tot);
-        if (threadIdx.x == 0) v.agg[0][t] = cta_total_xd(warp_tot);
+    // ---- hard tiles (rare, uniform per CTA): tables for the chain kernel.  Last,
+    // so that the streaming path keeps no registers live across the call.
+    if (c0 == kCtxHard || c1 == kCtxHard) {
         __syncthreads();
-    }
-    if (do1) {
-        (void)cta_excl_scan_xd(b, warp_tot);
-        if (threadIdx.x == 0) v.agg[1][t] = cta_total_xd(warp_tot);
+#pragma unroll 1
+        for (int lap = 0; lap < 2; ++lap) {
+            if ((lap ? c1 : c0) != kCtxHard) continue;
+            const int h = v.hix[lap][t];
+            if (h < 0 || h >= v.hcap) continue;
+            const int eA = v.hctx[lap][h];
+            if (eA == kCtxHard) continue;
+            hard_tile_prework(lw, win, n, m_glob, t, eA, v.hpa[lap] + (size_t)h * TILE,
+                              v.hsb[lap] + (size_t)h * TILE, v.hw[lap] + (size_t)h * TILE,
+                              warp_tot);
+        }
     }
 }
 
@@ -1309,22 +1335,31 @@ __device__ __forceinline__ bool staged_emit(const Comb& comb, int e, double Sin,
     }
     const int W = (int)(C1 - C0);
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
-    for (int wb = 0; wb < W; wb += STAGE_CAP) {
-        const int wn = (W - wb < STAGE_CAP) ? (W - wb) : STAGE_CAP;
-        const int wn8 = (wn + 7) & ~7;
+    // windows of at most STAGE_CAP - 4 slots; inside shared memory the window is
+    // shifted by a0 = (destination address / 4) mod 4 so that 16-byte groups of
+    // the staging buffer line up with 16-byte groups of the output array and
+    // the copy-out runs on 128-bit loads and stores
+    constexpr int WCAP = STAGE_CAP - 4;
+    for (int wb = 0; wb < W; wb += WCAP) {
+        const int wn = (W - wb < WCAP) ? (W - wb) : WCAP;
+        const i64 slot0 = out_offset + slot_of(C0 + wb, lap, order, J, n_new);
+        const bool vec = (A.world == 1) && (order != APOP_ORDER_REFERENCE);
+        const int a0 = vec ? (int)((reinterpret_cast<uintptr_t>(A.local + slot0) >> 2) & 3) : 0;
+        const int tot = a0 + wn;
+        const int wn8 = (tot + 7) & ~7;
         for (int i = tid * 4; i < wn8; i += TB * 4)
             *reinterpret_cast<int4*>(&st.buf[i]) = make_int4(0, 0, 0, 0);
         __syncthreads();
-        if (W <= STAGE_CAP) {
+        if (W <= WCAP) {
 #pragma unroll
             for (int j = 0; j < IPT; ++j)
-                if (kst[j] < ks[j]) st.buf[kst[j]] = tid * IPT + j + 1;
+                if (kst[j] < ks[j]) st.buf[a0 + kst[j]] = tid * IPT + j + 1;
         } else {
 #pragma unroll
             for (int j = 0; j < IPT; ++j) {
                 const int a = kst[j] > wb ? kst[j] : wb;
                 const int b = ks[j] < wb + wn ? ks[j] : wb + wn;
-                if (a < b) st.buf[a - wb] = tid * IPT + j + 1;
+                if (a < b) st.buf[a0 + a - wb] = tid * IPT + j + 1;
             }
         }
         __syncthreads();
@@ -1374,14 +1409,22 @@ __device__ __forceinline__ bool staged_emit(const Comb& comb, int e, double Sin,
             __syncthreads();
         }
         // coalesced copy-out (the three orders are contiguous runs, ascending or descending)
-        const i64 slot0 = out_offset + slot_of(C0 + wb, lap, order, J, n_new);
-        if (A.world == 1) {
-            int32_t* dst = A.local + slot0;
-            if (order == APOP_ORDER_REFERENCE) {
-                for (int i = tid; i < wn; i += TB) dst[-i] = st.buf[i];
-            } else {
-                for (int i = tid; i < wn; i += TB) dst[i] = st.buf[i];
+        if (vec) {
+            // entries [a0, tot) of the buffer go to dst[0 .. wn); dst - a0 is 16-byte aligned
+            int32_t* dst = A.local + slot0 - a0;
+            const int g_lo = (a0 + 3) >> 2, g_hi = tot >> 2;          // full groups [g_lo, g_hi)
+            for (int g = g_lo + tid; g < g_hi; g += TB)
+                *reinterpret_cast<int4*>(dst + 4 * g) = *reinterpret_cast<const int4*>(&st.buf[4 * g]);
+            if (tid < 8) {
+                // ragged ends: the first group's [a0, 4) and the last group's [4 g_hi, tot)
+                const int i = (tid < 4) ? tid : 4 * g_hi + (tid - 4);
+                const bool head = (tid < 4) && i >= a0 && i < tot && g_lo > 0;
+                const bool tail = (tid >= 4) && i < tot && i >= a0 && (g_hi >= g_lo);
+                if (head || tail) dst[i] = st.buf[i];
             }
+        } else if (A.world == 1) {
+            int32_t* dst = A.local + slot0;
+            for (int i = tid; i < wn; i += TB) dst[-i] = st.buf[i];
         } else {
             // the window may straddle shard boundaries: the part beyond this
             // rank's slots is stored into the owner's array over NVLink
@@ -1461,7 +1504,7 @@ union AncSmem {
     StageSmem stage;
 };
 
-__global__ void __launch_bounds__(TB, 2) k_ancestors(const double* __restrict__ lw,
+__global__ void __launch_bounds__(TB, APOP_ANC_CTAS) k_ancestors(const double* __restrict__ lw,
                                                      const double* __restrict__ win, int64_t n,
                                                      int64_t g0, WSView v, int order,
                                                      int32_t* __restrict__ anc,
@@ -1471,39 +1514,50 @@ __global__ void __launch_bounds__(TB, 2) k_ancestors(const double* __restrict__ 
     __shared__ AncSmem sm;
     const Comb& comb = *v.comb;          // global (L1/L2 resident); the fast path reads one segment
     const ResampleInfo* I = v.info;
-    if (I->err) return;
     const int t = blockIdx.x;
-    const double x0 = v.comb->x0, xlast = v.comb->xlast;
+    const int64_t base = (int64_t)t * TILE;
+    // Every global read of the common path is issued here, unconditionally and
+    // before the first branch, so that the tile data and its metadata arrive in
+    // one memory round trip instead of a chain of dependent ones.
+    double raw[IPT];
+    load_raw(lw, win, base, n, raw);
+    const int ierr = I->err;
+    const double x0 = comb.x0, xlast = comb.xlast;
     const double si0 = v.sin[0][t], so0 = v.sin[0][t + 1];
     const double si1 = v.sin[1][t], so1 = v.sin[1][t + 1];
-    const bool need0 = (so0 > x0) && !(si0 > xlast);
-    const bool need1 = !(si1 > xlast);
-    if (!need0 && !need1) return;
-    const int64_t base = (int64_t)t * TILE;
+    const i64 c00 = v.cnt[0][t], c01 = v.cnt[0][t + 1];
+    const i64 c10 = v.cnt[1][t], c11 = v.cnt[1][t + 1];
+    const int cls0 = v.cls[0][t], cls1 = v.cls[1][t];
+    const int gs0 = v.gseg[0][t], gs1 = v.gseg[1][t];
+    const double m = I->m;
+    const i64 J = I->J, n_new = I->n_new;
+    if (ierr) return;
+    // a lap emits if some pointer falls into this tile
+    const bool do0 = (so0 > x0) && !(si0 > xlast) && (c00 != c01);
+    const bool do1 = !(si1 > xlast) && (c10 != c11);
+    if (!do0 && !do1) return;
     const int nvalid = (int)((n - base < TILE) ? (n - base) : TILE);
     const int i0 = threadIdx.x * IPT;
-    const double m = I->m;
-    __syncthreads();
-    const i64 J = I->J, n_new = I->n_new;
     AncOut A;
     A.local = anc; A.peerp = &ancp; A.world = world; A.nl = n;
-    for (int lap = 0; lap < 2; ++lap) {
-        if (lap == 0 ? !need0 : !need1) continue;
-        if (v.cnt[lap][t] == v.cnt[lap][t + 1]) continue;       // no pointer falls into this tile
+    // x0 is uniform on the wheel, so all tiles but the one holding x0 emit in
+    // exactly one lap: that lap consumes the preloaded tile ...
+    const int lap = do0 ? 0 : 1;
+    {
         const double Sin = lap ? si1 : si0;
-        const int cls = v.cls[lap][t];
+        const int cls = lap ? cls1 : cls0;
         bool fast = (cls != kCtxHard) && (cls != kCtxSkip) && ctx_fast_ok(cls) &&
                     (ctx_of(Sin) == cls);
         if (fast) {
             double incD[IPT];
             {
                 double w[IPT];
-                load_weights(lw, win, base, n, m, w);
+                weights_from_raw(win != nullptr, raw, base, n, m, w);
                 fast = tile_quantize_f64(cls, w, incD);
             }
             if (fast)
-                fast = staged_emit(comb, cls, Sin, lap ? so1 : so0, v.cnt[lap][t],
-                                   v.cnt[lap][t + 1], v.gseg[lap][t], incD, (int32_t)(g0 + base),
+                fast = staged_emit(comb, cls, Sin, lap ? so1 : so0, lap ? c10 : c00,
+                                   lap ? c11 : c01, lap ? gs1 : gs0, incD, (int32_t)(g0 + base),
                                    A, out_offset, J, n_new, order, lap, sm.stage, &v.info->err);
         }
         if (!fast) {
@@ -1515,6 +1569,16 @@ __global__ void __launch_bounds__(TB, 2) k_ancestors(const double* __restrict__ 
             __syncthreads();
             generic_emit(comb, Sin, w, nvalid, (int32_t)(g0 + base + i0), E, sm.fold);
         }
+    }
+    // ... and the tile that straddles x0 emits its second lap on the general path
+    if (do0 && do1) {
+        EmitCtx E;
+        E.out = A; E.out_offset = out_offset; E.J = J; E.n_new = n_new; E.order = order;
+        E.lap = 1;
+        double w[IPT];
+        load_weights(lw, win, base, n, m, w);
+        __syncthreads();
+        generic_emit(comb, si1, w, nvalid, (int32_t)(g0 + base + i0), E, sm.fold);
     }
 }
 

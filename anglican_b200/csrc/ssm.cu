@@ -20,6 +20,13 @@
 #include "fastmath.cuh"
 #include "rng.cuh"
 
+#ifndef APOP_PROP_HW
+#define APOP_PROP_HW 2
+#endif
+#ifndef APOP_PROP_CTAS
+#define APOP_PROP_CTAS 3
+#endif
+
 namespace apop {
 
 // ------------------------------------------------------------------ state
@@ -165,7 +172,7 @@ __device__ __forceinline__ void propagate_tile(const PeerF64& xpeer,
     const int64_t base = (int64_t)blockIdx.x * TILE;
     const int64_t i0 = base + (int64_t)threadIdx.x * IPT;
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-    constexpr int HW = 4;                         // particles per half-step (register budget)
+    constexpr int HW = APOP_PROP_HW;              // particles per sub-step (register budget)
     constexpr float kL2E = 1.4426950408889634f;
     // running per-thread partials: exact max, fp32 (reference, sum of exp) pair
     double mx = -INFINITY;
@@ -188,8 +195,13 @@ __device__ __forceinline__ void propagate_tile(const PeerF64& xpeer,
 #pragma unroll
                 for (int j = 0; j < HW; ++j) par[j] = (int32_t)(ih + j);
             } else if (inb) {
-                const int4 a = __ldg(reinterpret_cast<const int4*>(anc + ih));
-                par[0] = a.x; par[1] = a.y; par[2] = a.z; par[3] = a.w;
+                if (HW == 4) {
+                    const int4 a = __ldg(reinterpret_cast<const int4*>(anc + ih));
+                    par[0] = a.x; par[1] = a.y; par[HW - 2] = a.z; par[HW - 1] = a.w;
+                } else {
+                    const int2 a = __ldg(reinterpret_cast<const int2*>(anc + ih));
+                    par[0] = a.x; par[1] = a.y;
+                }
             } else {
 #pragma unroll
                 for (int j = 0; j < HW; ++j) par[j] = (ih + j < n) ? anc[ih + j] : 0;
@@ -223,14 +235,16 @@ __device__ __forceinline__ void propagate_tile(const PeerF64& xpeer,
                 x[j] = (double)discrete_draw(M.hmm_trans + (int)x[j] * M.dim, M.dim, u);
             }
         } else {
-            double z0[2], z1[2];
+            double z0[HW / 2], z1[HW / 2];
             if (FULL && zpre) {
                 // this tile's draws were generated ahead of time by k_noise
-                const double2 za = __ldg(reinterpret_cast<const double2*>(zpre + ih));
-                const double2 zb = __ldg(reinterpret_cast<const double2*>(zpre + ih + 2));
-                z0[0] = za.x; z1[0] = za.y; z0[1] = zb.x; z1[1] = zb.y;
+#pragma unroll
+                for (int j = 0; j < HW / 2; ++j) {
+                    const double2 za = __ldg(reinterpret_cast<const double2*>(zpre + ih + 2 * j));
+                    z0[j] = za.x; z1[j] = za.y;
+                }
             } else {
-                normal_pairs_at<2>(seed, (uint64_t)(g0 + ih) >> 1, t, STREAM_TRANSITION, 0, z0, z1);
+                normal_pairs_at<HW / 2>(seed, (uint64_t)(g0 + ih) >> 1, t, STREAM_TRANSITION, 0, z0, z1);
             }
 #pragma unroll
             for (int j = 0; j < HW; j += 2) {
@@ -333,7 +347,7 @@ __device__ __forceinline__ void propagate_tile(const PeerF64& xpeer,
 }
 
 template <int KIND, bool SHARD>
-__global__ void __launch_bounds__(TB, 2) k_propagate(const ModelDev* __restrict__ Mp,
+__global__ void __launch_bounds__(TB, APOP_PROP_CTAS) k_propagate(const ModelDev* __restrict__ Mp,
                                                   const double* __restrict__ xp,
                                                   const int32_t* __restrict__ anc, int first_step,
                                                   double* __restrict__ xn, double* __restrict__ lw,

@@ -70,10 +70,14 @@ class Population:
         self.n = int(n)
         self.seed = int(seed)
         self.rank, self.world = rank, world
+        self._pin = None
 
     # ------------------------------------------------------------ lifecycle
     def close(self):
         if self.ctx:
+            if getattr(self, "_pin", None) is not None:
+                self.lib.apop_host_free(self.ctx, self._pin[0])
+                self._pin = None
             self.lib.apop_destroy(self.ctx)
             self.ctx = C.c_void_p()
 
@@ -257,10 +261,26 @@ class Population:
         L.check(self.ctx, self.lib.apop_set_seed(self.ctx, int(seed)))
         self.seed = int(seed)
 
+    def _pinned_f64(self, count):
+        """page-locked result buffer owned by this population (reused by every
+        sweep that asks for it; freed on close)"""
+        if self._pin is None or self._pin[1] < count:
+            if self._pin is not None:
+                L.check(self.ctx, self.lib.apop_host_free(self.ctx, self._pin[0]))
+                self._pin = None
+            p = C.c_void_p()
+            L.check(self.ctx, self.lib.apop_host_alloc(self.ctx, C.byref(p), int(count) * 8))
+            self._pin = (p, int(count))
+        buf = (C.c_double * count).from_address(self._pin[0].value)
+        return np.frombuffer(buf, dtype=np.float64, count=count)
+
     def sweep(self, model, y, retained=None, csmc=False, n_cond_steps=0, reset_weights=False,
-              keep_history=False, want_final=True, want_stats=True, want_filt=None):
+              keep_history=False, want_final=True, want_stats=True, want_filt=None,
+              pinned_final=False):
         """One `sweep` (smc.cljc:35-51; conditional: pgibbs.cljc:76-110,
-        ipmcmc.cljc:34-83).  Returns a SweepOutput."""
+        ipmcmc.cljc:34-83).  Returns a SweepOutput.  pinned_final: x_final is a
+        view of a page-locked buffer owned by the population, overwritten by its
+        next sweep (copy it to keep it)."""
         y = np.ascontiguousarray(y, dtype=np.float64)
         d = model.state_dim
         T = y.size // d
@@ -278,7 +298,11 @@ class Population:
             out.filt_mean = np.empty(T * d)
             res.filt_mean = _dp(out.filt_mean)
         if want_final:
-            out.x_final = np.empty((self.n, d)) if d > 1 else np.empty(self.n)
+            if pinned_final:
+                flat = self._pinned_f64(self.n * d)
+                out.x_final = flat.reshape(self.n, d) if d > 1 else flat
+            else:
+                out.x_final = np.empty((self.n, d)) if d > 1 else np.empty(self.n)
             res.x_final = _dp(out.x_final)
         ret = None
         if retained is not None:

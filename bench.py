@@ -229,11 +229,14 @@ def run_ours(args):
 
     # ---- e2e: public call, host buffers in/out, copies inside the timed region
     x_host_bytes = n_local * 8
+    # untimed: allocates the population's page-locked result buffer
+    pop.sweep(model, y[:4], want_final=True, want_stats=True, pinned_final=True)
     barrier()
     e0 = time.perf_counter()
     for i in range(args.steps):
         pop.set_seed(3000 + i)
-        out = pop.sweep(model, y, want_final=True, want_stats=True)
+        out = pop.sweep(model, y, want_final=True, want_stats=True, pinned_final=True)
+        x_mean = float(out.x_final[::4096].mean())      # the host reads the result
     barrier()
     e2e_s = time.perf_counter() - e0
 

@@ -84,6 +84,14 @@ int apop_synchronize(apop_ctx* ctx);
 int64_t apop_num_particles(apop_ctx* ctx);
 /* re-key the counter-based RNG (one key per sweep makes sweeps independent) */
 int apop_set_seed(apop_ctx* ctx, uint64_t seed);
+/* Page-locked host buffers for results that the caller reads back every sweep
+ * (the final particle states: 8 B x n).  A JVM binding allocates its result
+ * segments here once (Panama: MemorySegment.ofAddress; JNI: NewDirectByteBuffer)
+ * so that device->host copies run at PCIe speed instead of through the
+ * driver's pageable staging.  Replaces nothing in the reference (its states are
+ * JVM heap objects, smc.cljc:127-129); free with apop_host_free. */
+int apop_host_alloc(apop_ctx* ctx, void** out, uint64_t bytes);
+int apop_host_free(apop_ctx* ctx, void* p);
 /* number of kernels this ctx has launched so far (bench `gpu_launches`) */
 int64_t apop_launch_count(apop_ctx* ctx);
 /* raw CUDA stream (cudaStream_t) so callers can record events on it */
