@@ -118,11 +118,18 @@ _SIGS = [
     ("apop_trace_lineage", C.c_int, [_vp, C.c_int64, c_double_p]),
     ("apop_sweep_download_history", C.c_int, [_vp, c_int32_p, c_double_p]),
     ("apop_sweep_final_device", C.c_int, [_vp, C.POINTER(_vp)]),
+    ("apop_empirical_moments", C.c_int, [_vp, C.c_int32, C.c_int32, C.c_int32, c_double_p,
+                                         c_double_p, c_double_p, c_double_p]),
+    ("apop_empirical_covariance", C.c_int, [_vp, C.c_int32, C.c_int32, C.c_int32, c_double_p,
+                                            c_double_p]),
+    ("apop_collect_discrete", C.c_int, [_vp, C.c_int32, C.c_int32, C.c_int32, c_double_p,
+                                        c_double_p]),
     ("apop_pimh_accept", C.c_int, [C.c_double, C.c_double, C.c_double]),
     ("apop_ipmcmc_gibbs", C.c_int, [c_double_p, C.c_int, C.c_int, c_double_p, c_int32_p,
                                     c_double_p]),
     ("apop_ipmcmc_exchange_logz", C.c_int, [_vp, c_double_p, C.c_int, c_double_p]),
 ]
+COL_SWEEP_FINAL = -2
 DECLARED_SYMBOLS = [s[0] for s in _SIGS]
 
 _lib = None

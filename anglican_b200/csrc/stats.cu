@@ -1,0 +1,413 @@
+// stats.cu — result-side reductions of anglican.stat on the device (reference
+// src/anglican/stat.cljc): empirical-expectation / -mean / -variance / -std /
+// -skew / -kurtosis (56-120), empirical-covariance (84-91), collect-by +
+// empirical-distribution for discrete values (7-54).  The reference folds a
+// Clojure seq of [x log-w] pairs on the JVM, which would mean downloading every
+// particle (1 GiB per column at 2^27); here the particles stay in HBM and only
+// the moments cross the boundary.
+//
+// Weights follow stat.cljc:63-68: w_i = exp(lw_i - max lw).  Sums are plain
+// fp64 tree sums in a FIXED order (grid and block shape do not depend on the
+// device), so results are reproducible run to run; they differ from the
+// reference's left fold only by summation order (tests: 1e-12 relative, the
+// tolerance of stat_test.cljc:16).
+#include <math.h>
+
+#include "apop_internal.cuh"
+#include "fastmath.cuh"
+
+namespace apop {
+
+constexpr int SB = 256;                 // threads per stats CTA
+constexpr int SGRID = 592;              // 148 SMs x 4 resident CTAs
+constexpr int SCH = 8;                  // columns handled per pass over the particles
+
+__device__ __forceinline__ double stat_weight(const double* __restrict__ lw, int64_t i, double m) {
+    if (!lw) return 1.0;
+    const double l = lw[i];
+    if (l == m) return 1.0;                       // also covers m = +/-inf
+    if (!(l > -INFINITY)) return 0.0;
+    return fm::exp_any(l - m);
+}
+
+__device__ __forceinline__ double block_reduce_sum(double v, double* sm /*[SB/32]*/) {
+    v = warp_sum(v);
+    __syncthreads();
+    if ((threadIdx.x & 31) == 0) sm[threadIdx.x >> 5] = v;
+    __syncthreads();
+    double r = 0.0;
+    if (threadIdx.x < 32) {
+        r = (threadIdx.x < SB / 32) ? sm[threadIdx.x] : 0.0;
+        r = warp_sum(r);
+    }
+    return r;                                     // valid in thread 0
+}
+
+// partial maxima of the log-weights -> part[blockIdx.x]
+__global__ void __launch_bounds__(SB) k_stat_max(const double* __restrict__ lw, int64_t n,
+                                                 double* __restrict__ part) {
+    __shared__ double sm[SB / 32];
+    double mx = -INFINITY;
+    for (int64_t i = (int64_t)blockIdx.x * SB + threadIdx.x; i < n; i += (int64_t)gridDim.x * SB) {
+        const double l = lw[i];
+        mx = (l > mx || l != l) ? l : mx;         // NaN propagates like clojure.core/max
+    }
+    mx = warp_max(mx);
+    if ((threadIdx.x & 31) == 0) sm[threadIdx.x >> 5] = mx;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double a = sm[0];
+        for (int i = 1; i < SB / 32; ++i) a = fmax(a, sm[i]);
+        part[blockIdx.x] = a;
+    }
+}
+
+__device__ __forceinline__ double max_of_parts(const double* __restrict__ part, int g) {
+    double a = -INFINITY;
+    for (int i = 0; i < g; ++i) a = fmax(a, part[i]);       // every thread: tiny, L1 resident
+    return a;
+}
+
+// pass 1: sum w and sum w x_c for columns [c0, c0 + nc) -> part[blockIdx.x][1 + SCH]
+__global__ void __launch_bounds__(SB) k_stat_m1(const double* __restrict__ x,
+                                                const double* __restrict__ lw, int64_t n,
+                                                int width, int c0, int nc,
+                                                const double* __restrict__ mparts, int gm,
+                                                double* __restrict__ part) {
+    __shared__ double sm[SB / 32];
+    const double m = lw ? max_of_parts(mparts, gm) : 0.0;
+    double sw = 0.0, sx[SCH];
+#pragma unroll
+    for (int k = 0; k < SCH; ++k) sx[k] = 0.0;
+    for (int64_t i = (int64_t)blockIdx.x * SB + threadIdx.x; i < n; i += (int64_t)gridDim.x * SB) {
+        const double w = stat_weight(lw, i, m);
+        sw += w;
+        const double* row = x + i * width + c0;
+#pragma unroll
+        for (int k = 0; k < SCH; ++k)
+            if (k < nc) sx[k] += w * row[k];
+    }
+    double r = block_reduce_sum(sw, sm);
+    if (threadIdx.x == 0) part[(size_t)blockIdx.x * (1 + SCH)] = r;
+#pragma unroll
+    for (int k = 0; k < SCH; ++k) {
+        r = block_reduce_sum(sx[k], sm);
+        if (threadIdx.x == 0) part[(size_t)blockIdx.x * (1 + SCH) + 1 + k] = r;
+    }
+}
+
+// pass 2: sum w d^2, w d^3, w d^4 with d = x_c - mean_c -> part[blockIdx.x][3 * SCH]
+__global__ void __launch_bounds__(SB) k_stat_m2(const double* __restrict__ x,
+                                                const double* __restrict__ lw, int64_t n,
+                                                int width, int c0, int nc,
+                                                const double* __restrict__ mparts, int gm,
+                                                const double* __restrict__ mean,
+                                                double* __restrict__ part) {
+    __shared__ double sm[SB / 32];
+    const double m = lw ? max_of_parts(mparts, gm) : 0.0;
+    double s2[SCH], s3[SCH], s4[SCH], mu[SCH];
+#pragma unroll
+    for (int k = 0; k < SCH; ++k) { s2[k] = s3[k] = s4[k] = 0.0; mu[k] = (k < nc) ? mean[c0 + k] : 0.0; }
+    for (int64_t i = (int64_t)blockIdx.x * SB + threadIdx.x; i < n; i += (int64_t)gridDim.x * SB) {
+        const double w = stat_weight(lw, i, m);
+        const double* row = x + i * width + c0;
+#pragma unroll
+        for (int k = 0; k < SCH; ++k)
+            if (k < nc) {
+                const double d = row[k] - mu[k];
+                const double d2 = d * d;
+                s2[k] += w * d2;
+                s3[k] += w * (d2 * d);
+                s4[k] += w * (d2 * d2);
+            }
+    }
+#pragma unroll
+    for (int k = 0; k < SCH; ++k) {
+        double r = block_reduce_sum(s2[k], sm);
+        if (threadIdx.x == 0) part[(size_t)blockIdx.x * (3 * SCH) + k] = r;
+        r = block_reduce_sum(s3[k], sm);
+        if (threadIdx.x == 0) part[(size_t)blockIdx.x * (3 * SCH) + SCH + k] = r;
+        r = block_reduce_sum(s4[k], sm);
+        if (threadIdx.x == 0) part[(size_t)blockIdx.x * (3 * SCH) + 2 * SCH + k] = r;
+    }
+}
+
+// fixed-order sum of the per-block partials: out[j] = sum_b part[b][j] (* scale)
+__global__ void __launch_bounds__(SB) k_stat_fin(const double* __restrict__ part, int g, int stride,
+                                                 int cols, double* __restrict__ out) {
+    __shared__ double sm[SB / 32];
+    for (int j = blockIdx.x; j < cols; j += gridDim.x) {
+        double a = 0.0;
+        for (int b = threadIdx.x; b < g; b += SB) a += part[(size_t)b * stride + j];
+        const double r = block_reduce_sum(a, sm);
+        if (threadIdx.x == 0) out[j] = r;
+        __syncthreads();
+    }
+}
+
+// mean_c = sum w x_c / sum w  (stat.cljc:56-74), written to the device mean vector
+__global__ void k_stat_mean(const double* __restrict__ sums /*[1 + SCH]*/, int c0, int nc,
+                            double* __restrict__ mean, double* __restrict__ sumw) {
+    const int k = threadIdx.x;
+    if (k < nc) mean[c0 + k] = sums[1 + k] / sums[0];
+    if (k == 0) *sumw = sums[0];
+}
+
+// empirical-covariance (stat.cljc:84-91): sum_i w_i (x_i - mu)(x_i - mu)^T.
+// A CTA stages CP particles' deviations in shared memory; thread e owns the
+// entries e, e + SB, ... of the d x d matrix.  -> part[blockIdx.x][d * d]
+constexpr int CP = 32;
+constexpr int CMAXD = 64;
+__global__ void __launch_bounds__(SB) k_stat_cov(const double* __restrict__ x,
+                                                 const double* __restrict__ lw, int64_t n, int d,
+                                                 const double* __restrict__ mparts, int gm,
+                                                 const double* __restrict__ mean,
+                                                 double* __restrict__ part) {
+    __shared__ double D[CP][CMAXD + 1];
+    __shared__ double W[CP];
+    __shared__ double mu[CMAXD];
+    const double m = lw ? max_of_parts(mparts, gm) : 0.0;
+    const int dd = d * d;
+    constexpr int EPT = (CMAXD * CMAXD + SB - 1) / SB;
+    double acc[EPT];
+#pragma unroll
+    for (int k = 0; k < EPT; ++k) acc[k] = 0.0;
+    if (threadIdx.x < d) mu[threadIdx.x] = mean[threadIdx.x];
+    __syncthreads();
+    const int64_t chunks = (n + CP - 1) / CP;
+    for (int64_t ch = blockIdx.x; ch < chunks; ch += gridDim.x) {
+        const int64_t p0 = ch * CP;
+        for (int e = threadIdx.x; e < CP * d; e += SB) {
+            const int p = e / d, c = e - p * d;
+            D[p][c] = (p0 + p < n) ? x[(p0 + p) * d + c] - mu[c] : 0.0;
+        }
+        if (threadIdx.x < CP)
+            W[threadIdx.x] = (p0 + threadIdx.x < n) ? stat_weight(lw, p0 + threadIdx.x, m) : 0.0;
+        __syncthreads();
+#pragma unroll
+        for (int k = 0; k < EPT; ++k) {
+            const int e = threadIdx.x + k * SB;
+            if (e < dd) {
+                const int a = e / d, b = e - a * d;
+                double s = acc[k];
+                for (int p = 0; p < CP; ++p) s += W[p] * (D[p][a] * D[p][b]);
+                acc[k] = s;
+            }
+        }
+        __syncthreads();
+    }
+#pragma unroll
+    for (int k = 0; k < EPT; ++k) {
+        const int e = threadIdx.x + k * SB;
+        if (e < dd) part[(size_t)blockIdx.x * dd + e] = acc[k];
+    }
+}
+
+// collect-by over discrete values 0..K-1 (stat.cljc:7-24): per-value sum of
+// weights.  Shared-memory privatised histogram, one atomicAdd per particle.
+// -> part[blockIdx.x][K + 1] (last entry: weight of out-of-range values)
+template <typename T>
+__global__ void __launch_bounds__(SB) k_stat_hist(const T* __restrict__ v,
+                                                  const double* __restrict__ lw, int64_t n, int K,
+                                                  const double* __restrict__ mparts, int gm,
+                                                  double* __restrict__ part) {
+    extern __shared__ double h[];
+    const double m = lw ? max_of_parts(mparts, gm) : 0.0;
+    for (int k = threadIdx.x; k <= K; k += SB) h[k] = 0.0;
+    __syncthreads();
+    for (int64_t i = (int64_t)blockIdx.x * SB + threadIdx.x; i < n; i += (int64_t)gridDim.x * SB) {
+        const double w = stat_weight(lw, i, m);
+        const double fv = (double)v[i];
+        const int k = (fv >= 0.0 && fv < (double)K && fv == floor(fv)) ? (int)fv : K;
+        atomicAdd(&h[k], w);
+    }
+    __syncthreads();
+    for (int k = threadIdx.x; k <= K; k += SB) part[(size_t)blockIdx.x * (K + 1) + k] = h[k];
+}
+
+// ------------------------------------------------------------------ host
+struct StatBufs {
+    double *mparts, *part, *sums, *mean, *sumw;
+    int g;
+};
+
+static int stat_inputs(apop_ctx* c, apop_col xcol, int want_dtype, int width, apop_col lwcol,
+                       const void** x, int* dtype, const double** lw) {
+    if (xcol == APOP_COL_SWEEP_FINAL) {
+        void* p = nullptr;
+        APOP_TRY(apop_sweep_final_device(c, &p));
+        *x = p;
+        *dtype = APOP_F64;
+    } else {
+        Column* col = get_col(c, xcol, want_dtype, width);
+        if (!col) return APOP_ERR_INVALID;
+        *x = col->ptr;
+        *dtype = col->dtype;
+    }
+    *lw = nullptr;
+    if (lwcol >= 0) {
+        Column* l = get_col(c, lwcol, APOP_F64, 1);
+        if (!l) return APOP_ERR_INVALID;
+        *lw = (const double*)l->ptr;
+    }
+    return APOP_OK;
+}
+
+static int stat_bufs(apop_ctx* c, size_t part_cols, size_t width, StatBufs* B) {
+    const int64_t n = c->n;
+    int g = (int)((n + SB - 1) / SB);
+    if (g > SGRID) g = SGRID;
+    if (g < 1) g = 1;
+    const size_t doubles = (size_t)SGRID + (size_t)SGRID * part_cols + part_cols + width + 8;
+    APOP_TRY(ensure_scratch(c, doubles * sizeof(double)));
+    double* p = (double*)c->scratch;
+    B->mparts = p; p += SGRID;
+    B->part = p; p += (size_t)SGRID * part_cols;
+    B->sums = p; p += part_cols;
+    B->mean = p; p += width;
+    B->sumw = p;
+    B->g = g;
+    return APOP_OK;
+}
+
+// weighted mean of every column into B.mean (device), sum of weights into B.sumw
+static int stat_mean_enqueue(apop_ctx* c, const double* x, const double* lw, int width,
+                             const StatBufs& B) {
+    const int64_t n = c->n;
+    if (lw) { k_stat_max<<<B.g, SB, 0, c->stream>>>(lw, n, B.mparts); c->launches += 1; }
+    for (int c0 = 0; c0 < width; c0 += SCH) {
+        const int nc = (width - c0 < SCH) ? (width - c0) : SCH;
+        k_stat_m1<<<B.g, SB, 0, c->stream>>>(x, lw, n, width, c0, nc, B.mparts, B.g, B.part);
+        k_stat_fin<<<1 + SCH, SB, 0, c->stream>>>(B.part, B.g, 1 + SCH, 1 + SCH, B.sums);
+        k_stat_mean<<<1, 32, 0, c->stream>>>(B.sums, c0, nc, B.mean, B.sumw);
+        c->launches += 3;
+    }
+    return APOP_OK;
+}
+
+} // namespace apop
+
+using namespace apop;
+
+extern "C" {
+
+int apop_empirical_moments(apop_ctx* c, apop_col xcol, apop_col lwcol, int32_t width, double* mean,
+                           double* var, double* skew, double* kurt) {
+    if (!c) return APOP_ERR_INVALID;
+    if (width < 1 || width > 4096) return set_err(c, APOP_ERR_INVALID, "moments: bad width");
+    cudaSetDevice(c->device);
+    const void* xv; const double* lw; int dt;
+    APOP_TRY(stat_inputs(c, xcol, APOP_F64, width, lwcol, &xv, &dt, &lw));
+    const double* x = (const double*)xv;
+    StatBufs B;
+    APOP_TRY(stat_bufs(c, 3 * SCH + 1, (size_t)width, &B));
+    kt_begin(c, KT_STATS);
+    APOP_TRY(stat_mean_enqueue(c, x, lw, width, B));
+    std::vector<double> hmean(width), hm(3 * (size_t)width);
+    double hsumw = 0.0;
+    APOP_CUDA(c, cudaMemcpyAsync(hmean.data(), B.mean, sizeof(double) * width,
+                                 cudaMemcpyDeviceToHost, c->stream));
+    APOP_CUDA(c, cudaMemcpyAsync(&hsumw, B.sumw, sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+    const bool higher = var || skew || kurt;
+    if (higher) {
+        for (int c0 = 0; c0 < width; c0 += SCH) {
+            const int nc = (width - c0 < SCH) ? (width - c0) : SCH;
+            k_stat_m2<<<B.g, SB, 0, c->stream>>>(x, lw, c->n, width, c0, nc, B.mparts, B.g, B.mean,
+                                                 B.part);
+            k_stat_fin<<<3 * SCH, SB, 0, c->stream>>>(B.part, B.g, 3 * SCH, 3 * SCH, B.sums);
+            c->launches += 2;
+            for (int q = 0; q < 3; ++q)
+                APOP_CUDA(c, cudaMemcpyAsync(hm.data() + (size_t)q * width + c0, B.sums + q * SCH,
+                                             sizeof(double) * nc, cudaMemcpyDeviceToHost, c->stream));
+        }
+    }
+    kt_end(c, KT_STATS);
+    APOP_CUDA(c, cudaStreamSynchronize(c->stream));
+    if (!(hsumw > 0.0) || hsumw != hsumw)
+        return set_err(c, APOP_ERR_ZERO_WEIGHT, "moments: total weight %g", hsumw);
+    for (int k = 0; k < width; ++k) {
+        if (mean) mean[k] = hmean[k];
+        if (!higher) continue;
+        const double v = hm[k] / hsumw;                              // stat.cljc:93-98
+        const double s = sqrt(v);                                    // :100-104
+        if (var) var[k] = v;
+        if (skew) skew[k] = (hm[(size_t)width + k] / hsumw) / (s * s * s);          // :106-112
+        if (kurt) kurt[k] = (hm[2 * (size_t)width + k] / hsumw) / (v * v);          // :114-120
+    }
+    return APOP_OK;
+}
+
+int apop_empirical_covariance(apop_ctx* c, apop_col xcol, apop_col lwcol, int32_t width,
+                              double* mean, double* cov) {
+    if (!c) return APOP_ERR_INVALID;
+    if (width < 1 || width > CMAXD || !cov)
+        return set_err(c, APOP_ERR_INVALID, "covariance: 1 <= width <= %d", CMAXD);
+    cudaSetDevice(c->device);
+    const void* xv; const double* lw; int dt;
+    APOP_TRY(stat_inputs(c, xcol, APOP_F64, width, lwcol, &xv, &dt, &lw));
+    const double* x = (const double*)xv;
+    const int dd = width * width;
+    StatBufs B;
+    APOP_TRY(stat_bufs(c, (size_t)((dd > 1 + SCH) ? dd : 1 + SCH), (size_t)width, &B));
+    kt_begin(c, KT_STATS);
+    APOP_TRY(stat_mean_enqueue(c, x, lw, width, B));
+    k_stat_cov<<<B.g, SB, 0, c->stream>>>(x, lw, c->n, width, B.mparts, B.g, B.mean, B.part);
+    k_stat_fin<<<(dd < 256) ? dd : 256, SB, 0, c->stream>>>(B.part, B.g, dd, dd, B.sums);
+    c->launches += 2;
+    kt_end(c, KT_STATS);
+    std::vector<double> hmean(width);
+    double hsumw = 0.0;
+    APOP_CUDA(c, cudaMemcpyAsync(hmean.data(), B.mean, sizeof(double) * width,
+                                 cudaMemcpyDeviceToHost, c->stream));
+    APOP_CUDA(c, cudaMemcpyAsync(&hsumw, B.sumw, sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+    APOP_CUDA(c, cudaMemcpyAsync(cov, B.sums, sizeof(double) * dd, cudaMemcpyDeviceToHost,
+                                 c->stream));
+    APOP_CUDA(c, cudaStreamSynchronize(c->stream));
+    if (!(hsumw > 0.0) || hsumw != hsumw)
+        return set_err(c, APOP_ERR_ZERO_WEIGHT, "covariance: total weight %g", hsumw);
+    for (int k = 0; k < dd; ++k) cov[k] /= hsumw;
+    if (mean) for (int k = 0; k < width; ++k) mean[k] = hmean[k];
+    return APOP_OK;
+}
+
+int apop_collect_discrete(apop_ctx* c, apop_col xcol, apop_col lwcol, int32_t K,
+                          double* log_weight, double* prob) {
+    if (!c) return APOP_ERR_INVALID;
+    if (K < 1 || K > 4096) return set_err(c, APOP_ERR_INVALID, "collect: 1 <= K <= 4096");
+    cudaSetDevice(c->device);
+    const void* xv; const double* lw; int dt;
+    APOP_TRY(stat_inputs(c, xcol, -1, 1, lwcol, &xv, &dt, &lw));
+    StatBufs B;
+    APOP_TRY(stat_bufs(c, (size_t)K + 1, 1, &B));
+    kt_begin(c, KT_STATS);
+    if (lw) { k_stat_max<<<B.g, SB, 0, c->stream>>>(lw, c->n, B.mparts); c->launches += 1; }
+    const size_t smem = sizeof(double) * ((size_t)K + 1);
+    if (dt == APOP_F64)
+        k_stat_hist<double><<<B.g, SB, smem, c->stream>>>((const double*)xv, lw, c->n, K, B.mparts,
+                                                          B.g, B.part);
+    else
+        k_stat_hist<int32_t><<<B.g, SB, smem, c->stream>>>((const int32_t*)xv, lw, c->n, K,
+                                                           B.mparts, B.g, B.part);
+    k_stat_fin<<<(K + 1 < 256) ? K + 1 : 256, SB, 0, c->stream>>>(B.part, B.g, K + 1, K + 1, B.sums);
+    c->launches += 2;
+    kt_end(c, KT_STATS);
+    std::vector<double> h((size_t)K + 1), mp(B.g);
+    APOP_CUDA(c, cudaMemcpyAsync(h.data(), B.sums, sizeof(double) * (K + 1), cudaMemcpyDeviceToHost,
+                                 c->stream));
+    if (lw)
+        APOP_CUDA(c, cudaMemcpyAsync(mp.data(), B.mparts, sizeof(double) * B.g,
+                                     cudaMemcpyDeviceToHost, c->stream));
+    APOP_CUDA(c, cudaStreamSynchronize(c->stream));
+    double m = 0.0, tot = 0.0;
+    if (lw) { m = -INFINITY; for (int i = 0; i < B.g; ++i) m = fmax(m, mp[i]); }
+    for (int k = 0; k <= K; ++k) tot += h[k];
+    if (!(tot > 0.0) || tot != tot) return set_err(c, APOP_ERR_ZERO_WEIGHT, "collect: total weight %g", tot);
+    const double log_norm = log((double)c->n);                      // stat.cljc:14
+    for (int k = 0; k < K; ++k) {
+        if (log_weight) log_weight[k] = (h[k] > 0.0) ? log(h[k]) + m - log_norm : -INFINITY;
+        if (prob) prob[k] = h[k] / tot;                              // stat.cljc:43-54
+    }
+    return APOP_OK;
+}
+
+} // extern "C"

@@ -72,6 +72,44 @@ class Population:
         self.rank, self.world = rank, world
         self._pin = None
 
+    # ------------------------------------------------------------ anglican.stat on the device
+    @staticmethod
+    def _colh(col):
+        if col is None:
+            return -1
+        if isinstance(col, str):
+            assert col == "final"
+            return L.COL_SWEEP_FINAL
+        return col.handle
+
+    def empirical_moments(self, x, logw=None, width=None):
+        """empirical-mean / -variance / -skew / -kurtosis of stat.cljc:76-120 per
+        column of `x` (a Column, or "final" for the last sweep's final states),
+        weighted by exp(logw - max) (logw None: equal weights)."""
+        w = width if width is not None else (x.width if not isinstance(x, str) else 1)
+        out = [np.empty(w) for _ in range(4)]
+        L.check(self.ctx, self.lib.apop_empirical_moments(self.ctx, self._colh(x), self._colh(logw),
+                                                          int(w), *[_dp(o) for o in out]))
+        return {"mean": out[0], "variance": out[1], "std": np.sqrt(out[1]), "skew": out[2],
+                "kurtosis": out[3]}
+
+    def empirical_covariance(self, x, logw=None, width=None):
+        """empirical-mean and empirical-covariance (stat.cljc:84-91)"""
+        w = width if width is not None else (x.width if not isinstance(x, str) else 1)
+        mean, cov = np.empty(w), np.empty((w, w))
+        L.check(self.ctx, self.lib.apop_empirical_covariance(self.ctx, self._colh(x),
+                                                             self._colh(logw), int(w), _dp(mean),
+                                                             _dp(cov)))
+        return mean, cov
+
+    def collect_discrete(self, x, K, logw=None):
+        """collect-by + empirical-distribution over the values 0..K-1
+        (stat.cljc:7-54): (log weight per value, normalised probabilities)"""
+        lw, pr = np.empty(K), np.empty(K)
+        L.check(self.ctx, self.lib.apop_collect_discrete(self.ctx, self._colh(x), self._colh(logw),
+                                                         int(K), _dp(lw), _dp(pr)))
+        return lw, pr
+
     # ------------------------------------------------------------ lifecycle
     def close(self):
         if self.ctx:

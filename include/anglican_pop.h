@@ -251,6 +251,29 @@ int apop_sweep_download_history(apop_ctx* ctx, int32_t* anc, double* x);
 /* device pointer of the final state column of the last sweep (n*dim f64) */
 int apop_sweep_final_device(apop_ctx* ctx, void** out);
 
+/* ---- result-side reductions on the device (anglican.stat, stat.cljc) -----
+ * x: an f64 column of `width` values per particle, or APOP_COL_SWEEP_FINAL for
+ * the final states of the last sweep; logw: a width-1 f64 column of
+ * log-weights or -1 for equal weights (the states `infer :smc` returns all
+ * carry the same weight).  Weights are exp(lw - max lw) (stat.cljc:63-68).
+ * Outputs are host arrays, any of which may be NULL.
+ *   apop_empirical_moments    empirical-mean / -variance / -skew / -kurtosis
+ *                             per column (stat.cljc:76-82, 93-120)
+ *   apop_empirical_covariance empirical-mean + empirical-covariance [width^2]
+ *                             (stat.cljc:84-91), width <= 64
+ *   apop_collect_discrete     collect-by over the values 0..K-1 of an i32 (or
+ *                             integer-valued f64) column: log_weight[k] = log
+ *                             sum of the weights of value k - log N
+ *                             (stat.cljc:7-24), prob[k] = the normalised
+ *                             empirical-distribution (stat.cljc:43-54) */
+#define APOP_COL_SWEEP_FINAL (-2)
+int apop_empirical_moments(apop_ctx* ctx, apop_col x, apop_col logw, int32_t width, double* mean,
+                           double* var, double* skew, double* kurt);
+int apop_empirical_covariance(apop_ctx* ctx, apop_col x, apop_col logw, int32_t width,
+                              double* mean, double* cov);
+int apop_collect_discrete(apop_ctx* ctx, apop_col x, apop_col logw, int32_t K, double* log_weight,
+                          double* prob);
+
 /* ---- PIMH / IPMCMC scalars (host arithmetic, restated on the host side) -
  * accept?: lmh.cljc:146-151; gibbs-update-csmc-indices: ipmcmc.cljc:106-146
  * with the intended sampling rule; exchange: the only data

@@ -6,6 +6,7 @@ bench.py's cpu_baseline / --impl reference legs may import this module; the
 product package anglican_b200 must never do so.
 """
 import ctypes as C
+import math
 import os
 
 import numpy as np
@@ -408,3 +409,72 @@ def hmm_smooth(model, y):
     post = np.empty((y.size + 1, model.dim))
     lib().orc_hmm_smooth(C.byref(model.c), _dp(y), y.size, _dp(post))
     return post
+
+
+# ---------------------------------------------------------------- anglican.stat
+# Literal restatements of src/anglican/stat.cljc (test infrastructure; loops in
+# the reference's own left-fold order, so only for small cases).
+def empirical_expectation(f, weighted):
+    """stat.cljc:56-74: weights exp(lw - max lw), left fold of (v*w + sum) and w"""
+    xs = [np.asarray(f(x), dtype=np.float64) for x, _ in weighted]
+    lws = [float(lw) for _, lw in weighted]
+    max_lw = lws[0]
+    for l in lws[1:]:
+        max_lw = l if l > max_lw else max_lw
+    sum_wv, sum_w = 0.0, 0.0
+    for v, lw in zip(xs, lws):
+        w = math.exp(lw - max_lw)
+        sum_wv = v * w + sum_wv
+        sum_w = sum_w + w
+    return sum_wv / sum_w
+
+
+def empirical_mean(weighted):
+    return empirical_expectation(lambda x: x, weighted)          # stat.cljc:76-82
+
+
+def empirical_variance(weighted):
+    mu = empirical_mean(weighted)                                # stat.cljc:93-98
+    return empirical_expectation(lambda x: (np.asarray(x, float) - mu) ** 2, weighted)
+
+
+def empirical_std(weighted):
+    return np.sqrt(empirical_variance(weighted))                 # stat.cljc:100-104
+
+
+def empirical_skew(weighted):
+    mu, s = empirical_mean(weighted), empirical_std(weighted)    # stat.cljc:106-112
+    return empirical_expectation(lambda x: ((np.asarray(x, float) - mu) / s) ** 3, weighted)
+
+
+def empirical_kurtosis(weighted):
+    mu, s = empirical_mean(weighted), empirical_std(weighted)    # stat.cljc:114-120
+    return empirical_expectation(lambda x: ((np.asarray(x, float) - mu) / s) ** 4, weighted)
+
+
+def empirical_covariance(weighted):
+    mu = empirical_mean(weighted)                                # stat.cljc:84-91
+    dx = [(np.asarray(x, float) - mu, lw) for x, lw in weighted]
+    return empirical_expectation(lambda d: np.outer(d, d), dx)
+
+
+def collect_by(values, lws):
+    """stat.cljc:7-24: {v: log sum exp(lw - log N)} in order of first appearance"""
+    log_norm = math.log(len(values))
+    out = {}
+    for v, lw in zip(values, lws):
+        l = lw - log_norm
+        out[v] = log_sum_exp(out[v], l) if v in out else l
+    return out
+
+
+def empirical_distribution(weighted):
+    """stat.cljc:43-54: weighted = iterable of (x, log-w)"""
+    weighted = list(weighted)
+    log_z = None
+    for lw in sorted(lw for _, lw in weighted):
+        log_z = lw if log_z is None else log_sum_exp(log_z, lw)
+    dist = {}
+    for x, lw in weighted:
+        dist[x] = dist.get(x, 0.0) + math.exp(lw - log_z)
+    return dist

@@ -188,3 +188,20 @@ def test_samplers_distributional():
     assert stats.kstest(z, stats.norm.cdf).pvalue > 1e-3
     d = np.array([orc.dirichlet_sample([1.5, 0.7, 3.0], 5, s) for s in range(n)])
     assert np.abs(d.mean(0) - np.array([1.5, 0.7, 3.0]) / 5.2).max() < 0.02
+
+
+def test_stat_goldens():
+    """stat_test.cljc:16-21, 92-108: empirical-expectation / -mean of x = 0..10
+    weighted by observe*(normal 5 2) is 5.0 +- 1e-12; the empirical distribution
+    sums to 1 +- 1e-12."""
+    from oracle import pyoracle as orc
+    weighted = [(float(x), orc.normal_logpdf(float(x), 5.0, 2.0)) for x in range(11)]
+    assert abs(orc.empirical_expectation(lambda v: v, weighted) - 5.0) < 1e-12
+    assert abs(orc.empirical_mean(weighted) - 5.0) < 1e-12
+    dist = orc.empirical_distribution(weighted)
+    assert abs(sum(dist.values()) - 1.0) < 1e-12
+    # symmetric weights: odd central moments vanish, variance below the prior's 4
+    assert abs(float(orc.empirical_skew(weighted))) < 1e-12
+    assert 3.0 < float(orc.empirical_variance(weighted)) < 4.0
+    cb = orc.collect_by([0, 1, 0, 2], [0.0, 0.0, 0.0, 0.0])
+    assert abs(cb[0] - math.log(0.5)) < 1e-15 and abs(cb[1] - math.log(0.25)) < 1e-15
