@@ -40,12 +40,12 @@ class ApopSSM(C.Structure):
 class ApopSweepOpts(C.Structure):
     _fields_ = [("csmc", C.c_int32), ("n_cond_steps", C.c_int32), ("reset_weights", C.c_int32),
                 ("keep_history", C.c_int32), ("use_graph", C.c_int32), ("want_final", C.c_int32),
-                ("want_filt", C.c_int32), ("reserved", C.c_int32)]
+                ("want_filt", C.c_int32), ("no_resample", C.c_int32)]
 
 
 class ApopSweepResult(C.Structure):
     _fields_ = [("log_z", C.c_double), ("log_mean_w", c_double_p), ("ess", c_double_p),
-                ("filt_mean", c_double_p), ("x_final", c_double_p)]
+                ("filt_mean", c_double_p), ("x_final", c_double_p), ("lw_final", c_double_p)]
 
 
 class ApopError(RuntimeError):

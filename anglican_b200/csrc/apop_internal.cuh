@@ -217,6 +217,7 @@ int resample_fetch_info(apop_ctx* c, ResampleInfo* out);   // syncs
 int info_to_status(apop_ctx* c, const ResampleInfo& info);
 int multinomial_enqueue(apop_ctx* c, const double* lw, const double* w, const double* uni,
                         int64_t n_new, int32_t* anc);
+int stat_lse_enqueue(apop_ctx* c, const double* lw, int64_t n, double* out2);   // stats.cu
 int gather_enqueue(apop_ctx* c, const int32_t* anc, int64_t n_new, Column* col);
 // mvn.cu: fp64 tensor-core (DMMA) kernels
 struct MvnSweepArgs {

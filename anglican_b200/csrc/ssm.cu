@@ -55,6 +55,7 @@ struct SweepState {
     apop::SweepDev* sd = nullptr;
     apop::ModelDev* model = nullptr;
     double* traj = nullptr;
+    double* lse = nullptr;         // {max, sum exp} of the final log-weights (no_resample sweeps)
     double* mvn_mats = nullptr;    // LGMVN: A | Lq | iL, each [dim*dim]
     double mvn_Z = 0.0, mvn_s0 = 1.0;
     size_t cap_n = 0, cap_T = 0, cap_hist = 0;
@@ -85,7 +86,7 @@ void sweep_free(apop_ctx* c) {
     }
     void* ptrs[] = {s->xa, s->xb, s->lw, s->anc, s->x_hist, s->anc_hist, s->y, s->retained,
                     s->log_mean_w, s->ess, s->filt, s->tsx, s->x_final, s->sd, s->model, s->traj,
-                    s->mvn_mats, s->zbuf[0], s->zbuf[1]};
+                    s->mvn_mats, s->zbuf[0], s->zbuf[1], s->lse};
     for (void* p : ptrs)
         if (p) cudaFree(p);
     delete s;
@@ -166,7 +167,7 @@ __device__ __forceinline__ void propagate_tile(const PeerF64& xpeer,
                                                double wbase, int64_t n, int64_t g0, uint64_t seed,
                                                uint32_t t, double* __restrict__ tmax,
                                                double* __restrict__ tsum, int* errflag,
-                                               const double* __restrict__ zpre) {
+                                               const double* __restrict__ zpre, int accum) {
     __shared__ double red_mx[NWARP];
     __shared__ float red_ref[NWARP], red_s[NWARP];
     const int64_t base = (int64_t)blockIdx.x * TILE;
@@ -253,12 +254,21 @@ __device__ __forceinline__ void propagate_tile(const PeerF64& xpeer,
             }
         }
         if (h == 0 && retained_t && g0 + i0 == 0) x[0] = retained_t[0];    // conditional SMC: slot 0
+        // accumulated log-weight the observe adds to: common to all particles after
+        // a resample (smc.cljc:98-103), the particle's own without one (importance)
+        double wb[HW];
+#pragma unroll
+        for (int j = 0; j < HW; ++j) wb[j] = wbase;
+        if (accum) {
+#pragma unroll
+            for (int j = 0; j < HW; ++j) wb[j] = VALID(j) ? lw[ih + j] : 0.0;
+        }
         // ---- observe* (smc.cljc:23-27) + add-log-weight (state.cljc:27-31)
         if (KIND == APOP_SSM_LGSSM1D) {
 #pragma unroll
             for (int j = 0; j < HW; ++j) {
                 const double x1 = (y - (M.c * x[j] + M.d)) * c_obs;
-                l[j] = wbase + (-0.5 * x1 * x1 - M.obs_const);
+                l[j] = wb[j] + (-0.5 * x1 * x1 - M.obs_const);
             }
         } else if (KIND == APOP_SSM_SV) {
             // (normal 0 (* beta (exp (/ x 2)))): y/sd = (y/beta) exp(-x/2), log sd = log beta + x/2
@@ -274,11 +284,11 @@ __device__ __forceinline__ void propagate_tile(const PeerF64& xpeer,
 #pragma unroll
             for (int j = 0; j < HW; ++j) {
                 const double x1 = c_obs * l[j];
-                l[j] = wbase + (-0.5 * x1 * x1 - (0.5 * x[j] + M.obs_const));
+                l[j] = wb[j] + (-0.5 * x1 * x1 - (0.5 * x[j] + M.obs_const));
             }
         } else {
 #pragma unroll
-            for (int j = 0; j < HW; ++j) l[j] = wbase + obs_logpdf<KIND>(M, x[j], y);
+            for (int j = 0; j < HW; ++j) l[j] = wb[j] + obs_logpdf<KIND>(M, x[j], y);
         }
         // ---- store
         if (inb) {
@@ -358,17 +368,18 @@ __global__ void __launch_bounds__(TB, APOP_PROP_CTAS) k_propagate(const ModelDev
                                                   double* __restrict__ tmax,
                                                   double* __restrict__ tsum, int* errflag,
                                                   const __grid_constant__ PeerF64 xpeer,
-                                                  const double* __restrict__ zpre, int z_tiles) {
+                                                  const double* __restrict__ zpre, int z_tiles,
+                                                  int accum) {
     const ModelDev& M = *Mp;
     const double y = yt[0];
     const double wbase = sd->base;
     const double* zp = ((int)blockIdx.x < z_tiles) ? zpre : nullptr;     // CTA-uniform
     if ((int64_t)(blockIdx.x + 1) * TILE <= n)
         propagate_tile<KIND, true, SHARD>(xpeer, M, xp, anc, first_step, xn, lw, y, retained_t,
-                                          wbase, n, g0, seed, t, tmax, tsum, errflag, zp);
+                                          wbase, n, g0, seed, t, tmax, tsum, errflag, zp, accum);
     else
         propagate_tile<KIND, false, SHARD>(xpeer, M, xp, anc, first_step, xn, lw, y, retained_t,
-                                           wbase, n, g0, seed, t, tmax, tsum, errflag, nullptr);
+                                           wbase, n, g0, seed, t, tmax, tsum, errflag, nullptr, accum);
 }
 
 // transition noise of step t for the full tiles [0, gridDim.x): exactly the
@@ -469,6 +480,7 @@ static int sweep_prepare(apop_ctx* c, int T, int dim, bool history) {
     if (!s->sd) {
         APOP_TRY(dev_alloc(c, (void**)&s->sd, sizeof(SweepDev)));
         APOP_TRY(dev_alloc(c, (void**)&s->model, sizeof(ModelDev)));
+        APOP_TRY(dev_alloc(c, (void**)&s->lse, 2 * sizeof(double)));
     }
     if (s->cap_T < (size_t)T || s->dim != dim) {
         void* ptrs[] = {s->y, s->retained, s->log_mean_w, s->ess, s->filt, s->traj};
@@ -694,14 +706,14 @@ static int sweep_step(apop_ctx* c, int t, const apop_sweep_opts* o, bool csmc) {
         const PeerF64 xpeer = peer_f64(c, (t & 1) ? c->fab.off_xa : c->fab.off_xb);   // x_{t-1}
         k_propagate<(KIND == APOP_SSM_LGMVN) ? APOP_SSM_LGSSM1D : KIND, true><<<nt, TB, 0, c->stream>>>(
             s->model, x_prev, anc_prev, t == 1, x_new, s->lw, s->y + (t - 1), nullptr, s->sd, n,
-            c->g0, c->seed, (uint32_t)t, ws.tmax, ws.tsum, &ws.info->err, xpeer, zpre, zt);
+            c->g0, c->seed, (uint32_t)t, ws.tmax, ws.tsum, &ws.info->err, xpeer, zpre, zt, 0);
     } else {
         PeerF64 none;
         memset(&none, 0, sizeof none);
         k_propagate<(KIND == APOP_SSM_LGMVN) ? APOP_SSM_LGSSM1D : KIND, false><<<nt, TB, 0, c->stream>>>(
-            s->model, x_prev, anc_prev, t == 1, x_new, s->lw, s->y + (t - 1),
+            s->model, x_prev, anc_prev, t == 1 || o->no_resample, x_new, s->lw, s->y + (t - 1),
             csmc ? s->retained + t : nullptr, s->sd, n, c->g0, c->seed, (uint32_t)t, ws.tmax,
-            ws.tsum, &ws.info->err, none, zpre, zt);
+            ws.tsum, &ws.info->err, none, zpre, zt, (o->no_resample && t > 1) ? 1 : 0);
     }
     kt_end(c, KT_PROPAGATE);
     c->launches += 1;
@@ -717,6 +729,11 @@ static int sweep_step(apop_ctx* c, int t, const apop_sweep_opts* o, bool csmc) {
             APOP_CUDA(c, cudaEventRecord(s->ev_noise[nb], s->side));
             c->launches += 1;
         }
+    }
+    if (o->no_resample) {          // importance.cljc:16-22: weights accumulate per particle
+        c->step = (uint32_t)t;
+        s->last_x = x_new;
+        return APOP_OK;
     }
     const bool cond = csmc && t <= o->n_cond_steps;
     c->step = (uint32_t)t;
@@ -752,7 +769,13 @@ static int sweep_end(apop_ctx* c, int T, const apop_sweep_opts* opts, apop_sweep
     const int64_t n = c->n;
     const int dim = s->dim;
     APOP_CUDA(c, cudaGetLastError());
-    if (opts->want_final || result->x_final) {
+    if (opts->no_resample) {
+        // no resample, no gather: the final states are the last propagated ones
+        if (opts->want_final || result->x_final)
+            APOP_CUDA(c, cudaMemcpyAsync(s->x_final, s->last_x, sizeof(double) * n * dim,
+                                         cudaMemcpyDeviceToDevice, c->stream));
+        APOP_TRY(stat_lse_enqueue(c, s->lw, n, s->lse));
+    } else if (opts->want_final || result->x_final) {
         int blocks = (int)((n * dim + 255) / 256);
         if (blocks > 148 * 32) blocks = 148 * 32;
         kt_begin(c, KT_GATHER);
@@ -800,12 +823,25 @@ static int sweep_fetch(apop_ctx* c, int T, const apop_sweep_opts* opts, apop_swe
     if (result->x_final)
         APOP_CUDA(c, cudaMemcpyAsync(result->x_final, s->x_final, sizeof(double) * n * dim,
                                      cudaMemcpyDeviceToHost, c->stream));
+    double lse[2] = {0.0, 0.0};
+    if (opts->no_resample) {
+        APOP_CUDA(c, cudaMemcpyAsync(lse, s->lse, sizeof lse, cudaMemcpyDeviceToHost, c->stream));
+        if (result->lw_final)
+            APOP_CUDA(c, cudaMemcpyAsync(result->lw_final, s->lw, sizeof(double) * n,
+                                         cudaMemcpyDeviceToHost, c->stream));
+    }
     APOP_CUDA(c, cudaStreamSynchronize(c->stream));
     ResampleInfo I{};
     I.err = hsd.err | info_err;
     APOP_TRY(info_to_status(c, I));
     // :smc keeps the accumulated weight on the particles: final weight == log Z-hat
     result->log_z = opts->reset_weights ? hsd.log_z : hsd.base;
+    if (opts->no_resample) {
+        // log-marginal of the weighted samples (inference.cljc:181-186): log mean exp
+        if (lse[0] != lse[0]) return set_err(c, APOP_ERR_NAN_WEIGHT, "importance: NaN log-weight");
+        result->log_z = (lse[0] > -INFINITY && lse[0] < INFINITY)
+                            ? log(lse[1] / (double)n) + lse[0] : lse[0];
+    }
     return APOP_OK;
 }
 
@@ -871,6 +907,11 @@ static int sweep_group(apop_ctx* const* g, int ng, const apop_ssm* model, const 
         apop_ctx* c = g[i];
         if (opts->csmc && c->n < 2)
             return set_err(c, APOP_ERR_INVALID, "conditional sweep needs >= 2 particles");
+        if (opts->no_resample && (opts->csmc || opts->keep_history || c->world > 1 ||
+                                  model->kind == APOP_SSM_LGMVN))
+            return set_err(c, APOP_ERR_UNSUPPORTED,
+                           "no_resample (importance) sweeps: unconditional, unsharded, scalar-state, "
+                           "no lineages");
         if (c->world > 1 && (opts->csmc || opts->keep_history))
             return set_err(c, APOP_ERR_UNSUPPORTED,
                            "sharded sweep: conditional sweeps / lineages run one population "

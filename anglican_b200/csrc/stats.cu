@@ -285,6 +285,25 @@ static int stat_mean_enqueue(apop_ctx* c, const double* x, const double* lw, int
     return APOP_OK;
 }
 
+__global__ void k_stat_lse_out(const double* __restrict__ mparts, int g,
+                               const double* __restrict__ sums, double* __restrict__ out2) {
+    out2[0] = max_of_parts(mparts, g);
+    out2[1] = sums[0];
+}
+
+// {max lw, sum exp(lw - max)} of a log-weight array into out2 (device): the
+// pieces of log-sum-exp / log-marginal (runtime.cljc:130-138, inference.cljc:181-186)
+int stat_lse_enqueue(apop_ctx* c, const double* lw, int64_t n, double* out2) {
+    StatBufs B;
+    APOP_TRY(stat_bufs(c, 1 + SCH, 1, &B));
+    k_stat_max<<<B.g, SB, 0, c->stream>>>(lw, n, B.mparts);
+    k_stat_m1<<<B.g, SB, 0, c->stream>>>(lw, lw, n, 1, 0, 0, B.mparts, B.g, B.part);
+    k_stat_fin<<<1, SB, 0, c->stream>>>(B.part, B.g, 1 + SCH, 1, B.sums);
+    k_stat_lse_out<<<1, 1, 0, c->stream>>>(B.mparts, B.g, B.sums, out2);
+    c->launches += 4;
+    return APOP_OK;
+}
+
 } // namespace apop
 
 using namespace apop;

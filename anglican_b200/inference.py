@@ -1,9 +1,10 @@
 """Host-side mirror of `anglican.inference/infer` for the particle algorithms.
 
-    infer(:smc | :pimh | :pgibbs | :ipmcmc, model, observations, **options)
+    infer(:smc | :pimh | :pgibbs | :ipmcmc | :importance | :pfilter, model, observations, **options)
 
 keeps the reference's keywords, defaults and assertions
-(smc.cljc:53-57, pimh.cljc:41-45, pgibbs.cljc:112-116, ipmcmc.cljc:148-171) and
+(smc.cljc:53-57, pimh.cljc:41-45, pgibbs.cljc:112-116, ipmcmc.cljc:148-171,
+importance.cljc:16-22, pfilter.cljc:22-62) and
 its return contract: a lazy (generator) sequence of states carrying
 `log_weight`, `result`, `predicts` (stripdown, inference.cljc:114-117).  The
 control flow below (MH accept, retained-trajectory bookkeeping, node index
@@ -174,14 +175,59 @@ def _infer_ipmcmc(model, y, number_of_particles=2, number_of_nodes=32,
         pop.close()
 
 
+# ---------------------------------------------------------------- :importance
+def _infer_importance(model, y, number_of_particles=1024, seed=0xA11CE, device=0):
+    """importance.cljc:16-22: an endless sequence of independent samples, each
+    carrying its own log-weight (the default observe checkpoint,
+    inference.cljc:42-45).  The reference runs one sample at a time and takes
+    no options; `number_of_particles` here is only the device batch size."""
+    assert number_of_particles >= 1
+    pop = Population(number_of_particles, seed=seed, device=device)
+    seeds = _SeedSeq(seed)
+    try:
+        while True:
+            pop.set_seed(seeds.next_key())
+            out = pop.sweep(model, y, no_resample=True)
+            for k in range(pop.n):
+                yield State(float(out.lw_final[k]), _result_of(out, k, None))
+    finally:
+        pop.close()
+
+
+# ---------------------------------------------------------------- :pfilter
+def _infer_pfilter(model, y, number_of_particles=1, seed=0xA11CE, device=0):
+    """pfilter.cljc:22-62: every `observe` emits the batch of particle states
+    as they stand after the observe and BEFORE the resample, with the weight
+    reset to 0 ("so that all predicts have the same weight", pfilter.cljc:41-44);
+    when the program ends the particles restart.  A state-space program
+    predicts its latent state at every step, so each batch is x_t of all
+    particles; `predicts` carries (t, x_t)."""
+    assert number_of_particles >= 1, ":number-of-particles must be at least 1"   # pfilter.cljc:25-26
+    pop = Population(number_of_particles, seed=seed, device=device)
+    seeds = _SeedSeq(seed)
+    d = model.state_dim
+    try:
+        while True:                                   # "Restart the particles", pfilter.cljc:54-56
+            pop.set_seed(seeds.next_key())
+            out = pop.sweep(model, y, keep_history=True)
+            _, x = out.history()                      # x[t]: states before the t-th resample
+            for t in range(1, out.T + 1):
+                for k in range(pop.n):
+                    v = x[t][k, 0] if d == 1 else x[t][k].copy()
+                    yield State(0.0, None, [(t, float(v) if d == 1 else v)])
+    finally:
+        pop.close()
+
+
 _ALGORITHMS = {"smc": _infer_smc, "pimh": _infer_pimh, "pgibbs": _infer_pgibbs,
-               "ipmcmc": _infer_ipmcmc}
+               "ipmcmc": _infer_ipmcmc, "importance": _infer_importance,
+               "pfilter": _infer_pfilter}
 
 
 def infer(algorithm, model, observations, **options):
     """(infer algorithm prog value & options) — inference.cljc:25-28.
 
-    `algorithm`: "smc" / ":smc" / "pimh" / "pgibbs" / "ipmcmc".  Options use the
+    `algorithm`: "smc" / ":smc" / "pimh" / "pgibbs" / "ipmcmc" / "importance" / "pfilter".  Options use the
     reference's names with `-` -> `_` (number_of_particles, number_of_nodes,
     number_of_csmc_nodes, all_particles, pool)."""
     key = str(algorithm).lstrip(":")

@@ -314,18 +314,23 @@ class Population:
 
     def sweep(self, model, y, retained=None, csmc=False, n_cond_steps=0, reset_weights=False,
               keep_history=False, want_final=True, want_stats=True, want_filt=None,
-              pinned_final=False):
+              pinned_final=False, no_resample=False):
         """One `sweep` (smc.cljc:35-51; conditional: pgibbs.cljc:76-110,
         ipmcmc.cljc:34-83).  Returns a SweepOutput.  pinned_final: x_final is a
         view of a page-locked buffer owned by the population, overwritten by its
-        next sweep (copy it to keep it)."""
+        next sweep (copy it to keep it).  no_resample: `infer :importance`
+        (importance.cljc:16-22) — weights accumulate per particle, the output
+        carries lw_final and log_z = log mean exp(lw_final)."""
         y = np.ascontiguousarray(y, dtype=np.float64)
         d = model.state_dim
         T = y.size // d
+        if no_resample:                      # no resample, no per-step weight statistics
+            want_stats, want_filt = False, False
         if want_filt is None:
             want_filt = want_stats and d == 1
         opts = L.ApopSweepOpts(int(csmc), int(n_cond_steps), int(reset_weights),
-                               int(keep_history), 0, int(want_final), int(bool(want_filt)), 0)
+                               int(keep_history), 0, int(want_final), int(bool(want_filt)),
+                               int(bool(no_resample)))
         res = L.ApopSweepResult()
         out = SweepOutput(self, T, d)
         if want_stats:
@@ -342,6 +347,9 @@ class Population:
             else:
                 out.x_final = np.empty((self.n, d)) if d > 1 else np.empty(self.n)
             res.x_final = _dp(out.x_final)
+        if no_resample:
+            out.lw_final = np.empty(self.n)
+            res.lw_final = _dp(out.lw_final)
         ret = None
         if retained is not None:
             ret = np.ascontiguousarray(retained, dtype=np.float64)
@@ -358,7 +366,7 @@ class SweepOutput:
     def __init__(self, pop, T, d):
         self.pop, self.T, self.d = pop, T, d
         self.log_z = None
-        self.log_mean_w = self.ess = self.filt_mean = self.x_final = None
+        self.log_mean_w = self.ess = self.filt_mean = self.x_final = self.lw_final = None
         self.has_history = False
         self._hist = None
 

@@ -218,7 +218,10 @@ typedef struct {
     int32_t use_graph;         /* capture the step loop in a CUDA graph */
     int32_t want_final;        /* gather final states into x_final */
     int32_t want_filt;         /* per-step filtering means sum w x / sum w (reads x once more) */
-    int32_t reserved;
+    int32_t no_resample;       /* `infer :importance` (importance.cljc:16-22): every observe only
+                                * adds to the particle's own log-weight (inference.cljc:42-45),
+                                * nothing is resampled; log_z = log mean exp of the final
+                                * log-weights, which lw_final returns */
 } apop_sweep_opts;
 
 typedef struct {
@@ -227,6 +230,7 @@ typedef struct {
     double* ess;               /* [T] or NULL */
     double* filt_mean;         /* [T*dim] or NULL */
     double* x_final;           /* [n*dim] host or NULL */
+    double* lw_final;          /* [n] host or NULL: final log-weights (no_resample sweeps) */
 } apop_sweep_result;
 
 int apop_smc_sweep(apop_ctx* ctx, const apop_ssm* model, const double* y, int32_t T,

@@ -723,6 +723,29 @@ done:
     return rc;
 }
 
+/* `infer :importance` (importance.cljc:16-22) for a state-space program: every
+ * sample runs the whole program on its own; the default `observe` checkpoint
+ * adds the log-density to the sample's log-weight and continues
+ * (inference.cljc:42-45); nothing is ever resampled.  Sample k uses the same
+ * counter-based draws as particle k of a sweep.  Scalar-state models. */
+int orc_importance_sweep(const orc_ssm* model, const double* y, int32_t T, int64_t n,
+                         uint64_t seed, double* x_final, double* lw_final) {
+    if (model->kind == ORC_SSM_LGMVN) return -1;
+    double work[4];
+    for (int64_t k = 0; k < n; ++k) {
+        double x, xn, lw = 0.0;                          /* initial-state: log-weight 0 */
+        ssm_init(model, seed, k, &x);
+        for (int t = 1; t <= T; ++t) {
+            ssm_transition(model, seed, k, (uint32_t)t, &x, &xn, work);
+            lw = lw + ssm_obs_logpdf(model, &xn, y + (t - 1), NULL, 0.0, work);
+            x = xn;
+        }
+        x_final[k] = x;
+        lw_final[k] = lw;
+    }
+    return 0;
+}
+
 void orc_trace_lineage(const orc_sweep_out* out, int64_t n, int32_t T, int32_t dim,
                        int64_t slot, double* traj) {
     int64_t k = slot;

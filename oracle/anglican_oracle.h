@@ -168,6 +168,8 @@ int orc_smc_sweep(const orc_ssm* model, const double* y, const double* retained,
                   const orc_sweep_opts* opts, orc_sweep_out* out);
 
 /* lineage of final slot `slot` from keep_history arrays: out [(T+1)*dim] */
+int orc_importance_sweep(const orc_ssm* model, const double* y, int32_t T, int64_t n,
+                         uint64_t seed, double* x_final, double* lw_final);
 void orc_trace_lineage(const orc_sweep_out* out, int64_t n, int32_t T, int32_t dim,
                        int64_t slot, double* traj);
 

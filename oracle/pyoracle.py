@@ -125,6 +125,9 @@ def _declare(L):
     L.orc_smc_sweep.restype = C.c_int
     L.orc_trace_lineage.argtypes = [C.POINTER(OrcSweepOut), i64, i32, i32, i64, c_double_p]
     L.orc_trace_lineage.restype = None
+    L.orc_importance_sweep.argtypes = [C.POINTER(OrcSSM), c_double_p, i32, i64, C.c_uint64,
+                                       c_double_p, c_double_p]
+    L.orc_importance_sweep.restype = C.c_int
     L.orc_kalman1d_logz.argtypes = [C.POINTER(OrcSSM), c_double_p, C.c_int, c_double_p]
     L.orc_kalman1d_logz.restype = d
     L.orc_kalman_mvn_logz.argtypes = [C.POINTER(OrcSSM), c_double_p, C.c_int, c_double_p,
@@ -371,6 +374,16 @@ def smc_sweep(model, y, n, seed, retained=None, csmc=False, n_cond_steps=0,
     res["_out"] = out
     res["_n"], res["_T"], res["_d"] = n, T, d
     return res
+
+
+def importance_sweep(model, y, n, seed):
+    """`infer :importance` over a state-space program (importance.cljc:16-22)"""
+    y = _f64(y)
+    x, lw = np.empty(n), np.empty(n)
+    rc = lib().orc_importance_sweep(C.byref(model.c), _dp(y), y.size, n, seed, _dp(x), _dp(lw))
+    if rc:
+        raise ValueError(f"oracle importance sweep failed rc={rc}")
+    return {"x_final": x, "lw_final": lw, "log_z": log_marginal(lw)}
 
 
 def trace_lineage(res, slot):

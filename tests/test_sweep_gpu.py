@@ -227,3 +227,61 @@ def test_noise_prefetch_is_bit_identical(kind, monkeypatch):
         assert np.array_equal(o.ess, ref.ess)
         assert np.array_equal(o.filt_mean, ref.filt_mean)
         assert np.array_equal(o.x_final, ref.x_final)
+
+
+@pytest.mark.parametrize("kind,n", [("sv", 1000), ("lgssm", 4097), ("hmm", 30000)])
+def test_importance_sweep_matches_oracle(orc, kind, n):
+    """`infer :importance` (importance.cljc:16-22): no resampling, the observes
+    add to each sample's own log-weight (inference.cljc:42-45).  Same draws as
+    the oracle, so final states are identical and log-weights agree to 1e-9."""
+    from anglican_b200 import Population
+    from anglican_b200.models import GaussianHMM, LinearGaussian1D, StochasticVolatility
+    T = 12
+    if kind == "sv":
+        m, y = StochasticVolatility(), _sv_data(T)
+        om = orc.Model(orc.SSM_SV, m0=0.0, s0=m.c.s0, a=m.c.a, b=0.0, q=m.c.q, beta=m.c.beta)
+    elif kind == "lgssm":
+        m, y = LinearGaussian1D(), _lgssm_data(T)
+        om = orc.Model(orc.SSM_LGSSM1D, **m.params)
+    else:
+        init, trans = [1.0, 1.0, 1.0], [[0.1, 0.5, 0.4], [0.2, 0.2, 0.6], [0.15, 0.15, 0.7]]
+        m, y = GaussianHMM(init, trans, [-1, 1, 0], [1, 1, 1]), np.array(G["hmm"]["observations"][:T])
+        om = orc.Model(orc.SSM_HMM, dim=3, hmm_init=init, hmm_trans=trans, hmm_mu=[-1, 1, 0],
+                       hmm_sd=[1, 1, 1])
+    with Population(n, seed=808) as pop:
+        out = pop.sweep(m, y, no_resample=True)
+        mom = pop.empirical_moments("final")
+    ref = orc.importance_sweep(om, y, n, seed=808)
+    assert _rel(out.x_final, ref["x_final"]) < 1e-9
+    assert _rel(out.lw_final, ref["lw_final"]) < 1e-9
+    assert _rel(out.log_z, ref["log_z"]) < 1e-9          # log-marginal, inference.cljc:181-186
+    assert _rel(mom["mean"][0], out.x_final.mean()) < 1e-12
+
+
+def test_importance_log_marginal_vs_kalman(orc):
+    """importance weights of the 1-D linear-Gaussian model estimate the exact
+    (Kalman) marginal likelihood; short series so that the estimator is tight"""
+    from anglican_b200 import Population
+    from anglican_b200.models import LinearGaussian1D
+    y = _lgssm_data(5)
+    m = LinearGaussian1D()
+    om = orc.Model(orc.SSM_LGSSM1D, **m.params)
+    with Population(1 << 20, seed=3) as pop:
+        out = pop.sweep(m, y, no_resample=True, want_final=False)
+    truth = orc.kalman1d(om, y)[0]
+    assert abs(out.log_z - truth) < 0.02
+
+
+def test_infer_importance_and_pfilter_mirrors():
+    import itertools
+    from anglican_b200.inference import infer
+    from anglican_b200.models import LinearGaussian1D
+    y = _lgssm_data(6)
+    m = LinearGaussian1D()
+    imp = list(itertools.islice(infer(":importance", m, y, number_of_particles=500), 1200))
+    assert len(imp) == 1200 and len({s.log_weight for s in imp}) > 1000      # own weight each
+    pf = list(itertools.islice(infer("pfilter", m, y, number_of_particles=300), 300 * 6 + 10))
+    assert all(s.log_weight == 0.0 for s in pf)                             # pfilter.cljc:41-44
+    assert [s.predicts[0][0] for s in pf[::300]] == [1, 2, 3, 4, 5, 6, 1]   # batches, then restart
+    with pytest.raises(AssertionError):
+        next(infer("pfilter", m, y, number_of_particles=0))

@@ -1,2 +1,2 @@
-mkdir -p gpurun_out/r01o
-timeout 900 python -m pytest tests/test_stat_gpu.py -m gpu -x -q > gpurun_out/r01o/pytest.log 2>&1; tail -30 gpurun_out/r01o/pytest.log
+mkdir -p gpurun_out/r01p
+timeout 1200 python -m pytest tests -m gpu -x -q > gpurun_out/r01p/pytest.log 2>&1; tail -30 gpurun_out/r01p/pytest.log
