@@ -91,6 +91,8 @@ _SIGS = [
     ("apop_observe_beta", C.c_int, [_vp, ApopArg, ApopArg, ApopArg, C.c_int32]),
     ("apop_sample_uniform", C.c_int, [_vp, ApopArg, ApopArg, C.c_uint32, C.c_int32]),
     ("apop_observe_uniform", C.c_int, [_vp, ApopArg, ApopArg, ApopArg, C.c_int32]),
+    ("apop_sample_dist", C.c_int, [_vp, C.c_int32, C.POINTER(ApopArg), C.c_uint32, C.c_int32]),
+    ("apop_observe_dist", C.c_int, [_vp, C.c_int32, C.POINTER(ApopArg), ApopArg, C.c_int32]),
     ("apop_sample_discrete", C.c_int, [_vp, c_double_p, C.c_int, C.c_int32, C.c_uint32, C.c_int32]),
     ("apop_observe_discrete", C.c_int, [_vp, c_double_p, C.c_int, C.c_int32, C.c_int32, C.c_int32,
                                         C.c_int32]),
@@ -130,6 +132,10 @@ _SIGS = [
     ("apop_ipmcmc_exchange_logz", C.c_int, [_vp, c_double_p, C.c_int, c_double_p]),
 ]
 COL_SWEEP_FINAL = -2
+# apop_sample_dist / apop_observe_dist families (include/anglican_pop.h)
+DIST_FAMILIES = {"exponential": (1, 1), "laplace": (2, 2), "poisson": (3, 1), "bernoulli": (4, 1),
+                 "flip": (4, 1), "student-t": (5, 1), "student-t-loc-scale": (6, 3),
+                 "chi-squared": (7, 1), "uniform-discrete": (8, 2), "binomial": (9, 2)}
 DECLARED_SYMBOLS = [s[0] for s in _SIGS]
 
 _lib = None

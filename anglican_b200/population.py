@@ -237,6 +237,27 @@ class Population:
         L.check(self.ctx, self.lib.apop_observe_uniform(self.ctx, _arg(lo), _arg(hi), _arg(value),
                                                         logw.handle))
 
+    def _family(self, name, params):
+        fam, npar = L.DIST_FAMILIES[str(name).lstrip(":").replace("_", "-")]
+        if len(params) != npar:
+            raise TypeError(f"{name} takes {npar} parameter(s)")           # defdist arity
+        a = (L.ApopArg * 3)(*([_arg(p) for p in params] + [_arg(0.0)] * (3 - npar)))
+        return fam, a
+
+    def sample_dist(self, name, params, out, draw=0):
+        """sample* of exponential / laplace / poisson / bernoulli (flip) / student-t /
+        student-t-loc-scale / chi-squared / uniform-discrete / binomial
+        (runtime.cljc:241-475); params are scalars or Columns"""
+        fam, a = self._family(name, params)
+        L.check(self.ctx, self.lib.apop_sample_dist(self.ctx, fam, a, int(draw), out.handle))
+        return out
+
+    def observe_dist(self, name, params, value, logw):
+        """observe* of the same families: logw += log p(value)"""
+        fam, a = self._family(name, params)
+        L.check(self.ctx, self.lib.apop_observe_dist(self.ctx, fam, a, _arg(value), logw.handle))
+        return logw
+
     def sample_discrete(self, weights, out, draw=0):
         if isinstance(weights, Column):
             L.check(self.ctx, self.lib.apop_sample_discrete(self.ctx, None, weights.width,

@@ -255,6 +255,27 @@ int apop_sweep_download_history(apop_ctx* ctx, int32_t* anc, double* x);
 /* device pointer of the final state column of the last sweep (n*dim f64) */
 int apop_sweep_final_device(apop_ctx* ctx, void** out);
 
+/* ---- the other scalar-parameter families of anglican.runtime --------------
+ * One entry point pair for `sample*` / `observe*` (runtime.cljc:119-124) of
+ *   EXPONENTIAL(rate)                 runtime.cljc:308-313
+ *   LAPLACE(loc, scale)               :411-416
+ *   POISSON(lambda)                   :418-423
+ *   BERNOULLI(p) (= flip with 1/0)    :241-249, 315-323
+ *   STUDENT_T(nu)                     :425-444
+ *   STUDENT_T_LOC_SCALE(nu,loc,scale) :446-448
+ *   CHI_SQUARED(nu)                   :333-340
+ *   UNIFORM_DISCRETE(min, max)        :464-475  (values min .. max-1)
+ *   BINOMIAL(n, p)                    :258-263  (sampler: scalar n <= 400)
+ * params points at three apop_arg (unused ones are ignored).  Values and draws are f64 columns (integer
+ * valued for the discrete families); observe adds into the log-weight column. */
+enum { APOP_DIST_EXPONENTIAL = 1, APOP_DIST_LAPLACE = 2, APOP_DIST_POISSON = 3,
+       APOP_DIST_BERNOULLI = 4, APOP_DIST_STUDENT_T = 5, APOP_DIST_STUDENT_T_LOC_SCALE = 6,
+       APOP_DIST_CHI_SQUARED = 7, APOP_DIST_UNIFORM_DISCRETE = 8, APOP_DIST_BINOMIAL = 9 };
+int apop_sample_dist(apop_ctx* ctx, int32_t family, const apop_arg* params /* [3] */,
+                     uint32_t draw_id, apop_col out);
+int apop_observe_dist(apop_ctx* ctx, int32_t family, const apop_arg* params /* [3] */,
+                      apop_arg value, apop_col logw);
+
 /* ---- result-side reductions on the device (anglican.stat, stat.cljc) -----
  * x: an f64 column of `width` values per particle, or APOP_COL_SWEEP_FINAL for
  * the final states of the last sweep; logw: a width-1 f64 column of

@@ -491,3 +491,70 @@ def empirical_distribution(weighted):
     for x, lw in weighted:
         dist[x] = dist.get(x, 0.0) + math.exp(lw - log_z)
     return dist
+
+
+# ---------------------------------------------------------------- more runtime distributions
+# commons-math 3.6.1 log-densities behind `from-apache` (runtime.cljc:207-220)
+# and the defdist bodies of runtime.cljc:241-475.  Scalar restatements
+# (test infrastructure); checked against scipy in tests/test_oracle_golden.py.
+def exponential_logpdf(x, rate):
+    mean = 1.0 / rate                                   # (Exponential (/ 1. rate)), runtime.cljc:310-311
+    return -math.inf if x < 0 else -x / mean - math.log(mean)
+
+
+def laplace_logpdf(x, loc, scale):
+    d = math.exp(-abs(x - loc) / scale) / (2.0 * scale)  # LaplaceDistribution.density
+    return math.log(d) if d > 0 else -math.inf
+
+
+def poisson_logpmf(x, lam):
+    if x < 0 or x != math.floor(x):
+        return -math.inf
+    if x == 0:
+        return -lam
+    return x * math.log(lam) - lam - math.lgamma(x + 1.0)
+
+
+def bernoulli_logpmf(x, p):
+    v = p if x == 1 else (1.0 - p) if x == 0 else 0.0    # runtime.cljc:245-249
+    return math.log(v) if v > 0 else -math.inf
+
+
+def student_t_logpdf(x, nu, loc=0.0, scale=1.0, loc_scale=False):
+    v = (x - loc) / scale if loc_scale else x
+    h = (nu + 1.0) / 2.0
+    lp = (math.lgamma(h) - 0.5 * (math.log(math.pi) + math.log(nu)) - math.lgamma(nu / 2.0)
+          - h * math.log(1.0 + v * v / nu))
+    return lp - math.log(scale) if loc_scale else lp     # runtime.cljc:446-448
+
+
+def chi_squared_logpdf(x, nu):
+    return gamma_logpdf_direct(x, nu * 0.5, 0.5)         # runtime.cljc:333-340
+
+
+def uniform_discrete_logpmf(x, lo, hi):
+    lo, up = int(lo), int(hi) - 1                        # runtime.cljc:466-467
+    if x != math.floor(x) or x < lo or x > up:
+        return -math.inf
+    return math.log(1.0 / (up - lo + 1))
+
+
+def binomial_logpmf(x, n, p):
+    n = int(n)
+    if x != math.floor(x) or x < 0 or x > n:
+        return -math.inf
+    r = math.lgamma(n + 1.0) - math.lgamma(x + 1.0) - math.lgamma(n - x + 1.0)
+    if x > 0:
+        r += x * math.log(p)
+    if x < n:
+        r += (n - x) * math.log1p(-p)
+    return r
+
+
+DIST_LOGP = {
+    "exponential": exponential_logpdf, "laplace": laplace_logpdf, "poisson": poisson_logpmf,
+    "bernoulli": bernoulli_logpmf, "student-t": student_t_logpdf,
+    "student-t-loc-scale": lambda x, nu, loc, scale: student_t_logpdf(x, nu, loc, scale, True),
+    "chi-squared": chi_squared_logpdf, "uniform-discrete": uniform_discrete_logpmf,
+    "binomial": binomial_logpmf,
+}

@@ -205,3 +205,36 @@ def test_stat_goldens():
     assert 3.0 < float(orc.empirical_variance(weighted)) < 4.0
     cb = orc.collect_by([0, 1, 0, 2], [0.0, 0.0, 0.0, 0.0])
     assert abs(cb[0] - math.log(0.5)) < 1e-15 and abs(cb[1] - math.log(0.25)) < 1e-15
+
+
+def test_more_distributions_vs_scipy():
+    """commons-math log-densities of the remaining scalar families
+    (runtime.cljc:241-475, parameters of dist_test.cljc:334-396) vs scipy, 1e-12"""
+    import scipy.stats as st
+    from oracle import pyoracle as orc
+    xs = [0.0, 0.3, 1.0, 2.5, 7.0]
+    ks = [0, 1, 2, 5, 9]
+    cases = [
+        ("exponential", (3.1,), xs, lambda x: st.expon(scale=1 / 3.1).logpdf(x)),
+        ("exponential", (1.4,), xs, lambda x: st.expon(scale=1 / 1.4).logpdf(x)),
+        ("laplace", (2.1, 1.4), xs + [-3.0], lambda x: st.laplace(2.1, 1.4).logpdf(x)),
+        ("poisson", (2.1,), ks, lambda k: st.poisson(2.1).logpmf(k)),
+        ("poisson", (3.2,), ks + [40], lambda k: st.poisson(3.2).logpmf(k)),
+        ("bernoulli", (0.7,), [0, 1], lambda k: st.bernoulli(0.7).logpmf(k)),
+        ("student-t", (3.1,), xs + [-2.0], lambda x: st.t(3.1).logpdf(x)),
+        ("student-t-loc-scale", (2.5, -10.0, 2.0), xs + [-12.0],
+         lambda x: st.t(2.5, -10.0, 2.0).logpdf(x)),
+        ("chi-squared", (5.0,), xs[1:], lambda x: st.chi2(5).logpdf(x)),
+        ("uniform-discrete", (2, 5), [2, 3, 4], lambda k: st.randint(2, 5).logpmf(k)),
+        ("binomial", (5, 0.7), [0, 1, 3, 5], lambda k: st.binom(5, 0.7).logpmf(k)),
+    ]
+    for name, params, vals, truth in cases:
+        for v in vals:
+            got, ref = orc.DIST_LOGP[name](float(v), *params), float(truth(v))
+            assert abs(got - ref) <= 1e-12 * max(1.0, abs(ref)), (name, params, v, got, ref)
+    # outside the support
+    assert orc.exponential_logpdf(-1.0, 2.0) == -math.inf
+    assert orc.poisson_logpmf(1.5, 2.0) == -math.inf and orc.poisson_logpmf(-1.0, 2.0) == -math.inf
+    assert orc.bernoulli_logpmf(2.0, 0.3) == -math.inf
+    assert orc.uniform_discrete_logpmf(5.0, 2, 5) == -math.inf       # max is exclusive
+    assert orc.binomial_logpmf(6.0, 5, 0.7) == -math.inf
