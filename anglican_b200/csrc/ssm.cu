@@ -20,11 +20,15 @@
 #include "fastmath.cuh"
 #include "rng.cuh"
 
+// Particles per sub-step / resident CTAs per SM of k_propagate.  HW=2 with 3 CTAs
+// is ~3 % faster on a cold GPU but executes 13 % more instructions; in a long
+// sweep the B200 sits at its 1000 W power cap and the leaner HW=4 / 2 CTAs
+// configuration is ~5 % faster (profiles/r01s_propagate_config.txt).
 #ifndef APOP_PROP_HW
-#define APOP_PROP_HW 2
+#define APOP_PROP_HW 4
 #endif
 #ifndef APOP_PROP_CTAS
-#define APOP_PROP_CTAS 3
+#define APOP_PROP_CTAS 2
 #endif
 
 namespace apop {

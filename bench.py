@@ -44,10 +44,10 @@ ALGO_BYTES = {"k_propagate": 52.0, "k_fold_agg": 8.0, "k_ancestors": 12.0, "k_ti
 MOVED_BYTES = {"k_propagate": 28.0, "k_fold_agg": 8.0, "k_ancestors": 12.0, "k_tile_lse": 8.0,
                "k_gather": 20.0}
 # dram__bytes_read.sum + dram__bytes_write.sum per launch at 2^27 particles from the
-# committed `ncu --set full` capture (profiles/r01g_ncu_full_summary.csv), bytes/particle
-NCU_TRAFFIC_PER_PARTICLE = {"k_propagate": (1.6199e9 + 2.0980e9) / (1 << 27),
-                            "k_fold_agg": (1.0746e9 + 0.0104e9) / (1 << 27),
-                            "k_ancestors": (1.0753e9 + 0.5089e9) / (1 << 27)}
+# committed `ncu --set full` capture (profiles/r01r_ncu_full_summary.csv), bytes/particle
+NCU_TRAFFIC_PER_PARTICLE = {"k_propagate": (1.7403e9 + 2.1641e9) / (1 << 27),
+                            "k_fold_agg": (1.0744e9 + 0.0089e9) / (1 << 27),
+                            "k_ancestors": (1.0760e9 + 0.5119e9) / (1 << 27)}
 STEP_BYTES = 64.0          # whole particle-step: 32d + 32
 
 
