@@ -102,6 +102,13 @@ struct FabricHost {
     std::vector<apop_ctx*> group;          // in-process group, rank order
 };
 
+struct RunRec {
+    long long k0;                // first pointer index of the run
+    int count;                   // offspring
+    int val;                     // ancestor id | lap << 31
+};
+constexpr int HEAVY_W = 1 << 18; // offspring of one (tile, lap) above which emission is deferred
+constexpr int BIG_RUN = 1 << 16; // runs split over all CTAs of the fill kernel
 constexpr int SEGB = 512;        // tiles per block of the segmented tile scan (k_seg_scan)
 constexpr int HCAP = 128;        // hard tiles per lap with precomputed prefix / suffix tables
 
@@ -136,6 +143,14 @@ struct ResampleWS {
     double* send = nullptr;      // [2] exact running sum at the end of each lap (this rank)
     double* trace = nullptr;     // [2][256] chain diagnostics: ns per hard-tile event (lap 0 / 1)
     int hcap = 0;                // table slots allocated per lap (min(HCAP, nt))
+    // deferred emission of heavy tiles (a tile that owns more than HEAVY_W offspring
+    // would serialise the step): k_ancestors records one run per element and
+    // k_fill_runs writes them with the whole GPU
+    RunRec* runs = nullptr;      // [runs_cap], blocks of TILE records per heavy (tile, lap)
+    RunRec* bigruns = nullptr;   // [big_cap] copies of the runs of >= BIG_RUN offspring
+    int* nruns = nullptr;        // [0]: records reserved, [1]: big runs
+    int runs_cap = 0, big_cap = 0;
+    int heavy_w = HEAVY_W;       // APOP_HEAVY_W overrides (tests force the deferred path at small n)
     Comb* comb = nullptr;
     ResampleInfo* info = nullptr;      // device
     ResampleInfo* info_host = nullptr; // pinned

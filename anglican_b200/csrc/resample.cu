@@ -22,6 +22,7 @@
 // else takes the general parity-transducer path.
 #include <limits.h>
 #include <math.h>
+#include <stdlib.h>
 #include <stddef.h>
 
 #include "apop_internal.cuh"
@@ -801,7 +802,7 @@ __device__ __forceinline__ double apply_run(double S, const Xd& x, int cls_run, 
     if ((x.a0 | x.a1) == 0) return S;
     const int e = ctx_of(S);
     const i64 s = xd_apply(units_of(S), x);
-    if (s >= kTwo53 || e != cls_run) atomicOr(err, EB_CTX);
+    if (s >= kTwo53 || e != cls_run) atomicOr(err, EB_CTX | 0x100);      // high bits: which check
     return from_units(s, e);
 }
 
@@ -998,7 +999,7 @@ __device__ double chain_lap(const WSView& v, int lap, double S, int64_t stop, do
         apply_units(xb, ce);
     }
     S = from_units(su, se);
-    if (bad && threadIdx.x == 0) atomicOr(err, EB_CTX);
+    if (bad && threadIdx.x == 0) atomicOr(err, EB_CTX | 0x200);
     *reached_stop = !over;
     // everything the walk did not reach
     for (int i = b + threadIdx.x; i <= nb; i += TB) v.sblk[lap][i] = INFINITY;
@@ -1022,7 +1023,7 @@ __device__ __forceinline__ double tile_sin(const WSView& v, int lap, int64_t t, 
     const Xd x = v.ex[lap][t];
     if ((x.a0 | x.a1) == 0) return base;
     const i64 s = xd_apply(units_of(base), x);
-    if (s >= kTwo53 || ctx_of(base) != c) { atomicOr(err, EB_CTX); return INFINITY; }
+    if (s >= kTwo53 || ctx_of(base) != c) { atomicOr(err, EB_CTX | 0x400); return INFINITY; }
     return from_units(s, c);
 }
 
@@ -1164,7 +1165,7 @@ __global__ void __launch_bounds__(TB) k_chain(const double* __restrict__ lw,
         mail_send(&F.mbox[F.rank + 1]->s1[par], S, 0.0, 0.0, seq);
     // the walk may only end at a skipped tile if no pointer of the second lap lies beyond
     if (reached && stop < nt && !(S > xlast) && threadIdx.x == 0) {
-        atomicOr(&I->err, EB_CTX);
+        atomicOr(&I->err, EB_CTX | 0x800);
         if (so.sd) so.sd->err |= EB_CTX;
     }
     if (threadIdx.x == 0) v.send[1] = S;
@@ -1187,6 +1188,7 @@ __device__ __forceinline__ int64_t slot_of(i64 k, int lap, int order, i64 J, i64
 // where offspring indices go: the local ancestor array, or (sharded) the array
 // of whichever rank owns the output slot, written through peer memory
 struct AncOut {
+    RunRec* runs; RunRec* bigruns; int* nruns; int runs_cap, big_cap, heavy_w;
     int32_t* local;
     const PeerI32* peerp;        // points at the kernel's __grid_constant__ parameter
     int world;
@@ -1305,7 +1307,7 @@ __device__ __forceinline__ bool staged_emit(const Comb& comb, int e, double Sin,
     const i64 s_out = s_in + (i64)tile_units;
     // consistency: the tile's integer sum must land on the chain's exact edge
     if ((s_out >= kTwo53 || (Sout < INFINITY && from_units(s_out, e) != Sout)) && threadIdx.x == 0)
-        atomicOr(err, EB_CTX);
+        atomicOr(err, EB_CTX | 0x1000);
     const i64 C0 = C0in, C1 = C1in;
     const CombSeg& g = gs;
     const double qD = (double)g.q;
@@ -1335,6 +1337,33 @@ __device__ __forceinline__ bool staged_emit(const Comb& comb, int e, double Sin,
     }
     const int W = (int)(C1 - C0);
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    if (W > A.heavy_w) {
+        // This tile owns so many offspring that emitting them here would serialise
+        // the step (degenerate weights: one particle with millions of copies).
+        // Record one run per element; k_fill_runs writes them with the whole GPU.
+        if (tid == 0) {
+            const int b = atomicAdd(A.nruns, TILE);
+            st.gi = (b + TILE <= A.runs_cap) ? b : -1;
+        }
+        __syncthreads();
+        const int rb = st.gi;
+        __syncthreads();
+        if (rb >= 0) {
+#pragma unroll
+            for (int j = 0; j < IPT; ++j) {
+                RunRec r;
+                r.k0 = C0 + kst[j];
+                r.count = ks[j] - kst[j];
+                r.val = (int)((unsigned)(val_tile0 + tid * IPT + j) | ((unsigned)lap << 31));
+                A.runs[rb + tid * IPT + j] = r;
+                if (r.count >= BIG_RUN) {
+                    const int bi = atomicAdd(A.nruns + 1, 1);
+                    if (bi < A.big_cap) { A.bigruns[bi] = r; A.runs[rb + tid * IPT + j].count = 0; }
+                }
+            }
+            return true;
+        }
+    }
     // windows of at most STAGE_CAP - 4 slots; inside shared memory the window is
     // shifted by a0 = (destination address / 4) mod 4 so that 16-byte groups of
     // the staging buffer line up with 16-byte groups of the output array and
@@ -1462,16 +1491,27 @@ __device__ __noinline__ void generic_emit(const Comb& comb, double Sin, const do
         const bool valid = (i0 + j < nvalid);
         i64 c = c_prev;
         if (valid) c = comb_count_below(comb, edge[j], hint);
-        const i64 cnt = c - c_prev;
+        i64 cnt = c - c_prev;
         const int32_t val = val0 + j;
+        if (cnt >= BIG_RUN) {
+            // one element with a huge number of offspring: hand the run to k_fill_runs
+            const int bi = atomicAdd(E.out.nruns + 1, 1);
+            if (bi < E.out.big_cap) {
+                RunRec r;
+                r.k0 = c_prev; r.count = (int)cnt;
+                r.val = (int)((unsigned)val | ((unsigned)E.lap << 31));
+                E.out.bigruns[bi] = r;
+                cnt = 0;
+            }
+        }
         const bool heavy = cnt > 8;
         if (!heavy)
-            for (i64 k = c_prev; k < c; ++k) E.put(k, val);
+            for (i64 k = c_prev; k < c_prev + cnt; ++k) E.put(k, val);
         unsigned hm = __ballot_sync(0xffffffffu, heavy);
         while (hm) {
             const int src = __ffs(hm) - 1;
             hm &= hm - 1;
-            const i64 hs = shfl_i64(c_prev, src), he = shfl_i64(c, src);
+            const i64 hs = shfl_i64(c_prev, src), he = shfl_i64(c_prev + cnt, src);
             const int32_t hv = __shfl_sync(0xffffffffu, val, src);
             for (i64 k = hs + lane; k < he; k += 32) E.put(k, hv);
         }
@@ -1483,6 +1523,7 @@ __device__ __noinline__ void generic_emit(const Comb& comb, double Sin, const do
 // exact running sum entering every tile, both laps, from the chain's records
 __global__ void __launch_bounds__(256) k_expand(WSView v) {
     const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (t == 0) { v.nruns[0] = 0; v.nruns[1] = 0; }           // run lists of this resample
     if (t > v.nt) return;
     int* err = &v.info->err;
     const double s0 = tile_sin(v, 0, t, err), s1 = tile_sin(v, 1, t, err);
@@ -1540,6 +1581,8 @@ __global__ void __launch_bounds__(TB, APOP_ANC_CTAS) k_ancestors(const double* _
     const int i0 = threadIdx.x * IPT;
     AncOut A;
     A.local = anc; A.peerp = &ancp; A.world = world; A.nl = n;
+    A.runs = v.runs; A.bigruns = v.bigruns; A.nruns = v.nruns; A.runs_cap = v.runs_cap;
+    A.big_cap = v.big_cap; A.heavy_w = v.heavy_w;
     // x0 is uniform on the wheel, so all tiles but the one holding x0 emit in
     // exactly one lap: that lap consumes the preloaded tile ...
     const int lap = do0 ? 0 : 1;
@@ -1579,6 +1622,47 @@ __global__ void __launch_bounds__(TB, APOP_ANC_CTAS) k_ancestors(const double* _
         load_weights(lw, win, base, n, m, w);
         __syncthreads();
         generic_emit(comb, si1, w, nvalid, (int32_t)(g0 + base + i0), E, sm.fold);
+    }
+}
+
+// Deferred emission (see RunRec): every warp takes run records in turn; the
+// runs of >= BIG_RUN offspring are split in chunks over all CTAs.
+constexpr int FILL_TB = 256;
+constexpr int FILL_CHUNK = 8192;
+__global__ void __launch_bounds__(FILL_TB) k_fill_runs(WSView v, int order, int32_t* __restrict__ anc,
+                                                      int64_t out_offset, int64_t nl,
+                                                      const __grid_constant__ PeerI32 ancp,
+                                                      int world) {
+    const ResampleInfo* I = v.info;
+    int nr = v.nruns[0], nbig = v.nruns[1];
+    if (nr == 0 && nbig == 0) return;
+    if (I->err) return;
+    if (nr > v.runs_cap) nr = (v.runs_cap / TILE) * TILE;      // blocks that did not fit fell back
+    if (nbig > v.big_cap) nbig = v.big_cap;
+    const i64 J = I->J, n_new = I->n_new;
+    AncOut A;
+    A.local = anc; A.peerp = &ancp; A.world = world; A.nl = nl;
+    const int lane = threadIdx.x & 31;
+    const int warp = (blockIdx.x * FILL_TB + threadIdx.x) >> 5, nwarps = (gridDim.x * FILL_TB) >> 5;
+    for (int r = warp; r < nr; r += nwarps) {
+        const RunRec rec = v.runs[r];
+        if (rec.count <= 0) continue;
+        const int lap = (int)((unsigned)rec.val >> 31);
+        const int32_t val = rec.val & 0x7fffffff;
+        for (i64 k = rec.k0 + lane; k < rec.k0 + rec.count; k += 32)
+            *A.at(out_offset + slot_of(k, lap, order, J, n_new)) = val;
+    }
+    for (int r = 0; r < nbig; ++r) {
+        const RunRec rec = v.bigruns[r];
+        const int lap = (int)((unsigned)rec.val >> 31);
+        const int32_t val = rec.val & 0x7fffffff;
+        const int chunks = (rec.count + FILL_CHUNK - 1) / FILL_CHUNK;
+        for (int ch = blockIdx.x; ch < chunks; ch += gridDim.x) {
+            const i64 kb = rec.k0 + (i64)ch * FILL_CHUNK;
+            const i64 ke = (kb + FILL_CHUNK < rec.k0 + rec.count) ? kb + FILL_CHUNK : rec.k0 + rec.count;
+            for (i64 k = kb + threadIdx.x; k < ke; k += FILL_TB)
+                *A.at(out_offset + slot_of(k, lap, order, J, n_new)) = val;
+        }
     }
 }
 
@@ -1659,6 +1743,7 @@ void preload_resample_kernels() {
     cudaFuncGetAttributes(&a, k_chain);
     cudaFuncGetAttributes(&a, k_expand);
     cudaFuncGetAttributes(&a, k_ancestors);
+    cudaFuncGetAttributes(&a, k_fill_runs);
     cudaFuncGetAttributes(&a, k_info_reset);
 }
 
@@ -1701,6 +1786,23 @@ int ensure_resample_ws(apop_ctx* c) {
         w.send = (double*)carve(2 * 8);
         w.trace = (double*)carve(2 * 256 * 8);
         w.comb = (Comb*)carve(sizeof(Comb));
+        {
+            // a (tile, lap) is heavy when it owns > HEAVY_W of the n_new pointers; n_new is
+            // the global population in a sharded sweep.  A list that still overflows
+            // (callers asking for n_new >> n) falls back to in-tile emission.
+            const int64_t nmax = (c->n_global > c->n) ? c->n_global : c->n;
+            if (pass == 0) {
+                w.heavy_w = HEAVY_W;
+                if (const char* e = getenv("APOP_HEAVY_W")) w.heavy_w = atoi(e) > 0 ? atoi(e) : HEAVY_W;
+            }
+            int64_t blocks = nmax / w.heavy_w + 2;
+            if (blocks > nt + 2) blocks = nt + 2;
+            w.runs_cap = (int)(blocks * TILE);
+            w.big_cap = (int)(nmax / BIG_RUN + 8);
+            w.runs = (RunRec*)carve((size_t)w.runs_cap * sizeof(RunRec));
+            w.bigruns = (RunRec*)carve((size_t)w.big_cap * sizeof(RunRec));
+            w.nruns = (int*)carve(2 * sizeof(int));
+        }
         ResampleInfo* info = (ResampleInfo*)carve(sizeof(ResampleInfo));
         if (pass == 0) {
             if (cudaMalloc(&w.slab, off) != cudaSuccess) {
@@ -1755,8 +1857,10 @@ int resample_enqueue(apop_ctx* c, const ResampleArgs& a) {
         kt_begin(c, KT_ANCESTORS);
         k_ancestors<<<nt, TB, 0, c->stream>>>(a.lw, a.w, a.n, g0, v, a.order, a.anc_out,
                                               a.out_offset, a.anc_peer, F.world);
+        k_fill_runs<<<592, FILL_TB, 0, c->stream>>>(v, a.order, a.anc_out, a.out_offset, a.n,
+                                                     a.anc_peer, F.world);
         kt_end(c, KT_ANCESTORS);
-        c->launches += 1;
+        c->launches += 2;
     }
     APOP_CUDA(c, cudaGetLastError());
     return APOP_OK;

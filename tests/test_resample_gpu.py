@@ -180,3 +180,64 @@ def test_large_population_bit_exact(orc, logn):
     assert total == ref["total"]
     nbad = int(np.sum(got != ref["emission"]))
     assert nbad == 0, f"{nbad} ancestor mismatches at n=2^{logn}"
+
+
+@pytest.mark.parametrize("case", ["one_giant", "forty_heavy", "giant_plus_background", "logweights"])
+def test_degenerate_weights_deferred_runs(orc, case):
+    """Weights so peaked that one tile owns more than HEAVY_W (2^18) offspring:
+    k_ancestors hands those runs to k_fill_runs instead of emitting them from
+    one CTA.  Ancestors stay bit-exact in every output order."""
+    from anglican_b200 import _lib as L
+    n = 1 << 20
+    rng = np.random.default_rng(5)
+    w = np.full(n, 1e-10)
+    if case == "one_giant":
+        w[777777] = 1.0                                   # one run of ~2^20 (>= BIG_RUN)
+    elif case == "forty_heavy":
+        w[300000:300040] = 1.0 + rng.random(40)           # 40 runs of ~26000 in one tile
+    elif case == "giant_plus_background":
+        w = rng.random(n)
+        w[123] = 3.0 * n                                  # 3/4 of the offspring + ordinary tiles
+    else:
+        w = None
+    with _pop(n) as pop:
+        anc = pop.column(L.I32)
+        if w is not None:
+            wcol = pop.column(L.F64, data=w)
+            for u in (0.0, 0.37, 0.999999):
+                ref = orc.resample_weights(w, n, u)
+                for order, key in ((L.ORDER_EMISSION, "emission"), (L.ORDER_REFERENCE, "anc_ref")):
+                    _, total, _ = pop.resample_weights(wcol, u=u, n_new=n, order=order, anc=anc)
+                    assert total == ref["total"]
+                    assert np.array_equal(anc.download(), ref[key]), (case, u, order)
+        else:
+            lw = rng.normal(0, 1, n)
+            lw[999] = 40.0                                # exp(40) against ~1: one giant particle
+            lcol = pop.column(L.F64, data=lw)
+            ref_anc, ref_lw = orc.resample(lw, n, 0.42)      # reference order (smc.cljc:127)
+            _, new_lw, _ = pop.resample(lcol, u=0.42, order=L.ORDER_REFERENCE, anc=anc)
+            assert np.array_equal(anc.download(), ref_anc)
+            assert abs(new_lw - ref_lw) <= 1e-9 * abs(ref_lw)
+
+
+@pytest.mark.parametrize("n", [4097, 20000, 100003])
+def test_deferred_runs_forced_at_small_sizes(orc, n, monkeypatch):
+    """APOP_HEAVY_W lowers the threshold so that ordinary tiles take the deferred
+    (run list + k_fill_runs) path: every weight family, every order, bit-exact"""
+    from anglican_b200 import _lib as L
+    monkeypatch.setenv("APOP_HEAVY_W", "1500")
+    rng = np.random.default_rng(n)
+    with _pop(n) as pop:
+        wcol = pop.column(L.F64)
+        anc = pop.column(L.I32)
+        for name, w in families(n, rng).items():
+            w = np.ascontiguousarray(w, dtype=np.float64)
+            wcol.upload(w)
+            for u in (0.0, 0.6180339887):
+                ref = orc.resample_weights(w, n, u)
+                for order, key in ((L.ORDER_EMISSION, "emission"), (L.ORDER_REFERENCE, "anc_ref"),
+                                   (L.ORDER_SORTED, "anc_sorted")):
+                    if key not in ref:
+                        continue
+                    pop.resample_weights(wcol, u=u, n_new=n, order=order, anc=anc)
+                    assert np.array_equal(anc.download(), ref[key]), (name, u, key)
