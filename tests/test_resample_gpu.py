@@ -235,9 +235,9 @@ def test_deferred_runs_forced_at_small_sizes(orc, n, monkeypatch):
             wcol.upload(w)
             for u in (0.0, 0.6180339887):
                 ref = orc.resample_weights(w, n, u)
+                srt = orc.emission_to_sorted(ref["emission"], ref["lap"])
+                ref["anc_sorted"] = srt[0] if isinstance(srt, tuple) else srt
                 for order, key in ((L.ORDER_EMISSION, "emission"), (L.ORDER_REFERENCE, "anc_ref"),
                                    (L.ORDER_SORTED, "anc_sorted")):
-                    if key not in ref:
-                        continue
                     pop.resample_weights(wcol, u=u, n_new=n, order=order, anc=anc)
                     assert np.array_equal(anc.download(), ref[key]), (name, u, key)
