@@ -251,9 +251,14 @@ struct MvnSweepArgs {
     int64_t n, g0;
     uint64_t seed;
     uint32_t t;
+    // sharded population: parents are global ids; rows of a peer's shard are read
+    // from its heap over NVLink (world == 1: unused)
+    PeerF64 xpeer;
+    int world;
 };
 
 bool mvn_dim_supported(int d);
+void mvn_preload_kernels(int d);
 int mvn_propagate_enqueue(apop_ctx* c, int d, const MvnSweepArgs& a);
 int mvn_init_enqueue(apop_ctx* c, double* x, int d, double s0, const double* retained);
 int mvn_observe_dmma_enqueue(apop_ctx* c, int d, const double* iL, double Z, const double* mean,

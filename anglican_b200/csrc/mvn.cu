@@ -87,8 +87,24 @@ __global__ void __launch_bounds__(512, 1) k_propagate_mvn(MvnSweepArgs a) {
             const int64_t k = k0 + p;
             int64_t par = 0;
             if (k < a.n) par = a.first_step ? k : (int64_t)a.anc[k];
-            const double* src = a.xp + par * D;
-            for (int cidx = lane; cidx < D; cidx += 32) T[p * LD + cidx] = (k < a.n) ? src[cidx] : 0.0;
+            if (a.world > 1 && !a.first_step) {
+                // global parent id: the shard that owns it, local or a peer's heap
+                const int q = (int)(par / a.n);
+                const int64_t loc = par - (int64_t)q * a.n;
+                if (par - a.g0 >= 0 && par - a.g0 < a.n) {
+                    const double* src = a.xp + (par - a.g0) * D;
+                    for (int cidx = lane; cidx < D; cidx += 32)
+                        T[p * LD + cidx] = (k < a.n) ? src[cidx] : 0.0;
+                } else {
+                    const double* src = a.xpeer.p[q] + loc * D;
+                    for (int cidx = lane; cidx < D; cidx += 32)
+                        T[p * LD + cidx] = (k < a.n) ? __ldcv(src + cidx) : 0.0;
+                }
+            } else {
+                const double* src = a.xp + par * D;
+                for (int cidx = lane; cidx < D; cidx += 32)
+                    T[p * LD + cidx] = (k < a.n) ? src[cidx] : 0.0;
+            }
         }
         __syncwarp();
         double acc[D / 8][2];
@@ -210,11 +226,11 @@ template <int D>
 static int launch_propagate(apop_ctx* c, const MvnSweepArgs& a) {
     constexpr int LD = MvnSmem<D>::LD;
     const size_t smem = sizeof(double) * (size_t)(3 * D * LD + D + 16 * 8 * LD);
-    static bool configured = false;
-    if (!configured) {
+    static bool configured[64] = {};              // the attribute is per device
+    if (c->device < 0 || c->device >= 64 || !configured[c->device]) {
         APOP_CUDA(c, cudaFuncSetAttribute(k_propagate_mvn<D>,
                                           cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        configured = true;
+        if (c->device >= 0 && c->device < 64) configured[c->device] = true;
     }
     int sms = 148;
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, c->device);
@@ -228,6 +244,21 @@ static int launch_propagate(apop_ctx* c, const MvnSweepArgs& a) {
 }
 
 bool mvn_dim_supported(int d) { return d == 8 || d == 16 || d == 32 || d == 64; }
+
+// resolve the kernels of a sharded mvn sweep before the first launch (lazy module
+// loading would wait for an idle device while a peer's kernel spins, ssm.cu)
+void mvn_preload_kernels(int d) {
+    cudaFuncAttributes a;
+    cudaFuncGetAttributes(&a, k_init_mvn);
+    switch (d) {
+    case 8: cudaFuncGetAttributes(&a, k_propagate_mvn<8>); break;
+    case 16: cudaFuncGetAttributes(&a, k_propagate_mvn<16>); break;
+    case 32: cudaFuncGetAttributes(&a, k_propagate_mvn<32>); break;
+    case 64: cudaFuncGetAttributes(&a, k_propagate_mvn<64>); break;
+    default: break;
+    }
+    cudaGetLastError();
+}
 
 int mvn_propagate_enqueue(apop_ctx* c, int d, const MvnSweepArgs& a) {
     switch (d) {

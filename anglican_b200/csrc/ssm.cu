@@ -430,12 +430,14 @@ __global__ void k_gather_rows(const double* __restrict__ src, double* __restrict
 
 // final states of a sharded sweep: parents are global ids
 __global__ void k_gather_shard(const __grid_constant__ PeerF64 src, double* __restrict__ dst,
-                               const int32_t* __restrict__ anc, int64_t n) {
-    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n;
+                               const int32_t* __restrict__ anc, int64_t n, int d) {
+    const int64_t total = n * (int64_t)d;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total;
          i += (int64_t)gridDim.x * blockDim.x) {
-        const int64_t a = anc[i];
+        const int64_t k = i / d;
+        const int64_t a = anc[k];
         const int q = (int)(a / n);
-        dst[i] = __ldcv(src.p[q] + (a - (int64_t)q * n));
+        dst[i] = __ldcv(src.p[q] + (a - (int64_t)q * n) * d + (i - k * d));
     }
 }
 
@@ -453,8 +455,8 @@ static int sweep_prepare(apop_ctx* c, int T, int dim, bool history) {
     if (!s) { s = new SweepState(); c->sweep = s; }
     const size_t n = (size_t)c->n;
     if (c->world > 1) {
-        if (dim != 1) return set_err(c, APOP_ERR_UNSUPPORTED, "sharded sweep: scalar states only");
-        APOP_TRY(fabric_prepare(c, n));             // collective: (re)maps the peer heaps
+        // heap columns hold n * dim doubles (the ancestor column is oversized for dim > 1)
+        APOP_TRY(fabric_prepare(c, n * (size_t)dim));   // collective: (re)maps the peer heaps
         if (!c->fab.linked)
             return set_err(c, APOP_ERR_INVALID, "sharded sweep: ranks are not linked "
                                                 "(apop_link_group / NCCL id)");
@@ -704,6 +706,9 @@ static int sweep_step(apop_ctx* c, int t, const apop_sweep_opts* o, bool csmc) {
         ma.xn = x_new; ma.lw = s->lw; ma.y = s->y + (size_t)(t - 1) * dim;
         ma.retained = csmc ? s->retained + (size_t)t * dim : nullptr;
         ma.sd = s->sd; ma.n = n; ma.g0 = c->g0; ma.seed = c->seed; ma.t = (uint32_t)t;
+        ma.world = c->world;
+        memset(&ma.xpeer, 0, sizeof ma.xpeer);
+        if (shard) ma.xpeer = peer_f64(c, (t & 1) ? c->fab.off_xa : c->fab.off_xb);   // x_{t-1}
         APOP_TRY(mvn_propagate_enqueue(c, s->dim, ma));
         c->launches -= 1;                 // counted below
     } else if (shard) {
@@ -785,7 +790,7 @@ static int sweep_end(apop_ctx* c, int T, const apop_sweep_opts* opts, apop_sweep
         kt_begin(c, KT_GATHER);
         if (c->world > 1) {
             const PeerF64 src = peer_f64(c, (T & 1) ? c->fab.off_xb : c->fab.off_xa);    // x_T
-            k_gather_shard<<<blocks, 256, 0, c->stream>>>(src, s->x_final, s->last_anc, n);
+            k_gather_shard<<<blocks, 256, 0, c->stream>>>(src, s->x_final, s->last_anc, n, dim);
         } else {
             k_gather_rows<<<blocks, 256, 0, c->stream>>>(s->last_x, s->x_final, s->last_anc, n, dim);
         }
@@ -924,7 +929,7 @@ static int sweep_group(apop_ctx* const* g, int ng, const apop_ssm* model, const 
             return set_err(c, APOP_ERR_INVALID, "sharded sweep: particles per rank must be a "
                                                 "multiple of 8");
         cudaSetDevice(c->device);
-        if (c->world > 1) preload_sweep_kernels();
+        if (c->world > 1) { preload_sweep_kernels(); if (dim > 1) mvn_preload_kernels(dim); }
         APOP_TRY(sweep_prepare(c, T, dim, opts->keep_history != 0));
         APOP_TRY(noise_prepare(c, model->kind, opts->keep_history != 0));
         APOP_TRY(upload_model(c, model));

@@ -459,12 +459,14 @@ class PopulationGroup:
 
     def sweep(self, model, y, want_final=True, want_stats=True, want_filt=False):
         y = np.ascontiguousarray(y, dtype=np.float64)
-        T = y.size
-        opts = L.ApopSweepOpts(0, 0, 0, 0, 0, int(want_final), int(bool(want_filt)), 0)
+        d = model.state_dim
+        T = y.size // d
+        want_filt = bool(want_filt) and d == 1
+        opts = L.ApopSweepOpts(0, 0, 0, 0, 0, int(want_final), int(want_filt), 0)
         res = (L.ApopSweepResult * self.world)()
         outs = []
         for r, p in enumerate(self.ranks):
-            out = SweepOutput(p, T, 1)
+            out = SweepOutput(p, T, d)
             if want_stats:
                 out.log_mean_w, out.ess = np.empty(T), np.empty(T)
                 res[r].log_mean_w, res[r].ess = _dp(out.log_mean_w), _dp(out.ess)
@@ -472,7 +474,7 @@ class PopulationGroup:
                 out.filt_mean = np.empty(T)
                 res[r].filt_mean = _dp(out.filt_mean)
             if want_final:
-                out.x_final = np.empty(self.n_local)
+                out.x_final = np.empty((self.n_local, d)) if d > 1 else np.empty(self.n_local)
                 res[r].x_final = _dp(out.x_final)
             outs.append(out)
         rc = self.lib.apop_smc_sweep_group(self._arr, self.world, C.byref(model.c), _dp(y), T,
