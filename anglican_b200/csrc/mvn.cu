@@ -82,29 +82,33 @@ __global__ void __launch_bounds__(512, 1) k_propagate_mvn(MvnSweepArgs a) {
     for (int64_t g = (int64_t)blockIdx.x * NW + wid; g < ngroups; g += (int64_t)gridDim.x * NW) {
         const int64_t k0 = g * 8;
         // ---- parent rows -> tile (ancestor gather folded into the read)
+        // In the sorted order consecutive slots often share their parent (always,
+        // when the weights are degenerate): a row equal to the previous one is
+        // copied inside the tile instead of being fetched again.  Rows of a peer's
+        // shard come over NVLink with ordinary (L1-cacheable) loads: they were
+        // written by an earlier kernel and the fabric barrier kernel separates
+        // the two, so a kernel-lifetime L1 line can never be stale.
+        int64_t par_prev = -1;
 #pragma unroll 1
         for (int p = 0; p < 8; ++p) {
             const int64_t k = k0 + p;
             int64_t par = 0;
             if (k < a.n) par = a.first_step ? k : (int64_t)a.anc[k];
-            if (a.world > 1 && !a.first_step) {
+            if (p > 0 && par == par_prev && k < a.n) {
+                for (int cidx = lane; cidx < D; cidx += 32) T[p * LD + cidx] = T[(p - 1) * LD + cidx];
+            } else if (a.world > 1 && !a.first_step) {
                 // global parent id: the shard that owns it, local or a peer's heap
                 const int q = (int)(par / a.n);
-                const int64_t loc = par - (int64_t)q * a.n;
-                if (par - a.g0 >= 0 && par - a.g0 < a.n) {
-                    const double* src = a.xp + (par - a.g0) * D;
-                    for (int cidx = lane; cidx < D; cidx += 32)
-                        T[p * LD + cidx] = (k < a.n) ? src[cidx] : 0.0;
-                } else {
-                    const double* src = a.xpeer.p[q] + loc * D;
-                    for (int cidx = lane; cidx < D; cidx += 32)
-                        T[p * LD + cidx] = (k < a.n) ? __ldcv(src + cidx) : 0.0;
-                }
+                const double* src = (q == (int)(a.g0 / a.n)) ? a.xp + (par - a.g0) * D
+                                                             : a.xpeer.p[q] + (par - (int64_t)q * a.n) * D;
+                for (int cidx = lane; cidx < D; cidx += 32)
+                    T[p * LD + cidx] = (k < a.n) ? src[cidx] : 0.0;
             } else {
                 const double* src = a.xp + par * D;
                 for (int cidx = lane; cidx < D; cidx += 32)
                     T[p * LD + cidx] = (k < a.n) ? src[cidx] : 0.0;
             }
+            par_prev = (k < a.n) ? par : -1;
         }
         __syncwarp();
         double acc[D / 8][2];

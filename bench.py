@@ -61,6 +61,22 @@ def sv_observations(T, seed=20240602, phi=0.98, sigma=0.16, beta=0.65):
     return ys
 
 
+def lgmvn_workload(T, d=64):
+    """BASELINE config 5: A = 0.9 Q, process cov 0.1 I, obs cov 0.5 I + 0.5 11^T/d"""
+    rng = np.random.default_rng(20240603)
+    Q, _ = np.linalg.qr(rng.normal(size=(d, d)))
+    A = 0.9 * Q
+    Qc = 0.1 * np.eye(d)
+    R = 0.5 * np.eye(d) + 0.5 * np.ones((d, d)) / d
+    x = rng.normal(size=d)
+    Lr = np.linalg.cholesky(R)
+    ys = []
+    for _ in range(T):
+        x = A @ x + math.sqrt(0.1) * rng.normal(size=d)
+        ys.append(x + Lr @ rng.normal(size=d))
+    return A, Qc, R, np.array(ys).ravel()
+
+
 def measured_peak():
     try:
         pk = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
@@ -126,6 +142,21 @@ def dist_env():
     return rank, world, local
 
 
+def oracle_sample(args, T_cap):
+    """the bounded sample the CPU arms run: (oracle model, observations, particles, steps, label)"""
+    from oracle import pyoracle as orc
+    if args.workload == "lgmvn64":
+        n_s, T_s = 1 << 13, min(args.T, 20)
+        A, Qc, R, y = lgmvn_workload(args.T, 64)
+        m = orc.Model(orc.SSM_LGMVN, dim=64, s0=1.0, A=A, Lq=np.linalg.cholesky(Qc), R=R)
+        return m, y[:T_s * 64], n_s, T_s, "64-dim linear-Gaussian sweep"
+    n_s, T_s = 1 << 17, min(args.T, T_cap)
+    phi, sigma, beta = 0.98, 0.16, 0.65
+    m = orc.Model(orc.SSM_SV, m0=0.0, s0=sigma / math.sqrt(1 - phi * phi), a=phi, b=0.0, q=sigma,
+                  beta=beta)
+    return m, sv_observations(args.T)[:T_s], n_s, T_s, "SV sweep"
+
+
 # --------------------------------------------------------------------- reference arm
 def run_reference(args):
     """The reference's CPU path for the same workload.  The Clojure reference
@@ -138,11 +169,7 @@ def run_reference(args):
     from oracle import pyoracle as orc
     T = args.T
     cores = os.cpu_count() or 1
-    n_s, T_s = 1 << 17, min(T, 200)
-    y = sv_observations(T)[:T_s]
-    phi, sigma, beta = 0.98, 0.16, 0.65
-    m = orc.Model(orc.SSM_SV, m0=0.0, s0=sigma / math.sqrt(1 - phi * phi), a=phi, b=0.0, q=sigma,
-                  beta=beta)
+    m, y, n_s, T_s, label = oracle_sample(args, 200)
     times = []
     for i in range(args.warmup + args.steps):
         t0 = time.perf_counter()
@@ -152,7 +179,7 @@ def run_reference(args):
             times.append(dt)
     total = sum(times)
     v = n_s * T_s * len(times) / total
-    sample = (f"SV sweep, {n_s} particles x {T_s} of {T} steps per bench step (bounded sample of "
+    sample = (f"{label}, {n_s} particles x {T_s} of {T} steps per bench step (bounded sample of "
               f"the 2^{int(math.log2(args.particles))}-particle workload; per-particle-step cost is "
               "size-independent on the CPU)")
     line = {"impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus,
@@ -194,8 +221,15 @@ def run_ours(args):
     n_total, T = args.particles, args.T
     assert n_total % world == 0
     n_local = n_total // world
-    y = sv_observations(T)
-    model = StochasticVolatility()
+    mvn = args.workload == "lgmvn64"
+    dim = 64 if mvn else 1
+    if mvn:
+        from anglican_b200.models import LinearGaussianMVN
+        A, Qc, R, y = lgmvn_workload(T, dim)
+        model = LinearGaussianMVN(A, Qc, R)
+    else:
+        y = sv_observations(T)
+        model = StochasticVolatility()
     pop = Population(n_local, seed=0xA11CE, device=local, rank=rank, world=world, nccl_id=nccl_id)
 
     # ---- warm-up (>= 3 sweeps): device-resident path
@@ -228,15 +262,15 @@ def run_ours(args):
     pop.enable_kernel_timers(False)
 
     # ---- e2e: public call, host buffers in/out, copies inside the timed region
-    x_host_bytes = n_local * 8
+    x_host_bytes = n_local * 8 * dim
     # untimed: allocates the population's page-locked result buffer
-    pop.sweep(model, y[:4], want_final=True, want_stats=True, pinned_final=True)
+    pop.sweep(model, y[:4 * dim], want_final=True, want_stats=True, pinned_final=True)
     barrier()
     e0 = time.perf_counter()
     for i in range(args.steps):
         pop.set_seed(3000 + i)
         out = pop.sweep(model, y, want_final=True, want_stats=True, pinned_final=True)
-        x_mean = float(out.x_final[::4096].mean())      # the host reads the result
+        x_mean = float(out.x_final.reshape(-1)[::4096].mean())      # the host reads the result
     barrier()
     e2e_s = time.perf_counter() - e0
 
@@ -251,6 +285,19 @@ def run_ours(args):
         dom = max(((n, v) for n, v in kt.items() if n in ALGO_BYTES), key=lambda kv: kv[1][0],
                   default=None)
         roof = None
+        step_bytes = 32.0 * dim + 32.0                 # 32 d + 32
+        if mvn and "k_propagate" in kt:
+            # K6: the two d x d products per particle on the fp64 tensor pipe (DMMA)
+            ms, c = kt["k_propagate"]
+            avg_s = ms / 1e3 / c
+            flop = 4.0 * n_local * dim * dim
+            roof = {"kernel": "k_propagate_mvn<64>", "bound": "tensor", "achieved": flop / avg_s / 1e12,
+                    "peak": 40.0, "unit": "TFLOP/s", "frac": flop / avg_s / 1e12 / 40.0,
+                    "traffic": None, "peak_source": "nominal B200 fp64 (MEASURED_PEAKS.json has no "
+                    "fp64 figure); ncu: DMMA pipe 57 % active (profiles/r01t_ncu_mvn_summary.txt)",
+                    "avg_launch_us": avg_s * 1e6, "launches_timed": c,
+                    "algorithmic_flop_per_particle": 4.0 * dim * dim}
+            dom = None
         if dom:
             name, (ms, c) = dom
             avg_s = ms / 1e3 / c
@@ -264,9 +311,9 @@ def run_ours(args):
                     "avg_launch_us": avg_s * 1e6, "launches_timed": c,
                     "algorithmic_bytes_per_particle": MOVED_BYTES[name]}
         ksum_ms = sum(v[0] for v in kt.values())
-        path = {"bytes_per_particle_step": STEP_BYTES,
-                "achieved_gbs": STEP_BYTES * n_local * T * args.steps / (dev_s) / 1e9,
-                "frac": STEP_BYTES * n_local * T * args.steps / dev_s / 1e9 / peak,
+        path = {"bytes_per_particle_step": step_bytes,
+                "achieved_gbs": step_bytes * n_local * T * args.steps / (dev_s) / 1e9,
+                "frac": step_bytes * n_local * T * args.steps / dev_s / 1e9 / peak,
                 "kernel_share": {n: v[0] / ksum_ms for n, v in kt.items()} if ksum_ms else {},
                 "kernel_avg_us": {n: 1e3 * v[0] / v[1] for n, v in kt.items()}}
         line = {"metric": METRIC, "value": work / dev_s, "unit": UNIT, "n_gpus": world,
@@ -274,12 +321,14 @@ def run_ours(args):
                 "ms_per_step": 1e3 * dev_s / args.steps, "higher_is_better": True,
                 "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
                 "config": {"workload": args.workload_name, "particles_total": n_total,
-                           "particles_per_gpu": n_local, "T": T, "model": "stochastic volatility "
-                           "phi=0.98 sigma=0.16 beta=0.65", "resampling": "systematic, every step",
+                           "particles_per_gpu": n_local, "T": T,
+                           "model": ("64-dim linear-Gaussian SSM, mvn observe (DMMA)" if mvn else
+                                     "stochastic volatility phi=0.98 sigma=0.16 beta=0.65"),
+                           "resampling": "systematic, every step",
                            "l2": "inputs exceed L2 (columns of %d MiB per GPU)" % (n_local * 8 >> 20),
                            "timing": "CUDA events on the engine stream, max over ranks"},
                 "e2e": {"value": work / e2e_s, "unit": UNIT,
-                        "h2d_bytes_per_step": int(T * 8 + 4096),
+                        "h2d_bytes_per_step": int(T * 8 * dim + 4096),
                         "d2h_bytes_per_step": int(x_host_bytes + 2 * T * 8 + 64)},
                 "gpu_launches": int(launches), "clocks": clocks, "roofline": roof,
                 "path_roofline": path, "wall_ms_per_step": 1e3 * wall / args.steps,
@@ -296,16 +345,12 @@ def cpu_baseline(args):
     """oracle port of smc.cljc, 1 core (the reference's `infer :smc` is single
     threaded), on a bounded sample of the same workload."""
     from oracle import pyoracle as orc
-    n_s, T_s = 1 << 17, min(args.T, 300)
-    y = sv_observations(args.T)[:T_s]
-    phi, sigma, beta = 0.98, 0.16, 0.65
-    m = orc.Model(orc.SSM_SV, m0=0.0, s0=sigma / math.sqrt(1 - phi * phi), a=phi, b=0.0, q=sigma,
-                  beta=beta)
+    m, y, n_s, T_s, label = oracle_sample(args, 300)
     t0 = time.perf_counter()
     orc.smc_sweep(m, y, n_s, seed=1, threads=1, want_final=True)
     dt = time.perf_counter() - t0
     return {"value": n_s * T_s / dt, "unit": UNIT, "cores": 1, "kind": "port",
-            "sample": f"SV sweep of {n_s} particles x {T_s} steps ({dt:.1f} s), oracle C port of "
+            "sample": f"{label} of {n_s} particles x {T_s} steps ({dt:.1f} s), oracle C port of "
                       "smc.cljc; reference JVM path unavailable on this box (no JVM)"}
 
 
@@ -315,12 +360,22 @@ def main():
     ap.add_argument("--steps", type=int, default=2)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--particles", type=int, default=1 << 27)
-    ap.add_argument("--T", type=int, default=2000)
+    ap.add_argument("--workload", default="sv", choices=["sv", "lgmvn64"],
+                    help="sv: BASELINE configs[2] (the headline); lgmvn64: configs[4]")
+    ap.add_argument("--particles", type=int, default=0)
+    ap.add_argument("--T", type=int, default=0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
-    args.workload_name = ("configs[2]: stochastic-volatility SSM, T=%d, %d particles :smc sharded "
-                          "over %d B200" % (args.T, args.particles, args.gpus))
+    if args.workload == "lgmvn64":
+        args.particles = args.particles or (1 << 24)
+        args.T = args.T or 100
+        args.workload_name = ("configs[4]: 64-dim linear-Gaussian SSM, mvn observe, T=%d, %d particles "
+                              ":smc sharded over %d B200" % (args.T, args.particles, args.gpus))
+    else:
+        args.particles = args.particles or (1 << 27)
+        args.T = args.T or 2000
+        args.workload_name = ("configs[2]: stochastic-volatility SSM, T=%d, %d particles :smc sharded "
+                              "over %d B200" % (args.T, args.particles, args.gpus))
     if args.impl == "reference":
         run_reference(args)
     else:
