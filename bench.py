@@ -4,9 +4,13 @@
     python bench.py --gpus N --steps K --warmup W          (our arm)
     python bench.py --impl reference --gpus N --steps K --warmup W
 
-One "step" = one full `sweep` (smc.cljc:35-51) of BASELINE config 3: the
-stochastic-volatility SSM, T=2000 observations, 2^27 particles in total,
-sharded contiguously over the N ranks (strong scaling, north_star).  `value` is
+One "step" = `--inflight` (default 2) independent full `sweep`s (smc.cljc:35-51;
+`infer :smc` is an endless sequence of independent sweeps, smc.cljc:58-63) of
+BASELINE config 3: the stochastic-volatility SSM, T=2000 observations, 2^27
+particles in total per sweep, sharded contiguously over the N ranks (strong
+scaling, north_star), each sweep on its own population (context + stream) so
+that the serial phases of one overlap the streaming kernels of the other.
+`--workload lgmvn64` measures BASELINE config 5 instead.  `value` is
 whole-job particle-steps/s timed on the device (CUDA events on the engine's
 stream, max over ranks) with inputs resident in HBM; `e2e` is the same metric
 through the public call (host observations in, log-marginal + per-step stats +
@@ -25,6 +29,9 @@ import numpy as np
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
+# several populations (streams) per GPU, some of whose kernels wait on a peer: give
+# every stream its own hardware queue so that none is serialised behind another
+os.environ.setdefault("CUDA_DEVICE_MAX_CONNECTIONS", "32")
 
 METRIC = "smc_particle_steps_per_sec"
 UNIT = "particle-steps/s"
@@ -230,55 +237,101 @@ def run_ours(args):
     else:
         y = sv_observations(T)
         model = StochasticVolatility()
-    pop = Population(n_local, seed=0xA11CE, device=local, rank=rank, world=world, nccl_id=nccl_id)
+    # `infer :smc` is an endless sequence of INDEPENDENT sweeps (sample-seq,
+    # smc.cljc:58-63).  F of them are kept in flight, each on its own population
+    # (context + stream): the single-CTA phases of one sweep's exact resampler
+    # (k_finalize, k_chain) overlap with the streaming kernels of the other.
+    from concurrent.futures import ThreadPoolExecutor
+    F = max(1, min(args.inflight, 3))
+    pops = []
+    for f in range(F):
+        nid = nccl_id
+        if world > 1 and f > 0:
+            from anglican_b200.distributed import nccl_unique_id
+            nid = nccl_unique_id(rank)            # one communicator per population
+        pops.append(Population(n_local, seed=0xA11CE + f, device=local, rank=rank, world=world,
+                               nccl_id=nid))
+    pop = pops[0]
+    pool = ThreadPoolExecutor(max_workers=F)
 
-    # ---- warm-up (>= 3 sweeps): device-resident path
-    for i in range(args.warmup):
-        pop.set_seed(1000 + i)
-        pop.sweep(model, y, want_final=False, want_stats=False)
-    pop.timer_reset()
-    pop.enable_kernel_timers(True)
+    def sweeps(f, count, seed0, **kw):
+        zs = []
+        for i in range(count):
+            pops[f].set_seed(seed0 + 100 * f + i)
+            o = pops[f].sweep(model, y, **kw)
+            if kw.get("want_final"):
+                zs.append(float(o.x_final.reshape(-1)[::4096].mean()))   # the host reads the result
+            else:
+                zs.append(o.log_z)
+        return zs
+
+    # ---- warm-up (>= 3 sweeps per population): the first sweep of each population
+    # runs alone (allocations, and for N > 1 the NCCL / IPC set-up, are collective)
+    for f in range(F):
+        sweeps(f, 1, 900, want_final=False, want_stats=False)
+        barrier()
+    if args.warmup > 1:
+        list(pool.map(lambda f: sweeps(f, args.warmup - 1, 1000, want_final=False, want_stats=False),
+                      range(F)))
+    # ---- per-kernel timers (roofline, kernel shares): one population alone when
+    # several are in flight, so that launches of another stream do not overlap
+    kt = {}
+    if F > 1:
+        barrier()
+        pop.timer_reset()
+        pop.enable_kernel_timers(True)
+        sweeps(0, 1, 1500, want_final=False, want_stats=False)
+        pop.synchronize()
+        for tag, name in KT_NAMES.items():
+            ms, c = pop.timer_ms(tag)
+            if c:
+                kt[name] = (ms, c)
+        pop.enable_kernel_timers(False)
+    for p_ in pops:
+        p_.timer_reset()
+    if F == 1:
+        pop.enable_kernel_timers(True)
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
-    launches0 = pop.launches
+    launches0 = sum(p_.launches for p_ in pops)
     barrier()
     wall0 = time.perf_counter()
-    log_zs = []
-    for i in range(args.steps):
-        pop.set_seed(2000 + i)
-        out = pop.sweep(model, y, want_final=False, want_stats=False)
-        log_zs.append(out.log_z)
+    zs = list(pool.map(lambda f: sweeps(f, args.steps, 2000, want_final=False, want_stats=False),
+                       range(F)))
     barrier()
     wall = time.perf_counter() - wall0
-    launches = pop.launches - launches0
-    dev_ms, cnt = pop.timer_ms(0)            # kernels of the sweeps, CUDA events on the engine stream
-    kt = {}
-    for tag, name in KT_NAMES.items():
-        ms, c = pop.timer_ms(tag)
-        if c:
-            kt[name] = (ms, c)
+    log_zs = [z for l in zs for z in l]
+    launches = sum(p_.launches for p_ in pops) - launches0
+    # device time of the timed sweeps: CUDA events on each population's stream
+    # (sum over its back-to-back sweeps); populations run concurrently -> max
+    dev_ms = max(p_.timer_ms(0)[0] for p_ in pops)
+    if F == 1:
+        for tag, name in KT_NAMES.items():
+            ms, c = pop.timer_ms(tag)
+            if c:
+                kt[name] = (ms, c)
+        pop.enable_kernel_timers(False)
     clocks = sampler.stop() if rank == 0 else None
-    pop.enable_kernel_timers(False)
 
     # ---- e2e: public call, host buffers in/out, copies inside the timed region
     x_host_bytes = n_local * 8 * dim
-    # untimed: allocates the population's page-locked result buffer
-    pop.sweep(model, y[:4 * dim], want_final=True, want_stats=True, pinned_final=True)
-    barrier()
+    # untimed: allocates the populations' page-locked result buffers
+    for f in range(F):
+        pops[f].sweep(model, y[:4 * dim], want_final=True, want_stats=True, pinned_final=True)
+        barrier()
     e0 = time.perf_counter()
-    for i in range(args.steps):
-        pop.set_seed(3000 + i)
-        out = pop.sweep(model, y, want_final=True, want_stats=True, pinned_final=True)
-        x_mean = float(out.x_final.reshape(-1)[::4096].mean())      # the host reads the result
+    list(pool.map(lambda f: sweeps(f, args.steps, 3000, want_final=True, want_stats=True,
+                                   pinned_final=True), range(F)))
     barrier()
     e2e_s = time.perf_counter() - e0
+    pool.shutdown()
 
     t_dev = torch.tensor([dev_ms / 1e3, e2e_s, wall], dtype=torch.float64, device="cuda")
     if world > 1:
         dist.all_reduce(t_dev, op=dist.ReduceOp.MAX)
     dev_s, e2e_s, wall = [float(v) for v in t_dev.cpu()]
-    work = float(n_total) * T * args.steps
+    work = float(n_total) * T * args.steps * F
 
     if rank == 0:
         peak, peak_kind = measured_peak()
@@ -312,8 +365,8 @@ def run_ours(args):
                     "algorithmic_bytes_per_particle": MOVED_BYTES[name]}
         ksum_ms = sum(v[0] for v in kt.values())
         path = {"bytes_per_particle_step": step_bytes,
-                "achieved_gbs": step_bytes * n_local * T * args.steps / (dev_s) / 1e9,
-                "frac": step_bytes * n_local * T * args.steps / dev_s / 1e9 / peak,
+                "achieved_gbs": step_bytes * n_local * T * args.steps * F / (dev_s) / 1e9,
+                "frac": step_bytes * n_local * T * args.steps * F / dev_s / 1e9 / peak,
                 "kernel_share": {n: v[0] / ksum_ms for n, v in kt.items()} if ksum_ms else {},
                 "kernel_avg_us": {n: 1e3 * v[0] / v[1] for n, v in kt.items()}}
         line = {"metric": METRIC, "value": work / dev_s, "unit": UNIT, "n_gpus": world,
@@ -325,18 +378,22 @@ def run_ours(args):
                            "model": ("64-dim linear-Gaussian SSM, mvn observe (DMMA)" if mvn else
                                      "stochastic volatility phi=0.98 sigma=0.16 beta=0.65"),
                            "resampling": "systematic, every step",
+                           "sweeps_in_flight": F,
+                           "step": "one step = %d independent sweep(s) of the workload in flight, "
+                                   "one population (context + stream) each" % F,
                            "l2": "inputs exceed L2 (columns of %d MiB per GPU)" % (n_local * 8 >> 20),
                            "timing": "CUDA events on the engine stream, max over ranks"},
                 "e2e": {"value": work / e2e_s, "unit": UNIT,
-                        "h2d_bytes_per_step": int(T * 8 * dim + 4096),
-                        "d2h_bytes_per_step": int(x_host_bytes + 2 * T * 8 + 64)},
+                        "h2d_bytes_per_step": int(T * 8 * dim + 4096) * F,
+                        "d2h_bytes_per_step": int(x_host_bytes + 2 * T * 8 + 64) * F},
                 "gpu_launches": int(launches), "clocks": clocks, "roofline": roof,
                 "path_roofline": path, "wall_ms_per_step": 1e3 * wall / args.steps,
                 "log_z_mean": float(np.mean(log_zs))}
         if world == 1 and not args.no_cpu_baseline:
             line["cpu_baseline"] = cpu_baseline(args)
         print(json.dumps(line), flush=True)
-    pop.close()
+    for p_ in pops:
+        p_.close()
     if world > 1:
         dist.destroy_process_group()
 
@@ -365,6 +422,10 @@ def main():
     ap.add_argument("--particles", type=int, default=0)
     ap.add_argument("--T", type=int, default=0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--inflight", type=int, default=2,
+                    help="independent sweeps kept in flight, one population each (measured: "
+                         "1 GPU 59 -> 62 G, 8 GPUs 214 -> 318 (2) -> 365 (3) G particle-steps/s; "
+                         "4 and more stalled on peer waits at 8 GPUs, profiles/r02b_*)")
     args = ap.parse_args()
     if args.workload == "lgmvn64":
         args.particles = args.particles or (1 << 24)

@@ -2,7 +2,7 @@
 """Secondary measurements on the other BASELINE configs (bench.py measures
 config 3).  One JSON line per config; copied into profiles/ by hand.
 
-    python tools/bench_configs.py c2 | c5 [--particles N] [--T T]
+    python tools/bench_configs.py c2 | c4 | c5 [--particles N] [--T T]
 """
 import argparse
 import json
@@ -96,12 +96,80 @@ def c5(args):
             "compulsory_gbs_whole_step": byts / dev_s / 1e9, "log_z": zs, "kernel_avg_us": kt}
 
 
+def c4(args):
+    """config 4 on one GPU: IPMCMC on the SV model; the nodes of this GPU run one after
+    the other on the device (conditional and unconditional sweeps with lineages kept),
+    only the node log-marginals and the retained paths leave it (ipmcmc.cljc:34-208)."""
+    import ctypes as C
+    from anglican_b200 import _lib as L
+    from anglican_b200.models import StochasticVolatility
+    from bench import sv_observations
+    M = args.nodes
+    P = M // 2
+    n, T = args.particles or (1 << 22), args.T or 200
+    y = sv_observations(2000)[:T]
+    m = StochasticVolatility()
+    lib = L.load()
+    rng = np.random.default_rng(1)
+    from concurrent.futures import ThreadPoolExecutor
+    # one context (own stream) per node, driven by a pool like the reference's
+    # cp/pmap over nodes (ipmcmc.cljc:176-182): the single-CTA phases of one node's
+    # resampler overlap with the streaming kernels of the others
+    W = M if args.concurrent else 1
+    pops = [Population(n, seed=77 + w) for w in range(W)]
+    pool = ThreadPoolExecutor(max_workers=W)
+    try:
+        retained = [None] * P
+        log_hist = []
+        t_all = []
+        for it in range(args.warmup + args.steps):
+            for p_ in pops:
+                p_.synchronize()
+            t0 = time.perf_counter()
+            picks = [int(rng.random() * n) for _ in range(M)]
+
+            def node(j):
+                pop = pops[j % W]
+                ret = retained[j] if j < P else None
+                pop.set_seed(1000 * it + j + 1)
+                out = pop.sweep(m, y, retained=ret, csmc=ret is not None, n_cond_steps=T,
+                                reset_weights=True, keep_history=True, want_final=False,
+                                want_stats=False)
+                return out.log_z, out.trace(picks[j])               # rand-nth, ipmcmc.cljc:189
+
+            res = list(pool.map(node, range(M)))
+            log_zs = np.array([r[0] for r in res])
+            cand = [r[1] for r in res]
+            u = rng.random(P)
+            cs, zs = np.empty(P, dtype=np.int32), np.empty(M)
+            rc = lib.apop_ipmcmc_gibbs(log_zs.ctypes.data_as(L.c_double_p), M, P,
+                                       u.ctypes.data_as(L.c_double_p),
+                                       cs.ctypes.data_as(L.c_int32_p), zs.ctypes.data_as(L.c_double_p))
+            assert rc == 0
+            retained = [cand[int(c)] for c in cs]
+            dt = time.perf_counter() - t0
+            if it >= args.warmup:
+                t_all.append(dt)
+                log_hist.append(log_zs.tolist())
+    finally:
+        pool.shutdown()
+        for p_ in pops:
+            p_.close()
+    tot = sum(t_all)
+    return {"config": "configs[3] on 1 B200: IPMCMC on the SV model, %d nodes (%d conditional) x %d "
+                      "particles, T=%d, lineages kept, %s" % (M, P, n, T, "nodes concurrent (one ctx + stream each)" if args.concurrent else "nodes one after the other"),
+            "particle_steps_per_s": M * n * T * len(t_all) / tot, "s_per_mcmc_iteration": tot / len(t_all),
+            "node_log_z": log_hist, "timing": "wall clock around the iteration, device synchronised"}
+
+
 if __name__ == "__main__":
     ap = argparse.ArgumentParser()
-    ap.add_argument("config", choices=["c2", "c5"])
+    ap.add_argument("config", choices=["c2", "c4", "c5"])
+    ap.add_argument("--nodes", type=int, default=4)
+    ap.add_argument("--concurrent", action="store_true")
     ap.add_argument("--particles", type=int, default=0)
     ap.add_argument("--T", type=int, default=0)
     ap.add_argument("--steps", type=int, default=2)
     ap.add_argument("--warmup", type=int, default=2)
     a = ap.parse_args()
-    print(json.dumps({"c2": c2, "c5": c5}[a.config](a)), flush=True)
+    print(json.dumps({"c2": c2, "c4": c4, "c5": c5}[a.config](a)), flush=True)
