@@ -1,0 +1,47 @@
+"""bench.py's reference arm runs without a GPU: its JSON line must carry the
+keys the driver reads (same metric / unit / config as our arm)."""
+import json
+import os
+import subprocess
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _run(*extra):
+    out = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--impl", "reference",
+                          "--steps", "1", "--warmup", "0", *extra],
+                         capture_output=True, text=True, timeout=600, cwd=ROOT)
+    assert out.returncode == 0, out.stderr[-2000:]
+    lines = [l for l in out.stdout.splitlines() if l.startswith("{")]
+    assert len(lines) == 1                      # ONE JSON line
+    return json.loads(lines[0])
+
+
+def test_reference_arm_line_sv():
+    d = _run("--T", "12")
+    assert d["impl"] == "reference" and d["metric"] == "smc_particle_steps_per_sec"
+    assert d["unit"] == "particle-steps/s" and d["higher_is_better"] is True
+    assert d["value"] > 0 and d["n_gpus"] == 1 and d["steps"] == 1 and d["warmup"] == 0
+    assert d["vs_baseline"] is None and d["dtype"] == "f64" and d["data"] == "synthetic"
+    assert "configs[2]" in d["config"]["workload"]
+    cb = d["cpu_baseline"]
+    assert cb["kind"] == "port" and cb["cores"] >= 1 and cb["value"] == d["value"] and cb["sample"]
+    e = d["e2e"]
+    assert e["value"] == d["value"] and e["h2d_bytes_per_step"] == 0 and e["d2h_bytes_per_step"] == 0
+
+
+def test_reference_arm_line_lgmvn64():
+    d = _run("--workload", "lgmvn64", "--T", "3")
+    assert "configs[4]" in d["config"]["workload"] and d["value"] > 0
+
+
+def test_workload_generators_are_deterministic():
+    sys.path.insert(0, ROOT)
+    import bench
+    import numpy as np
+    assert np.array_equal(bench.sv_observations(50), bench.sv_observations(50))
+    a, b = bench.lgmvn_workload(4, 8), bench.lgmvn_workload(4, 8)
+    assert all(np.array_equal(x, y) for x, y in zip(a, b))
+    A, Qc, R, y = a
+    assert y.shape == (32,) and np.allclose(A @ A.T, 0.81 * np.eye(8))       # A = 0.9 Q, Q orthogonal
