@@ -29,9 +29,6 @@ import numpy as np
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
-# several populations (streams) per GPU, some of whose kernels wait on a peer: give
-# every stream its own hardware queue so that none is serialised behind another
-os.environ.setdefault("CUDA_DEVICE_MAX_CONNECTIONS", "32")
 
 METRIC = "smc_particle_steps_per_sec"
 UNIT = "particle-steps/s"
