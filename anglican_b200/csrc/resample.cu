@@ -292,6 +292,10 @@ __global__ void __launch_bounds__(TB) k_tile_lse(const double* __restrict__ lw,
 constexpr int FB = 1024;
 constexpr int FCH = 4;                 // values per thread per scan chunk
 
+// Exclusive prefix sums of non-negative values.  Exclusive values are taken from
+// the neighbour's inclusive one (never "inclusive - own": one dominant value
+// would cancel the whole prefix and break the relative error bound that
+// classify_tile relies on).
 __device__ __forceinline__ double block_excl_scan_f64(double v, double* sm /*[33]*/,
                                                       double& total) {
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
@@ -301,21 +305,24 @@ __device__ __forceinline__ double block_excl_scan_f64(double v, double* sm /*[33
         double o = __shfl_up_sync(0xffffffffu, inc, d);
         if (lane >= d) inc += o;
     }
+    double ex = __shfl_up_sync(0xffffffffu, inc, 1);
+    if (lane == 0) ex = 0.0;
     if (lane == 31) sm[wid] = inc;
     __syncthreads();
     if (wid == 0) {
-        double ws = (lane < (int)(blockDim.x >> 5)) ? sm[lane] : 0.0;
-        double winc = ws;
+        double winc = (lane < (int)(blockDim.x >> 5)) ? sm[lane] : 0.0;
 #pragma unroll
         for (int d = 1; d < 32; d <<= 1) {
             double o = __shfl_up_sync(0xffffffffu, winc, d);
             if (lane >= d) winc += o;
         }
-        sm[lane] = winc - ws;                       // exclusive over warps
+        double wex = __shfl_up_sync(0xffffffffu, winc, 1);
+        if (lane == 0) wex = 0.0;
+        sm[lane] = wex;                             // exclusive over warps
         if (lane == 31) sm[32] = winc;
     }
     __syncthreads();
-    double r = sm[wid] + (inc - v);
+    double r = sm[wid] + ex;
     total = sm[32];
     __syncthreads();
     return r;
