@@ -239,7 +239,7 @@ def run_ours(args):
     # (context + stream): the single-CTA phases of one sweep's exact resampler
     # (k_finalize, k_chain) overlap with the streaming kernels of the other.
     from concurrent.futures import ThreadPoolExecutor
-    F = max(1, min(args.inflight, 3))
+    F = max(1, min(args.inflight, 3 if args.max_connections <= 0 else 8))
     pops = []
     for f in range(F):
         nid = nccl_id
@@ -423,7 +423,12 @@ def main():
                     help="independent sweeps kept in flight, one population each (measured: "
                          "1 GPU 59 -> 62 G, 8 GPUs 214 -> 318 (2) -> 365 (3) G particle-steps/s; "
                          "4 and more stalled on peer waits at 8 GPUs, profiles/r02b_*)")
+    ap.add_argument("--max-connections", type=int, default=0,
+                    help="experiment: CUDA_DEVICE_MAX_CONNECTIONS for this process (0 = leave the "
+                         "driver default); to try with --inflight > 3 on several GPUs")
     args = ap.parse_args()
+    if args.max_connections > 0:         # must be set before the CUDA context exists
+        os.environ["CUDA_DEVICE_MAX_CONNECTIONS"] = str(args.max_connections)
     if args.workload == "lgmvn64":
         args.particles = args.particles or (1 << 24)
         args.T = args.T or 100
