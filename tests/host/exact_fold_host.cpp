@@ -180,6 +180,13 @@ int host_exact_resample(const double* w, int64_t n, int64_t n_new, double u, int
     return 0;
 }
 
+// classification of one tile from its approximate prefix (k_finalize)
+int host_classify_tile(double a_in, double a_out, int64_t idx_out) {
+    return classify_tile(a_in, a_out, idx_out);
+}
+int host_ctx_of(double S) { return ctx_of(S); }
+int host_ctx_hard() { return kCtxHard; }
+
 // exact comb values, for direct comparison with repeated addition
 void host_comb_values(double total, double u, int64_t n_new, double* out) {
     Comb comb;
