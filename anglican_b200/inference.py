@@ -125,9 +125,27 @@ def _infer_pgibbs(model, y, number_of_particles=2, seed=0xA11CE, device=0, paths
 
 
 # ---------------------------------------------------------------- :ipmcmc
+def _dist_world():
+    try:
+        import torch.distributed as dist
+    except ImportError:
+        return 1
+    return dist.get_world_size() if dist.is_available() and dist.is_initialized() else 1
+
+
 def _infer_ipmcmc(model, y, number_of_particles=2, number_of_nodes=32,
                   number_of_csmc_nodes=None, all_particles=True, pool=None, seed=0xA11CE,
-                  device=0, paths=False, exchange=None):
+                  device=0, paths=False, exchange=None, group=None, width=4):
+    """one process: the nodes run one after the other on one population.  Under
+    `torch.distributed` with more than one rank (or an explicit `group`): the
+    nodes are partitioned over the ranks' GPUs (anglican_b200/ipmcmc.py) and this
+    rank yields the states of its own nodes."""
+    if group is not None or _dist_world() > 1:
+        from .ipmcmc import infer_ipmcmc
+        yield from infer_ipmcmc(model, y, number_of_particles, number_of_nodes,
+                                number_of_csmc_nodes, all_particles, seed, None, group, paths,
+                                width)
+        return
     assert number_of_particles > 1, ":number-of-particles must be larger than 1"
     assert number_of_nodes > 1, ":number-of-nodes must be larger 1"
     M, n = number_of_nodes, number_of_particles

@@ -162,14 +162,68 @@ def c4(args):
             "node_log_z": log_hist, "timing": "wall clock around the iteration, device synchronised"}
 
 
+def c4dist(args):
+    """config 4 over the GPUs of the box (one process per GPU under torchrun):
+    M nodes split over the ranks, `--width` node sweeps in flight per GPU,
+    log-marginals all-reduced, retained paths moved point to point
+    (anglican_b200/ipmcmc.py).  Prints on rank 0.
+        python -m torch.distributed.run --nproc-per-node 8 --master-addr 127.0.0.1 \
+            tools/bench_configs.py c4dist --nodes 32 [--particles N] [--T T]"""
+    import os
+    import torch
+    import torch.distributed as dist
+    from anglican_b200.ipmcmc import ipmcmc_iterations
+    from anglican_b200.models import StochasticVolatility
+    from bench import sv_observations
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    rank, world = dist.get_rank(), dist.get_world_size()
+    M = args.nodes
+    n, T = args.particles or (1 << 22), args.T or 200
+    y = sv_observations(2000)[:T]
+    gen = ipmcmc_iterations(StochasticVolatility(), y, n, M, M // 2, seed=77, device=local,
+                            width=args.width)
+    times, zs, moved = [], [], 0
+    for it in range(args.warmup + args.steps):
+        torch.cuda.synchronize()
+        dist.barrier()
+        t0 = time.perf_counter()
+        st = next(gen)
+        torch.cuda.synchronize()
+        dist.barrier()
+        dt = time.perf_counter() - t0
+        if it >= args.warmup:
+            times.append(dt)
+            zs.append(st["log_zs"].tolist())
+            moved += st["paths_moved"]
+    gen.close()
+    t = torch.tensor([sum(times)], dtype=torch.float64, device="cuda")
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    tot = float(t)
+    dist.destroy_process_group()
+    if rank != 0:
+        return None
+    return {"config": "configs[3] on %d B200: IPMCMC on the SV model, %d nodes (%d conditional) x %d "
+                      "particles, T=%d, %d node sweeps in flight per GPU" % (world, M, M // 2, n, T,
+                                                                            args.width),
+            "particle_steps_per_s": M * n * T * len(times) / tot,
+            "s_per_mcmc_iteration": tot / len(times), "node_log_z": zs,
+            "paths_moved_rank0": moved,
+            "timing": "wall clock around the iteration, devices synchronised, max over ranks"}
+
+
 if __name__ == "__main__":
     ap = argparse.ArgumentParser()
-    ap.add_argument("config", choices=["c2", "c4", "c5"])
+    ap.add_argument("config", choices=["c2", "c4", "c4dist", "c5"])
     ap.add_argument("--nodes", type=int, default=4)
     ap.add_argument("--concurrent", action="store_true")
+    ap.add_argument("--width", type=int, default=4, help="c4dist: node sweeps in flight per GPU")
     ap.add_argument("--particles", type=int, default=0)
     ap.add_argument("--T", type=int, default=0)
     ap.add_argument("--steps", type=int, default=2)
     ap.add_argument("--warmup", type=int, default=2)
     a = ap.parse_args()
-    print(json.dumps({"c2": c2, "c4": c4, "c5": c5}[a.config](a)), flush=True)
+    r = {"c2": c2, "c4": c4, "c4dist": c4dist, "c5": c5}[a.config](a)
+    if r is not None:
+        print(json.dumps(r), flush=True)
