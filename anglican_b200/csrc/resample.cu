@@ -442,7 +442,8 @@ __global__ void __launch_bounds__(FB) k_finalize(WSView v, int64_t n, int64_t n_
 
     const double u = (u_in != u_in) ? uniform_at(seed, 0, step, STREAM_RESAMPLE, 0) : u_in;
     // x_last < x_0 + total <= total*(u+1): generous upper bound for the skip test
-    const double eps_tot = ((double)(2 * n_global) + 8192.0) * 4.44089209850062616e-16 + rel_eps;
+    // (the comb is n_new repeated additions: its rounding error grows with n_new, not n)
+    const double eps_tot = ((double)(2 * n_global) + (double)n_new + 8192.0) * 4.44089209850062616e-16 + rel_eps;
     const double xlast_ub = atot * (u + 1.0) * (1.0 + 4.0 * eps_tot);
 
     // ---- classification of every tile for both laps (coalesced, tiles striped
