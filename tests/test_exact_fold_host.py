@@ -68,3 +68,21 @@ def test_comb_closed_form_equals_repeated_addition(host):
             ref[j] = x
             x = x + step
         assert np.array_equal(out, ref), (tot, u, n)
+
+
+@pytest.mark.parametrize("n,small,pos,giant", [
+    (600000, 1e-30, 360000, 1.0), (600000, 1e-30, 570000, 1.0), (1 << 20, 1e-30, 777777, 1.5),
+    (1 << 20, 1e-20, 777777, 1.0), (1 << 20, 1e-9, 777777, 1e6), (3 * 4096, 1e-30, 3 * 4096 - 1, 1.0),
+    (100000, 1e-300, 5, 1e300), (100000, 5e-324, 99999, 1.0),
+])
+def test_dominant_weight_shapes(host, n, small, pos, giant):
+    """one particle outweighing the rest by more than 2^53 (every other increment
+    vanishes against the running sum); cf. tests/test_zz_dominant_weight_gpu.py"""
+    w = np.full(n, small)
+    w[pos] = giant
+    for u in (0.37, 0.999999, 0.0):
+        ref = orc.resample_weights(w, n, u)
+        rc, em, lap, tot = _run(host, w, n, u, 4096)
+        assert rc == 0, (u, rc)
+        assert tot == ref["total"]
+        assert np.array_equal(em, ref["emission"]) and np.array_equal(lap, ref["lap"])
