@@ -9,6 +9,8 @@ for n in (450000, 600000, 800000, 1<<20):
         cases.append((n, 1e-30, int(n*frac), 1.0, False))
 cases.append((1<<20, 1e-30, 777777, 1.0, True))
 cases.append((1<<20, 1e-5, 777777, 1e6, False))
+cases.append((1<<20, 1e-30, 777777, 1.5, False))
+cases.append((1<<22, 1e-30, (1<<22)-5, 3.0, False))
 for n, small, pos, g, rnd in cases:
     w = np.full(n, small) * (rng.random(n) + 0.5 if rnd else 1.0); w[pos] = g
     with Population(n) as pop:
