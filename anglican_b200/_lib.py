@@ -40,7 +40,8 @@ class ApopSSM(C.Structure):
 class ApopSweepOpts(C.Structure):
     _fields_ = [("csmc", C.c_int32), ("n_cond_steps", C.c_int32), ("reset_weights", C.c_int32),
                 ("keep_history", C.c_int32), ("use_graph", C.c_int32), ("want_final", C.c_int32),
-                ("want_filt", C.c_int32), ("no_resample", C.c_int32)]
+                ("want_filt", C.c_int32), ("no_resample", C.c_int32),
+                ("ancestor_sampling", C.c_int32)]
 
 
 class ApopSweepResult(C.Structure):
@@ -120,6 +121,7 @@ _SIGS = [
     ("apop_trace_lineage", C.c_int, [_vp, C.c_int64, c_double_p]),
     ("apop_sweep_download_history", C.c_int, [_vp, c_int32_p, c_double_p]),
     ("apop_sweep_final_device", C.c_int, [_vp, C.POINTER(_vp)]),
+    ("apop_sizeof_sweep_opts", C.c_int, []),
     ("apop_empirical_moments", C.c_int, [_vp, C.c_int32, C.c_int32, C.c_int32, c_double_p,
                                          c_double_p, c_double_p, c_double_p]),
     ("apop_empirical_covariance", C.c_int, [_vp, C.c_int32, C.c_int32, C.c_int32, c_double_p,
@@ -162,6 +164,9 @@ def load(build_if_needed: bool = True):
         fn = getattr(lib, name)          # AttributeError if the ABI lost a symbol
         fn.restype = res
         fn.argtypes = args
+    if lib.apop_sizeof_sweep_opts() != C.sizeof(ApopSweepOpts):
+        raise ImportError(f"{LIB_PATH}: apop_sweep_opts has {lib.apop_sizeof_sweep_opts()} bytes, "
+                          f"the binding expects {C.sizeof(ApopSweepOpts)}: rebuild the library")
     _lib = lib
     return lib
 

@@ -226,6 +226,7 @@ struct ResampleArgs {
     StepOut step;            // optional per-step outputs (sd == nullptr: none)
     bool sharded;            // world > 1: exchange through the fabric, offspring stored to peers
     PeerI32 anc_peer;        // sharded: anc_peer.p[q] = rank q's ancestor array
+    bool keep_err;           // second resample inside a sweep step: error bits stay sticky
 };
 int resample_enqueue(apop_ctx* c, const ResampleArgs& a);
 int resample_fetch_info(apop_ctx* c, ResampleInfo* out);   // syncs

@@ -1837,11 +1837,11 @@ int resample_enqueue(apop_ctx* c, const ResampleArgs& a) {
     const int nt = (int)v.nt;
     const int wm = a.w ? 1 : 0;
     if (!a.have_partials) {
-        k_info_reset<<<1, 1, 0, c->stream>>>(v.info);
+        if (!a.keep_err) k_info_reset<<<1, 1, 0, c->stream>>>(v.info);
         kt_begin(c, KT_TILE_LSE);
         k_tile_lse<<<nt, TB, 0, c->stream>>>(a.lw, a.w, a.n, v);
         kt_end(c, KT_TILE_LSE);
-        c->launches += 2;
+        c->launches += a.keep_err ? 1 : 2;
     }
     Fabric F = fabric_view(c);
     if (!a.sharded) { F.world = 1; F.rank = 0; }

@@ -60,6 +60,8 @@ struct SweepState {
     apop::ModelDev* model = nullptr;
     double* traj = nullptr;
     double* lse = nullptr;         // {max, sum exp} of the final log-weights (no_resample sweeps)
+    int32_t* as_anc = nullptr;     // PGAS: ancestor drawn for the retained particle (1 index)
+    double trans_const = 0.0;      // log(q) + 0.5 log(2 pi): transition log-density constant
     double* mvn_mats = nullptr;    // LGMVN: A | Lq | iL, each [dim*dim]
     double mvn_Z = 0.0, mvn_s0 = 1.0;
     size_t cap_n = 0, cap_T = 0, cap_hist = 0;
@@ -90,7 +92,7 @@ void sweep_free(apop_ctx* c) {
     }
     void* ptrs[] = {s->xa, s->xb, s->lw, s->anc, s->x_hist, s->anc_hist, s->y, s->retained,
                     s->log_mean_w, s->ess, s->filt, s->tsx, s->x_final, s->sd, s->model, s->traj,
-                    s->mvn_mats, s->zbuf[0], s->zbuf[1], s->lse};
+                    s->mvn_mats, s->zbuf[0], s->zbuf[1], s->lse, s->as_anc};
     for (void* p : ptrs)
         if (p) cudaFree(p);
     delete s;
@@ -407,6 +409,38 @@ __global__ void k_sweep_reset(SweepDev* sd, ResampleInfo* I) {
     I->err = 0;
 }
 
+// ---- PGAS ancestor sampling (resample-retained, pgas.cljc:107-131) ----------
+// v_i = logw_i + log f(x*_{t+1} | x_t^i): the rescored transition `sample` of the
+// retained path against particle i's state (NormalDistribution.logDensity /
+// `discrete` observe*, runtime.cljc:403-409, 288-290).  next == nullptr (last
+// observe: nothing left to rescore): v = logw.
+template <int KIND>
+__global__ void __launch_bounds__(256) k_as_logw(const ModelDev* __restrict__ Mp,
+                                                 const double* __restrict__ x,
+                                                 const double* __restrict__ lw,
+                                                 const double* __restrict__ next, double tconst,
+                                                 double* __restrict__ v, int64_t n) {
+    const ModelDev& M = *Mp;
+    const int64_t k = (int64_t)blockIdx.x * 256 + threadIdx.x;
+    if (k >= n) return;
+    double r = lw[k];
+    if (next) {
+        const double xn = next[0];
+        if (KIND == APOP_SSM_HMM) {
+            const int s = (int)x[k], c = (int)xn;
+            const double* row = M.hmm_trans + s * M.dim;
+            double tot = 0.0;
+            for (int i = 0; i < M.dim; ++i) tot = tot + row[i];
+            r += (c >= 0 && c < M.dim) ? log(row[c] / tot) : -INFINITY;
+        } else {
+            const double x1 = (xn - (M.a * x[k] + M.b)) / M.q;
+            r += -0.5 * x1 * x1 - tconst;
+        }
+    }
+    v[k] = r;
+}
+__global__ void k_as_commit(int32_t* anc_step, const int32_t* drawn) { anc_step[0] = drawn[0]; }
+
 __global__ void k_trace(const int32_t* __restrict__ anc_hist, const double* __restrict__ x_hist,
                         int64_t n, int T, int d, int64_t slot, double* traj) {
     int64_t k = slot;
@@ -487,6 +521,7 @@ static int sweep_prepare(apop_ctx* c, int T, int dim, bool history) {
         APOP_TRY(dev_alloc(c, (void**)&s->sd, sizeof(SweepDev)));
         APOP_TRY(dev_alloc(c, (void**)&s->model, sizeof(ModelDev)));
         APOP_TRY(dev_alloc(c, (void**)&s->lse, 2 * sizeof(double)));
+        APOP_TRY(dev_alloc(c, (void**)&s->as_anc, 4 * sizeof(int32_t)));
     }
     if (s->cap_T < (size_t)T || s->dim != dim) {
         void* ptrs[] = {s->y, s->retained, s->log_mean_w, s->ess, s->filt, s->traj};
@@ -564,6 +599,7 @@ static int upload_model(apop_ctx* c, const apop_ssm* m) {
     h.c = m->c; h.d = m->d; h.r = m->r; h.beta = m->beta;
     if (m->kind == APOP_SSM_LGSSM1D) h.obs_const = log(m->r) + kHalfLog2Pi_;
     if (m->kind == APOP_SSM_SV) h.obs_const = log(m->beta) + kHalfLog2Pi_;
+    c->sweep->trans_const = (m->q > 0.0) ? log(m->q) + kHalfLog2Pi_ : 0.0;
     if (m->kind == APOP_SSM_HMM) {
         const int K = m->dim;
         if (K < 1 || K > 16 || !m->hmm_init || !m->hmm_trans || !m->hmm_mu || !m->hmm_sd)
@@ -761,6 +797,23 @@ static int sweep_step(apop_ctx* c, int t, const apop_sweep_opts* o, bool csmc) {
     a.sharded = shard;
     if (shard) a.anc_peer = peer_i32(c, c->fab.off_anc);
     APOP_TRY(resample_enqueue(c, a));
+    if (o->ancestor_sampling && cond && KIND != APOP_SSM_LGMVN) {
+        // PGAS: redraw the retained particle's ancestor among the N pre-resample
+        // particles.  x_final is free until the sweep ends: it holds v for the draw.
+        constexpr int K2 = (KIND == APOP_SSM_LGMVN) ? APOP_SSM_LGSSM1D : KIND;
+        double* v = s->x_final;
+        k_as_logw<K2><<<(int)((n + 255) / 256), 256, 0, c->stream>>>(
+            s->model, x_new, s->lw, (t < s->T) ? s->retained + (t + 1) : nullptr, s->trans_const,
+            v, n);
+        ResampleArgs b{};
+        b.lw = v; b.w = nullptr; b.n = n; b.n_new = 1;
+        b.u = uniform_at(c->seed, 0, (uint32_t)t, STREAM_AUX, 0);
+        b.order = APOP_ORDER_EMISSION; b.anc_out = s->as_anc; b.out_offset = 0;
+        b.have_partials = false; b.keep_err = true; b.rel_eps = 0.0; b.sharded = false;
+        APOP_TRY(resample_enqueue(c, b));
+        k_as_commit<<<1, 1, 0, c->stream>>>(anc_new, s->as_anc);
+        c->launches += 2;
+    }
     // sharded: offspring indices were stored into peers' arrays and the next
     // propagate reads parents from peers' x_t: all ranks meet here
     if (shard) {
@@ -921,6 +974,11 @@ static int sweep_group(apop_ctx* const* g, int ng, const apop_ssm* model, const 
             return set_err(c, APOP_ERR_UNSUPPORTED,
                            "no_resample (importance) sweeps: unconditional, unsharded, scalar-state, "
                            "no lineages");
+        if (opts->ancestor_sampling && (!opts->csmc || c->world > 1 || opts->no_resample ||
+                                        model->kind == APOP_SSM_LGMVN))
+            return set_err(c, APOP_ERR_UNSUPPORTED,
+                           "ancestor sampling (pgas): conditional sweeps of scalar-state models "
+                           "on one GPU");
         if (c->world > 1 && (opts->csmc || opts->keep_history))
             return set_err(c, APOP_ERR_UNSUPPORTED,
                            "sharded sweep: conditional sweeps / lineages run one population "
@@ -1005,6 +1063,8 @@ int apop_sweep_download_history(apop_ctx* c, int32_t* anc, double* x) {
     APOP_CUDA(c, cudaStreamSynchronize(c->stream));
     return APOP_OK;
 }
+
+int apop_sizeof_sweep_opts(void) { return (int)sizeof(apop_sweep_opts); }
 
 int apop_sweep_final_device(apop_ctx* c, void** out) {
     if (!c || !out) return APOP_ERR_INVALID;

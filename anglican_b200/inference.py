@@ -1,6 +1,6 @@
 """Host-side mirror of `anglican.inference/infer` for the particle algorithms.
 
-    infer(:smc | :pimh | :pgibbs | :ipmcmc | :importance | :pfilter, model, observations, **options)
+    infer(:smc | :pimh | :pgibbs | :pgas | :ipmcmc | :importance | :pfilter, model, observations, **options)
 
 keeps the reference's keywords, defaults and assertions
 (smc.cljc:53-57, pimh.cljc:41-45, pgibbs.cljc:112-116, ipmcmc.cljc:148-171,
@@ -124,6 +124,32 @@ def _infer_pgibbs(model, y, number_of_particles=2, seed=0xA11CE, device=0, paths
         pop.close()
 
 
+# ---------------------------------------------------------------- :pgas
+def _infer_pgas(model, y, number_of_particles=2, seed=0xA11CE, device=0, paths=False):
+    """Particle Gibbs with ancestor sampling (pgas.cljc:107-168) for state-space
+    programs.  Every observe is a conditional resample (N-1 of N, pgas.cljc:146-151)
+    and the retained particle's ancestor is redrawn among all N particles rescored
+    against the retained path (resample-retained, 107-131).  The first sweep has an
+    empty retained database (pgas.cljc:168): an unconditional sweep here."""
+    assert number_of_particles >= 2, ":number-of-particles must be at least 2"   # pgas.cljc:158-159
+    n = number_of_particles
+    pop = Population(n, seed=seed, device=device)
+    seeds = _SeedSeq(seed)
+    T = len(y) // model.state_dim
+    retained = None
+    try:
+        while True:
+            pop.set_seed(seeds.next_key())
+            cond = retained is not None
+            out = pop.sweep(model, y, retained=retained, csmc=cond, n_cond_steps=T,
+                            reset_weights=True, keep_history=True, ancestor_sampling=cond)
+            b = int(seeds.rng.random() * n)                         # rand-nth, pgas.cljc:166-167
+            retained = out.trace(b)
+            yield from _states(out, 0.0 if math.isfinite(out.log_z) else -math.inf, paths)
+    finally:
+        pop.close()
+
+
 # ---------------------------------------------------------------- :ipmcmc
 def _dist_world():
     try:
@@ -237,7 +263,7 @@ def _infer_pfilter(model, y, number_of_particles=1, seed=0xA11CE, device=0):
         pop.close()
 
 
-_ALGORITHMS = {"smc": _infer_smc, "pimh": _infer_pimh, "pgibbs": _infer_pgibbs,
+_ALGORITHMS = {"smc": _infer_smc, "pimh": _infer_pimh, "pgibbs": _infer_pgibbs, "pgas": _infer_pgas,
                "ipmcmc": _infer_ipmcmc, "importance": _infer_importance,
                "pfilter": _infer_pfilter}
 

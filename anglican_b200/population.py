@@ -335,13 +335,15 @@ class Population:
 
     def sweep(self, model, y, retained=None, csmc=False, n_cond_steps=0, reset_weights=False,
               keep_history=False, want_final=True, want_stats=True, want_filt=None,
-              pinned_final=False, no_resample=False):
+              pinned_final=False, no_resample=False, ancestor_sampling=False):
         """One `sweep` (smc.cljc:35-51; conditional: pgibbs.cljc:76-110,
         ipmcmc.cljc:34-83).  Returns a SweepOutput.  pinned_final: x_final is a
         view of a page-locked buffer owned by the population, overwritten by its
         next sweep (copy it to keep it).  no_resample: `infer :importance`
         (importance.cljc:16-22) — weights accumulate per particle, the output
-        carries lw_final and log_z = log mean exp(lw_final)."""
+        carries lw_final and log_z = log mean exp(lw_final).  ancestor_sampling:
+        `infer :pgas` (pgas.cljc:107-131) — in a conditional sweep the retained
+        particle's ancestor is redrawn at every conditional observe."""
         y = np.ascontiguousarray(y, dtype=np.float64)
         d = model.state_dim
         T = y.size // d
@@ -351,7 +353,7 @@ class Population:
             want_filt = want_stats and d == 1
         opts = L.ApopSweepOpts(int(csmc), int(n_cond_steps), int(reset_weights),
                                int(keep_history), 0, int(want_final), int(bool(want_filt)),
-                               int(bool(no_resample)))
+                               int(bool(no_resample)), int(bool(ancestor_sampling)))
         res = L.ApopSweepResult()
         out = SweepOutput(self, T, d)
         if want_stats:

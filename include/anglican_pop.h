@@ -222,7 +222,16 @@ typedef struct {
                                 * adds to the particle's own log-weight (inference.cljc:42-45),
                                 * nothing is resampled; log_z = log mean exp of the final
                                 * log-weights, which lw_final returns */
+    int32_t ancestor_sampling; /* `infer :pgas` (pgas.cljc:107-168), conditional sweeps only: at
+                                * every conditional observe the retained particle's ancestor is
+                                * redrawn, one `(sample* (discrete weights))` with weights
+                                * exp(v - max v), v_i = logw_i + log f(retained_{t+1} | x_t^i)
+                                * (the rescored transition `sample`; the retained path's later
+                                * terms are common to all i and left out).  Scalar-state models,
+                                * one GPU.  Only the recorded ancestry changes (lineages). */
 } apop_sweep_opts;
+/* sizeof(apop_sweep_opts) of the loaded library, for bindings that mirror the struct */
+int apop_sizeof_sweep_opts(void);
 
 typedef struct {
     double log_z;              /* sum of per-step log-mean-weights */

@@ -621,6 +621,53 @@ static void ssm_transition(const orc_ssm* m, uint64_t seed, int64_t k, uint32_t 
     }
 }
 
+/* log f(x_next | x): the `observe*` of the transition `sample` when PGAS rescores
+ * the retained value against another particle's state (pgas.cljc:66-82).
+ * Scalar-state models. */
+static double ssm_transition_logpdf(const orc_ssm* m, const double* x, const double* x_next) {
+    switch (m->kind) {
+    case ORC_SSM_LGSSM1D:
+    case ORC_SSM_SV:
+        return orc_normal_logpdf(x_next[0], m->a * x[0] + m->b, m->q);
+    case ORC_SSM_HMM: {
+        const int s = (int)x[0], c = (int)x_next[0];
+        const double* row = m->hmm_trans + s * m->dim;
+        double tot = 0.0;
+        for (int i = 0; i < m->dim; ++i) tot = tot + row[i];
+        return (c >= 0 && c < m->dim) ? log(row[c] / tot) : -INFINITY;   /* runtime.cljc:288-290 */
+    }
+    default: return NAN;
+    }
+}
+
+/* Ancestor of the retained particle at a conditional observe (resample-retained,
+ * pgas.cljc:107-131): every particle -- the retained one included -- is rescored
+ * against the retained random database, i.e. against the retained path's next
+ * state; the terms of the later states and observes are the same number for
+ * every particle and are left out (the reference adds them before subtracting the
+ * max).  Then one `(sample* (discrete weights))`: x = u * total, first k with
+ * x < w_0 + ... + w_k (runtime.cljc:281-287). */
+static int64_t pgas_ancestor(const orc_ssm* m, const double* x, const double* lw, int64_t n,
+                             const double* next_retained, double u, double* v) {
+    double mx = -INFINITY;
+    for (int64_t k = 0; k < n; ++k) {
+        v[k] = lw[k] + (next_retained ? ssm_transition_logpdf(m, x + k, next_retained) : 0.0);
+        if (v[k] > mx) mx = v[k];
+    }
+    double total = 0.0;
+    for (int64_t k = 0; k < n; ++k) {
+        v[k] = (v[k] == mx) ? 1.0 : (!(v[k] > -INFINITY) ? 0.0 : exp(v[k] - mx));
+        total = total + v[k];
+    }
+    const double xr = u * total;
+    double acc = 0.0;
+    for (int64_t k = 0; k < n; ++k) {
+        acc = acc + v[k];
+        if (xr < acc) return k;
+    }
+    return n - 1;
+}
+
 int orc_smc_sweep(const orc_ssm* model, const double* y, const double* retained,
                   const orc_sweep_opts* o, orc_sweep_out* out) {
     const int64_t n = o->n;
@@ -702,6 +749,12 @@ int orc_smc_sweep(const orc_ssm* model, const double* y, const double* retained,
         if (cond) {
             anc[0] = 0;                               /* retained back at position 0 */
             orc_emission_to_sorted(emission, lap, n_new, anc + 1, NULL);
+            if (o->ancestor_sampling) {
+                if (model->kind == ORC_SSM_LGMVN) { rc = -1; goto done; }
+                const double ua = orc_uniform_at(o->seed, 0, (uint32_t)t, ORC_STREAM_AUX, 0);
+                anc[0] = (int32_t)pgas_ancestor(model, xb, lw, n,
+                                                (t < T) ? retained + (size_t)(t + 1) : NULL, ua, w);
+            }
         } else {
             orc_emission_to_sorted(emission, lap, n_new, anc, NULL);
         }

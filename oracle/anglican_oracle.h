@@ -150,6 +150,9 @@ typedef struct {
     int32_t reset_weights;  /* pgibbs.cljc:88 / ipmcmc.cljc:69-72: lw := 0 after resample */
     int32_t keep_history;   /* store ancestors + states for lineage tracing */
     int32_t threads;        /* >1: OpenMP over particles in propagate/weight */
+    int32_t ancestor_sampling; /* pgas.cljc:107-131: at each conditional observe the retained
+                             * particle's ancestor is redrawn from discrete(exp(v - max v)),
+                             * v_i = lw_i + log f(retained_{t+1} | x_t^i) */
 } orc_sweep_opts;
 
 typedef struct {

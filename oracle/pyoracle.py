@@ -57,7 +57,7 @@ class OrcSweepOpts(C.Structure):
     _fields_ = [("n", C.c_int64), ("T", C.c_int32), ("seed", C.c_uint64),
                 ("csmc", C.c_int32), ("n_cond_steps", C.c_int32),
                 ("reset_weights", C.c_int32), ("keep_history", C.c_int32),
-                ("threads", C.c_int32)]
+                ("threads", C.c_int32), ("ancestor_sampling", C.c_int32)]
 
 
 class OrcSweepOut(C.Structure):
@@ -348,13 +348,14 @@ class Model:
 
 
 def smc_sweep(model, y, n, seed, retained=None, csmc=False, n_cond_steps=0,
-              reset_weights=False, keep_history=False, threads=1, want_final=True):
+              reset_weights=False, keep_history=False, threads=1, want_final=True,
+              ancestor_sampling=False):
     y = _f64(y)
     d = model.state_dim
     T = y.size // d
     o = OrcSweepOpts(n=n, T=T, seed=seed, csmc=int(csmc), n_cond_steps=n_cond_steps,
                      reset_weights=int(reset_weights), keep_history=int(keep_history),
-                     threads=threads)
+                     threads=threads, ancestor_sampling=int(ancestor_sampling))
     out = OrcSweepOut()
     res = dict(log_mean_w=np.empty(T), ess=np.empty(T), filt_mean=np.empty((T, d)))
     out.log_mean_w, out.ess = _dp(res["log_mean_w"]), _dp(res["ess"])

@@ -1,0 +1,92 @@
+"""`infer :pgas` on the device: conditional sweeps with the
+retained particle's ancestor redrawn at every observe (pgas.cljc:107-131,
+`ancestor_sampling` of apop_smc_sweep) against the oracle.  Written after the
+round's GPU budget was spent: not yet run on a GPU; test_zz_* so that it runs
+after the rest of the GPU suite."""
+import math
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+
+def _models():
+    from anglican_b200.models import GaussianHMM, LinearGaussian1D, StochasticVolatility
+    from oracle import pyoracle as orc
+    rng = np.random.default_rng(3)
+    lg = LinearGaussian1D()
+    sv = StochasticVolatility()
+    init, trans = [1.0, 1.0, 1.0], [[0.1, 0.5, 0.4], [0.2, 0.2, 0.6], [0.15, 0.15, 0.7]]
+    mu, sd = [-1.0, 1.0, 0.0], [1.0, 1.0, 1.0]
+    return [
+        ("lgssm", lg, orc.Model(orc.SSM_LGSSM1D, **lg.params), rng.normal(0, 1.5, 12)),
+        ("sv", sv, orc.Model(orc.SSM_SV, m0=0.0, s0=sv.c.s0, a=sv.c.a, b=0.0, q=sv.c.q,
+                             beta=sv.c.beta), rng.normal(0, 0.7, 12)),
+        ("hmm", GaussianHMM(init, trans, mu, sd),
+         orc.Model(orc.SSM_HMM, dim=3, hmm_init=init, hmm_trans=trans, hmm_mu=mu, hmm_sd=sd),
+         np.array([0.9, 0.8, 0.7, 0.0, -0.025, -5.0, -2.0, -0.1, 0.0, 0.13, 0.45, 6.0])),
+    ]
+
+
+@pytest.mark.parametrize("n", [64, 5000, 20000])
+def test_ancestor_sampling_sweep_equals_oracle(n):
+    from anglican_b200 import Population
+    from oracle import pyoracle as orc
+    for name, m, om, y in _models():
+        T = y.size
+        with Population(n, seed=1) as pop:
+            retained = None
+            for it in range(3):
+                cond = retained is not None
+                pop.set_seed(500 + it)
+                out = pop.sweep(m, y, retained=retained, csmc=cond, n_cond_steps=T,
+                                reset_weights=True, keep_history=True, ancestor_sampling=cond)
+                ref = orc.smc_sweep(om, y, n, seed=500 + it, retained=retained, csmc=cond,
+                                    n_cond_steps=T, reset_weights=True, keep_history=True,
+                                    ancestor_sampling=cond)
+                anc, x = out.history()
+                assert np.array_equal(anc, ref["anc_hist"]), (name, n, it)
+                assert np.array_equal(x[:, :, 0], ref["x_hist"][:, :, 0])
+                assert np.array_equal(out.x_final, ref["x_final"][:, 0])
+                assert abs(out.log_z - ref["log_z"]) <= 1e-9 * abs(ref["log_z"])
+                if cond:
+                    assert np.any(anc[:, 0] != 0), (name, n)       # the draw did something
+                slot = (7 * it + 3) % n
+                tr = out.trace(slot)
+                assert np.array_equal(tr, orc.trace_lineage(ref, slot)[:, 0])
+                retained = tr
+
+
+def test_pgas_needs_a_conditional_sweep():
+    from anglican_b200 import Population, _lib as L
+    from anglican_b200.models import LinearGaussian1D
+    with Population(64, seed=1) as pop:
+        with pytest.raises(L.ApopError):
+            pop.sweep(LinearGaussian1D(), np.zeros(4), ancestor_sampling=True)
+
+
+def test_infer_pgas_matches_the_smoother():
+    """few particles, long series: only ancestor sampling keeps refreshing x_0"""
+    from anglican_b200.inference import infer
+    from anglican_b200.models import LinearGaussian1D
+    from tests.test_pgas_oracle_cpu import PAR, lgssm_series, rts_smoother
+    y = lgssm_series(40)
+    ms, Ps = rts_smoother(y, **PAR)
+    n, iters, burn = 6, 3000, 200
+    acc, acc2, k = np.zeros(41), np.zeros(41), 0
+    it = infer("pgas", LinearGaussian1D(**PAR), y, number_of_particles=n, paths=True, seed=99)
+    for i, s in enumerate(it):
+        if i >= iters * n:
+            break
+        if i >= burn * n:
+            r = np.asarray(s.result)
+            acc += r
+            acc2 += r * r
+            k += 1
+        assert s.log_weight == 0.0 or not math.isfinite(s.log_weight)
+    it.close()
+    mean = acc / k
+    var = acc2 / k - mean * mean
+    assert np.abs(mean - ms).max() < 0.15
+    assert np.all(np.abs(var / Ps - 1.0) < 0.25)
