@@ -25,6 +25,7 @@ def _first(gen):
     ("smc", dict(number_of_particles=0), ":number-of-particles must be at least 1"),      # smc.cljc:56-57
     ("pimh", dict(number_of_particles=0), ":number-of-particles must be at least 1"),     # pimh.cljc:44-45
     ("pgibbs", dict(number_of_particles=1), ":number-of-particles must be at least 2"),   # pgibbs.cljc:115-116
+    ("pgas", dict(number_of_particles=1), ":number-of-particles must be at least 2"),     # pgas.cljc:158-159
     ("ipmcmc", dict(number_of_particles=1), ":number-of-particles must be larger than 1"),  # ipmcmc.cljc:157-160
     ("ipmcmc", dict(number_of_nodes=1), ":number-of-nodes must be larger 1"),
     ("ipmcmc", dict(number_of_nodes=4, number_of_csmc_nodes=4),
@@ -43,7 +44,8 @@ def test_unknown_algorithm():
         infer("lmh", LinearGaussian1D(), Y)            # core.cljc:15-26: no such namespace here
 
 
-@pytest.mark.parametrize("alg", ["smc", ":smc", "pimh", "pgibbs", "ipmcmc", "importance", "pfilter"])
+@pytest.mark.parametrize("alg", ["smc", ":smc", "pimh", "pgibbs", "pgas", "ipmcmc", "importance",
+                                 "pfilter"])
 def test_valid_call_without_device_fails_loudly(alg):
     if L.load().apop_device_count() > 0:
         pytest.skip("a CUDA device is present")
