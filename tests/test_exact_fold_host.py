@@ -86,3 +86,19 @@ def test_dominant_weight_shapes(host, n, small, pos, giant):
         assert rc == 0, (u, rc)
         assert tot == ref["total"]
         assert np.array_equal(em, ref["emission"]) and np.array_equal(lap, ref["lap"])
+
+
+def test_single_pointer_is_a_discrete_draw(host):
+    """n_new = 1: the wheel is `(sample* (discrete weights))` (runtime.cljc:281-287),
+    the draw `infer :pgas` uses for the retained particle's ancestor"""
+    rng = np.random.default_rng(12)
+    for n in (5, 4096, 30011):
+        for name, w in families(n, rng).items():
+            for u in (0.0, 0.25, 0.6180339887, 1 - 2 ** -53):
+                ref = orc.resample_weights(w, 1, u)
+                rc, em, lap, tot = _run(host, w, 1, u, 4096)
+                assert rc == 0 and tot == ref["total"], (name, u, rc)
+                assert em[0] == ref["emission"][0] and lap[0] == 0
+                # first k with u*total < w_0 + ... + w_k (left fold, strict)
+                edges = np.cumsum(w)
+                assert em[0] == int(np.searchsorted(edges, u * edges[-1], side="right"))

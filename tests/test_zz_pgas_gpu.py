@@ -90,3 +90,24 @@ def test_infer_pgas_matches_the_smoother():
     var = acc2 / k - mean * mean
     assert np.abs(mean - ms).max() < 0.15
     assert np.all(np.abs(var / Ps - 1.0) < 0.25)
+
+
+@pytest.mark.parametrize("n", [5, 4096, 30011, 1 << 20])
+def test_one_pointer_resample_is_a_discrete_draw(n):
+    """the draw behind the ancestor: apop_resample with n_new = 1 on any weights"""
+    from anglican_b200 import Population, _lib as L
+    from oracle import pyoracle as orc
+    from tests.weights_cases import families
+    rng = np.random.default_rng(12 + n)
+    with Population(n, seed=1) as pop:
+        wcol = pop.column(L.F64)
+        anc = pop.column(L.I32)
+        for name, w in families(n, rng).items():
+            w = np.ascontiguousarray(w, dtype=np.float64)
+            wcol.upload(w)
+            for u in (0.0, 0.25, 0.6180339887, 1 - 2 ** -53):
+                ref = orc.resample_weights(w, 1, u)
+                _, total, _ = pop.resample_weights(wcol, u=u, n_new=1, order=L.ORDER_EMISSION,
+                                                   anc=anc)
+                assert total == ref["total"], (name, u)
+                assert anc.download()[0] == ref["emission"][0], (name, u)
