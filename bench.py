@@ -173,7 +173,7 @@ def run_reference(args):
     from oracle import pyoracle as orc
     T = args.T
     cores = os.cpu_count() or 1
-    m, y, n_s, T_s, label = oracle_sample(args, 200)
+    m, y, n_s, T_s, label = oracle_sample(args, 1000)      # ~2 s per step on 16 threads
     times = []
     for i in range(args.warmup + args.steps):
         t0 = time.perf_counter()
@@ -399,7 +399,7 @@ def cpu_baseline(args):
     """oracle port of smc.cljc, 1 core (the reference's `infer :smc` is single
     threaded), on a bounded sample of the same workload."""
     from oracle import pyoracle as orc
-    m, y, n_s, T_s, label = oracle_sample(args, 300)
+    m, y, n_s, T_s, label = oracle_sample(args, 1500)      # ~13 s of one core
     t0 = time.perf_counter()
     orc.smc_sweep(m, y, n_s, seed=1, threads=1, want_final=True)
     dt = time.perf_counter() - t0
