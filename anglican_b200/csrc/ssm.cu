@@ -173,7 +173,8 @@ __device__ __forceinline__ void propagate_tile(const PeerF64& xpeer,
                                                double wbase, int64_t n, int64_t g0, uint64_t seed,
                                                uint32_t t, double* __restrict__ tmax,
                                                double* __restrict__ tsum, int* errflag,
-                                               const double* __restrict__ zpre, int accum) {
+                                               const double* __restrict__ zpre, int accum,
+                                               bool aligned) {
     __shared__ double red_mx[NWARP];
     __shared__ float red_ref[NWARP], red_s[NWARP];
     const int64_t base = (int64_t)blockIdx.x * TILE;
@@ -192,7 +193,7 @@ __device__ __forceinline__ void propagate_tile(const PeerF64& xpeer,
 #pragma unroll
     for (int h = 0; h < IPT; h += HW) {
         const int64_t ih = i0 + h;
-        const bool inb = FULL || ih + HW <= n;
+        const bool inb = FULL || (aligned && ih + HW <= n);     // 128-bit accesses allowed
 #define VALID(j) (FULL || ih + (j) < n)
         double x[HW], l[HW];
         // ---- parents (gather folded into the read)
@@ -380,12 +381,16 @@ __global__ void __launch_bounds__(TB, APOP_PROP_CTAS) k_propagate(const ModelDev
     const double y = yt[0];
     const double wbase = sd->base;
     const double* zp = ((int)blockIdx.x < z_tiles) ? zpre : nullptr;     // CTA-uniform
-    if ((int64_t)(blockIdx.x + 1) * TILE <= n)
+    // rows of a lineage history start at multiples of n elements: 16-byte aligned
+    // only when n is a multiple of 4 (ancestors) / 2 (states)
+    const bool aligned = (((uintptr_t)anc | (uintptr_t)xn | (uintptr_t)lw) & 15) == 0;
+    if ((int64_t)(blockIdx.x + 1) * TILE <= n && aligned)
         propagate_tile<KIND, true, SHARD>(xpeer, M, xp, anc, first_step, xn, lw, y, retained_t,
-                                          wbase, n, g0, seed, t, tmax, tsum, errflag, zp, accum);
+                                          wbase, n, g0, seed, t, tmax, tsum, errflag, zp, accum, true);
     else
         propagate_tile<KIND, false, SHARD>(xpeer, M, xp, anc, first_step, xn, lw, y, retained_t,
-                                           wbase, n, g0, seed, t, tmax, tsum, errflag, nullptr, accum);
+                                           wbase, n, g0, seed, t, tmax, tsum, errflag, nullptr, accum,
+                                           aligned);
 }
 
 // transition noise of step t for the full tiles [0, gridDim.x): exactly the

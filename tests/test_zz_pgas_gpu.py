@@ -1,14 +1,36 @@
 """`infer :pgas` on the device: conditional sweeps with the
 retained particle's ancestor redrawn at every observe (pgas.cljc:107-131,
-`ancestor_sampling` of apop_smc_sweep) against the oracle.  Written after the
-round's GPU budget was spent: not yet run on a GPU; test_zz_* so that it runs
-after the rest of the GPU suite."""
+`ancestor_sampling` of apop_smc_sweep) against the oracle.
+
+Ancestry (integers) and the HMM's integer states must be bit-exact.  Continuous
+states (lgssm, sv) are compared at the suite's 1e-9 relative: the device draws its
+normals with the polynomial Box-Muller of fastmath.cuh (<= 2 ulp from libm, which
+the oracle uses), as every other Gaussian comparison in tests/ does.  The largest
+distance seen is printed in ulps so that a real kernel bug (>> 2 ulp) stands out."""
 import math
 
 import numpy as np
 import pytest
 
 pytestmark = pytest.mark.gpu
+
+
+def _rel(a, b):
+    a, b = np.asarray(a, float), np.asarray(b, float)
+    return float(np.max(np.abs(a - b) / np.maximum(1.0, np.abs(b))))
+
+
+def _ulps(a, b):
+    a, b = np.asarray(a, float), np.asarray(b, float)
+    return float(np.max(np.abs(a - b) / np.spacing(np.maximum(np.abs(b), 1.0))))     # same scale as _rel
+
+
+def _same_states(name, got, ref, ctx):
+    if name == "hmm":                                   # integer states: exact
+        assert np.array_equal(got, ref), ctx
+    else:
+        r = _rel(got, ref)
+        assert r < 1e-9, ctx + (r, _ulps(got, ref))
 
 
 def _models():
@@ -29,7 +51,7 @@ def _models():
     ]
 
 
-@pytest.mark.parametrize("n", [64, 5000, 20000])
+@pytest.mark.parametrize("n", [6, 7, 64, 5000, 20000])    # 6, 7: history rows not 16-byte aligned
 def test_ancestor_sampling_sweep_equals_oracle(n):
     from anglican_b200 import Population
     from oracle import pyoracle as orc
@@ -47,14 +69,17 @@ def test_ancestor_sampling_sweep_equals_oracle(n):
                                     ancestor_sampling=cond)
                 anc, x = out.history()
                 assert np.array_equal(anc, ref["anc_hist"]), (name, n, it)
-                assert np.array_equal(x[:, :, 0], ref["x_hist"][:, :, 0])
-                assert np.array_equal(out.x_final, ref["x_final"][:, 0])
-                assert abs(out.log_z - ref["log_z"]) <= 1e-9 * abs(ref["log_z"])
+                _same_states(name, x[:, :, 0], ref["x_hist"][:, :, 0], (name, n, it, "x_hist"))
+                _same_states(name, out.x_final, ref["x_final"][:, 0], (name, n, it, "x_final"))
+                assert abs(out.log_z - ref["log_z"]) <= 1e-9 * abs(ref["log_z"]), (name, n, it)
+                if name != "hmm":
+                    print("pgas %s n=%d it=%d: max |x - x_ref| = %.2f ulp"
+                          % (name, n, it, _ulps(x[:, :, 0], ref["x_hist"][:, :, 0])))
                 if cond:
                     assert np.any(anc[:, 0] != 0), (name, n)       # the draw did something
                 slot = (7 * it + 3) % n
                 tr = out.trace(slot)
-                assert np.array_equal(tr, orc.trace_lineage(ref, slot)[:, 0])
+                _same_states(name, tr, orc.trace_lineage(ref, slot)[:, 0], (name, n, it, "trace"))
                 retained = tr
 
 
