@@ -107,6 +107,24 @@ struct RunRec {
     int count;                   // offspring
     int val;                     // ancestor id | lap << 31
 };
+// Everything the streaming path of k_ancestors needs to know about one tile, built
+// by k_expand (one 64-byte record, read with four 128-bit loads).  Fast mode: the
+// tile emits in exactly one lap, all its edges and the pointers below them live in
+// one binade / one comb segment, and k_fold_agg saw no tie and no saturated
+// element; anything else takes the general path.
+struct TileRec {
+    double sD0;                  // (units of the exact running sum entering the tile) - X0 of the segment
+    double qD, invq;             // comb stride of the segment in units of the binade, 1 / stride
+    double inv_u;                // 2^-e of the binade
+    double units;                // >= 0: exact units the tile must add; < 0: -(bound it must stay below)
+    double m;                    // max log-weight (smc.cljc:75)
+    int32_t* dst;                // where window entry 0 goes (local ancestor array or a peer's)
+    int k0;                      // index, relative to the segment, of the first pointer of the window
+    unsigned wm;                 // window length | mode << 28
+};
+enum { TM_NONE = 0, TM_FAST = 1, TM_GENERAL = 2 };
+static_assert(sizeof(TileRec) == 64, "TileRec is read as four 16-byte words");
+
 constexpr int HEAVY_W = 1 << 18; // offspring of one (tile, lap) above which emission is deferred
 constexpr int BIG_RUN = 1 << 16; // runs split over all CTAs of the fill kernel
 constexpr int SEGB = 512;        // tiles per block of the segmented tile scan (k_seg_scan)
@@ -134,6 +152,10 @@ struct ResampleWS {
     double* sin[2] = {};         // exact running sum entering every tile (k_expand), [nt + 1]
     long long* cnt[2] = {};      // pointers of the comb strictly below sin[lap][t], [nt + 1]
     int* gseg[2] = {};           // comb segment that holds pointer cnt[lap][t]
+    TileRec* rec = nullptr;      // per tile: what k_ancestors does with it (k_expand)
+    int* tflag = nullptr;        // per tile: bit lap set = integer fast path valid in that lap (k_fold_agg)
+    int* glist = nullptr;        // tiles listed for k_ancestors_general, ngen[0] of them
+    int* ngen = nullptr;
     double* shin[2] = {};        // exact running sum entering / leaving each hard tile
     double* shout[2] = {};
     Xd* hpa[2] = {};             // [HCAP][TILE] per-element inclusive prefix transducers, context eA
@@ -161,6 +183,7 @@ struct ResampleWS {
 
 struct apop_ctx {
     int device = 0;
+    int sm_count = 148;       // multiprocessors of the device (grid sizing)
     int rank = 0, world = 1;
     int64_t n = 0;            // local particles
     int64_t n_global = 0;

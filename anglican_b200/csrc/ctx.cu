@@ -135,6 +135,11 @@ int apop_create(apop_ctx** out, int64_t n_local, uint64_t seed, int device, int 
     if (cudaSetDevice(device) != cudaSuccess) return APOP_ERR_CUDA;
     apop_ctx* c = new apop_ctx();
     c->device = device;
+    {
+        int sms = 0;
+        if (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device) == cudaSuccess && sms > 0)
+            c->sm_count = sms;
+    }
     c->rank = rank;
     c->world = world;
     c->n = n_local;
@@ -394,7 +399,7 @@ int apop_column_fill(apop_ctx* c, apop_col h, double value) {
     if (!col) return APOP_ERR_INVALID;
     const int64_t total = c->n * col->width;
     int blocks = (int)((total + 255) / 256);
-    if (blocks > 148 * 32) blocks = 148 * 32;
+    if (blocks > c->sm_count * 32) blocks = c->sm_count * 32;
     if (col->dtype == APOP_F64)
         k_fill_f64<<<blocks, 256, 0, c->stream>>>((double*)col->ptr, total, value);
     else

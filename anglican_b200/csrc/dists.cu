@@ -209,9 +209,9 @@ __global__ void k_selftest_math(int fn, const double* __restrict__ in, double* _
 }
 
 // ------------------------------------------------------------------ host
-static int grid_for(int64_t n, int tb) {
+static int grid_for(const apop_ctx* c, int64_t n, int tb) {
     int64_t b = (n + tb - 1) / tb;
-    const int64_t cap = 148LL * 32;
+    const int64_t cap = (int64_t)c->sm_count * 32;
     return (int)(b < cap ? (b > 0 ? b : 1) : cap);
 }
 
@@ -240,7 +240,7 @@ int apop_selftest_math(apop_ctx* c, int fn, apop_col in, apop_col out) {
     Column* i = get_col(c, in, APOP_F64, 1);
     Column* o = get_col(c, out, APOP_F64, 1);
     if (!i || !o) return APOP_ERR_INVALID;
-    k_selftest_math<<<grid_for(c->n, 256), 256, 0, c->stream>>>(fn, (const double*)i->ptr,
+    k_selftest_math<<<grid_for(c, c->n, 256), 256, 0, c->stream>>>(fn, (const double*)i->ptr,
                                                                  (double*)o->ptr, c->n);
     LAUNCH_DONE(c);
     return APOP_OK;
@@ -252,7 +252,7 @@ int apop_sample_normal(apop_ctx* c, apop_arg mean, apop_arg sd, uint32_t draw, a
     APOP_TRY(resolve_arg(c, mean, &m)); APOP_TRY(resolve_arg(c, sd, &s));
     Column* o = get_col(c, out, APOP_F64, 1);
     if (!o) return APOP_ERR_INVALID;
-    k_sample_normal<<<grid_for(c->n, 256), 256, 0, c->stream>>>(m, s, (double*)o->ptr, c->n, c->g0,
+    k_sample_normal<<<grid_for(c, c->n, 256), 256, 0, c->stream>>>(m, s, (double*)o->ptr, c->n, c->g0,
                                                                  c->seed, c->step, draw);
     LAUNCH_DONE(c);
     return APOP_OK;
@@ -264,7 +264,7 @@ int apop_observe_normal(apop_ctx* c, apop_arg mean, apop_arg sd, apop_arg value,
     APOP_TRY(resolve_arg(c, value, &v));
     Column* l = get_col(c, logw, APOP_F64, 1);
     if (!l) return APOP_ERR_INVALID;
-    k_observe_normal<<<grid_for(c->n, 256), 256, 0, c->stream>>>(m, s, v, (double*)l->ptr, c->n);
+    k_observe_normal<<<grid_for(c, c->n, 256), 256, 0, c->stream>>>(m, s, v, (double*)l->ptr, c->n);
     LAUNCH_DONE(c);
     return APOP_OK;
 }
@@ -274,7 +274,7 @@ int apop_sample_gamma(apop_ctx* c, apop_arg shape, apop_arg rate, uint32_t draw,
     APOP_TRY(resolve_arg(c, shape, &a)); APOP_TRY(resolve_arg(c, rate, &b));
     Column* o = get_col(c, out, APOP_F64, 1);
     if (!o) return APOP_ERR_INVALID;
-    k_sample_gamma<<<grid_for(c->n, 256), 256, 0, c->stream>>>(a, b, (double*)o->ptr, c->n, c->g0,
+    k_sample_gamma<<<grid_for(c, c->n, 256), 256, 0, c->stream>>>(a, b, (double*)o->ptr, c->n, c->g0,
                                                                 c->seed, c->step, draw);
     LAUNCH_DONE(c);
     return APOP_OK;
@@ -286,7 +286,7 @@ int apop_observe_gamma(apop_ctx* c, apop_arg shape, apop_arg rate, apop_arg valu
     APOP_TRY(resolve_arg(c, value, &v));
     Column* l = get_col(c, logw, APOP_F64, 1);
     if (!l) return APOP_ERR_INVALID;
-    k_observe_gamma<<<grid_for(c->n, 256), 256, 0, c->stream>>>(a, b, v, (double*)l->ptr, c->n);
+    k_observe_gamma<<<grid_for(c, c->n, 256), 256, 0, c->stream>>>(a, b, v, (double*)l->ptr, c->n);
     LAUNCH_DONE(c);
     return APOP_OK;
 }
@@ -296,7 +296,7 @@ int apop_sample_beta(apop_ctx* c, apop_arg alpha, apop_arg beta, uint32_t draw, 
     APOP_TRY(resolve_arg(c, alpha, &a)); APOP_TRY(resolve_arg(c, beta, &b));
     Column* o = get_col(c, out, APOP_F64, 1);
     if (!o) return APOP_ERR_INVALID;
-    k_sample_beta<<<grid_for(c->n, 256), 256, 0, c->stream>>>(a, b, (double*)o->ptr, c->n, c->g0,
+    k_sample_beta<<<grid_for(c, c->n, 256), 256, 0, c->stream>>>(a, b, (double*)o->ptr, c->n, c->g0,
                                                                c->seed, c->step, draw);
     LAUNCH_DONE(c);
     return APOP_OK;
@@ -308,7 +308,7 @@ int apop_observe_beta(apop_ctx* c, apop_arg alpha, apop_arg beta, apop_arg value
     APOP_TRY(resolve_arg(c, value, &v));
     Column* l = get_col(c, logw, APOP_F64, 1);
     if (!l) return APOP_ERR_INVALID;
-    k_observe_beta<<<grid_for(c->n, 256), 256, 0, c->stream>>>(a, b, v, (double*)l->ptr, c->n);
+    k_observe_beta<<<grid_for(c, c->n, 256), 256, 0, c->stream>>>(a, b, v, (double*)l->ptr, c->n);
     LAUNCH_DONE(c);
     return APOP_OK;
 }
@@ -318,7 +318,7 @@ int apop_sample_uniform(apop_ctx* c, apop_arg lo, apop_arg hi, uint32_t draw, ap
     APOP_TRY(resolve_arg(c, lo, &a)); APOP_TRY(resolve_arg(c, hi, &b));
     Column* o = get_col(c, out, APOP_F64, 1);
     if (!o) return APOP_ERR_INVALID;
-    k_sample_uniform<<<grid_for(c->n, 256), 256, 0, c->stream>>>(a, b, (double*)o->ptr, c->n,
+    k_sample_uniform<<<grid_for(c, c->n, 256), 256, 0, c->stream>>>(a, b, (double*)o->ptr, c->n,
                                                                   c->g0, c->seed, c->step, draw);
     LAUNCH_DONE(c);
     return APOP_OK;
@@ -330,7 +330,7 @@ int apop_observe_uniform(apop_ctx* c, apop_arg lo, apop_arg hi, apop_arg value, 
     APOP_TRY(resolve_arg(c, value, &v));
     Column* l = get_col(c, logw, APOP_F64, 1);
     if (!l) return APOP_ERR_INVALID;
-    k_observe_uniform<<<grid_for(c->n, 256), 256, 0, c->stream>>>(a, b, v, (double*)l->ptr, c->n);
+    k_observe_uniform<<<grid_for(c, c->n, 256), 256, 0, c->stream>>>(a, b, v, (double*)l->ptr, c->n);
     LAUNCH_DONE(c);
     return APOP_OK;
 }
@@ -360,7 +360,7 @@ int apop_sample_discrete(apop_ctx* c, const double* weights, int k, apop_col wco
     APOP_TRY(discrete_weights(c, weights, k, wcol, &w, &stride));
     Column* o = get_col(c, out, APOP_I32, 1);
     if (!o) return APOP_ERR_INVALID;
-    k_sample_discrete<<<grid_for(c->n, 256), 256, 0, c->stream>>>(w, k, stride, (int32_t*)o->ptr,
+    k_sample_discrete<<<grid_for(c, c->n, 256), 256, 0, c->stream>>>(w, k, stride, (int32_t*)o->ptr,
                                                                    c->n, c->g0, c->seed, c->step,
                                                                    draw);
     LAUNCH_DONE(c);
@@ -379,7 +379,7 @@ int apop_observe_discrete(apop_ctx* c, const double* weights, int k, apop_col wc
     }
     Column* l = get_col(c, logw, APOP_F64, 1);
     if (!l) return APOP_ERR_INVALID;
-    k_observe_discrete<<<grid_for(c->n, 256), 256, 0, c->stream>>>(w, k, stride, v, value_scalar,
+    k_observe_discrete<<<grid_for(c, c->n, 256), 256, 0, c->stream>>>(w, k, stride, v, value_scalar,
                                                                     (double*)l->ptr, c->n);
     LAUNCH_DONE(c);
     return APOP_OK;
@@ -392,7 +392,7 @@ int apop_sample_dirichlet(apop_ctx* c, const double* alpha, int k, uint32_t draw
     if (!o) return APOP_ERR_INVALID;
     void* d = nullptr;
     APOP_TRY(param_upload(c, alpha, sizeof(double) * (size_t)k, &d));
-    k_sample_dirichlet<<<grid_for(c->n, 128), 128, 0, c->stream>>>((const double*)d, k,
+    k_sample_dirichlet<<<grid_for(c, c->n, 128), 128, 0, c->stream>>>((const double*)d, k,
                                                                     (double*)o->ptr, c->n, c->g0,
                                                                     c->seed, c->step, draw);
     LAUNCH_DONE(c);
@@ -411,7 +411,7 @@ int apop_observe_dirichlet(apop_ctx* c, const double* alpha, int k, apop_col val
     const double Z = sl - lgamma(sa);
     void* d = nullptr;
     APOP_TRY(param_upload(c, alpha, sizeof(double) * (size_t)k, &d));
-    k_observe_dirichlet<<<grid_for(c->n, 256), 256, 0, c->stream>>>(
+    k_observe_dirichlet<<<grid_for(c, c->n, 256), 256, 0, c->stream>>>(
         (const double*)d, k, Z, (const double*)v->ptr, (double*)l->ptr, c->n);
     LAUNCH_DONE(c);
     return APOP_OK;
@@ -479,7 +479,7 @@ int apop_sample_mvn(apop_ctx* c, const double* mean, apop_col mean_col, const do
         mp = (const double*)dm; ms = 0;
     }
     const int tb = 128, nw = tb / 32;
-    k_sample_mvn<<<grid_for(c->n, nw), tb, sizeof(double) * (size_t)d * nw, c->stream>>>(
+    k_sample_mvn<<<grid_for(c, c->n, nw), tb, sizeof(double) * (size_t)d * nw, c->stream>>>(
         (const double*)dL, d, mp, ms, (double*)o->ptr, c->n, c->g0, c->seed, c->step, draw);
     LAUNCH_DONE(c);
     return APOP_OK;
@@ -518,7 +518,7 @@ int apop_observe_mvn(apop_ctx* c, const double* mean, apop_col mean_col, const d
         return mvn_observe_dmma_enqueue(c, d, (const double*)diL, Z, mp, ms, vp, vs,
                                         (double*)l->ptr);
     const int tb = 128, nw = tb / 32;
-    k_observe_mvn<<<grid_for(c->n, nw), tb, sizeof(double) * (size_t)d * nw, c->stream>>>(
+    k_observe_mvn<<<grid_for(c, c->n, nw), tb, sizeof(double) * (size_t)d * nw, c->stream>>>(
         (const double*)diL, Z, d, mp, ms, vp, vs, (double*)l->ptr, c->n);
     LAUNCH_DONE(c);
     return APOP_OK;

@@ -163,9 +163,9 @@ __global__ void k_observe_fam(DArg2 a, DArg2 b, DArg2 c, DArg2 val, double* __re
         lw[k] += fam_logp<FAM>(val.at(k), a.at(k), b.at(k), c.at(k));
 }
 
-static int grid2(int64_t n) {
+static int grid2(const apop_ctx* c, int64_t n) {
     int64_t b = (n + 255) / 256;
-    const int64_t cap = 148LL * 32;
+    const int64_t cap = (int64_t)c->sm_count * 32;
     return (int)(b < cap ? (b > 0 ? b : 1) : cap);
 }
 
@@ -213,7 +213,7 @@ int apop_sample_dist(apop_ctx* c, int32_t family, const apop_arg* params, uint32
     if (family == APOP_DIST_BINOMIAL && (p0.col >= 0 || !(p0.scalar >= 0 && p0.scalar <= 400)))
         return set_err(c, APOP_ERR_UNSUPPORTED, "binomial sampler: scalar n <= 400");
     cudaSetDevice(c->device);
-#define CALL(F) k_sample_fam<F><<<grid2(c->n), 256, 0, c->stream>>>(a, b, d, (double*)o->ptr, c->n, \
+#define CALL(F) k_sample_fam<F><<<grid2(c, c->n), 256, 0, c->stream>>>(a, b, d, (double*)o->ptr, c->n, \
                                                                      c->g0, c->seed, c->step, draw)
     FAM_SWITCH(family, CALL)
 #undef CALL
@@ -233,7 +233,7 @@ int apop_observe_dist(apop_ctx* c, int32_t family, const apop_arg* params, apop_
     Column* l = get_col(c, logw, APOP_F64, 1);
     if (!l) return APOP_ERR_INVALID;
     cudaSetDevice(c->device);
-#define CALL(F) k_observe_fam<F><<<grid2(c->n), 256, 0, c->stream>>>(a, b, d, v, (double*)l->ptr, c->n)
+#define CALL(F) k_observe_fam<F><<<grid2(c, c->n), 256, 0, c->stream>>>(a, b, d, v, (double*)l->ptr, c->n)
     FAM_SWITCH(family, CALL)
 #undef CALL
     c->launches += 1;

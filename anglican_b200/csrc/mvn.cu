@@ -236,8 +236,7 @@ static int launch_propagate(apop_ctx* c, const MvnSweepArgs& a) {
                                           cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         if (c->device >= 0 && c->device < 64) configured[c->device] = true;
     }
-    int sms = 148;
-    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, c->device);
+    const int sms = c->sm_count;
     const int64_t groups = (a.n + 7) / 8;
     int grid = (int)((groups + 15) / 16);
     if (grid > sms) grid = sms;                   // persistent: one CTA (16 warps) per SM
@@ -279,7 +278,7 @@ int mvn_propagate_enqueue(apop_ctx* c, int d, const MvnSweepArgs& a) {
 int mvn_init_enqueue(apop_ctx* c, double* x, int d, double s0, const double* retained) {
     const int64_t total = c->n * (int64_t)d;
     int blocks = (int)((total + 255) / 256);
-    if (blocks > 148 * 16) blocks = 148 * 16;
+    if (blocks > c->sm_count * 16) blocks = c->sm_count * 16;
     k_init_mvn<<<blocks, 256, 0, c->stream>>>(x, c->n, d, s0, c->g0, c->seed, retained);
     c->launches += 1;
     APOP_CUDA(c, cudaGetLastError());
@@ -299,7 +298,7 @@ static int launch_observe(apop_ctx* c, const double* iL, double Z, const double*
     }
     const int64_t groups = (c->n + 7) / 8;
     int grid = (int)((groups + 7) / 8);
-    if (grid > 148 * 2) grid = 148 * 2;
+    if (grid > c->sm_count * 2) grid = c->sm_count * 2;
     k_observe_mvn_dmma<D><<<grid, 256, smem, c->stream>>>(iL, Z, mean, ms, val, vs, lw, c->n);
     c->launches += 1;
     APOP_CUDA(c, cudaGetLastError());

@@ -437,7 +437,7 @@ __global__ void __launch_bounds__(FB) k_finalize(WSView v, int64_t n, int64_t n_
         __syncthreads();
     }
     const double atot = (F.world > 1) ? gtot : carry;
-    if (tid == 0) { v.ain[nt] = carry; sh_skip = (nt < INT_MAX) ? (int)nt : INT_MAX; }
+    if (tid == 0) { v.ain[nt] = carry; sh_skip = (nt < INT_MAX) ? (int)nt : INT_MAX; v.ngen[0] = 0; }
     __syncthreads();
 
     const double u = (u_in != u_in) ? uniform_at(seed, 0, step, STREAM_RESAMPLE, 0) : u_in;
@@ -667,6 +667,7 @@ __global__ void __launch_bounds__(TB, APOP_FOLD_CTAS) k_fold_agg(const double* _
         for (int i = 0; i < NWARP; ++i) { a += wa[i]; b += wb[i]; t0 += ws0[i]; t1 += ws1[i]; }
         v.tacc[t] = a;
         v.tacc2[t] = b;
+        v.tflag[t] = any_bad ? 0 : ((f0 ? 1 : 0) | (f1 ? 2 : 0));
         if (!any_bad) {
             Xd x0; x0.a0 = t0; x0.a1 = t0;
             Xd x1; x1.a0 = t1; x1.a1 = t1;
@@ -1528,24 +1529,98 @@ __device__ __noinline__ void generic_emit(const Comb& comb, double Sin, const do
     __syncthreads();
 }
 
-// exact running sum entering every tile, both laps, from the chain's records
-__global__ void __launch_bounds__(256) k_expand(WSView v) {
-    const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+// exact running sum entering every tile, both laps, from the chain's records, the
+// pointer counts at the tile boundaries and the comb segment they fall in, and from
+// those the per-tile record of k_ancestors: the emission kernel needs no serial
+// search and no decision of its own.  A block covers 255 tiles (256 boundaries).
+constexpr int XB = 256;
+__global__ void __launch_bounds__(XB) k_expand(WSView v, int order, int32_t* __restrict__ anc,
+                                               int64_t out_offset,
+                                               const __grid_constant__ PeerI32 ancp, int world,
+                                               int64_t nl) {
+    __shared__ double sS[2][XB];
+    __shared__ i64 sC[2][XB];
+    __shared__ int sG[2][XB];
+    const int64_t t = (int64_t)blockIdx.x * (XB - 1) + threadIdx.x;
     if (t == 0) { v.nruns[0] = 0; v.nruns[1] = 0; }           // run lists of this resample
-    if (t > v.nt) return;
-    int* err = &v.info->err;
-    const double s0 = tile_sin(v, 0, t, err), s1 = tile_sin(v, 1, t, err);
-    v.sin[0][t] = s0;
-    v.sin[1][t] = s1;
-    // pointer counts at the tile boundary and the comb segment they fall in: the
-    // emission kernel then needs no serial search per tile
+    const ResampleInfo* I = v.info;
     const Comb& comb = *v.comb;
-    if (comb.err || comb.nseg <= 0) { v.cnt[0][t] = 0; v.cnt[1][t] = 0; v.gseg[0][t] = 0; v.gseg[1][t] = 0; return; }
-    int h0 = comb.nseg - 1, h1 = comb.nseg - 1;
-    const i64 c0 = comb_count_below(comb, s0, h0), c1 = comb_count_below(comb, s1, h1);
-    v.cnt[0][t] = c0; v.cnt[1][t] = c1;
-    v.gseg[0][t] = find_seg_of_index(comb, c0);
-    v.gseg[1][t] = find_seg_of_index(comb, c1);
+    const bool dead = comb.err || comb.nseg <= 0;
+    if (t <= v.nt) {
+        int* err = &v.info->err;
+        const double s0 = tile_sin(v, 0, t, err), s1 = tile_sin(v, 1, t, err);
+        i64 c0 = 0, c1 = 0;
+        int g0 = 0, g1 = 0;
+        if (!dead) {
+            int h0 = comb.nseg - 1, h1 = comb.nseg - 1;
+            c0 = comb_count_below(comb, s0, h0);
+            c1 = comb_count_below(comb, s1, h1);
+            g0 = find_seg_of_index(comb, c0);
+            g1 = find_seg_of_index(comb, c1);
+        }
+        sS[0][threadIdx.x] = s0; sS[1][threadIdx.x] = s1;
+        sC[0][threadIdx.x] = c0; sC[1][threadIdx.x] = c1;
+        sG[0][threadIdx.x] = g0; sG[1][threadIdx.x] = g1;
+        if (threadIdx.x < XB - 1 || t == v.nt) {               // each boundary written once
+            v.sin[0][t] = s0; v.sin[1][t] = s1;
+            v.cnt[0][t] = c0; v.cnt[1][t] = c1;
+            v.gseg[0][t] = g0; v.gseg[1][t] = g1;
+        }
+    }
+    __syncthreads();
+    if (threadIdx.x >= XB - 1 || t >= v.nt) return;
+    const int i = threadIdx.x;
+    TileRec R;
+    R.sD0 = 0.0; R.qD = 1.0; R.invq = 1.0; R.inv_u = 1.0; R.units = 0.0; R.m = I->m;
+    R.dst = nullptr; R.k0 = 0; R.wm = (unsigned)TM_NONE << 28;
+    if (!dead && !I->err) {
+        const double x0 = comb.x0, xlast = comb.xlast;
+        // a lap emits if some pointer falls into this tile (x0 is uniform on the wheel:
+        // all tiles but the one holding x0 emit in exactly one lap)
+        const bool do0 = (sS[0][i + 1] > x0) && !(sS[0][i] > xlast) && (sC[0][i] != sC[0][i + 1]);
+        const bool do1 = !(sS[1][i] > xlast) && (sC[1][i] != sC[1][i + 1]);
+        if (do0 || do1) {
+            R.wm = (unsigned)TM_GENERAL << 28;
+            const int lap = do0 ? 0 : 1;
+            const int cls = v.cls[lap][t];
+            const double Sin = sS[lap][i], Sout = sS[lap][i + 1];
+            const i64 C0 = sC[lap][i], C1 = sC[lap][i + 1];
+            const i64 W = C1 - C0;
+            const CombSeg& gs = comb.seg[sG[lap][i]];
+            constexpr int WCAP = 8192 - 4;
+            if (!(do0 && do1) && ((v.tflag[t] >> lap) & 1) && cls != kCtxHard && cls != kCtxSkip &&
+                ctx_fast_ok(cls) && ctx_of(Sin) == cls && gs.e == cls && gs.q > 0 && C0 > gs.j0 &&
+                C1 < gs.j0 + gs.len && W <= WCAP && W <= v.heavy_w &&
+                order != APOP_ORDER_REFERENCE) {
+                const i64 slot0 = out_offset + slot_of(C0, lap, order, I->J, I->n_new);
+                int32_t* dst = nullptr;
+                if (world == 1) {
+                    dst = anc + slot0;
+                } else {
+                    const int q0 = (int)(slot0 / nl), q1 = (int)((slot0 + W - 1) / nl);
+                    if (q0 == q1) dst = ancp.p[q0] + (slot0 - (i64)q0 * nl);   // one owner: peer stores
+                }
+                if (dst) {
+                    const i64 s_in = units_of(Sin);
+                    R.sD0 = (double)(s_in - gs.X0);                            // exact
+                    R.qD = (double)gs.q;
+                    R.invq = fm::div_fast(1.0, R.qD);
+                    R.inv_u = pow2(-cls);
+                    // the tile's integer sum must land on the chain's exact edge
+                    if (Sout < INFINITY)
+                        R.units = (ctx_of(Sout) == cls) ? (double)(units_of(Sout) - s_in)
+                                                        : 1152921504606846976.0;   // 2^60: never
+                    else
+                        R.units = -(double)(kTwo53 - s_in);
+                    R.dst = dst;
+                    R.k0 = (int)(C0 - gs.j0);
+                    R.wm = (unsigned)W | ((unsigned)TM_FAST << 28);
+                }
+            }
+        }
+    }
+    v.rec[t] = R;
+    if ((R.wm >> 28) == TM_GENERAL) v.glist[atomicAdd(v.ngen, 1)] = (int)t;
 }
 
 union AncSmem {
@@ -1553,17 +1628,16 @@ union AncSmem {
     StageSmem stage;
 };
 
-__global__ void __launch_bounds__(TB, APOP_ANC_CTAS) k_ancestors(const double* __restrict__ lw,
-                                                     const double* __restrict__ win, int64_t n,
-                                                     int64_t g0, WSView v, int order,
-                                                     int32_t* __restrict__ anc,
-                                                     int64_t out_offset,
-                                                     const __grid_constant__ PeerI32 ancp,
-                                                     int world) {
-    __shared__ AncSmem sm;
+// general path of one tile: any class, any order, both laps, deferred runs.  The
+// tiles that need it (hard tiles, the tile that holds x0, ties, windows that straddle
+// a shard boundary, reference order) were listed by k_expand.
+__device__ __forceinline__ void ancestors_general(const int t, const double* __restrict__ lw,
+                                               const double* __restrict__ win, int64_t n,
+                                               int64_t g0, const WSView& v, int order,
+                                               int32_t* __restrict__ anc, int64_t out_offset,
+                                               const PeerI32& ancp, int world, AncSmem& sm) {
     const Comb& comb = *v.comb;          // global (L1/L2 resident); the fast path reads one segment
     const ResampleInfo* I = v.info;
-    const int t = blockIdx.x;
     const int64_t base = (int64_t)t * TILE;
     // Every global read of the common path is issued here, unconditionally and
     // before the first branch, so that the tile data and its metadata arrive in
@@ -1631,6 +1705,152 @@ __global__ void __launch_bounds__(TB, APOP_ANC_CTAS) k_ancestors(const double* _
         __syncthreads();
         generic_emit(comb, si1, w, nvalid, (int32_t)(g0 + base + i0), E, sm.fold);
     }
+}
+
+
+// ---- streaming path of one tile (TileRec mode TM_FAST) ----------------------
+// Integer increments by the 2^52 magic add (k_fold_agg has checked that no element
+// ties or saturates), exact prefix in integer-valued doubles, pointer index per
+// edge k(s) = ceil((s - X0) / q) in exact fp64, then the offspring are staged as
+// "head" marks (element j writes j+1 at its first slot), a max-scan fills the runs
+// and every thread stores its E consecutive window entries with 128-bit stores.
+template <int E>
+__device__ __forceinline__ void scan_store(StageSmem& st, int a0, int tot, int32_t* dstA,
+                                           int32_t val_tile0) {
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    const int i = tid * E;
+    int x[E];
+#pragma unroll
+    for (int g = 0; g < E / 4; ++g) {
+        const int4 a = *reinterpret_cast<const int4*>(&st.buf[i + 4 * g]);
+        x[4 * g] = a.x; x[4 * g + 1] = a.y; x[4 * g + 2] = a.z; x[4 * g + 3] = a.w;
+    }
+#pragma unroll
+    for (int q = 1; q < E; ++q) x[q] = max(x[q], x[q - 1]);
+    int inc = x[E - 1];
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        const int o = __shfl_up_sync(0xffffffffu, inc, d);
+        if (lane >= d) inc = max(inc, o);
+    }
+    int ex = __shfl_up_sync(0xffffffffu, inc, 1);
+    if (lane == 0) ex = 0;
+    if (lane == 31) st.wmax[wid] = inc;
+    __syncthreads();
+    int wm = (lane < NWARP) ? st.wmax[lane] : 0;
+#pragma unroll
+    for (int d = 1; d < NWARP; d <<= 1) {
+        const int o = __shfl_up_sync(0xffffffffu, wm, d);
+        if (lane >= d) wm = max(wm, o);
+    }
+    const int pre_w = __shfl_sync(0xffffffffu, wm, (wid > 0) ? wid - 1 : 0);
+    if (wid > 0) ex = max(ex, pre_w);
+    const int add = val_tile0 - 1;
+#pragma unroll
+    for (int q = 0; q < E; ++q) x[q] = max(x[q], ex) + add;
+#pragma unroll
+    for (int g = 0; g < E / 4; ++g) {
+        const int idx = i + 4 * g;
+        if (idx >= a0 && idx + 4 <= tot) {
+            *reinterpret_cast<int4*>(dstA + idx) = make_int4(x[4 * g], x[4 * g + 1], x[4 * g + 2], x[4 * g + 3]);
+        } else {
+#pragma unroll
+            for (int c = 0; c < 4; ++c)
+                if (idx + c >= a0 && idx + c < tot) dstA[idx + c] = x[4 * g + c];
+        }
+    }
+}
+
+__device__ __forceinline__ void ancestors_fast(const TileRec& R, const double (&raw)[IPT], bool is_w,
+                                               int64_t base, int64_t n, int32_t val_tile0,
+                                               StageSmem& st, int* err) {
+    const int tid = threadIdx.x;
+    const int W = (int)(R.wm & 0x0fffffffu);
+    // the window is shifted by a0 = (destination address / 4) mod 4 inside the staging
+    // buffer so that 16-byte groups of the buffer line up with those of the output
+    const int a0 = (int)((reinterpret_cast<uintptr_t>(R.dst) >> 2) & 3);
+    const int tot = a0 + W;
+    const int E = ((tot + TB * 4 - 1) / (TB * 4)) * 4;             // entries per thread: 4 .. 16
+    for (int e = tid * 4; e < TB * E; e += TB * 4)
+        *reinterpret_cast<int4*>(&st.buf[e]) = make_int4(0, 0, 0, 0);
+    double inc[IPT], loc = 0.0;
+    {
+        double w[IPT];
+        weights_from_raw(is_w, raw, base, n, R.m, w);
+        const double inv_u = R.inv_u;
+#pragma unroll
+        for (int j = 0; j < IPT; ++j) {
+            inc[j] = (w[j] * inv_u + 4503599627370496.0) - 4503599627370496.0;
+            loc += inc[j];
+        }
+    }
+    double tile_units;
+    const double pre = cta_excl_scan_f64(loc, st.dsum, tile_units);     // two barriers: zeroing done
+    if (tid == 0) {
+        const double u = R.units;
+        if ((u >= 0.0) ? (tile_units != u) : !(tile_units < -u)) atomicOr(err, EB_CTX | 0x1000);
+    }
+    const double qD = R.qD, invq = R.invq;
+    const double magic = 6755399441055744.0;                           // 1.5 * 2^52
+    const int k0 = R.k0 - a0;
+    double sD = R.sD0 + pre;                                           // exact
+    int kprev;
+    {
+        const double tm = sD * invq + magic;
+        const double r = fma(-(tm - magic), qD, sD);
+        kprev = __double2loint(tm) + (r > 0.0 ? 1 : 0);
+    }
+#pragma unroll
+    for (int j = 0; j < IPT; ++j) {
+        sD += inc[j];
+        const double tm = sD * invq + magic;
+        const double r = fma(-(tm - magic), qD, sD);
+        const int k = __double2loint(tm) + (r > 0.0 ? 1 : 0);
+        if (kprev < k) st.buf[kprev - k0] = tid * IPT + j + 1;          // head of element j's run
+        kprev = k;
+    }
+    __syncthreads();
+    int32_t* dstA = R.dst - a0;                                        // 16-byte aligned
+    if (E == 8) scan_store<8>(st, a0, tot, dstA, val_tile0);
+    else if (E == 12) scan_store<12>(st, a0, tot, dstA, val_tile0);
+    else if (E == 4) scan_store<4>(st, a0, tot, dstA, val_tile0);
+    else scan_store<16>(st, a0, tot, dstA, val_tile0);
+}
+
+__global__ void __launch_bounds__(TB) k_ancestors_general(const double* __restrict__ lw,
+                                                     const double* __restrict__ win, int64_t n,
+                                                     int64_t g0, const __grid_constant__ WSView v,
+                                                     int order, int32_t* __restrict__ anc,
+                                                     int64_t out_offset,
+                                                     const __grid_constant__ PeerI32 ancp,
+                                                     int world) {
+    __shared__ AncSmem sm;
+    const int ng = v.ngen[0];
+    for (int i = blockIdx.x; i < ng; i += gridDim.x) {
+        ancestors_general(v.glist[i], lw, win, n, g0, v, order, anc, out_offset, ancp, world, sm);
+        __syncthreads();
+    }
+}
+
+__global__ void __launch_bounds__(TB, APOP_ANC_CTAS) k_ancestors(const double* __restrict__ lw,
+                                                     const double* __restrict__ win, int64_t n,
+                                                     int64_t g0, const TileRec* __restrict__ rec,
+                                                     int* err) {
+    __shared__ StageSmem sm;
+    const int t = blockIdx.x;
+    const int64_t base = (int64_t)t * TILE;
+    // the tile and its record: all global reads of the streaming path, issued up front
+    double raw[IPT];
+    load_raw(lw, win, base, n, raw);
+    TileRec R;
+    {
+        const int4* rp = reinterpret_cast<const int4*>(rec + t);
+        int4* rq = reinterpret_cast<int4*>(&R);
+#pragma unroll
+        for (int k = 0; k < 4; ++k) rq[k] = __ldg(rp + k);
+    }
+    if ((R.wm >> 28) != TM_FAST) return;           // nothing to emit, or listed for the general kernel
+    ancestors_fast(R, raw, win != nullptr, base, n, (int32_t)(g0 + base), sm, err);
 }
 
 // Deferred emission (see RunRec): every warp takes run records in turn; the
@@ -1751,6 +1971,7 @@ void preload_resample_kernels() {
     cudaFuncGetAttributes(&a, k_chain);
     cudaFuncGetAttributes(&a, k_expand);
     cudaFuncGetAttributes(&a, k_ancestors);
+    cudaFuncGetAttributes(&a, k_ancestors_general);
     cudaFuncGetAttributes(&a, k_fill_runs);
     cudaFuncGetAttributes(&a, k_info_reset);
 }
@@ -1776,6 +1997,8 @@ int ensure_resample_ws(apop_ctx* c) {
         w.tmax = (double*)carve(nd * 8); w.tsum = (double*)carve(nd * 8);
         w.tsum2 = (double*)carve(nd * 8); w.ain = (double*)carve(nd * 8);
         w.tacc = (double*)carve(nd * 8); w.tacc2 = (double*)carve(nd * 8);
+        w.rec = (TileRec*)carve(nd * sizeof(TileRec)); w.tflag = (int*)carve(nd * 4);
+        w.glist = (int*)carve(nd * 4); w.ngen = (int*)carve(4);
         for (int l = 0; l < 2; ++l) {
             w.cls[l] = (int*)carve(nd * 4); w.agg[l] = (Xd*)carve(nd * sizeof(Xd));
             w.ex[l] = (Xd*)carve(nd * sizeof(Xd)); w.hix[l] = (int*)carve(nd * 4);
@@ -1858,17 +2081,20 @@ int resample_enqueue(apop_ctx* c, const ResampleArgs& a) {
     kt_begin(c, KT_RESOLVE);
     k_seg_scan<<<c->ws.nb, SEGB, 0, c->stream>>>(v, a.xfilt ? 1 : 0);
     k_chain<<<1, TB, 0, c->stream>>>(a.lw, a.w, a.n, n_glob, v, a.step, F, seq);
-    k_expand<<<(int)((v.nt + 1 + 255) / 256), 256, 0, c->stream>>>(v);
+    k_expand<<<(int)((v.nt + 1 + XB - 2) / (XB - 1)), XB, 0, c->stream>>>(
+        v, a.order, a.anc_out, a.out_offset, a.anc_peer, F.world, a.n);
     kt_end(c, KT_RESOLVE);
     c->launches += 5;
     if (a.anc_out) {
         kt_begin(c, KT_ANCESTORS);
-        k_ancestors<<<nt, TB, 0, c->stream>>>(a.lw, a.w, a.n, g0, v, a.order, a.anc_out,
-                                              a.out_offset, a.anc_peer, F.world);
-        k_fill_runs<<<592, FILL_TB, 0, c->stream>>>(v, a.order, a.anc_out, a.out_offset, a.n,
+        k_ancestors<<<nt, TB, 0, c->stream>>>(a.lw, a.w, a.n, g0, v.rec, &v.info->err);
+        k_ancestors_general<<<c->sm_count, TB, 0, c->stream>>>(a.lw, a.w, a.n, g0, v, a.order,
+                                                               a.anc_out, a.out_offset, a.anc_peer,
+                                                               F.world);
+        k_fill_runs<<<c->sm_count * 4, FILL_TB, 0, c->stream>>>(v, a.order, a.anc_out, a.out_offset, a.n,
                                                      a.anc_peer, F.world);
         kt_end(c, KT_ANCESTORS);
-        c->launches += 2;
+        c->launches += 3;
     }
     APOP_CUDA(c, cudaGetLastError());
     return APOP_OK;
@@ -1908,7 +2134,7 @@ int multinomial_enqueue(apop_ctx* c, const double* lw, const double* w, const do
     WSView v = view_of(c->ws);
     k_edges<<<(int)v.nt, TB, 0, c->stream>>>(lw, w, c->n, v, c->ws.edges);
     int blocks = (int)((n_new + 255) / 256);
-    if (blocks > 148 * 16) blocks = 148 * 16;
+    if (blocks > c->sm_count * 16) blocks = c->sm_count * 16;
     k_multinomial_search<<<blocks, 256, 0, c->stream>>>(c->ws.edges, c->n, uni, c->seed, c->step,
                                                         n_new, v.info, anc, c->g0);
     c->launches += 2;
@@ -1922,7 +2148,7 @@ int gather_enqueue(apop_ctx* c, const int32_t* anc, int64_t n_new, Column* col) 
     APOP_TRY(ensure_scratch(c, bytes));
     const int64_t total = n_new * col->width;
     int blocks = (int)((total + 255) / 256);
-    if (blocks > 148 * 32) blocks = 148 * 32;
+    if (blocks > c->sm_count * 32) blocks = c->sm_count * 32;
     kt_begin(c, KT_GATHER);
     if (col->dtype == APOP_F64)
         k_gather_f64<<<blocks, 256, 0, c->stream>>>((const double*)col->ptr, (double*)c->scratch,

@@ -844,7 +844,7 @@ static int sweep_end(apop_ctx* c, int T, const apop_sweep_opts* opts, apop_sweep
         APOP_TRY(stat_lse_enqueue(c, s->lw, n, s->lse));
     } else if (opts->want_final || result->x_final) {
         int blocks = (int)((n * dim + 255) / 256);
-        if (blocks > 148 * 32) blocks = 148 * 32;
+        if (blocks > c->sm_count * 32) blocks = c->sm_count * 32;
         kt_begin(c, KT_GATHER);
         if (c->world > 1) {
             const PeerF64 src = peer_f64(c, (T & 1) ? c->fab.off_xb : c->fab.off_xa);    // x_T

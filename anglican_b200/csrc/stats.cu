@@ -19,7 +19,7 @@
 namespace apop {
 
 constexpr int SB = 256;                 // threads per stats CTA
-constexpr int SGRID = 592;              // 148 SMs x 4 resident CTAs
+constexpr int SGRID = 592;              // partial-sum slots: 4 resident CTAs on each of 148 SMs (a cap, not a requirement)
 constexpr int SCH = 8;                  // columns handled per pass over the particles
 
 __device__ __forceinline__ double stat_weight(const double* __restrict__ lw, int64_t i, double m) {
