@@ -156,6 +156,16 @@ struct ResampleWS {
     int* tflag = nullptr;        // per tile: bit lap set = integer fast path valid in that lap (k_fold_agg)
     int* glist = nullptr;        // tiles listed for k_ancestors_general, ngen[0] of them
     int* ngen = nullptr;
+    // finalize (k_fin_a / k_fin_b)
+    long long* gmax = nullptr;   // ordered-integer key of the max log-weight (atomicMax by the
+                                 //   producer of the tile partials), reset by k_fin_b
+    int* ticket = nullptr;       // [2] CTAs done in k_fin_a / k_fin_b
+    int* hcnt = nullptr;         // [2] hard tiles staged per lap
+    int* skipmin = nullptr;      // first tile skipped in lap 1
+    double* fsc = nullptr;       // [8] scalars between the two finalize kernels
+    double *csum = nullptr, *coff = nullptr;   // per chunk of 1024 tiles: sum, exclusive offset
+    int* hst[2] = {};            // staged hard tiles (unsorted) and their table context
+    int* hea[2] = {};
     double* shin[2] = {};        // exact running sum entering / leaving each hard tile
     double* shout[2] = {};
     Xd* hpa[2] = {};             // [HCAP][TILE] per-element inclusive prefix transducers, context eA
@@ -177,6 +187,7 @@ struct ResampleWS {
     ResampleInfo* info = nullptr;      // device
     ResampleInfo* info_host = nullptr; // pinned
     double* edges = nullptr;           // multinomial only, lazily allocated
+    double* wbuf = nullptr;            // [n] weights exp(lw - m), written by k_fold_agg
 };
 
 } // namespace apop
@@ -299,6 +310,15 @@ void fabric_free(apop_ctx* c);
 } // namespace apop
 #include "fastmath.cuh"
 namespace apop {
+
+// ordered-integer key of a double (no NaN): integer max == floating-point max
+__device__ __forceinline__ long long dkey(double x) {
+    const long long b = __double_as_longlong(x);
+    return b >= 0 ? b : (b ^ 0x7fffffffffffffffLL);
+}
+__device__ __forceinline__ double dkey_inv(long long k) {
+    return __longlong_as_double(k >= 0 ? k : (k ^ 0x7fffffffffffffffLL));
+}
 
 __device__ __forceinline__ double weight_from_lw(double lw, double m) {
     // smc.cljc:78-82

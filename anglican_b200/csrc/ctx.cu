@@ -146,8 +146,7 @@ int apop_create(apop_ctx** out, int64_t n_local, uint64_t seed, int device, int 
     c->n_global = n_local * world;
     c->g0 = n_local * rank;
     c->seed = seed;
-    // the engine stream takes the greatest priority so that helper work on
-    // low-priority side streams (noise prefetch, ssm.cu) only fills idle SMs
+    // the engine stream takes the greatest priority
     int prio_lo = 0, prio_hi = 0;
     cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi);
     if (cudaStreamCreateWithPriority(&c->stream, cudaStreamNonBlocking, prio_hi) != cudaSuccess) {
@@ -199,6 +198,7 @@ int apop_destroy(apop_ctx* c) {
     ResampleWS& w = c->ws;
     if (w.slab) cudaFree(w.slab);
     if (w.edges) cudaFree(w.edges);
+    if (w.wbuf) cudaFree(w.wbuf);
     if (w.info_host) cudaFreeHost(w.info_host);
     if (c->scratch) cudaFree(c->scratch);
     for (auto& t : c->timers) {

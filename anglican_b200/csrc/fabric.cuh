@@ -11,9 +11,10 @@
 //     array of the rank that owns the output slot (the particle migration of
 //     SURVEY §8(e) never materialises as a separate all-to-all);
 //   * k_propagate reads the parent state through the owner's heap pointer;
-//   * the scalars of the per-step exchange (local max / weight sum, the exact
-//     running sum that chains the sequential fold of smc.cljc:94,118-137 from
-//     rank to rank, the total) travel through a small mailbox with
+//   * the scalars of the per-step exchange (local max / weight sum, each shard's
+//     contribution to the sequential fold of smc.cljc:94,118-137 -- a composable
+//     transducer where the shard stays in one binade, its exact output where it
+//     does not -- and the accurate sums) travel through a small mailbox with
 //     release/acquire flags at system scope.
 // NCCL is used only to bootstrap (exchange of the IPC handles) and for the
 // IPMCMC log-Z allgather.
@@ -32,9 +33,9 @@ struct MailSlot {
 struct Mailbox {
     MailSlot fin[2][kMaxWorld];   // per source rank: (local max, local sum rel. local max, err bits)
     MailSlot acc[2][kMaxWorld];   // per source rank: accurate (sum w, sum w^2, sum w x)
-    MailSlot s0[2];               // exact running sum entering this rank, first lap
-    MailSlot tot[2];              // exact total (from the last rank)
-    MailSlot s1[2];               // exact running sum entering this rank, second lap
+    MailSlot comp[2][2][kMaxWorld];   // [parity][lap][source rank]: the shard's part of the exact
+                                      //   fold (CK_EASY: transducer + binade, CK_EXACT: running
+                                      //   sum leaving the shard), see k_chain
     unsigned long long bar[kMaxWorld];
     unsigned long long pad[8];
 };
@@ -80,6 +81,21 @@ __device__ __forceinline__ bool spin_until(const unsigned long long* flag, unsig
         __nanosleep(64);
     }
     return true;
+}
+// raw 64-bit payloads (integer transducers travel bit for bit)
+__device__ __forceinline__ void mail_send_bits(MailSlot* s, long long a, long long b, long long c,
+                                               unsigned long long seq) {
+    volatile long long* v = reinterpret_cast<volatile long long*>(s->v);
+    v[0] = a; v[1] = b; v[2] = c;
+    __threadfence_system();
+    st_release_sys(&s->seq, seq);
+}
+__device__ __forceinline__ bool mail_wait_bits(MailSlot* s, unsigned long long seq,
+                                               long long (&out)[3]) {
+    const bool ok = spin_until(&s->seq, seq);
+    volatile long long* v = reinterpret_cast<volatile long long*>(s->v);
+    out[0] = v[0]; out[1] = v[1]; out[2] = v[2];
+    return ok;
 }
 __device__ __forceinline__ bool mail_wait(MailSlot* s, unsigned long long seq, double (&out)[3]) {
     const bool ok = spin_until(&s->seq, seq);

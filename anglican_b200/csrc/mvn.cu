@@ -116,7 +116,7 @@ __global__ void __launch_bounds__(512, 1) k_propagate_mvn(MvnSweepArgs a) {
         for (int j = 0; j < D / 8; ++j) { acc[j][0] = 0.0; acc[j][1] = 0.0; }
         warp_gemm_8xD<D, LD, false>(T, sA, acc);                       // A x
         __syncwarp();
-        // ---- noise: component c of particles (2q, 2q+1) share one Box-Muller pair
+        // ---- noise: component c of particles (2q, 2q+1) share one Philox block
         //      (normal_at, rng.cuh); 4 pairs x D components per warp
         for (int i = lane; i < 4 * D; i += 32) {
             const int q = i / D, cidx = i - q * D;

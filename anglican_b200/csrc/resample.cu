@@ -285,6 +285,7 @@ __global__ void __launch_bounds__(TB) k_tile_lse(const double* __restrict__ lw,
         double a = 0, b = 0;
         for (int i = 0; i < NWARP; ++i) { a += red[i]; b += red2[i]; }
         v.tmax[blockIdx.x] = mx; v.tsum[blockIdx.x] = a; (void)b;
+        atomicMax(v.gmax, dkey(mx));
     }
 }
 
@@ -344,49 +345,55 @@ __device__ __forceinline__ double block_sum_f64(double v, double* sm /*[33]*/) {
     return r;
 }
 
-// single CTA; every global access is coalesced (tiles are walked striped)
-__global__ void __launch_bounds__(FB) k_finalize(WSView v, int64_t n, int64_t n_new, double u_in,
-                                                 uint64_t seed, uint32_t step, int weights_mode,
-                                                 double rel_eps, Fabric F, unsigned long long seq,
-                                                 int64_t g0, int64_t n_global) {
-    __shared__ double buf[FB * FCH];
+// Finalize, in two launches of ceil(nt / FB) CTAs (one tile per thread).  The global
+// max arrives as an ordered-integer atomicMax from the kernel that produced the tile
+// partials (k_propagate / k_tile_lse), so nothing here walks the tile arrays serially:
+//   k_fin_a  rescale the tile sums to the max, per-chunk sums; the LAST CTA to finish
+//            turns them into chunk offsets (exclusive prefix), runs the sharded
+//            exchange and writes the scalars;
+//   k_fin_b  approximate exclusive prefix ain[t], classification of every tile for
+//            both laps, hard tiles appended to a staging list; the LAST CTA ranks
+//            the list (hard tiles are rare) and resets the counters.
+// fsc[]: 0 gfac (local max -> global max), 1 atot, 2 upper bound of the last pointer
+__global__ void __launch_bounds__(FB) k_fin_a(WSView v, int64_t n, int64_t n_new, double u_in,
+                                              uint64_t seed, uint32_t step, int weights_mode,
+                                              double rel_eps, Fabric F, unsigned long long seq,
+                                              int64_t n_global) {
     __shared__ double smd[33];
-    __shared__ int sh_skip;
+    __shared__ int s_last;
     __shared__ double pm[kMaxWorld], ps[kMaxWorld];
     __shared__ int perr[kMaxWorld];
     const int64_t nt = v.nt;
-    const int tid = threadIdx.x;
-
-    // ---- global max (smc.cljc:75)
-    double m = 0.0;
-    if (!weights_mode) {
-        double mx = -INFINITY;
-        for (int64_t t = tid; t < nt; t += FB) mx = fmax(mx, v.tmax[t]);
-        mx = warp_max(mx);
-        if ((tid & 31) == 0) smd[tid >> 5] = mx;
-        __syncthreads();
-        double a = smd[0];
-        for (int i = 1; i < FB / 32; ++i) a = fmax(a, smd[i]);
-        m = a;
-        __syncthreads();
-    }
-    // ---- rescale the tile partials to the (local) max (in place)
-    if (!weights_mode) {
-        for (int64_t t = tid; t < nt; t += FB) {
+    const int tid = threadIdx.x, G = gridDim.x;
+    const int64_t t = (int64_t)blockIdx.x * FB + tid;
+    // ---- global max (smc.cljc:75) and tile sums relative to it
+    double m = weights_mode ? 0.0 : dkey_inv(v.gmax[0]);
+    double val = 0.0;
+    if (t < nt) {
+        val = v.tsum[t];
+        if (!weights_mode) {
             const double tm = v.tmax[t];
-            const double fac = (tm == m) ? 1.0 : fm::exp_any(tm - m);
-            v.tsum[t] = v.tsum[t] * fac;
+            val *= (tm == m) ? 1.0 : fm::exp_any(tm - m);
+            v.tsum[t] = val;
         }
     }
-    // ---- sharded: exchange (local max, local sum, error bits) with every peer
-    //      through the mailboxes; afterwards m is the global max, `offset` the
-    //      approximate weight of all lower ranks and gtot the global total.
+    const double cs = block_sum_f64(val, smd);
+    if (tid == 0) {
+        v.csum[blockIdx.x] = cs;
+        __threadfence();
+        s_last = (atomicAdd(v.ticket, 1) == G - 1);
+    }
+    __syncthreads();
+    if (!s_last) return;
+    __threadfence();
+    // ---- tail, one CTA: chunk offsets and scalars (G <= FB: nt < 2^31 / TILE)
+    const double cv = (tid < G) ? __ldcg(v.csum + tid) : 0.0;
     double gfac = 1.0, offset = 0.0, gtot = 0.0;
     if (F.world > 1) {
-        double ls = 0.0;
-        for (int64_t t = tid; t < nt; t += FB) ls += v.tsum[t];
-        __syncthreads();
-        const double lsum = block_sum_f64(ls, smd);
+        // exchange (local max, local sum, error bits) with every peer through the
+        // mailboxes; afterwards m is the global max, `offset` the approximate weight
+        // of all lower ranks and gtot the global total
+        const double lsum = block_sum_f64(cv, smd);
         const int par = (int)(seq & 1);
         if (tid < F.world) {
             mail_send(&F.mbox[tid]->fin[par][F.rank], m, lsum, (double)v.info->err, seq);
@@ -411,117 +418,21 @@ __global__ void __launch_bounds__(FB) k_finalize(WSView v, int64_t n, int64_t n_
         if (tid == 0 && gerr) atomicOr(&v.info->err, gerr);
         __syncthreads();
     }
-    // ---- approximate exclusive prefix of tile sums: ain[t]
-    double carry = offset;
-    for (int64_t base = 0; base < nt; base += FB * FCH) {
-#pragma unroll
-        for (int k = 0; k < FCH; ++k) {
-            const int64_t idx = base + k * FB + tid;
-            buf[k * FB + tid] = (idx < nt) ? v.tsum[idx] * gfac : 0.0;
-        }
-        __syncthreads();
-        double a[FCH], loc = 0.0;
-#pragma unroll
-        for (int k = 0; k < FCH; ++k) { a[k] = buf[tid * FCH + k]; loc += a[k]; }
-        double chunk_total;
-        double run = carry + block_excl_scan_f64(loc, smd, chunk_total);
-#pragma unroll
-        for (int k = 0; k < FCH; ++k) { buf[tid * FCH + k] = run; run += a[k]; }
-        __syncthreads();
-#pragma unroll
-        for (int k = 0; k < FCH; ++k) {
-            const int64_t idx = base + k * FB + tid;
-            if (idx < nt) v.ain[idx] = buf[k * FB + tid];
-        }
-        carry += chunk_total;
-        __syncthreads();
-    }
-    const double atot = (F.world > 1) ? gtot : carry;
-    if (tid == 0) { v.ain[nt] = carry; sh_skip = (nt < INT_MAX) ? (int)nt : INT_MAX; v.ngen[0] = 0; }
-    __syncthreads();
-
-    const double u = (u_in != u_in) ? uniform_at(seed, 0, step, STREAM_RESAMPLE, 0) : u_in;
-    // x_last < x_0 + total <= total*(u+1): generous upper bound for the skip test
-    // (the comb is n_new repeated additions: its rounding error grows with n_new, not n)
-    const double eps_tot = ((double)(2 * n_global) + (double)n_new + 8192.0) * 4.44089209850062616e-16 + rel_eps;
-    const double xlast_ub = atot * (u + 1.0) * (1.0 + 4.0 * eps_tot);
-
-    // ---- classification of every tile for both laps (coalesced, tiles striped
-    //      over the threads).  Hard tiles are rare: they are collected in shared
-    //      memory and rank-sorted afterwards; if they overflow the buffer the
-    //      lists are rebuilt by the slow contiguous walk below.
-    constexpr int HB = FB * FCH;                   // ints per lap in the staging buffer
-    int* hbuf = reinterpret_cast<int*>(buf);       // buf is free again: [2][HB]
-    __shared__ int hcnt[2];
-    if (tid < 2) hcnt[tid] = 0;
-    __syncthreads();
-    for (int64_t t = tid; t < nt; t += FB) {
-        const int64_t hi = ((t + 1) * TILE < n) ? (t + 1) * TILE : n;
-        const double a_in = v.ain[t], ao = v.ain[t + 1];
-        const int c0 = classify_tile(a_in, ao, g0 + hi, rel_eps);
-        v.cls[0][t] = c0;
-        int c1;
-        const double eps1 = ((double)(n_global + g0 + hi) + 4096.0) * 4.44089209850062616e-16 + rel_eps;
-        if ((atot + a_in) * (1.0 - eps1) > xlast_ub) {
-            c1 = kCtxSkip;
-            atomicMin(&sh_skip, (int)t);
-        } else {
-            c1 = classify_tile(atot + a_in, atot + ao, n_global + g0 + hi, rel_eps);
-        }
-        v.cls[1][t] = c1;
-        v.hix[0][t] = -1;
-        v.hix[1][t] = -1;
-        if (c0 == kCtxHard) { const int k = atomicAdd(&hcnt[0], 1); if (k < HB) hbuf[k] = (int)t; }
-        if (c1 == kCtxHard) { const int k = atomicAdd(&hcnt[1], 1); if (k < HB) hbuf[HB + k] = (int)t; }
-    }
-    __syncthreads();
-    const int skip1 = sh_skip;
-    const int h0tot = hcnt[0], h1tot = hcnt[1];
-    auto emit_hard = [&](int lap, int rank, int64_t t) {
-        const int64_t hi = ((t + 1) * TILE < n) ? (t + 1) * TILE : n;
-        const double a_in = v.ain[t], ao = v.ain[t + 1];
-        int ea, eb;
-        if (lap == 0) classify_tile2(a_in, ao, g0 + hi, rel_eps, &ea, &eb);
-        else classify_tile2(atot + a_in, atot + ao, n_global + g0 + hi, rel_eps, &ea, &eb);
-        // tiles at or beyond the first skipped tile are never folded in lap 1
-        const bool usable = (lap == 0 || t < skip1) && ea != kCtxHard && eb == ea + 1 &&
-                            ea > -1000 && ea < 900;
-        v.hl[lap][rank] = (int)t;
-        v.hctx[lap][rank] = usable ? ea : kCtxHard;
-        v.hix[lap][t] = rank;
-    };
-    if (h0tot <= HB && h1tot <= HB) {
-#pragma unroll 1
-        for (int lap = 0; lap < 2; ++lap) {
-            const int cnt = lap ? h1tot : h0tot;
-            const int* list = hbuf + lap * HB;
-            for (int i = tid; i < cnt; i += FB) {
-                const int t = list[i];
-                int rank = 0;
-                for (int k = 0; k < cnt; ++k) rank += (list[k] < t);
-                emit_hard(lap, rank, t);
-            }
-        }
-    } else {
-        // overflow: contiguous walk, each thread owns a range of tiles
-        const int64_t per = (nt + FB - 1) / FB;
-        const int64_t tb = (int64_t)tid * per;
-        const int64_t te = (tb + per < nt) ? tb + per : nt;
-        int nh0 = 0, nh1 = 0;
-        for (int64_t t = tb; t < te; ++t) {
-            nh0 += (v.cls[0][t] == kCtxHard);
-            nh1 += (v.cls[1][t] == kCtxHard);
-        }
-        double d0, d1;
-        __syncthreads();
-        int o0 = (int)block_excl_scan_f64((double)nh0, smd, d0);
-        int o1 = (int)block_excl_scan_f64((double)nh1, smd, d1);
-        for (int64_t t = tb; t < te; ++t) {
-            if (v.cls[0][t] == kCtxHard) emit_hard(0, o0++, t);
-            if (v.cls[1][t] == kCtxHard) emit_hard(1, o1++, t);
-        }
-    }
+    double ctot;
+    const double ex = offset + block_excl_scan_f64(cv * gfac, smd, ctot);
+    if (tid < G) v.coff[tid] = ex;
     if (tid == 0) {
+        const double carry = offset + ctot;
+        const double atot = (F.world > 1) ? gtot : carry;
+        v.coff[G] = carry;
+        v.ain[nt] = carry;
+        const double u = (u_in != u_in) ? uniform_at(seed, 0, step, STREAM_RESAMPLE, 0) : u_in;
+        // x_last < x_0 + total <= total*(u+1): generous upper bound for the skip test
+        // (the comb is n_new repeated additions: its rounding error grows with n_new, not n)
+        const double eps_tot = ((double)(2 * n_global) + (double)n_new + 8192.0) * 4.44089209850062616e-16 + rel_eps;
+        v.fsc[0] = gfac;
+        v.fsc[1] = atot;
+        v.fsc[2] = atot * (u + 1.0) * (1.0 + 4.0 * eps_tot);
         ResampleInfo* I = v.info;
         I->m = m;
         I->atot = atot;
@@ -531,11 +442,134 @@ __global__ void __launch_bounds__(FB) k_finalize(WSView v, int64_t n, int64_t n_
                                                                : -INFINITY;
         I->u = u;
         I->n_new = n_new;
+        I->weights_mode = weights_mode;
+        if (!weights_mode && m != m) I->err |= EB_NAN;
+        v.ngen[0] = 0;
+        v.ticket[0] = 0;
+        v.hcnt[0] = 0; v.hcnt[1] = 0;
+        v.skipmin[0] = (nt < INT_MAX) ? (int)nt : INT_MAX;
+    }
+}
+
+constexpr int HB = 4096;                   // staged hard tiles per lap
+
+__global__ void __launch_bounds__(FB) k_fin_b(WSView v, int64_t n, double rel_eps, int64_t g0,
+                                              int64_t n_global) {
+    __shared__ double smd[33];
+    __shared__ double sA[FB + 1];
+    __shared__ int s_last;
+    const int64_t nt = v.nt;
+    const int tid = threadIdx.x, G = gridDim.x;
+    const int64_t t = (int64_t)blockIdx.x * FB + tid;
+    const double gfac = v.fsc[0], atot = v.fsc[1], xlast_ub = v.fsc[2];
+    // ---- approximate exclusive prefix of the tile sums.  Exclusive values come from
+    // the scan itself, never as "inclusive - own" (one dominant value would cancel the
+    // prefix and break the relative error bound classify_tile relies on).
+    const double val = (t < nt) ? v.tsum[t] * gfac : 0.0;
+    double ctot;
+    const double a_in = v.coff[blockIdx.x] + block_excl_scan_f64(val, smd, ctot);
+    sA[tid] = a_in;
+    if (tid == 0) sA[FB] = v.coff[blockIdx.x + 1];
+    __syncthreads();
+    if (t < nt) {
+        const double ao = (t + 1 == nt) ? v.coff[G] : sA[tid + 1];
+        v.ain[t] = a_in;
+        const int64_t hi = ((t + 1) * TILE < n) ? (t + 1) * TILE : n;
+        int ea0, eb0, ea1 = kCtxHard, eb1 = kCtxHard;
+        const int c0 = classify_tile2(a_in, ao, g0 + hi, rel_eps, &ea0, &eb0);
+        v.cls[0][t] = c0;
+        int c1;
+        const double eps1 = ((double)(n_global + g0 + hi) + 4096.0) * 4.44089209850062616e-16 + rel_eps;
+        if ((atot + a_in) * (1.0 - eps1) > xlast_ub) {
+            c1 = kCtxSkip;
+            atomicMin(v.skipmin, (int)t);
+        } else {
+            c1 = classify_tile2(atot + a_in, atot + ao, n_global + g0 + hi, rel_eps, &ea1, &eb1);
+        }
+        v.cls[1][t] = c1;
+        v.hix[0][t] = -1;
+        v.hix[1][t] = -1;
+        // a hard tile whose bounds span exactly two binades gets prefix / suffix tables
+        if (c0 == kCtxHard) {
+            const int k = atomicAdd(&v.hcnt[0], 1);
+            if (k < HB) {
+                v.hst[0][k] = (int)t;
+                v.hea[0][k] = (ea0 != kCtxHard && eb0 == ea0 + 1 && ea0 > -1000 && ea0 < 900) ? ea0 : kCtxHard;
+            }
+        }
+        if (c1 == kCtxHard) {
+            const int k = atomicAdd(&v.hcnt[1], 1);
+            if (k < HB) {
+                v.hst[1][k] = (int)t;
+                v.hea[1][k] = (ea1 != kCtxHard && eb1 == ea1 + 1 && ea1 > -1000 && ea1 < 900) ? ea1 : kCtxHard;
+            }
+        }
+    }
+    __syncthreads();
+    if (tid == 0) {
+        __threadfence();
+        s_last = (atomicAdd(v.ticket + 1, 1) == G - 1);
+    }
+    __syncthreads();
+    if (!s_last) return;
+    __threadfence();
+    // ---- tail, one CTA: the sorted hard lists
+    const int skip1 = __ldcg(v.skipmin);
+    const int h0tot = __ldcg(v.hcnt), h1tot = __ldcg(v.hcnt + 1);
+    if (h0tot <= HB && h1tot <= HB) {
+#pragma unroll 1
+        for (int lap = 0; lap < 2; ++lap) {
+            const int cnt = lap ? h1tot : h0tot;
+            const int* list = v.hst[lap];
+            for (int i = tid; i < cnt; i += FB) {
+                const int tt = __ldcg(list + i);
+                int rank = 0;
+                for (int k = 0; k < cnt; ++k) rank += (__ldcg(list + k) < tt);
+                // tiles at or beyond the first skipped tile are never folded in lap 1
+                const bool usable = (lap == 0 || tt < skip1);
+                v.hl[lap][rank] = tt;
+                v.hctx[lap][rank] = usable ? __ldcg(v.hea[lap] + i) : kCtxHard;
+                v.hix[lap][tt] = rank;
+            }
+        }
+    } else {
+        // overflow (pathological weights): contiguous walk, each thread owns a range of tiles
+        auto emit_hard = [&](int lap, int rank, int64_t tt) {
+            const int64_t hi = ((tt + 1) * TILE < n) ? (tt + 1) * TILE : n;
+            const double ai = __ldcg(v.ain + tt), ao = __ldcg(v.ain + tt + 1);
+            int ea, eb;
+            if (lap == 0) classify_tile2(ai, ao, g0 + hi, rel_eps, &ea, &eb);
+            else classify_tile2(atot + ai, atot + ao, n_global + g0 + hi, rel_eps, &ea, &eb);
+            const bool usable = (lap == 0 || tt < skip1) && ea != kCtxHard && eb == ea + 1 &&
+                                ea > -1000 && ea < 900;
+            v.hl[lap][rank] = (int)tt;
+            v.hctx[lap][rank] = usable ? ea : kCtxHard;
+            v.hix[lap][tt] = rank;
+        };
+        const int64_t per = (nt + FB - 1) / FB;
+        const int64_t tb = (int64_t)tid * per;
+        const int64_t te = (tb + per < nt) ? tb + per : nt;
+        int nh0 = 0, nh1 = 0;
+        for (int64_t tt = tb; tt < te; ++tt) {
+            nh0 += (__ldcg(v.cls[0] + tt) == kCtxHard);
+            nh1 += (__ldcg(v.cls[1] + tt) == kCtxHard);
+        }
+        double d0, d1;
+        __syncthreads();
+        int o0 = (int)block_excl_scan_f64((double)nh0, smd, d0);
+        int o1 = (int)block_excl_scan_f64((double)nh1, smd, d1);
+        for (int64_t tt = tb; tt < te; ++tt) {
+            if (__ldcg(v.cls[0] + tt) == kCtxHard) emit_hard(0, o0++, tt);
+            if (__ldcg(v.cls[1] + tt) == kCtxHard) emit_hard(1, o1++, tt);
+        }
+    }
+    if (tid == 0) {
+        ResampleInfo* I = v.info;
         I->nh0 = h0tot;
         I->nh1 = h1tot;
         I->first_skip1 = skip1;
-        I->weights_mode = weights_mode;
-        if (!weights_mode && m != m) I->err |= EB_NAN;
+        v.ticket[1] = 0;
+        v.gmax[0] = dkey(-INFINITY);        // for the next producer of tile partials
     }
 }
 
@@ -594,9 +628,14 @@ __device__ __noinline__ void hard_tile_prework(const double* __restrict__ lw,
     hard_tile_tables(w, eA, pa, sb, hw, warp_tot);
 }
 
+// wout (log-weight mode): the weights exp(lw - m) are written out once, so that the
+// chain, the emission kernels and the multinomial edges read them back instead of
+// evaluating the exponential a second time (8 more bytes per particle; these
+// kernels are bound by instruction issue, not by HBM).
 __global__ void __launch_bounds__(TB, APOP_FOLD_CTAS) k_fold_agg(const double* __restrict__ lw,
                                                     const double* __restrict__ win, int64_t n,
-                                                    WSView v, const double* __restrict__ xf) {
+                                                    WSView v, const double* __restrict__ xf,
+                                                    double* __restrict__ wout) {
     __shared__ Xd warp_tot[NWARP];
     __shared__ i64 ws0[NWARP], ws1[NWARP];
     __shared__ double wa[NWARP], wb[NWARP];
@@ -612,6 +651,18 @@ __global__ void __launch_bounds__(TB, APOP_FOLD_CTAS) k_fold_agg(const double* _
     const bool do0 = (c0 != kCtxHard), do1 = (c1 != kCtxHard && c1 != kCtxSkip);
     double w[IPT];
     weights_from_raw(win != nullptr, raw, base, n, m_glob, w);
+    if (wout) {
+        const int64_t i0 = base + (int64_t)threadIdx.x * IPT;
+        if (i0 + IPT <= n) {
+            double2* q = reinterpret_cast<double2*>(wout + i0);      // cudaMalloc'ed: 16-byte aligned
+#pragma unroll
+            for (int j = 0; j < IPT / 2; ++j) q[j] = make_double2(w[2 * j], w[2 * j + 1]);
+        } else {
+#pragma unroll
+            for (int j = 0; j < IPT; ++j)
+                if (i0 + j < n) wout[i0 + j] = w[j];
+        }
+    }
     // accurate sum w, sum w^2 of the tile (ESS, log-mean-weight)
     double s = 0.0, s2 = 0.0;
 #pragma unroll
@@ -1036,6 +1087,43 @@ __device__ __forceinline__ double tile_sin(const WSView& v, int lap, int64_t t, 
     return from_units(s, c);
 }
 
+// ---- sharded fold: what one shard contributes to a lap of the sequential fold ----
+// While the running sum stays inside one binade a whole shard is ONE parity
+// transducer (exact_fold.cuh), and transducers compose: a shard without a
+// binade-crossing ("hard") tile publishes its composite right away, without knowing
+// the sum entering it (CK_EASY), and every rank applies the composites of the lower
+// ranks itself.  Only a shard that owns a crossing has to wait for its exact input;
+// it publishes the exact sum leaving it (CK_EXACT).  The fold of smc.cljc:94,118-137
+// crosses about log2(N) binades in all, nearly all of them in rank 0, so a lap
+// costs a handful of dependent hops instead of one per rank.
+enum { CK_EASY = 1, CK_EXACT = 2 };
+
+// all ranks receive this rank's part of lap `lap` (threads 0 .. world-1 send)
+__device__ __forceinline__ void comp_publish(const Fabric& F, int par, int lap, int kind,
+                                             long long a, long long b, int cls,
+                                             unsigned long long seq) {
+    if ((int)threadIdx.x < F.world)
+        mail_send_bits(&F.mbox[threadIdx.x]->comp[par][lap][F.rank], a, b,
+                       ((long long)kind << 32) | (long long)(unsigned)cls, seq);
+}
+// the running sum after the parts of ranks [q0, q1) have been applied to S, in rank
+// order (one thread)
+__device__ double comp_walk(const Fabric& F, int par, int lap, double S, int q0, int q1,
+                            unsigned long long seq, int* err, int* comm) {
+    for (int q = q0; q < q1; ++q) {
+        long long o[3];
+        if (!mail_wait_bits(&F.mbox[F.rank]->comp[par][lap][q], seq, o)) { *comm = 1; return S; }
+        const int kind = (int)(o[2] >> 32), cls = (int)(unsigned)(o[2] & 0xffffffffLL);
+        if (kind == CK_EXACT) {
+            S = __longlong_as_double(o[0]);
+        } else {
+            Xd x; x.a0 = o[0]; x.a1 = o[1];
+            S = apply_run(S, x, cls, err);
+        }
+    }
+    return S;
+}
+
 __global__ void __launch_bounds__(TB) k_chain(const double* __restrict__ lw,
                                                 const double* __restrict__ win, int64_t n,
                                                 int64_t n_total, WSView v, StepOut so, Fabric F,
@@ -1045,39 +1133,48 @@ __global__ void __launch_bounds__(TB) k_chain(const double* __restrict__ lw,
     __shared__ double sh_in;
     __shared__ double pa[kMaxWorld], pb[kMaxWorld], px[kMaxWorld];
     __shared__ int sh_comm;
+    __shared__ Xd sh_x;
     const int64_t nt = v.nt;
     ResampleInfo* I = v.info;
     const double m = I->m;
     const bool sharded = F.world > 1;
-    const bool last_rank = F.rank == F.world - 1;
     const int par = (int)(seq & 1);
     if (threadIdx.x == 0) sh_comm = 0;
     long long tg0 = 0, tg1 = 0, tg2 = 0;
     if (threadIdx.x == 0) tg0 = gtimer_ns();
-
-    // ---------------- lap 0: exact total (smc.cljc:94).  Sharded: the sequential
-    // fold runs through the ranks in order; the exact running sum entering this
-    // shard arrives from the previous rank.
-    double S0 = 0.0;
-    if (sharded && F.rank > 0) {
+    // composite of this rank's blocks [0, nbk) of lap `lap` (no hard tile among them)
+    auto shard_composite = [&](int lap, int nbk) {
         if (threadIdx.x == 0) {
-            double o[3];
-            if (!mail_wait(&F.mbox[F.rank]->s0[par], seq, o)) sh_comm = 1;
-            sh_in = o[0];
+            Xd x = xd_identity();
+            for (int b = 0; b < nbk; ++b) x = xd_compose(x, v.bc[lap][b]);
+            sh_x = x;
         }
+        __syncthreads();
+    };
+
+    // ---------------- lap 0: exact total (smc.cljc:94)
+    double S0 = 0.0;
+    const bool easy0 = sharded && I->nh0 == 0;
+    if (sharded) {
+        if (easy0) {
+            shard_composite(0, v.nb);
+            comp_publish(F, par, 0, CK_EASY, sh_x.a0, sh_x.a1, v.cls[0][0], seq);
+        }
+        if (threadIdx.x == 0)
+            sh_in = comp_walk(F, par, 0, 0.0, 0, F.rank, seq, &I->err, &sh_comm);
         __syncthreads();
         S0 = sh_in;
     }
     bool reached;
     const double Send0 = chain_lap(v, 0, S0, nt, INFINITY, I->nh0, lw, win, n, m, sm, &I->err,
                                    &reached);
-    if (sharded && threadIdx.x == 0) {
-        if (!last_rank) {
-            mail_send(&F.mbox[F.rank + 1]->s0[par], Send0, 0.0, 0.0, seq);
-        } else {
-            for (int q = 0; q < F.world - 1; ++q)
-                mail_send(&F.mbox[q]->tot[par], Send0, 0.0, 0.0, seq);
-        }
+    double total = Send0;
+    if (sharded) {
+        if (!easy0) comp_publish(F, par, 0, CK_EXACT, __double_as_longlong(Send0), 0, 0, seq);
+        if (threadIdx.x == 0)
+            sh_in = comp_walk(F, par, 0, Send0, F.rank + 1, F.world, seq, &I->err, &sh_comm);
+        __syncthreads();
+        total = sh_in;
     }
     if (threadIdx.x == 0) tg1 = gtimer_ns();
     // accurate sum w / sum w^2 (ESS = (sum w)^2 / sum w^2, dist_test.cljc:83-94)
@@ -1086,7 +1183,6 @@ __global__ void __launch_bounds__(TB) k_chain(const double* __restrict__ lw,
     double acc = block_sum_f64(la, smd);
     double acc2 = block_sum_f64(lb, smd);
     double accx = block_sum_f64(lx, smd);
-    double total = Send0;
     if (sharded) {
         if (threadIdx.x < F.world) {
             const int q = threadIdx.x;
@@ -1095,15 +1191,9 @@ __global__ void __launch_bounds__(TB) k_chain(const double* __restrict__ lw,
             if (!mail_wait(&F.mbox[F.rank]->acc[par][q], seq, o)) sh_comm = 1;
             pa[q] = o[0]; pb[q] = o[1]; px[q] = o[2];
         }
-        if (threadIdx.x == 0 && !last_rank) {
-            double o[3];
-            if (!mail_wait(&F.mbox[F.rank]->tot[par], seq, o)) sh_comm = 1;
-            sh_in = o[0];
-        }
         __syncthreads();
         acc = 0.0; acc2 = 0.0; accx = 0.0;
         for (int q = 0; q < F.world; ++q) { acc += pa[q]; acc2 += pb[q]; accx += px[q]; }
-        if (!last_rank) total = sh_in;
         __syncthreads();
     }
     if (threadIdx.x == 0) {
@@ -1146,32 +1236,38 @@ __global__ void __launch_bounds__(TB) k_chain(const double* __restrict__ lw,
         for (int i = threadIdx.x; i <= v.nb; i += TB) v.sblk[1][i] = INFINITY;
         for (int i = threadIdx.x; i < I->nh1; i += TB) { v.shin[1][i] = INFINITY; v.shout[1][i] = INFINITY; }
         if (threadIdx.x == 0) v.send[1] = INFINITY;
-        // keep the chain moving so that no peer waits for this rank
-        if (sharded && !last_rank && threadIdx.x == 0)
-            mail_send(&F.mbox[F.rank + 1]->s1[par], INFINITY, 0.0, 0.0, seq);
+        // keep the fold moving so that no peer waits for this rank
+        if (sharded) comp_publish(F, par, 1, CK_EXACT, __double_as_longlong(INFINITY), 0, 0, seq);
         return;
     }
     const double xlast = v.comb->xlast;
 
-    // ---------------- lap 1: the wheel wraps with acc NOT reset (smc.cljc:133-136)
+    // ---------------- lap 1: the wheel wraps with acc NOT reset (smc.cljc:133-136).
+    // The lap ends at the first tile that no pointer can reach (first_skip1): a shard
+    // that is folded completely and owns no crossing is one transducer again, a shard
+    // that is skipped completely is the identity.
+    int64_t stop = I->first_skip1;
+    if (stop > nt) stop = nt;
     double S1 = total;
-    if (sharded && F.rank > 0) {
+    const bool easy1 = sharded && ((stop == nt && I->nh1 == 0) || stop == 0);
+    if (sharded) {
+        if (easy1) {
+            shard_composite(1, stop == 0 ? 0 : v.nb);
+            comp_publish(F, par, 1, CK_EASY, sh_x.a0, sh_x.a1, stop == 0 ? 0 : v.cls[1][0], seq);
+        }
         if (threadIdx.x == 0) {
-            double o[3];
-            if (!mail_wait(&F.mbox[F.rank]->s1[par], seq, o)) {
+            int comm = 0;
+            sh_in = comp_walk(F, par, 1, total, 0, F.rank, seq, &I->err, &comm);
+            if (comm) {
                 atomicOr(&I->err, EB_COMM);
                 if (so.sd) so.sd->err |= EB_COMM;
             }
-            sh_in = o[0];
         }
         __syncthreads();
         S1 = sh_in;
     }
-    int64_t stop = I->first_skip1;
-    if (stop > nt) stop = nt;
     const double S = chain_lap(v, 1, S1, stop, xlast, I->nh1, lw, win, n, m, sm, &I->err, &reached);
-    if (sharded && !last_rank && threadIdx.x == 0)
-        mail_send(&F.mbox[F.rank + 1]->s1[par], S, 0.0, 0.0, seq);
+    if (sharded && !easy1) comp_publish(F, par, 1, CK_EXACT, __double_as_longlong(S), 0, 0, seq);
     // the walk may only end at a skipped tile if no pointer of the second lap lies beyond
     if (reached && stop < nt && !(S > xlast) && threadIdx.x == 0) {
         atomicOr(&I->err, EB_CTX | 0x800);
@@ -1180,7 +1276,7 @@ __global__ void __launch_bounds__(TB) k_chain(const double* __restrict__ lw,
     if (threadIdx.x == 0) v.send[1] = S;
     if (threadIdx.x == 0) {          // phase durations in ns (apop_debug_resolve_phases)
         const long long tg3 = gtimer_ns();
-        I->wx_sum[0] = (double)(tg1 - tg0);      // lap 0 (incl. waiting for the previous rank)
+        I->wx_sum[0] = (double)(tg1 - tg0);      // lap 0 (incl. waiting for the lower ranks)
         I->wx_sum[1] = (double)(tg2 - tg1);      // sums, exchange, comb table
         I->wx_sum[2] = (double)(tg3 - tg2);      // lap 1
         I->wx_sum[3] = (double)v.comb->nseg;
@@ -1761,9 +1857,8 @@ __device__ __forceinline__ void scan_store(StageSmem& st, int a0, int tot, int32
     }
 }
 
-__device__ __forceinline__ void ancestors_fast(const TileRec& R, const double (&raw)[IPT], bool is_w,
-                                               int64_t base, int64_t n, int32_t val_tile0,
-                                               StageSmem& st, int* err) {
+__device__ __forceinline__ void ancestors_fast(const TileRec& R, const double (&w)[IPT],
+                                               int32_t val_tile0, StageSmem& st, int* err) {
     const int tid = threadIdx.x;
     const int W = (int)(R.wm & 0x0fffffffu);
     // the window is shifted by a0 = (destination address / 4) mod 4 inside the staging
@@ -1775,8 +1870,6 @@ __device__ __forceinline__ void ancestors_fast(const TileRec& R, const double (&
         *reinterpret_cast<int4*>(&st.buf[e]) = make_int4(0, 0, 0, 0);
     double inc[IPT], loc = 0.0;
     {
-        double w[IPT];
-        weights_from_raw(is_w, raw, base, n, R.m, w);
         const double inv_u = R.inv_u;
 #pragma unroll
         for (int j = 0; j < IPT; ++j) {
@@ -1832,16 +1925,16 @@ __global__ void __launch_bounds__(TB) k_ancestors_general(const double* __restri
     }
 }
 
-__global__ void __launch_bounds__(TB, APOP_ANC_CTAS) k_ancestors(const double* __restrict__ lw,
-                                                     const double* __restrict__ win, int64_t n,
-                                                     int64_t g0, const TileRec* __restrict__ rec,
-                                                     int* err) {
+// w: the weights themselves (the caller's, or the ones k_fold_agg wrote out)
+__global__ void __launch_bounds__(TB, APOP_ANC_CTAS) k_ancestors(const double* __restrict__ w,
+                                                     int64_t n, int64_t g0,
+                                                     const TileRec* __restrict__ rec, int* err) {
     __shared__ StageSmem sm;
     const int t = blockIdx.x;
     const int64_t base = (int64_t)t * TILE;
     // the tile and its record: all global reads of the streaming path, issued up front
     double raw[IPT];
-    load_raw(lw, win, base, n, raw);
+    load_blocked(w, base, n, raw, 0.0);
     TileRec R;
     {
         const int4* rp = reinterpret_cast<const int4*>(rec + t);
@@ -1850,7 +1943,7 @@ __global__ void __launch_bounds__(TB, APOP_ANC_CTAS) k_ancestors(const double* _
         for (int k = 0; k < 4; ++k) rq[k] = __ldg(rp + k);
     }
     if ((R.wm >> 28) != TM_FAST) return;           // nothing to emit, or listed for the general kernel
-    ancestors_fast(R, raw, win != nullptr, base, n, (int32_t)(g0 + base), sm, err);
+    ancestors_fast(R, raw, (int32_t)(g0 + base), sm, err);
 }
 
 // Deferred emission (see RunRec): every warp takes run records in turn; the
@@ -1953,7 +2046,9 @@ __global__ void k_multinomial_search(const double* __restrict__ edges, int64_t n
     }
 }
 
-__global__ void k_info_reset(ResampleInfo* I) {
+__global__ void k_info_reset(ResampleInfo* I, WSView v) {
+    v.gmax[0] = dkey(-INFINITY);
+    v.ticket[0] = 0; v.ticket[1] = 0;
     I->err = 0;
     I->J = 0;
     I->total = 0;
@@ -1965,7 +2060,8 @@ __global__ void k_info_reset(ResampleInfo* I) {
 void preload_resample_kernels() {
     cudaFuncAttributes a;
     cudaFuncGetAttributes(&a, k_tile_lse);
-    cudaFuncGetAttributes(&a, k_finalize);
+    cudaFuncGetAttributes(&a, k_fin_a);
+    cudaFuncGetAttributes(&a, k_fin_b);
     cudaFuncGetAttributes(&a, k_fold_agg);
     cudaFuncGetAttributes(&a, k_seg_scan);
     cudaFuncGetAttributes(&a, k_chain);
@@ -1999,6 +2095,10 @@ int ensure_resample_ws(apop_ctx* c) {
         w.tacc = (double*)carve(nd * 8); w.tacc2 = (double*)carve(nd * 8);
         w.rec = (TileRec*)carve(nd * sizeof(TileRec)); w.tflag = (int*)carve(nd * 4);
         w.glist = (int*)carve(nd * 4); w.ngen = (int*)carve(4);
+        w.gmax = (long long*)carve(8); w.ticket = (int*)carve(8); w.hcnt = (int*)carve(8);
+        w.skipmin = (int*)carve(4); w.fsc = (double*)carve(8 * 8);
+        w.csum = (double*)carve((nd / 1024 + 2) * 8); w.coff = (double*)carve((nd / 1024 + 3) * 8);
+        for (int l = 0; l < 2; ++l) { w.hst[l] = (int*)carve(4096 * 4); w.hea[l] = (int*)carve(4096 * 4); }
         for (int l = 0; l < 2; ++l) {
             w.cls[l] = (int*)carve(nd * 4); w.agg[l] = (Xd*)carve(nd * sizeof(Xd));
             w.ex[l] = (Xd*)carve(nd * sizeof(Xd)); w.hix[l] = (int*)carve(nd * 4);
@@ -2045,7 +2145,14 @@ int ensure_resample_ws(apop_ctx* c) {
             w.info = info;
         }
     }
+    if (cudaMalloc(&w.wbuf, ((size_t)c->n + 8) * 8) != cudaSuccess) {
+        w.wbuf = nullptr;
+        w.info = nullptr;
+        return set_err(c, APOP_ERR_OOM, "resample workspace: weight column of %zu bytes",
+                       ((size_t)c->n + 8) * 8);
+    }
     APOP_CUDA(c, cudaMemsetAsync(w.info, 0, sizeof(ResampleInfo), c->stream));
+    k_info_reset<<<1, 1, 0, c->stream>>>(w.info, view_of(w));      // max cell, tickets
     APOP_CUDA(c, cudaMallocHost(&w.info_host, sizeof(ResampleInfo)));
     return APOP_OK;
 }
@@ -2060,7 +2167,7 @@ int resample_enqueue(apop_ctx* c, const ResampleArgs& a) {
     const int nt = (int)v.nt;
     const int wm = a.w ? 1 : 0;
     if (!a.have_partials) {
-        if (!a.keep_err) k_info_reset<<<1, 1, 0, c->stream>>>(v.info);
+        if (!a.keep_err) k_info_reset<<<1, 1, 0, c->stream>>>(v.info, v);
         kt_begin(c, KT_TILE_LSE);
         k_tile_lse<<<nt, TB, 0, c->stream>>>(a.lw, a.w, a.n, v);
         kt_end(c, KT_TILE_LSE);
@@ -2072,23 +2179,28 @@ int resample_enqueue(apop_ctx* c, const ResampleArgs& a) {
     const int64_t n_glob = a.sharded ? c->n_global : a.n;
     const unsigned long long seq = a.sharded ? ++c->fab.epoch : 0ULL;
     kt_begin(c, KT_FINALIZE);
-    k_finalize<<<1, FB, 0, c->stream>>>(v, a.n, a.n_new, a.u, c->seed, c->step, wm, a.rel_eps, F,
-                                        seq, g0, n_glob);
+    const int fg = (int)((v.nt + FB - 1) / FB);
+    k_fin_a<<<fg, FB, 0, c->stream>>>(v, a.n, a.n_new, a.u, c->seed, c->step, wm, a.rel_eps, F, seq,
+                                      n_glob);
+    k_fin_b<<<fg, FB, 0, c->stream>>>(v, a.n, a.rel_eps, g0, n_glob);
     kt_end(c, KT_FINALIZE);
+    // from here on every kernel reads weights: the caller's, or exp(lw - m) as
+    // written out by k_fold_agg
+    const double* wsrc = a.w ? a.w : c->ws.wbuf;
     kt_begin(c, KT_FOLD_AGG);
-    k_fold_agg<<<nt, TB, 0, c->stream>>>(a.lw, a.w, a.n, v, a.xfilt);
+    k_fold_agg<<<nt, TB, 0, c->stream>>>(a.lw, a.w, a.n, v, a.xfilt, a.w ? nullptr : c->ws.wbuf);
     kt_end(c, KT_FOLD_AGG);
     kt_begin(c, KT_RESOLVE);
     k_seg_scan<<<c->ws.nb, SEGB, 0, c->stream>>>(v, a.xfilt ? 1 : 0);
-    k_chain<<<1, TB, 0, c->stream>>>(a.lw, a.w, a.n, n_glob, v, a.step, F, seq);
+    k_chain<<<1, TB, 0, c->stream>>>(nullptr, wsrc, a.n, n_glob, v, a.step, F, seq);
     k_expand<<<(int)((v.nt + 1 + XB - 2) / (XB - 1)), XB, 0, c->stream>>>(
         v, a.order, a.anc_out, a.out_offset, a.anc_peer, F.world, a.n);
     kt_end(c, KT_RESOLVE);
-    c->launches += 5;
+    c->launches += 6;
     if (a.anc_out) {
         kt_begin(c, KT_ANCESTORS);
-        k_ancestors<<<nt, TB, 0, c->stream>>>(a.lw, a.w, a.n, g0, v.rec, &v.info->err);
-        k_ancestors_general<<<c->sm_count, TB, 0, c->stream>>>(a.lw, a.w, a.n, g0, v, a.order,
+        k_ancestors<<<nt, TB, 0, c->stream>>>(wsrc, a.n, g0, v.rec, &v.info->err);
+        k_ancestors_general<<<c->sm_count, TB, 0, c->stream>>>(nullptr, wsrc, a.n, g0, v, a.order,
                                                                a.anc_out, a.out_offset, a.anc_peer,
                                                                F.world);
         k_fill_runs<<<c->sm_count * 4, FILL_TB, 0, c->stream>>>(v, a.order, a.anc_out, a.out_offset, a.n,
@@ -2132,7 +2244,7 @@ int multinomial_enqueue(apop_ctx* c, const double* lw, const double* w, const do
     a.anc_out = nullptr; a.out_offset = 0; a.have_partials = false;
     APOP_TRY(resample_enqueue(c, a));
     WSView v = view_of(c->ws);
-    k_edges<<<(int)v.nt, TB, 0, c->stream>>>(lw, w, c->n, v, c->ws.edges);
+    k_edges<<<(int)v.nt, TB, 0, c->stream>>>(nullptr, w ? w : c->ws.wbuf, c->n, v, c->ws.edges);
     int blocks = (int)((n_new + 255) / 256);
     if (blocks > c->sm_count * 16) blocks = c->sm_count * 16;
     k_multinomial_search<<<blocks, 256, 0, c->stream>>>(c->ws.edges, c->n, uni, c->seed, c->step,

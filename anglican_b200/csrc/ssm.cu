@@ -67,16 +67,6 @@ struct SweepState {
     size_t cap_n = 0, cap_T = 0, cap_hist = 0;
     const double* last_x = nullptr;    // pre-resample states of the last step
     const int32_t* last_anc = nullptr;
-    // transition-noise prefetch: the draws of step t+1 do not depend on step t, so
-    // a low-priority side stream generates them for the first z_tiles tiles while
-    // the single-CTA kernels of the resampler (k_finalize, k_chain) leave the
-    // other SMs idle; k_propagate then reads them instead of running Philox +
-    // Box-Muller.  Same device function, same bits.
-    cudaStream_t side = nullptr;
-    cudaEvent_t ev_prop[2] = {nullptr, nullptr}, ev_noise[2] = {nullptr, nullptr};
-    double* zbuf[2] = {nullptr, nullptr};
-    size_t z_cap = 0;                  // particles per buffer
-    int64_t z_tiles = 0;               // tiles prefetched per step of this sweep (0: off)
 };
 
 namespace apop {
@@ -85,14 +75,9 @@ void sweep_free(apop_ctx* c) {
     SweepState* s = c->sweep;
     if (!s) return;
     if (s->heap_backed) { s->xa = nullptr; s->xb = nullptr; s->anc = nullptr; }
-    if (s->side) { cudaStreamSynchronize(s->side); cudaStreamDestroy(s->side); }
-    for (int i = 0; i < 2; ++i) {
-        if (s->ev_prop[i]) cudaEventDestroy(s->ev_prop[i]);
-        if (s->ev_noise[i]) cudaEventDestroy(s->ev_noise[i]);
-    }
     void* ptrs[] = {s->xa, s->xb, s->lw, s->anc, s->x_hist, s->anc_hist, s->y, s->retained,
                     s->log_mean_w, s->ess, s->filt, s->tsx, s->x_final, s->sd, s->model, s->traj,
-                    s->mvn_mats, s->zbuf[0], s->zbuf[1], s->lse, s->as_anc};
+                    s->mvn_mats, s->lse, s->as_anc};
     for (void* p : ptrs)
         if (p) cudaFree(p);
     delete s;
@@ -144,7 +129,7 @@ __global__ void __launch_bounds__(TB) k_init(const ModelDev* __restrict__ Mp, do
         v1 = discrete_draw(M.hmm_init, M.dim, uniform_at(seed, (uint64_t)(g0 + k0 + 1), 0, STREAM_INIT, 0));
     } else {
         double z0, z1;
-        normal_pair_at(seed, (uint64_t)(g0 + k0) >> 1, 0, STREAM_INIT, 0, z0, z1);
+        normal_pair_at(seed, (uint64_t)(g0 + k0) >> 1, 0, STREAM_INIT, 0, z0, z1);   // global table
         v0 = M.m0 + M.s0 * z0;
         v1 = M.m0 + M.s0 * z1;
     }
@@ -172,8 +157,9 @@ __device__ __forceinline__ void propagate_tile(const PeerF64& xpeer,
                                                double y, const double* __restrict__ retained_t,
                                                double wbase, int64_t n, int64_t g0, uint64_t seed,
                                                uint32_t t, double* __restrict__ tmax,
-                                               double* __restrict__ tsum, int* errflag,
-                                               const double* __restrict__ zpre, int accum,
+                                               double* __restrict__ tsum, long long* gmax,
+                                               int* errflag,
+                                               const double* __restrict__ s_tab, int accum,
                                                bool aligned) {
     __shared__ double red_mx[NWARP];
     __shared__ float red_ref[NWARP], red_s[NWARP];
@@ -244,16 +230,7 @@ __device__ __forceinline__ void propagate_tile(const PeerF64& xpeer,
             }
         } else {
             double z0[HW / 2], z1[HW / 2];
-            if (FULL && zpre) {
-                // this tile's draws were generated ahead of time by k_noise
-#pragma unroll
-                for (int j = 0; j < HW / 2; ++j) {
-                    const double2 za = __ldg(reinterpret_cast<const double2*>(zpre + ih + 2 * j));
-                    z0[j] = za.x; z1[j] = za.y;
-                }
-            } else {
-                normal_pairs_at<HW / 2>(seed, (uint64_t)(g0 + ih) >> 1, t, STREAM_TRANSITION, 0, z0, z1);
-            }
+            normal_pairs_at<HW / 2>(s_tab, seed, (uint64_t)(g0 + ih) >> 1, t, STREAM_TRANSITION, 0, z0, z1);
 #pragma unroll
             for (int j = 0; j < HW; j += 2) {
                 x[j] = (M.a * x[j] + M.b) + M.q * z0[j >> 1];              // sd*z + mean
@@ -359,7 +336,10 @@ __device__ __forceinline__ void propagate_tile(const PeerF64& xpeer,
         a = warp_sum(a);
         // all log-weights -inf: every weight is 1 (smc.cljc:80)
         if (!(m > -INFINITY)) a = (double)((n - base < TILE) ? (n - base) : TILE);
-        if (lane == 0) { tmax[blockIdx.x] = m; tsum[blockIdx.x] = a; }
+        if (lane == 0) {
+            tmax[blockIdx.x] = m; tsum[blockIdx.x] = a;
+            atomicMax(gmax, dkey(m));                 // global max for k_fin_a (smc.cljc:75)
+        }
     }
 }
 
@@ -373,44 +353,32 @@ __global__ void __launch_bounds__(TB, APOP_PROP_CTAS) k_propagate(const ModelDev
                                                   const SweepDev* __restrict__ sd, int64_t n,
                                                   int64_t g0, uint64_t seed, uint32_t t,
                                                   double* __restrict__ tmax,
-                                                  double* __restrict__ tsum, int* errflag,
+                                                  double* __restrict__ tsum, long long* gmax,
+                                                  int* errflag,
                                                   const __grid_constant__ PeerF64 xpeer,
-                                                  const double* __restrict__ zpre, int z_tiles,
                                                   int accum) {
+    // inverse-normal-CDF table of the transition draws (rng.cuh), staged per CTA
+    __shared__ __align__(16) double s_tab[(KIND == APOP_SSM_HMM) ? 2 : NT_ROWS * NT_STRIDE];
+    if (KIND != APOP_SSM_HMM) normal_table_to_smem(s_tab);
     const ModelDev& M = *Mp;
     const double y = yt[0];
     const double wbase = sd->base;
-    const double* zp = ((int)blockIdx.x < z_tiles) ? zpre : nullptr;     // CTA-uniform
+    if (KIND != APOP_SSM_HMM) __syncthreads();
     // rows of a lineage history start at multiples of n elements: 16-byte aligned
     // only when n is a multiple of 4 (ancestors) / 2 (states)
     const bool aligned = (((uintptr_t)anc | (uintptr_t)xn | (uintptr_t)lw) & 15) == 0;
     if ((int64_t)(blockIdx.x + 1) * TILE <= n && aligned)
         propagate_tile<KIND, true, SHARD>(xpeer, M, xp, anc, first_step, xn, lw, y, retained_t,
-                                          wbase, n, g0, seed, t, tmax, tsum, errflag, zp, accum, true);
+                                          wbase, n, g0, seed, t, tmax, tsum, gmax, errflag, s_tab, accum, true);
     else
         propagate_tile<KIND, false, SHARD>(xpeer, M, xp, anc, first_step, xn, lw, y, retained_t,
-                                           wbase, n, g0, seed, t, tmax, tsum, errflag, nullptr, accum,
+                                           wbase, n, g0, seed, t, tmax, tsum, gmax, errflag, s_tab, accum,
                                            aligned);
 }
 
-// transition noise of step t for the full tiles [0, gridDim.x): exactly the
-// draws propagate_tile would make (same counters, same Box-Muller code)
-__global__ void __launch_bounds__(TB) k_noise(double* __restrict__ z, int64_t g0, uint64_t seed,
-                                              uint32_t t) {
-    const int64_t i0 = (int64_t)blockIdx.x * TILE + (int64_t)threadIdx.x * IPT;
-#pragma unroll
-    for (int h = 0; h < IPT; h += 4) {
-        const int64_t ih = i0 + h;
-        double z0[2], z1[2];
-        normal_pairs_at<2>(seed, (uint64_t)(g0 + ih) >> 1, t, STREAM_TRANSITION, 0, z0, z1);
-        double2* q = reinterpret_cast<double2*>(z + ih);
-        q[0] = make_double2(z0[0], z1[0]);
-        q[1] = make_double2(z0[1], z1[1]);
-    }
-}
-
-__global__ void k_sweep_reset(SweepDev* sd, ResampleInfo* I) {
+__global__ void k_sweep_reset(SweepDev* sd, ResampleInfo* I, long long* gmax, int* ticket) {
     sd->base = 0.0; sd->log_z = 0.0; sd->err = 0;
+    gmax[0] = dkey(-INFINITY); ticket[0] = 0; ticket[1] = 0;
     I->err = 0;
 }
 
@@ -554,48 +522,6 @@ static int sweep_prepare(apop_ctx* c, int T, int dim, bool history) {
     return APOP_OK;
 }
 
-// Noise prefetch set-up (host-blocking calls: staging phase only).
-// APOP_NOISE_PREFETCH_TILES = tiles per step (default 0 = off).  Measured on one
-// B200 at 2^27 particles (profiles/r01h_noise_prefetch.txt): the extra 16 B per
-// prefetched particle cost more than the idle SM time recovers (k_propagate is
-// already at ~60 % of HBM), so it is off by default.
-static int noise_prepare(apop_ctx* c, int kind, bool history) {
-    SweepState* s = c->sweep;
-    s->z_tiles = 0;
-    if (kind != APOP_SSM_LGSSM1D && kind != APOP_SSM_SV) return APOP_OK;
-    const int64_t full_tiles = c->n / TILE;
-    int64_t want = 0;
-    if (const char* e = getenv("APOP_NOISE_PREFETCH_TILES")) want = atoll(e);
-    if (want > full_tiles) want = full_tiles;
-    if (want <= 0) return APOP_OK;
-    (void)history;
-    if (!s->side) {
-        int lo = 0, hi = 0;
-        cudaDeviceGetStreamPriorityRange(&lo, &hi);          // lo: least priority
-        if (cudaStreamCreateWithPriority(&s->side, cudaStreamNonBlocking, lo) != cudaSuccess)
-            return set_err(c, APOP_ERR_CUDA, "sweep: side stream");
-        for (int i = 0; i < 2; ++i) {
-            if (cudaEventCreateWithFlags(&s->ev_prop[i], cudaEventDisableTiming) != cudaSuccess ||
-                cudaEventCreateWithFlags(&s->ev_noise[i], cudaEventDisableTiming) != cudaSuccess)
-                return set_err(c, APOP_ERR_CUDA, "sweep: events");
-        }
-    }
-    const size_t need = (size_t)want * TILE;
-    if (s->z_cap < need) {
-        cudaStreamSynchronize(s->side);
-        for (int i = 0; i < 2; ++i) {
-            if (s->zbuf[i]) cudaFree(s->zbuf[i]);
-            s->zbuf[i] = nullptr;
-        }
-        s->z_cap = 0;
-        APOP_TRY(dev_alloc(c, (void**)&s->zbuf[0], need * 8));
-        APOP_TRY(dev_alloc(c, (void**)&s->zbuf[1], need * 8));
-        s->z_cap = need;
-    }
-    s->z_tiles = want;
-    return APOP_OK;
-}
-
 static int upload_model(apop_ctx* c, const apop_ssm* m) {
     ModelDev h;
     memset(&h, 0, sizeof h);
@@ -698,7 +624,7 @@ static int sweep_begin(apop_ctx* c, const double* retained, const apop_sweep_opt
             tm.open = true;
         }
     }
-    k_sweep_reset<<<1, 1, 0, c->stream>>>(s->sd, ws.info);
+    k_sweep_reset<<<1, 1, 0, c->stream>>>(s->sd, ws.info, ws.gmax, ws.ticket);
     // sharded: peers may still be reading this rank's buffers (final gather of
     // the previous sweep)
     APOP_TRY(fabric_barrier_enqueue(c));
@@ -714,10 +640,6 @@ static int sweep_begin(apop_ctx* c, const double* retained, const apop_sweep_opt
     c->launches += 2;
     s->last_x = x0;
     s->last_anc = s->anc;
-    if (s->z_tiles > 0) {
-        // the noise buffers may still be read by the previous sweep's last steps
-        for (int i = 0; i < 2; ++i) APOP_CUDA(c, cudaEventRecord(s->ev_prop[i], c->stream));
-    }
     return APOP_OK;
 }
 
@@ -733,10 +655,6 @@ static int sweep_step(apop_ctx* c, int t, const apop_sweep_opts* o, bool csmc) {
     const size_t dim = (size_t)s->dim;
     double* x_new = s->history ? s->x_hist + (size_t)t * n * dim : ((t & 1) ? s->xb : s->xa);
     int32_t* anc_new = s->history ? s->anc_hist + (size_t)(t - 1) * n : s->anc;
-    constexpr bool kGauss = (KIND == APOP_SSM_LGSSM1D || KIND == APOP_SSM_SV);
-    const int zt = (kGauss && t >= 2) ? (int)s->z_tiles : 0;      // step 1 draws inline
-    const double* zpre = zt ? s->zbuf[t & 1] : nullptr;
-    if (zt) APOP_CUDA(c, cudaStreamWaitEvent(c->stream, s->ev_noise[t & 1], 0));
     kt_begin(c, KT_PROPAGATE);
     if (KIND == APOP_SSM_LGMVN) {
         MvnSweepArgs ma;
@@ -756,30 +674,17 @@ static int sweep_step(apop_ctx* c, int t, const apop_sweep_opts* o, bool csmc) {
         const PeerF64 xpeer = peer_f64(c, (t & 1) ? c->fab.off_xa : c->fab.off_xb);   // x_{t-1}
         k_propagate<(KIND == APOP_SSM_LGMVN) ? APOP_SSM_LGSSM1D : KIND, true><<<nt, TB, 0, c->stream>>>(
             s->model, x_prev, anc_prev, t == 1, x_new, s->lw, s->y + (t - 1), nullptr, s->sd, n,
-            c->g0, c->seed, (uint32_t)t, ws.tmax, ws.tsum, &ws.info->err, xpeer, zpre, zt, 0);
+            c->g0, c->seed, (uint32_t)t, ws.tmax, ws.tsum, ws.gmax, &ws.info->err, xpeer, 0);
     } else {
         PeerF64 none;
         memset(&none, 0, sizeof none);
         k_propagate<(KIND == APOP_SSM_LGMVN) ? APOP_SSM_LGSSM1D : KIND, false><<<nt, TB, 0, c->stream>>>(
             s->model, x_prev, anc_prev, t == 1 || o->no_resample, x_new, s->lw, s->y + (t - 1),
             csmc ? s->retained + t : nullptr, s->sd, n, c->g0, c->seed, (uint32_t)t, ws.tmax,
-            ws.tsum, &ws.info->err, none, zpre, zt, (o->no_resample && t > 1) ? 1 : 0);
+            ws.tsum, ws.gmax, &ws.info->err, none, (o->no_resample && t > 1) ? 1 : 0);
     }
     kt_end(c, KT_PROPAGATE);
     c->launches += 1;
-    if (kGauss && s->z_tiles > 0) {
-        // propagate(t) has been enqueued: Z[t&1] is busy until it completes.  The
-        // draws of step t+1 go to the other buffer, last read by propagate(t-1).
-        APOP_CUDA(c, cudaEventRecord(s->ev_prop[t & 1], c->stream));
-        if (t < s->T) {
-            const int nb = (t + 1) & 1;
-            APOP_CUDA(c, cudaStreamWaitEvent(s->side, s->ev_prop[nb], 0));
-            k_noise<<<(int)s->z_tiles, TB, 0, s->side>>>(s->zbuf[nb], c->g0, c->seed,
-                                                         (uint32_t)(t + 1));
-            APOP_CUDA(c, cudaEventRecord(s->ev_noise[nb], s->side));
-            c->launches += 1;
-        }
-    }
     if (o->no_resample) {          // importance.cljc:16-22: weights accumulate per particle
         c->step = (uint32_t)t;
         s->last_x = x_new;
@@ -957,7 +862,7 @@ static void preload_sweep_kernels() {
     preload(k_init<APOP_SSM_LGSSM1D>); preload(k_init<APOP_SSM_SV>); preload(k_init<APOP_SSM_HMM>);
     preload(k_propagate<APOP_SSM_LGSSM1D, true>); preload(k_propagate<APOP_SSM_SV, true>);
     preload(k_propagate<APOP_SSM_HMM, true>);
-    preload(k_sweep_reset); preload(k_gather_shard); preload(k_noise);
+    preload(k_sweep_reset); preload(k_gather_shard);
     preload_resample_kernels();
     preload_comm_kernels();
     cudaGetLastError();
@@ -994,7 +899,6 @@ static int sweep_group(apop_ctx* const* g, int ng, const apop_ssm* model, const 
         cudaSetDevice(c->device);
         if (c->world > 1) { preload_sweep_kernels(); if (dim > 1) mvn_preload_kernels(dim); }
         APOP_TRY(sweep_prepare(c, T, dim, opts->keep_history != 0));
-        APOP_TRY(noise_prepare(c, model->kind, opts->keep_history != 0));
         APOP_TRY(upload_model(c, model));
     }
     switch (model->kind) {

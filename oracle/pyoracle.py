@@ -70,6 +70,8 @@ def _declare(L):
     d, i64, i32, u64, u32 = C.c_double, C.c_int64, C.c_int32, C.c_uint64, C.c_uint32
     L.orc_philox4x32.argtypes = [u32] * 6 + [C.POINTER(u32)]
     L.orc_philox4x32.restype = None
+    L.orc_normal_from_bits.argtypes = [u32, u32]
+    L.orc_normal_from_bits.restype = d
     L.orc_normal_at.argtypes = [u64, u64, u32, u32, u32]
     L.orc_normal_at.restype = d
     L.orc_uniform_at.argtypes = [u64, u64, u32, u32, u32]
@@ -148,6 +150,11 @@ def philox(c, k):
     out = (C.c_uint32 * 4)()
     lib().orc_philox4x32(c[0], c[1], c[2], c[3], k[0], k[1], out)
     return [int(v) for v in out]
+
+
+def normal_from_bits(hi, lo):
+    """z = sign * Q(v) from 64 random bits (table-driven inverse normal CDF)"""
+    return lib().orc_normal_from_bits(int(hi) & 0xFFFFFFFF, int(lo) & 0xFFFFFFFF)
 
 
 def normal_at(seed, slot, t, stream, draw=0):

@@ -187,6 +187,28 @@ int host_classify_tile(double a_in, double a_out, int64_t idx_out) {
 int host_ctx_of(double S) { return ctx_of(S); }
 int host_ctx_hard() { return kCtxHard; }
 
+// ---- sharded fold (k_chain, csrc/resample.cu): a shard that stays in binade `e`
+// is one parity transducer; returns 0 and (a0, a1), or 1 if an element saturates
+int host_shard_composite(const double* w, int64_t n, int e, int64_t* a0, int64_t* a1) {
+    Xd t = xd_identity();
+    for (int64_t i = 0; i < n; ++i) {
+        i64 f; int up, tie;
+        quantize(w[i], e, f, up, tie);
+        xd_push(t, f, up, tie);
+    }
+    *a0 = t.a0; *a1 = t.a1;
+    return (t.a0 >= kSat || t.a1 >= kSat) ? 1 : 0;
+}
+// S' = S + transducer; *ok = 0 if S is not in binade `e` or the sum leaves it
+double host_apply_composite(double S, int64_t a0, int64_t a1, int e, int* ok) {
+    Xd t; t.a0 = a0; t.a1 = a1;
+    *ok = 1;
+    if ((a0 | a1) == 0) return S;
+    const i64 s = xd_apply(units_of(S), t);
+    if (s >= kTwo53 || ctx_of(S) != e) *ok = 0;
+    return from_units(s, ctx_of(S));
+}
+
 // exact comb values, for direct comparison with repeated addition
 void host_comb_values(double total, double u, int64_t n_new, double* out) {
     Comb comb;
