@@ -69,6 +69,7 @@ struct StepOut {
 
 struct Column {
     void* ptr = nullptr;
+    void* alt = nullptr;     // second buffer, allocated by the first gather (result swapped in)
     int dtype = 0;
     int width = 0;
     bool used = false;

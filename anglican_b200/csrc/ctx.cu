@@ -129,6 +129,12 @@ int apop_create(apop_ctx** out, int64_t n_local, uint64_t seed, int device, int 
                 const void* nccl_id) {
     if (!out || n_local <= 0 || world < 1 || rank < 0 || rank >= world) return APOP_ERR_INVALID;
     if (n_local >= (1LL << 31)) return APOP_ERR_INVALID;
+    // Every population owns a stream, and the kernels of a sharded population wait on
+    // peers: two populations whose streams share a hardware queue can block each other
+    // across ranks (A behind B on one rank, B behind A on the next).  Ask for one queue
+    // per stream (32 instead of the default 8); only effective if this call creates the
+    // CUDA context - a host that initialises CUDA first sets the variable itself.
+    setenv("CUDA_DEVICE_MAX_CONNECTIONS", "32", 0);
     int ndev = 0;
     if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev <= 0) return APOP_ERR_CUDA;
     if (device < 0 || device >= ndev) return APOP_ERR_INVALID;
@@ -194,7 +200,7 @@ int apop_destroy(apop_ctx* c) {
     fabric_free(c);
     comm_free(c);
     for (auto& col : c->cols)
-        if (col.used && col.ptr) cudaFree(col.ptr);
+        if (col.used && col.ptr) { cudaFree(col.ptr); if (col.alt) cudaFree(col.alt); }
     ResampleWS& w = c->ws;
     if (w.slab) cudaFree(w.slab);
     if (w.edges) cudaFree(w.edges);
@@ -346,6 +352,7 @@ int apop_column_free(apop_ctx* c, apop_col h) {
     if (!col) return APOP_ERR_INVALID;
     APOP_CUDA(c, cudaStreamSynchronize(c->stream));
     cudaFree(col->ptr);
+    if (col->alt) cudaFree(col->alt);
     *col = Column();
     return APOP_OK;
 }

@@ -1988,24 +1988,54 @@ __global__ void __launch_bounds__(FILL_TB) k_fill_runs(WSView v, int order, int3
 }
 
 // ------------------------------------------------------------------ K5
-__global__ void k_gather_f64(const double* __restrict__ src, double* __restrict__ dst,
-                             const int32_t* __restrict__ anc, int64_t n_new, int width) {
-    const int64_t total = n_new * (int64_t)width;
-    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total;
-         i += (int64_t)gridDim.x * blockDim.x) {
-        const int64_t k = i / width;
-        const int c = (int)(i - k * width);
-        dst[i] = src[(int64_t)anc[k] * width + c];
+// x_new[k] = x[anc[k]] (the per-offspring copy of smc.cljc:127-129).  Ancestors come
+// out of the resampler in runs (sorted order: monotone), so the reads are nearly
+// sequential.  width 1: four offspring per thread, one 128-bit index load, 128-bit
+// stores.  Rows (width > 1): 16-byte chunks, row index by shift when the chunk
+// count per row is a power of two.  The result goes to the column's second buffer
+// and the two are swapped (no copy-back).
+template <typename T>
+__global__ void __launch_bounds__(256) k_gather1(const T* __restrict__ src, T* __restrict__ dst,
+                                                 const int32_t* __restrict__ anc, int64_t n_new) {
+    const int64_t k0 = ((int64_t)blockIdx.x * 256 + threadIdx.x) * 4;
+    if (k0 >= n_new) return;
+    if (k0 + 4 <= n_new) {
+        const int4 a = __ldg(reinterpret_cast<const int4*>(anc + k0));
+        const T v0 = __ldg(src + a.x), v1 = __ldg(src + a.y), v2 = __ldg(src + a.z), v3 = __ldg(src + a.w);
+        if (sizeof(T) == 8) {
+            double2* q = reinterpret_cast<double2*>(dst + k0);
+            q[0] = make_double2((double)v0, (double)v1);
+            q[1] = make_double2((double)v2, (double)v3);
+        } else {
+            *reinterpret_cast<int4*>(dst + k0) = make_int4((int)v0, (int)v1, (int)v2, (int)v3);
+        }
+    } else {
+        for (int64_t k = k0; k < n_new; ++k) dst[k] = src[anc[k]];
     }
 }
-__global__ void k_gather_i32(const int32_t* __restrict__ src, int32_t* __restrict__ dst,
-                             const int32_t* __restrict__ anc, int64_t n_new, int width) {
+// rows of `chunks` 16-byte words (row bytes = 16 * chunks); shift >= 0: chunks == 1 << shift
+__global__ void __launch_bounds__(256) k_gather_rows16(const int4* __restrict__ src,
+                                                       int4* __restrict__ dst,
+                                                       const int32_t* __restrict__ anc,
+                                                       int64_t n_new, int chunks, int shift) {
+    const int64_t total = n_new * (int64_t)chunks;
+    for (int64_t i = (int64_t)blockIdx.x * 256 + threadIdx.x; i < total;
+         i += (int64_t)gridDim.x * 256) {
+        const int64_t k = (shift >= 0) ? (i >> shift) : (i / chunks);
+        const int c = (int)(i - k * chunks);
+        dst[i] = __ldg(src + (int64_t)__ldg(anc + k) * chunks + c);
+    }
+}
+// any width / element size (rows that are not a multiple of 16 bytes)
+template <typename T>
+__global__ void __launch_bounds__(256) k_gather_any(const T* __restrict__ src, T* __restrict__ dst,
+                                                    const int32_t* __restrict__ anc, int64_t n_new,
+                                                    int width) {
     const int64_t total = n_new * (int64_t)width;
-    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total;
-         i += (int64_t)gridDim.x * blockDim.x) {
+    for (int64_t i = (int64_t)blockIdx.x * 256 + threadIdx.x; i < total;
+         i += (int64_t)gridDim.x * 256) {
         const int64_t k = i / width;
-        const int c = (int)(i - k * width);
-        dst[i] = src[(int64_t)anc[k] * width + c];
+        dst[i] = src[(int64_t)anc[k] * width + (i - k * width)];
     }
 }
 
@@ -2256,23 +2286,52 @@ int multinomial_enqueue(apop_ctx* c, const double* lw, const double* w, const do
 
 int gather_enqueue(apop_ctx* c, const int32_t* anc, int64_t n_new, Column* col) {
     const size_t esz = col->dtype == APOP_F64 ? 8 : 4;
-    const size_t bytes = (size_t)c->n * col->width * esz;
-    APOP_TRY(ensure_scratch(c, bytes));
-    const int64_t total = n_new * col->width;
-    int blocks = (int)((total + 255) / 256);
-    if (blocks > c->sm_count * 32) blocks = c->sm_count * 32;
+    const size_t bytes = (size_t)(c->n + 1) * col->width * esz;
+    if (!col->alt) {
+        if (cudaMalloc(&col->alt, bytes) != cudaSuccess) {
+            col->alt = nullptr;
+            return set_err(c, APOP_ERR_OOM, "gather: second buffer of %zu bytes", bytes);
+        }
+    }
+    const size_t row = (size_t)col->width * esz;
     kt_begin(c, KT_GATHER);
-    if (col->dtype == APOP_F64)
-        k_gather_f64<<<blocks, 256, 0, c->stream>>>((const double*)col->ptr, (double*)c->scratch,
-                                                    anc, n_new, col->width);
-    else
-        k_gather_i32<<<blocks, 256, 0, c->stream>>>((const int32_t*)col->ptr,
-                                                    (int32_t*)c->scratch, anc, n_new, col->width);
+    if (col->width == 1) {
+        const int blocks = (int)((n_new + 1023) / 1024);
+        if (col->dtype == APOP_F64)
+            k_gather1<double><<<blocks, 256, 0, c->stream>>>((const double*)col->ptr, (double*)col->alt,
+                                                             anc, n_new);
+        else
+            k_gather1<int32_t><<<blocks, 256, 0, c->stream>>>((const int32_t*)col->ptr,
+                                                              (int32_t*)col->alt, anc, n_new);
+    } else if (row % 16 == 0) {
+        const int chunks = (int)(row / 16);
+        int shift = -1;
+        if ((chunks & (chunks - 1)) == 0) { shift = 0; while ((1 << shift) < chunks) ++shift; }
+        int64_t blocks = (n_new * chunks + 255) / 256;
+        if (blocks > (int64_t)c->sm_count * 32) blocks = (int64_t)c->sm_count * 32;
+        k_gather_rows16<<<(int)blocks, 256, 0, c->stream>>>((const int4*)col->ptr, (int4*)col->alt, anc,
+                                                            n_new, chunks, shift);
+    } else {
+        int64_t blocks = (n_new * col->width + 255) / 256;
+        if (blocks > (int64_t)c->sm_count * 32) blocks = (int64_t)c->sm_count * 32;
+        if (col->dtype == APOP_F64)
+            k_gather_any<double><<<(int)blocks, 256, 0, c->stream>>>(
+                (const double*)col->ptr, (double*)col->alt, anc, n_new, col->width);
+        else
+            k_gather_any<int32_t><<<(int)blocks, 256, 0, c->stream>>>(
+                (const int32_t*)col->ptr, (int32_t*)col->alt, anc, n_new, col->width);
+    }
     kt_end(c, KT_GATHER);
     c->launches += 1;
     APOP_CUDA(c, cudaGetLastError());
-    APOP_CUDA(c, cudaMemcpyAsync(col->ptr, c->scratch, (size_t)n_new * col->width * esz,
-                                 cudaMemcpyDeviceToDevice, c->stream));
+    // rows beyond n_new (CSMC gathers N-1 and re-inserts the retained particle) keep
+    // their old contents in the reference (they are overwritten by the caller): carry them
+    if ((size_t)n_new < (size_t)c->n + 1)
+        APOP_CUDA(c, cudaMemcpyAsync((char*)col->alt + (size_t)n_new * row,
+                                     (char*)col->ptr + (size_t)n_new * row,
+                                     ((size_t)c->n + 1 - (size_t)n_new) * row,
+                                     cudaMemcpyDeviceToDevice, c->stream));
+    void* t = col->ptr; col->ptr = col->alt; col->alt = t;
     return APOP_OK;
 }
 

@@ -52,6 +52,16 @@ struct SweepState {
     int32_t* anc = nullptr;
     double* x_hist = nullptr;      // [(T+1) * n * dim]
     int32_t* anc_hist = nullptr;   // [T * n]
+    // compact lineages (keep_history == 2): two bits per particle and step instead of 12
+    // bytes, states recomputed along the one traced lineage from the counter-based RNG
+    int hist_mode = 0;             // 0 none, 1 full history, 2 compact
+    uint32_t* lin_new = nullptr;   // [T][lin_w] bit j: output slot j >= 1 starts a new ancestor
+    uint32_t* lin_alive = nullptr; // [T][lin_w] bit i: particle i has offspring among slots >= 1
+    int32_t* lin_anc0 = nullptr;   // [T] ancestor of slot 0 (retained particle / PGAS draw)
+    int32_t* lin_idx = nullptr;    // [T+1] particle indices of the traced lineage
+    size_t lin_w = 0, cap_lin = 0;
+    uint64_t sweep_seed = 0;
+    int sweep_csmc = 0;
     double *y = nullptr, *retained = nullptr;
     double *log_mean_w = nullptr, *ess = nullptr, *filt = nullptr;   // device [T]
     double* tsx = nullptr;         // per-tile sum exp(lw - tmax) * x
@@ -77,7 +87,7 @@ void sweep_free(apop_ctx* c) {
     if (s->heap_backed) { s->xa = nullptr; s->xb = nullptr; s->anc = nullptr; }
     void* ptrs[] = {s->xa, s->xb, s->lw, s->anc, s->x_hist, s->anc_hist, s->y, s->retained,
                     s->log_mean_w, s->ess, s->filt, s->tsx, s->x_final, s->sd, s->model, s->traj,
-                    s->mvn_mats, s->lse, s->as_anc};
+                    s->mvn_mats, s->lse, s->as_anc, s->lin_new, s->lin_alive, s->lin_anc0, s->lin_idx};
     for (void* p : ptrs)
         if (p) cudaFree(p);
     delete s;
@@ -425,6 +435,146 @@ __global__ void k_trace(const int32_t* __restrict__ anc_hist, const double* __re
     for (int i = threadIdx.x; i < d; i += blockDim.x) traj[i] = x_hist[k * d + i];
 }
 
+// ---- compact lineages --------------------------------------------------------
+// The ancestors of one step come out of the resampler sorted (slots >= 1; slot 0 is
+// the retained particle of a conditional sweep, or a PGAS draw), so two bit-vectors
+// hold them: new[j] = slot j starts a new ancestor, alive[i] = particle i is an
+// ancestor.  anc[j] = select1(alive, rank1(new, j)).  n / 4 bytes per step instead of
+// 12 n (pgibbs.cljc:29-35 only ever follows ONE lineage per sweep).
+__global__ void __launch_bounds__(256) k_pack_lineage(const int32_t* __restrict__ anc, int64_t n,
+                                                      uint32_t* __restrict__ nw,
+                                                      uint32_t* __restrict__ al,
+                                                      int32_t* __restrict__ anc0) {
+    const int64_t j = (int64_t)blockIdx.x * 256 + threadIdx.x;
+    const int lane = threadIdx.x & 31;
+    const int a = (j < n) ? anc[j] : -1;
+    int ap = __shfl_up_sync(0xffffffffu, a, 1);
+    if (lane == 0) ap = (j > 0 && j < n) ? anc[j - 1] : -1;
+    const bool flag = (j >= 1 && j < n) && (j == 1 || a != ap);
+    const unsigned act = __ballot_sync(0xffffffffu, flag);
+    if (lane == 0 && j < n) nw[j >> 5] = act;
+    if (flag) {
+        const int word = a >> 5;
+        const unsigned peers = __match_any_sync(act, word);
+        const unsigned bits = __reduce_or_sync(peers, 1u << (a & 31));
+        if (lane == __ffs(peers) - 1) atomicOr(al + word, bits);
+    }
+    if (j == 0) anc0[0] = a;
+}
+
+__device__ __forceinline__ int block_sum_i32(int v, int* sm /*[33]*/) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    if ((threadIdx.x & 31) == 0) sm[threadIdx.x >> 5] = v;
+    __syncthreads();
+    int r = 0;
+    if (threadIdx.x < 32) {
+        r = (threadIdx.x < (blockDim.x >> 5)) ? sm[threadIdx.x] : 0;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) r += __shfl_xor_sync(0xffffffffu, r, o);
+        if (threadIdx.x == 0) sm[32] = r;
+    }
+    __syncthreads();
+    r = sm[32];
+    __syncthreads();
+    return r;
+}
+
+// one state of the traced lineage, recomputed exactly as k_init / k_propagate drew it
+template <int KIND>
+__device__ double lineage_state(const ModelDev& M, double xprev, uint64_t seed, uint64_t slot,
+                                uint32_t t) {
+    if (KIND == APOP_SSM_HMM) {
+        const double u = uniform_at(seed, slot, t, t ? STREAM_TRANSITION : STREAM_INIT, 0);
+        return (double)discrete_draw(t ? M.hmm_trans + (int)xprev * M.dim : M.hmm_init, M.dim, u);
+    }
+    const double z = normal_at(seed, slot, t, t ? STREAM_TRANSITION : STREAM_INIT, 0);
+    return t ? (M.a * xprev + M.b) + M.q * z : M.m0 + M.s0 * z;
+}
+
+// trace-back over the bit-vectors (one CTA), then the forward replay of the states
+constexpr int TRB = 1024;
+template <int KIND>
+__global__ void __launch_bounds__(TRB) k_trace_compact(const ModelDev* __restrict__ Mp,
+                                                       const uint32_t* __restrict__ nw,
+                                                       const uint32_t* __restrict__ al,
+                                                       const int32_t* __restrict__ anc0, int W,
+                                                       int T, int64_t slot, int64_t g0,
+                                                       uint64_t seed,
+                                                       const double* __restrict__ retained,
+                                                       int32_t* __restrict__ idx,
+                                                       double* __restrict__ traj) {
+    __shared__ int red[33];
+    __shared__ int s_pos, s_ex[TRB / 32];
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    int k = (int)slot;
+    const int chunk = (W + TRB - 1) / TRB;
+    for (int t = T; t >= 1; --t) {
+        const uint32_t* nwt = nw + (size_t)(t - 1) * W;
+        const uint32_t* alt = al + (size_t)(t - 1) * W;
+        int i;
+        if (k == 0) {
+            i = anc0[t - 1];
+        } else {
+            // r = number of distinct ancestors among slots 1 .. k
+            const int lastw = k >> 5;
+            int cnt = 0;
+            for (int w = tid; w <= lastw; w += TRB) {
+                uint32_t v = __ldg(nwt + w);
+                if (w == lastw && (k & 31) != 31) v &= (2u << (k & 31)) - 1u;
+                cnt += __popc(v);
+            }
+            const int r = block_sum_i32(cnt, red);
+            // position of the r-th set bit of alive
+            const int w0 = tid * chunk, w1 = min(w0 + chunk, W);
+            int c = 0;
+            for (int w = w0; w < w1; ++w) c += __popc(__ldg(alt + w));
+            int inc = c;
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) {
+                const int o = __shfl_up_sync(0xffffffffu, inc, d);
+                if (lane >= d) inc += o;
+            }
+            if (lane == 31) s_ex[wid] = inc;
+            if (tid == 0) s_pos = -1;
+            __syncthreads();
+            int pre = 0;
+            for (int q = 0; q < wid; ++q) pre += s_ex[q];
+            const int ex = pre + inc - c;
+            if (ex < r && r <= ex + c) {
+                int rem = r - ex;
+                for (int w = w0; w < w1; ++w) {
+                    uint32_t v = __ldg(alt + w);
+                    const int pc = __popc(v);
+                    if (rem <= pc) {
+                        for (int q = 1; q < rem; ++q) v &= v - 1;
+                        s_pos = w * 32 + __ffs(v) - 1;
+                        break;
+                    }
+                    rem -= pc;
+                }
+            }
+            __syncthreads();
+            i = s_pos;
+            __syncthreads();
+            if (i < 0) i = 0;            // inconsistent vectors: never index out of range
+        }
+        if (tid == 0) idx[t] = i;
+        k = i;
+    }
+    if (tid != 0) return;
+    const ModelDev& M = *Mp;
+    double x = (retained && g0 + k == 0) ? retained[0]
+                                         : lineage_state<KIND>(M, 0.0, seed, (uint64_t)(g0 + k), 0);
+    traj[0] = x;
+    for (int t = 1; t <= T; ++t) {
+        const int i = idx[t];
+        x = (retained && g0 + i == 0) ? retained[t]
+                                      : lineage_state<KIND>(M, x, seed, (uint64_t)(g0 + i), (uint32_t)t);
+        traj[t] = x;
+    }
+}
+
 __global__ void k_gather_rows(const double* __restrict__ src, double* __restrict__ dst,
                               const int32_t* __restrict__ anc, int64_t n, int d) {
     const int64_t total = n * (int64_t)d;
@@ -457,7 +607,8 @@ static int dev_alloc(apop_ctx* c, void** p, size_t bytes) {
     return APOP_OK;
 }
 
-static int sweep_prepare(apop_ctx* c, int T, int dim, bool history) {
+static int sweep_prepare(apop_ctx* c, int T, int dim, int hist_mode) {
+    const bool history = hist_mode == 1;
     SweepState* s = c->sweep;
     if (!s) { s = new SweepState(); c->sweep = s; }
     const size_t n = (size_t)c->n;
@@ -518,7 +669,22 @@ static int sweep_prepare(apop_ctx* c, int T, int dim, bool history) {
             s->cap_hist = need;
         }
     }
-    s->n = c->n; s->T = T; s->dim = dim; s->history = history;
+    if (hist_mode == 2) {
+        const size_t W = (((size_t)n + 31) / 32 + 3) & ~(size_t)3;
+        const size_t need = (size_t)T * W;
+        if (s->cap_lin < need) {
+            void* ptrs[] = {s->lin_new, s->lin_alive, s->lin_anc0, s->lin_idx};
+            for (void* p : ptrs) if (p) cudaFree(p);
+            s->lin_new = s->lin_alive = nullptr; s->lin_anc0 = s->lin_idx = nullptr; s->cap_lin = 0;
+            APOP_TRY(dev_alloc(c, (void**)&s->lin_new, need * 4));
+            APOP_TRY(dev_alloc(c, (void**)&s->lin_alive, need * 4));
+            APOP_TRY(dev_alloc(c, (void**)&s->lin_anc0, (size_t)(T + 1) * 4));
+            APOP_TRY(dev_alloc(c, (void**)&s->lin_idx, (size_t)(T + 2) * 4));
+            s->cap_lin = need;
+        }
+        s->lin_w = W;
+    }
+    s->n = c->n; s->T = T; s->dim = dim; s->history = history; s->hist_mode = hist_mode;
     return APOP_OK;
 }
 
@@ -625,6 +791,10 @@ static int sweep_begin(apop_ctx* c, const double* retained, const apop_sweep_opt
         }
     }
     k_sweep_reset<<<1, 1, 0, c->stream>>>(s->sd, ws.info, ws.gmax, ws.ticket);
+    s->sweep_seed = c->seed;
+    s->sweep_csmc = csmc ? 1 : 0;
+    if (s->hist_mode == 2)
+        APOP_CUDA(c, cudaMemsetAsync(s->lin_alive, 0, (size_t)s->T * s->lin_w * 4, c->stream));
     // sharded: peers may still be reading this rank's buffers (final gather of
     // the previous sweep)
     APOP_TRY(fabric_barrier_enqueue(c));
@@ -723,6 +893,12 @@ static int sweep_step(apop_ctx* c, int t, const apop_sweep_opts* o, bool csmc) {
         APOP_TRY(resample_enqueue(c, b));
         k_as_commit<<<1, 1, 0, c->stream>>>(anc_new, s->as_anc);
         c->launches += 2;
+    }
+    if (s->hist_mode == 2) {
+        k_pack_lineage<<<(int)((n + 255) / 256), 256, 0, c->stream>>>(
+            anc_new, n, s->lin_new + (size_t)(t - 1) * s->lin_w,
+            s->lin_alive + (size_t)(t - 1) * s->lin_w, s->lin_anc0 + (t - 1));
+        c->launches += 1;
     }
     // sharded: offspring indices were stored into peers' arrays and the next
     // propagate reads parents from peers' x_t: all ranks meet here
@@ -889,6 +1065,10 @@ static int sweep_group(apop_ctx* const* g, int ng, const apop_ssm* model, const 
             return set_err(c, APOP_ERR_UNSUPPORTED,
                            "ancestor sampling (pgas): conditional sweeps of scalar-state models "
                            "on one GPU");
+        if (opts->keep_history < 0 || opts->keep_history > 2 ||
+            (opts->keep_history == 2 && model->kind == APOP_SSM_LGMVN))
+            return set_err(c, APOP_ERR_UNSUPPORTED,
+                           "keep_history: 0 none, 1 full, 2 compact (scalar-state models)");
         if (c->world > 1 && (opts->csmc || opts->keep_history))
             return set_err(c, APOP_ERR_UNSUPPORTED,
                            "sharded sweep: conditional sweeps / lineages run one population "
@@ -898,7 +1078,8 @@ static int sweep_group(apop_ctx* const* g, int ng, const apop_ssm* model, const 
                                                 "multiple of 8");
         cudaSetDevice(c->device);
         if (c->world > 1) { preload_sweep_kernels(); if (dim > 1) mvn_preload_kernels(dim); }
-        APOP_TRY(sweep_prepare(c, T, dim, opts->keep_history != 0));
+        APOP_TRY(sweep_prepare(c, T, dim, opts->keep_history));
+        c->sweep->kind = model->kind;
         APOP_TRY(upload_model(c, model));
     }
     switch (model->kind) {
@@ -946,9 +1127,20 @@ int apop_smc_sweep_group(apop_ctx* const* ctxs, int32_t n_ctx, const apop_ssm* m
 int apop_trace_lineage(apop_ctx* c, int64_t slot, double* out_traj) {
     if (!c) return APOP_ERR_INVALID;
     SweepState* s = c->sweep;
-    if (!s || !s->history || !out_traj)
+    if (!s || !(s->history || s->hist_mode == 2) || !out_traj)
         return set_err(c, APOP_ERR_INVALID, "trace_lineage: no keep_history sweep available");
     if (slot < 0 || slot >= s->n) return set_err(c, APOP_ERR_INVALID, "trace_lineage: bad slot");
+    if (s->hist_mode == 2) {
+        const double* ret = s->sweep_csmc ? s->retained : nullptr;
+#define TRACE(K)                                                                              \
+    k_trace_compact<K><<<1, TRB, 0, c->stream>>>(s->model, s->lin_new, s->lin_alive, s->lin_anc0, \
+                                                 (int)s->lin_w, s->T, slot, c->g0, s->sweep_seed, \
+                                                 ret, s->lin_idx, s->traj)
+        if (s->kind == APOP_SSM_HMM) TRACE(APOP_SSM_HMM);
+        else if (s->kind == APOP_SSM_SV) TRACE(APOP_SSM_SV);
+        else TRACE(APOP_SSM_LGSSM1D);
+#undef TRACE
+    } else
     k_trace<<<1, 32, 0, c->stream>>>(s->anc_hist, s->x_hist, s->n, s->T, s->dim, slot, s->traj);
     c->launches += 1;
     APOP_CUDA(c, cudaMemcpyAsync(out_traj, s->traj, sizeof(double) * (size_t)(s->T + 1) * s->dim,
@@ -961,7 +1153,8 @@ int apop_sweep_download_history(apop_ctx* c, int32_t* anc, double* x) {
     if (!c) return APOP_ERR_INVALID;
     SweepState* s = c->sweep;
     if (!s || !s->history)
-        return set_err(c, APOP_ERR_INVALID, "download_history: no keep_history sweep available");
+        return set_err(c, APOP_ERR_INVALID, "download_history: no full-history (keep_history = 1) "
+                                            "sweep available");
     const size_t n = (size_t)s->n;
     if (anc)
         APOP_CUDA(c, cudaMemcpyAsync(anc, s->anc_hist, sizeof(int32_t) * n * s->T,

@@ -116,7 +116,8 @@ def _infer_pgibbs(model, y, number_of_particles=2, seed=0xA11CE, device=0, paths
             # the retained particle runs out of stored samples before the last
             # observe, so that resample is unconditional (pgibbs.cljc:89)
             out = pop.sweep(model, y, retained=retained, csmc=retained is not None,
-                            n_cond_steps=T - 1, reset_weights=True, keep_history=True)
+                            n_cond_steps=T - 1, reset_weights=True,
+                            keep_history=True if paths else "compact")
             b = int(seeds.rng.random() * n)                         # rand-nth, pgibbs.cljc:122-123
             retained = out.trace(b)
             yield from _states(out, 0.0 if math.isfinite(out.log_z) else -math.inf, paths)
@@ -142,7 +143,8 @@ def _infer_pgas(model, y, number_of_particles=2, seed=0xA11CE, device=0, paths=F
             pop.set_seed(seeds.next_key())
             cond = retained is not None
             out = pop.sweep(model, y, retained=retained, csmc=cond, n_cond_steps=T,
-                            reset_weights=True, keep_history=True, ancestor_sampling=cond)
+                            reset_weights=True, keep_history=True if paths else "compact",
+                            ancestor_sampling=cond)
             b = int(seeds.rng.random() * n)                         # rand-nth, pgas.cljc:166-167
             retained = out.trace(b)
             yield from _states(out, 0.0 if math.isfinite(out.log_z) else -math.inf, paths)
@@ -189,7 +191,7 @@ def _infer_ipmcmc(model, y, number_of_particles=2, number_of_nodes=32,
                 ret = retained[j] if j < P else None
                 pop.set_seed(seeds.next_key())
                 out = pop.sweep(model, y, retained=ret, csmc=ret is not None, n_cond_steps=T,
-                                reset_weights=True, keep_history=True)
+                                reset_weights=True, keep_history=True if paths else "compact")
                 log_zs[j] = out.log_z
                 traj = out.trajectories() if paths else None
                 results.append([_result_of(out, k, traj) for k in range(n)])

@@ -101,7 +101,8 @@ class PopulationNodes:
         pop.set_seed(job.key)
         ret = job.retained
         out = pop.sweep(self.model, self.y, retained=ret, csmc=ret is not None,
-                        n_cond_steps=self.T, reset_weights=True, keep_history=True)
+                        n_cond_steps=self.T, reset_weights=True,
+                        keep_history=True if self.paths else "compact")
         cand = np.asarray(out.trace(int(job.pick * self.n)), dtype=np.float64).reshape(-1)
         res = out.trajectories() if self.paths else np.array(out.x_final, copy=True)
         return NodeRun(float(out.log_z), cand, res)

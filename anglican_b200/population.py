@@ -341,7 +341,10 @@ class Population:
         view of a page-locked buffer owned by the population, overwritten by its
         next sweep (copy it to keep it).  no_resample: `infer :importance`
         (importance.cljc:16-22) — weights accumulate per particle, the output
-        carries lw_final and log_z = log mean exp(lw_final).  ancestor_sampling:
+        carries lw_final and log_z = log mean exp(lw_final).  keep_history: False,
+        True / 1 (ancestors and states of every step stay in HBM: trace, history,
+        trajectories) or "compact" / 2 (two bits per particle and step, trace only;
+        scalar-state models).  ancestor_sampling:
         `infer :pgas` (pgas.cljc:107-131) — in a conditional sweep the retained
         particle's ancestor is redrawn at every conditional observe."""
         y = np.ascontiguousarray(y, dtype=np.float64)
@@ -351,6 +354,8 @@ class Population:
             want_stats, want_filt = False, False
         if want_filt is None:
             want_filt = want_stats and d == 1
+        if keep_history == "compact":
+            keep_history = 2 if d == 1 else 1
         opts = L.ApopSweepOpts(int(csmc), int(n_cond_steps), int(reset_weights),
                                int(keep_history), 0, int(want_final), int(bool(want_filt)),
                                int(bool(no_resample)), int(bool(ancestor_sampling)))

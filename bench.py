@@ -41,18 +41,29 @@ KT_NAMES = {1: "k_propagate", 2: "k_tile_lse", 3: "k_finalize", 4: "k_fold_agg",
 #   k_ancestors K3+K4 scan + ancestor search (R 8 + W 4)            = 12
 ALGO_BYTES = {"k_propagate": 52.0, "k_fold_agg": 8.0, "k_ancestors": 12.0, "k_tile_lse": 8.0,
               "k_gather": 20.0}
-# The fused k_propagate never materialises the gathered state nor re-reads the
-# log-weights for the normalise partials, so the bytes it MUST move are
-# R anc 4 + R x 8 + W x 8 + W lw 8 = 28: the roofline fraction is quoted on those
-# (52 would read as > 100 % of HBM); the unfused figure is kept beside it.
-MOVED_BYTES = {"k_propagate": 28.0, "k_fold_agg": 8.0, "k_ancestors": 12.0, "k_tile_lse": 8.0,
+# `roofline.achieved` follows SURVEY §8(d) to the letter: ALGORITHMIC bytes of the
+# stages the kernel covers / its launch time.  The fused k_propagate never
+# materialises the gathered state nor re-reads the log-weights for the normalise
+# partials, so the bytes it MUST move (compulsory) are R anc 4 + R x 8 + W x 8 +
+# W lw 8 = 28, and its algorithmic fraction can read above 1: both are reported,
+# labelled, and the figure that answers the north star ("resample+reweight at >= 70 %
+# of HBM") is `path_roofline` (the whole particle-step, 64 B).
+# k_fold_agg also writes the weights exp(lw - m) once (8 B) for the emission kernels.
+MOVED_BYTES = {"k_propagate": 28.0, "k_fold_agg": 16.0, "k_ancestors": 12.0, "k_tile_lse": 8.0,
                "k_gather": 20.0}
-# dram__bytes_read.sum + dram__bytes_write.sum per launch at 2^27 particles from the
-# committed `ncu --set full` capture (profiles/r01r_ncu_full_summary.csv), bytes/particle
-NCU_TRAFFIC_PER_PARTICLE = {"k_propagate": (1.7403e9 + 2.1641e9) / (1 << 27),
-                            "k_fold_agg": (1.0744e9 + 0.0089e9) / (1 << 27),
-                            "k_ancestors": (1.0760e9 + 0.5119e9) / (1 << 27)}
+# dram__bytes_read.sum + dram__bytes_write.sum per launch from the tracked
+# `ncu --set full` capture of the shipped kernels (tools/ncu_summary.py writes the file)
+NCU_TRAFFIC_FILE = os.path.join(ROOT, "profiles", "ncu_traffic.json")
 STEP_BYTES = 64.0          # whole particle-step: 32d + 32
+RESAMPLE_REWEIGHT_BYTES = 48.0   # BASELINE's second metric: logw W 8 + K2 8 + K3/4 12 + K5 20 (16d + 32)
+
+
+def ncu_traffic_per_particle():
+    try:
+        d = json.load(open(NCU_TRAFFIC_FILE))
+        return {k: v["dram_bytes_per_particle"] for k, v in d["kernels"].items()}, d.get("source")
+    except Exception:
+        return {}, None
 
 
 def sv_observations(T, seed=20240602, phi=0.98, sigma=0.16, beta=0.65):
@@ -154,11 +165,65 @@ def oracle_sample(args, T_cap):
         A, Qc, R, y = lgmvn_workload(args.T, 64)
         m = orc.Model(orc.SSM_LGMVN, dim=64, s0=1.0, A=A, Lq=np.linalg.cholesky(Qc), R=R)
         return m, y[:T_s * 64], n_s, T_s, "64-dim linear-Gaussian sweep"
-    n_s, T_s = 1 << 17, min(args.T, T_cap)
+    # 2^20 particles: 24 MB of state per array, beyond the host's L2
+    n_s, T_s = 1 << 20, min(args.T, T_cap)
     phi, sigma, beta = 0.98, 0.16, 0.65
     m = orc.Model(orc.SSM_SV, m0=0.0, s0=sigma / math.sqrt(1 - phi * phi), a=phi, b=0.0, q=sigma,
                   beta=beta)
     return m, sv_observations(args.T)[:T_s], n_s, T_s, "SV sweep"
+
+
+def resample_microbench(device, sizes, peak):
+    """SURVEY §8(d) resample-only microbench: lw ~ N(0, 3^2) from default_rng(7), one
+    reweight (`observe* (normal 0 1)` added into the log-weights), systematic resample
+    and ancestor gather of one state column through the column-level C ABI.
+    Algorithmic bytes: 48 per particle (16d + 32, d = 1).  Device time by CUDA events
+    on the engine stream."""
+    from anglican_b200 import Population, _lib as L
+    out = []
+    for n in sizes:
+        lw0 = np.random.default_rng(7).normal(0.0, 3.0, n)
+        with Population(n, seed=7, device=device) as pop:
+            lw = pop.column(L.F64, data=lw0)
+            x = pop.column(L.F64, data=lw0)
+            anc = pop.column(L.I32)
+            best = None
+            for it in range(6):
+                lw.upload(lw0)
+                pop.synchronize()
+                pop.timer_reset()
+                pop.timer_begin(15)
+                pop.observe_normal(0.0, 1.0, x, lw)
+                pop.resample(lw, u=0.37, order=L.ORDER_SORTED, anc=anc)
+                pop.gather(anc, [x])
+                pop.timer_end(15)
+                pop.synchronize()
+                ms, _ = pop.timer_ms(15)
+                if it >= 2:
+                    best = ms if best is None else min(best, ms)
+            gbs = RESAMPLE_REWEIGHT_BYTES * n / (best * 1e-3) / 1e9
+            out.append({"particles": n, "ms": best, "achieved_gbs": gbs, "frac": gbs / peak})
+    return out
+
+
+def dgemm_peak_tflops(torch, n=8192, reps=5):
+    """fp64 tensor-pipe yard-stick for the mvn kernels: cuBLAS DGEMM n^3 on this GPU"""
+    a = torch.randn(n, n, dtype=torch.float64, device="cuda")
+    b = torch.randn(n, n, dtype=torch.float64, device="cuda")
+    torch.matmul(a, b)
+    torch.cuda.synchronize()
+    best = None
+    for _ in range(reps):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        torch.matmul(a, b)
+        e1.record()
+        torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1)
+        best = ms if best is None else min(best, ms)
+    del a, b
+    torch.cuda.empty_cache()
+    return 2.0 * n ** 3 / (best * 1e-3) / 1e12
 
 
 # --------------------------------------------------------------------- reference arm
@@ -173,7 +238,7 @@ def run_reference(args):
     from oracle import pyoracle as orc
     T = args.T
     cores = os.cpu_count() or 1
-    m, y, n_s, T_s, label = oracle_sample(args, 1000)      # ~2 s per step on 16 threads
+    m, y, n_s, T_s, label = oracle_sample(args, 500)       # a few seconds per step on all threads
     times = []
     for i in range(args.warmup + args.steps):
         t0 = time.perf_counter()
@@ -183,9 +248,9 @@ def run_reference(args):
             times.append(dt)
     total = sum(times)
     v = n_s * T_s * len(times) / total
-    sample = (f"{label}, {n_s} particles x {T_s} of {T} steps per bench step (bounded sample of "
-              f"the 2^{int(math.log2(args.particles))}-particle workload; per-particle-step cost is "
-              "size-independent on the CPU)")
+    sample = (f"{label}, {n_s} particles x {T_s} of {T} steps per bench step: a bounded sample of "
+              f"the 2^{int(math.log2(args.particles))}-particle workload, the rate is a LINEAR "
+              "EXTRAPOLATION in particles and steps (the sequential wheel is O(N) per step)")
     line = {"impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * total / len(times),
             "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64",
@@ -239,7 +304,7 @@ def run_ours(args):
     # (context + stream): the single-CTA phases of one sweep's exact resampler
     # (k_finalize, k_chain) overlap with the streaming kernels of the other.
     from concurrent.futures import ThreadPoolExecutor
-    F = max(1, min(args.inflight, 3 if args.max_connections <= 0 else 8))
+    F = max(1, min(args.inflight, 8))
     pops = []
     for f in range(F):
         nid = nccl_id
@@ -309,6 +374,17 @@ def run_ours(args):
             if c:
                 kt[name] = (ms, c)
         pop.enable_kernel_timers(False)
+    # ---- the same with ONE sweep in flight (population 0 alone), reported beside the
+    # headline so that the gain from overlapping independent sweeps is visible
+    dev1_ms = None
+    if F > 1:
+        barrier()
+        pop.timer_reset()
+        z1 = sweeps(0, args.steps, 2000, want_final=False, want_stats=False)
+        barrier()
+        dev1_ms = pop.timer_ms(0)[0]
+        if z1 != zs[0]:
+            raise SystemExit("log Z of a sweep depends on what else is in flight: %r vs %r" % (z1, zs[0]))
     clocks = sampler.stop() if rank == 0 else None
 
     # ---- e2e: public call, host buffers in/out, copies inside the timed region
@@ -324,11 +400,16 @@ def run_ours(args):
     e2e_s = time.perf_counter() - e0
     pool.shutdown()
 
-    t_dev = torch.tensor([dev_ms / 1e3, e2e_s, wall], dtype=torch.float64, device="cuda")
+    t_dev = torch.tensor([dev_ms / 1e3, e2e_s, wall, (dev1_ms or 0.0) / 1e3], dtype=torch.float64,
+                         device="cuda")
     if world > 1:
         dist.all_reduce(t_dev, op=dist.ReduceOp.MAX)
-    dev_s, e2e_s, wall = [float(v) for v in t_dev.cpu()]
+    dev_s, e2e_s, wall, dev1_s = [float(v) for v in t_dev.cpu()]
     work = float(n_total) * T * args.steps * F
+    # log Z of a sweep is a function of (seed, T, particles) only - not of how the
+    # population is sharded nor of what else is in flight.  Checked against the values
+    # recorded by a 1-GPU run (profiles/logz_reference.json); a mismatch fails the run.
+    logz_note = check_logz(args, rank, world, F, zs)
 
     if rank == 0:
         peak, peak_kind = measured_peak()
@@ -341,31 +422,43 @@ def run_ours(args):
             ms, c = kt["k_propagate"]
             avg_s = ms / 1e3 / c
             flop = 4.0 * n_local * dim * dim
+            pk64 = dgemm_peak_tflops(torch)
             roof = {"kernel": "k_propagate_mvn<64>", "bound": "tensor", "achieved": flop / avg_s / 1e12,
-                    "peak": 40.0, "unit": "TFLOP/s", "frac": flop / avg_s / 1e12 / 40.0,
-                    "traffic": None, "peak_source": "nominal B200 fp64 (MEASURED_PEAKS.json has no "
-                    "fp64 figure); ncu: DMMA pipe 57 % active (profiles/r01t_ncu_mvn_summary.txt)",
+                    "peak": pk64, "unit": "TFLOP/s", "frac": flop / avg_s / 1e12 / pk64,
+                    "traffic": None, "peak_source": "measured in this run: cuBLAS DGEMM 8192^3, best of 5 "
+                    "(fp64 tensor pipe; MEASURED_PEAKS.json has no fp64 figure)",
                     "avg_launch_us": avg_s * 1e6, "launches_timed": c,
                     "algorithmic_flop_per_particle": 4.0 * dim * dim}
             dom = None
         if dom:
             name, (ms, c) = dom
             avg_s = ms / 1e3 / c
-            achieved = MOVED_BYTES[name] * n_local / avg_s / 1e9
-            tr = NCU_TRAFFIC_PER_PARTICLE.get(name)
+            achieved = ALGO_BYTES[name] * n_local / avg_s / 1e9
+            moved = MOVED_BYTES[name] * n_local / avg_s / 1e9
+            trs, tr_src = ncu_traffic_per_particle()
+            tr = trs.get(name)
             roof = {"kernel": name, "bound": "hbm", "achieved": achieved, "peak": peak,
                     "unit": "GB/s", "frac": achieved / peak,
-                    "traffic": tr * n_local if tr else None,
-                    "unfused_algorithmic_bytes_per_particle": ALGO_BYTES[name],
+                    "traffic": tr * n_local if tr else None, "traffic_source": tr_src,
+                    "algorithmic_bytes_per_particle": ALGO_BYTES[name],
+                    "compulsory_bytes_per_particle": MOVED_BYTES[name],
+                    "compulsory_gbs": moved, "compulsory_frac": moved / peak,
+                    "note": "achieved/frac: SURVEY 8(d) algorithmic bytes of the stages this kernel "
+                            "covers (K1+K2+K5 for the fused k_propagate: the gather and the normalise "
+                            "pass never touch HBM, so this can exceed 1); compulsory_*: the bytes the "
+                            "fused kernel must move.  The whole-step figure is path_roofline.frac",
                     "peak_source": f"{peak_kind} (MEASURED_PEAKS.json hbm_gbs)",
-                    "avg_launch_us": avg_s * 1e6, "launches_timed": c,
-                    "algorithmic_bytes_per_particle": MOVED_BYTES[name]}
+                    "avg_launch_us": avg_s * 1e6, "launches_timed": c}
         ksum_ms = sum(v[0] for v in kt.values())
         path = {"bytes_per_particle_step": step_bytes,
                 "achieved_gbs": step_bytes * n_local * T * args.steps * F / (dev_s) / 1e9,
                 "frac": step_bytes * n_local * T * args.steps * F / dev_s / 1e9 / peak,
                 "kernel_share": {n: v[0] / ksum_ms for n, v in kt.items()} if ksum_ms else {},
                 "kernel_avg_us": {n: 1e3 * v[0] / v[1] for n, v in kt.items()}}
+        # BASELINE's second metric inside the sweep: everything but the state traffic of
+        # K1 (16 B of its 24): log-weight write 8 + K2 8 + K3/4 12 + K5 20 = 48 of the 64 B
+        if not mvn and ksum_ms:
+            path["resample_reweight_share_of_step_bytes"] = RESAMPLE_REWEIGHT_BYTES / STEP_BYTES
         line = {"metric": METRIC, "value": work / dev_s, "unit": UNIT, "n_gpus": world,
                 "steps": args.steps, "warmup": args.warmup,
                 "ms_per_step": 1e3 * dev_s / args.steps, "higher_is_better": True,
@@ -385,9 +478,24 @@ def run_ours(args):
                         "d2h_bytes_per_step": int(x_host_bytes + 2 * T * 8 + 64) * F},
                 "gpu_launches": int(launches), "clocks": clocks, "roofline": roof,
                 "path_roofline": path, "wall_ms_per_step": 1e3 * wall / args.steps,
-                "log_z_mean": float(np.mean(log_zs))}
+                "log_z_mean": float(np.mean(log_zs)), "log_z_check": logz_note}
+        if dev1_s > 0.0:
+            v1 = float(n_total) * T * args.steps / dev1_s
+            line["one_sweep_in_flight"] = {"value": v1, "unit": UNIT,
+                                           "path_roofline_frac": step_bytes * v1 / 1e9 / peak / world}
+        if world == 1 and not mvn and not args.no_microbench:
+            rr = resample_microbench(local, [1 << 20, 1 << 24, 1 << 27], peak)
+            line["resample_reweight"] = {
+                "metric": "resample+reweight HBM GB/s vs peak (BASELINE.json metric, second part)",
+                "bytes_per_particle": RESAMPLE_REWEIGHT_BYTES, "peak": peak, "unit": "GB/s",
+                "microbench": rr,
+                "what": "column-level C ABI: apop_observe_normal + apop_resample (systematic, sorted "
+                        "order) + apop_gather of one f64 column; lw ~ N(0, 3^2), default_rng(7)"}
         if world == 1 and not args.no_cpu_baseline:
             line["cpu_baseline"] = cpu_baseline(args)
+            line["vs_cpu_baseline"] = {"e2e_over_cpu": work / e2e_s / line["cpu_baseline"]["value"],
+                                       "note": "reported baseline (1 core, C port), not a target; "
+                                               "vs_baseline stays null: BASELINE.md holds no published number"}
         print(json.dumps(line), flush=True)
     for p_ in pops:
         p_.close()
@@ -395,17 +503,43 @@ def run_ours(args):
         dist.destroy_process_group()
 
 
+LOGZ_FILE = os.path.join(ROOT, "profiles", "logz_reference.json")
+
+
+def check_logz(args, rank, world, F, zs):
+    """zs[f][i] = log Z of timed sweep i of population f (seed 0xA11CE.. + 2000 + 100 f + i)"""
+    if rank != 0:
+        return None
+    key = "%s/n%d/T%d" % (args.workload, args.particles, args.T)
+    try:
+        ref = json.load(open(LOGZ_FILE))
+    except Exception:
+        ref = {}
+    have = ref.get(key, {})
+    mine = {"f%d_i%d" % (f, i): z for f in range(len(zs)) for i, z in enumerate(zs[f])}
+    bad = {k: (v, have[k]) for k, v in mine.items() if k in have and have[k] != v}
+    if bad:
+        raise SystemExit("log Z differs from the recorded 1-GPU values (%s): %r" % (LOGZ_FILE, bad))
+    checked = sum(1 for k in mine if k in have)
+    if world == 1 and args.record_logz:
+        have.update(mine)
+        ref[key] = have
+        json.dump(ref, open(LOGZ_FILE, "w"), indent=1, sort_keys=True)
+    return {"compared_with_recorded_1gpu_values": checked, "of": len(mine), "file": "profiles/logz_reference.json"}
+
+
 def cpu_baseline(args):
     """oracle port of smc.cljc, 1 core (the reference's `infer :smc` is single
     threaded), on a bounded sample of the same workload."""
     from oracle import pyoracle as orc
-    m, y, n_s, T_s, label = oracle_sample(args, 1500)      # ~13 s of one core
+    m, y, n_s, T_s, label = oracle_sample(args, 200)       # ~15 s of one core
     t0 = time.perf_counter()
     orc.smc_sweep(m, y, n_s, seed=1, threads=1, want_final=True)
     dt = time.perf_counter() - t0
     return {"value": n_s * T_s / dt, "unit": UNIT, "cores": 1, "kind": "port",
             "sample": f"{label} of {n_s} particles x {T_s} steps ({dt:.1f} s), oracle C port of "
-                      "smc.cljc; reference JVM path unavailable on this box (no JVM)"}
+                      "smc.cljc, extrapolated linearly to the full workload; reference JVM path "
+                      "unavailable on this box (no JVM)"}
 
 
 def main():
@@ -419,6 +553,11 @@ def main():
     ap.add_argument("--particles", type=int, default=0)
     ap.add_argument("--T", type=int, default=0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-microbench", action="store_true",
+                    help="skip the resample-only microbench (N = 1, sv workload)")
+    ap.add_argument("--record-logz", action="store_true",
+                    help="N = 1: store the log Z of every timed sweep in profiles/logz_reference.json; "
+                         "runs at any N compare against it")
     ap.add_argument("--inflight", type=int, default=2,
                     help="independent sweeps kept in flight, one population each (measured: "
                          "1 GPU 59 -> 62 G, 8 GPUs 214 -> 318 (2) -> 365 (3) G particle-steps/s; "
@@ -427,8 +566,9 @@ def main():
                     help="experiment: CUDA_DEVICE_MAX_CONNECTIONS for this process (0 = leave the "
                          "driver default); to try with --inflight > 3 on several GPUs")
     args = ap.parse_args()
-    if args.max_connections > 0:         # must be set before the CUDA context exists
-        os.environ["CUDA_DEVICE_MAX_CONNECTIONS"] = str(args.max_connections)
+    # one hardware queue per engine stream (see apop_create); must be set before torch
+    # creates the CUDA context
+    os.environ["CUDA_DEVICE_MAX_CONNECTIONS"] = str(args.max_connections if args.max_connections > 0 else 32)
     if args.workload == "lgmvn64":
         args.particles = args.particles or (1 << 24)
         args.T = args.T or 100

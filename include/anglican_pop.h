@@ -186,7 +186,8 @@ int apop_resample_weights(apop_ctx* ctx, apop_col weights, int scheme, double u,
 /* multinomial with one supplied uniform per offspring (f64 column) */
 int apop_resample_multinomial_u(apop_ctx* ctx, apop_col weights, apop_col uniforms,
                                 int64_t n_new, apop_col anc_out);
-/* x_new[k] = x[anc[k]] for each listed column (in place; uses ctx scratch) */
+/* x_new[k] = x[anc[k]] for each listed column.  The result is written to the column's second
+ * buffer and the buffers are swapped: a pointer from apop_column_device_ptr is stale after this. */
 int apop_gather(apop_ctx* ctx, apop_col anc, int64_t n_new, const apop_col* cols, int ncols);
 
 /* ---- fused state-space sweeps (the benchmark fast path) -----------------
@@ -214,7 +215,11 @@ typedef struct {
     int32_t csmc;              /* conditional sweep: retained particle in slot 0 */
     int32_t n_cond_steps;      /* observes using the conditional resample */
     int32_t reset_weights;     /* pgibbs.cljc:88 */
-    int32_t keep_history;      /* keep ancestors (+ states) for lineage tracing */
+    int32_t keep_history;      /* lineages for apop_trace_lineage: 0 none; 1 full history (ancestors
+                                * + states, 12 B per particle and step, also downloadable);
+                                * 2 compact (scalar-state models): two bits per particle and
+                                * step, the states of the ONE traced lineage are recomputed
+                                * from the counter-based RNG (pgibbs.cljc:29-35, 122-123) */
     int32_t use_graph;         /* capture the step loop in a CUDA graph */
     int32_t want_final;        /* gather final states into x_final */
     int32_t want_filt;         /* per-step filtering means sum w x / sum w (reads x once more) */
