@@ -103,6 +103,13 @@ _SIGS = [
                                   C.c_int32]),
     ("apop_observe_mvn", C.c_int, [_vp, c_double_p, C.c_int32, c_double_p, C.c_int, c_double_p,
                                    C.c_int32, C.c_int32]),
+    ("apop_sample_mvt", C.c_int, [_vp, C.c_double, c_double_p, C.c_int32, c_double_p, C.c_int,
+                                  C.c_uint32, C.c_int32]),
+    ("apop_observe_mvt", C.c_int, [_vp, C.c_double, c_double_p, C.c_int32, c_double_p, C.c_int,
+                                   c_double_p, C.c_int32, C.c_int32]),
+    ("apop_sample_wishart", C.c_int, [_vp, C.c_double, c_double_p, C.c_int, C.c_uint32, C.c_int32]),
+    ("apop_observe_wishart", C.c_int, [_vp, C.c_double, c_double_p, C.c_int, C.c_int32, C.c_int32]),
+    ("apop_column_take", C.c_int, [_vp, c_double_p, C.c_int, C.c_int, C.c_int32, C.c_int32]),
     ("apop_selftest_math", C.c_int, [_vp, C.c_int, C.c_int32, C.c_int32]),
     ("apop_debug_resolve_phases", C.c_int, [_vp, c_double_p]),
     ("apop_debug_chain_trace", C.c_int, [_vp, c_double_p]),

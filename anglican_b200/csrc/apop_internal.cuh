@@ -188,7 +188,6 @@ struct ResampleWS {
     ResampleInfo* info = nullptr;      // device
     ResampleInfo* info_host = nullptr; // pinned
     double* edges = nullptr;           // multinomial only, lazily allocated
-    double* wbuf = nullptr;            // [n] weights exp(lw - m), written by k_fold_agg
 };
 
 } // namespace apop

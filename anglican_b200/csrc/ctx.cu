@@ -204,7 +204,6 @@ int apop_destroy(apop_ctx* c) {
     ResampleWS& w = c->ws;
     if (w.slab) cudaFree(w.slab);
     if (w.edges) cudaFree(w.edges);
-    if (w.wbuf) cudaFree(w.wbuf);
     if (w.info_host) cudaFreeHost(w.info_host);
     if (c->scratch) cudaFree(c->scratch);
     for (auto& t : c->timers) {

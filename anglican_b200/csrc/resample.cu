@@ -628,14 +628,12 @@ __device__ __noinline__ void hard_tile_prework(const double* __restrict__ lw,
     hard_tile_tables(w, eA, pa, sb, hw, warp_tot);
 }
 
-// wout (log-weight mode): the weights exp(lw - m) are written out once, so that the
-// chain, the emission kernels and the multinomial edges read them back instead of
-// evaluating the exponential a second time (8 more bytes per particle; these
-// kernels are bound by instruction issue, not by HBM).
+// (Writing the weights exp(lw - m) out here for the emission kernels was measured:
+// k_ancestors 617 -> 530 us, k_fold_agg 348 -> 461 us at 2^27 particles - the extra
+// 8 B per particle cost more than the second exponential, so the kernels recompute.)
 __global__ void __launch_bounds__(TB, APOP_FOLD_CTAS) k_fold_agg(const double* __restrict__ lw,
                                                     const double* __restrict__ win, int64_t n,
-                                                    WSView v, const double* __restrict__ xf,
-                                                    double* __restrict__ wout) {
+                                                    WSView v, const double* __restrict__ xf) {
     __shared__ Xd warp_tot[NWARP];
     __shared__ i64 ws0[NWARP], ws1[NWARP];
     __shared__ double wa[NWARP], wb[NWARP];
@@ -651,18 +649,6 @@ __global__ void __launch_bounds__(TB, APOP_FOLD_CTAS) k_fold_agg(const double* _
     const bool do0 = (c0 != kCtxHard), do1 = (c1 != kCtxHard && c1 != kCtxSkip);
     double w[IPT];
     weights_from_raw(win != nullptr, raw, base, n, m_glob, w);
-    if (wout) {
-        const int64_t i0 = base + (int64_t)threadIdx.x * IPT;
-        if (i0 + IPT <= n) {
-            double2* q = reinterpret_cast<double2*>(wout + i0);      // cudaMalloc'ed: 16-byte aligned
-#pragma unroll
-            for (int j = 0; j < IPT / 2; ++j) q[j] = make_double2(w[2 * j], w[2 * j + 1]);
-        } else {
-#pragma unroll
-            for (int j = 0; j < IPT; ++j)
-                if (i0 + j < n) wout[i0 + j] = w[j];
-        }
-    }
     // accurate sum w, sum w^2 of the tile (ESS, log-mean-weight)
     double s = 0.0, s2 = 0.0;
 #pragma unroll
@@ -1857,8 +1843,9 @@ __device__ __forceinline__ void scan_store(StageSmem& st, int a0, int tot, int32
     }
 }
 
-__device__ __forceinline__ void ancestors_fast(const TileRec& R, const double (&w)[IPT],
-                                               int32_t val_tile0, StageSmem& st, int* err) {
+__device__ __forceinline__ void ancestors_fast(const TileRec& R, const double (&raw)[IPT], bool is_w,
+                                               int64_t base, int64_t n, int32_t val_tile0,
+                                               StageSmem& st, int* err) {
     const int tid = threadIdx.x;
     const int W = (int)(R.wm & 0x0fffffffu);
     // the window is shifted by a0 = (destination address / 4) mod 4 inside the staging
@@ -1870,6 +1857,8 @@ __device__ __forceinline__ void ancestors_fast(const TileRec& R, const double (&
         *reinterpret_cast<int4*>(&st.buf[e]) = make_int4(0, 0, 0, 0);
     double inc[IPT], loc = 0.0;
     {
+        double w[IPT];
+        weights_from_raw(is_w, raw, base, n, R.m, w);
         const double inv_u = R.inv_u;
 #pragma unroll
         for (int j = 0; j < IPT; ++j) {
@@ -1925,16 +1914,16 @@ __global__ void __launch_bounds__(TB) k_ancestors_general(const double* __restri
     }
 }
 
-// w: the weights themselves (the caller's, or the ones k_fold_agg wrote out)
-__global__ void __launch_bounds__(TB, APOP_ANC_CTAS) k_ancestors(const double* __restrict__ w,
-                                                     int64_t n, int64_t g0,
-                                                     const TileRec* __restrict__ rec, int* err) {
+__global__ void __launch_bounds__(TB, APOP_ANC_CTAS) k_ancestors(const double* __restrict__ lw,
+                                                     const double* __restrict__ win, int64_t n,
+                                                     int64_t g0, const TileRec* __restrict__ rec,
+                                                     int* err) {
     __shared__ StageSmem sm;
     const int t = blockIdx.x;
     const int64_t base = (int64_t)t * TILE;
     // the tile and its record: all global reads of the streaming path, issued up front
     double raw[IPT];
-    load_blocked(w, base, n, raw, 0.0);
+    load_raw(lw, win, base, n, raw);
     TileRec R;
     {
         const int4* rp = reinterpret_cast<const int4*>(rec + t);
@@ -1943,7 +1932,7 @@ __global__ void __launch_bounds__(TB, APOP_ANC_CTAS) k_ancestors(const double* _
         for (int k = 0; k < 4; ++k) rq[k] = __ldg(rp + k);
     }
     if ((R.wm >> 28) != TM_FAST) return;           // nothing to emit, or listed for the general kernel
-    ancestors_fast(R, raw, (int32_t)(g0 + base), sm, err);
+    ancestors_fast(R, raw, win != nullptr, base, n, (int32_t)(g0 + base), sm, err);
 }
 
 // Deferred emission (see RunRec): every warp takes run records in turn; the
@@ -2175,12 +2164,6 @@ int ensure_resample_ws(apop_ctx* c) {
             w.info = info;
         }
     }
-    if (cudaMalloc(&w.wbuf, ((size_t)c->n + 8) * 8) != cudaSuccess) {
-        w.wbuf = nullptr;
-        w.info = nullptr;
-        return set_err(c, APOP_ERR_OOM, "resample workspace: weight column of %zu bytes",
-                       ((size_t)c->n + 8) * 8);
-    }
     APOP_CUDA(c, cudaMemsetAsync(w.info, 0, sizeof(ResampleInfo), c->stream));
     k_info_reset<<<1, 1, 0, c->stream>>>(w.info, view_of(w));      // max cell, tickets
     APOP_CUDA(c, cudaMallocHost(&w.info_host, sizeof(ResampleInfo)));
@@ -2214,23 +2197,20 @@ int resample_enqueue(apop_ctx* c, const ResampleArgs& a) {
                                       n_glob);
     k_fin_b<<<fg, FB, 0, c->stream>>>(v, a.n, a.rel_eps, g0, n_glob);
     kt_end(c, KT_FINALIZE);
-    // from here on every kernel reads weights: the caller's, or exp(lw - m) as
-    // written out by k_fold_agg
-    const double* wsrc = a.w ? a.w : c->ws.wbuf;
     kt_begin(c, KT_FOLD_AGG);
-    k_fold_agg<<<nt, TB, 0, c->stream>>>(a.lw, a.w, a.n, v, a.xfilt, a.w ? nullptr : c->ws.wbuf);
+    k_fold_agg<<<nt, TB, 0, c->stream>>>(a.lw, a.w, a.n, v, a.xfilt);
     kt_end(c, KT_FOLD_AGG);
     kt_begin(c, KT_RESOLVE);
     k_seg_scan<<<c->ws.nb, SEGB, 0, c->stream>>>(v, a.xfilt ? 1 : 0);
-    k_chain<<<1, TB, 0, c->stream>>>(nullptr, wsrc, a.n, n_glob, v, a.step, F, seq);
+    k_chain<<<1, TB, 0, c->stream>>>(a.lw, a.w, a.n, n_glob, v, a.step, F, seq);
     k_expand<<<(int)((v.nt + 1 + XB - 2) / (XB - 1)), XB, 0, c->stream>>>(
         v, a.order, a.anc_out, a.out_offset, a.anc_peer, F.world, a.n);
     kt_end(c, KT_RESOLVE);
     c->launches += 6;
     if (a.anc_out) {
         kt_begin(c, KT_ANCESTORS);
-        k_ancestors<<<nt, TB, 0, c->stream>>>(wsrc, a.n, g0, v.rec, &v.info->err);
-        k_ancestors_general<<<c->sm_count, TB, 0, c->stream>>>(nullptr, wsrc, a.n, g0, v, a.order,
+        k_ancestors<<<nt, TB, 0, c->stream>>>(a.lw, a.w, a.n, g0, v.rec, &v.info->err);
+        k_ancestors_general<<<c->sm_count, TB, 0, c->stream>>>(a.lw, a.w, a.n, g0, v, a.order,
                                                                a.anc_out, a.out_offset, a.anc_peer,
                                                                F.world);
         k_fill_runs<<<c->sm_count * 4, FILL_TB, 0, c->stream>>>(v, a.order, a.anc_out, a.out_offset, a.n,
@@ -2274,7 +2254,7 @@ int multinomial_enqueue(apop_ctx* c, const double* lw, const double* w, const do
     a.anc_out = nullptr; a.out_offset = 0; a.have_partials = false;
     APOP_TRY(resample_enqueue(c, a));
     WSView v = view_of(c->ws);
-    k_edges<<<(int)v.nt, TB, 0, c->stream>>>(nullptr, w ? w : c->ws.wbuf, c->n, v, c->ws.edges);
+    k_edges<<<(int)v.nt, TB, 0, c->stream>>>(lw, w, c->n, v, c->ws.edges);
     int blocks = (int)((n_new + 255) / 256);
     if (blocks > c->sm_count * 16) blocks = c->sm_count * 16;
     k_multinomial_search<<<blocks, 256, 0, c->stream>>>(c->ws.edges, c->n, uni, c->seed, c->step,

@@ -92,19 +92,26 @@ static __device__ __noinline__ double normal_tail(uint32_t hi, uint32_t lo) {
     return (hi & 0x80000000u) ? -z : z;
 }
 
-// tab: NT_TABLE in shared memory (hot kernels) or g_ntab.  idx < 0: the draw belongs
-// to the tail and the returned value must be replaced by normal_tail(hi, lo).
+// tab: NT_TABLE in global memory (g_ntab, COPIES = 1) or replicated in shared memory
+// (hot kernels).  Shared-memory layout: the 16-byte word k of row r, copy c, sits at
+// double2 index (3 r + k) * COPIES + c; lane l reads copy l % COPIES, so the lanes
+// of a quarter warp that share a bank group are 1 in COPIES / 8 instead of all
+// (random rows: a 24 KB table read by 32 lanes at random is bank-conflict bound
+// otherwise - measured, k_propagate 992 -> 1368 us with a single copy).
+// idx < 0: the draw belongs to the tail and the returned value must be replaced by
+// normal_tail(hi, lo).
+template <int COPIES>
 __device__ __forceinline__ double normal_core(const double* __restrict__ tab, uint32_t hi,
-                                              uint32_t lo, int& idx) {
+                                              uint32_t lo, int& idx, int copy = 0) {
     const double v = __hiloint2double((int)((hi & 0x000fffffu) | 0x3fe00000u), (int)lo) - 0.5;
     const int vh = __double2hiint(v);
     idx = (vh >> (20 - NT_LOG2K)) - ((1022 - NT_OCT) << NT_LOG2K);
-    const int r = max(idx, 0) * NT_STRIDE;
     const double mid = __hiloint2double((vh & ~((1 << (20 - NT_LOG2K)) - 1)) | (1 << (19 - NT_LOG2K)), 0);
     const double d = v - mid;                                   // exact
-    const double2 c01 = *reinterpret_cast<const double2*>(tab + r);
-    const double2 c23 = *reinterpret_cast<const double2*>(tab + r + 2);
-    const double c4 = tab[r + 4];
+    const double2* row = reinterpret_cast<const double2*>(tab) + (max(idx, 0) * 3 * COPIES + copy);
+    const double2 c01 = row[0];
+    const double2 c23 = row[COPIES];
+    const double c4 = row[2 * COPIES].x;
     double p = fma(c4, d, c23.y);
     p = fma(p, d, c23.x);
     p = fma(p, d, c01.y);
@@ -114,15 +121,20 @@ __device__ __forceinline__ double normal_core(const double* __restrict__ tab, ui
 __device__ __forceinline__ double normal_from_bits(const double* __restrict__ tab, uint32_t hi,
                                                    uint32_t lo) {
     int idx;
-    const double z = normal_core(tab, hi, lo, idx);
+    const double z = normal_core<1>(tab, hi, lo, idx);
     return (idx < 0) ? normal_tail(hi, lo) : z;
 }
 
-// cooperative copy of the table into shared memory (caller synchronises)
+// cooperative copy of the table into shared memory, COPIES times (caller synchronises)
+template <int COPIES>
 __device__ __forceinline__ void normal_table_to_smem(double* s_tab) {
     const double2* src = reinterpret_cast<const double2*>(g_ntab);
     double2* dst = reinterpret_cast<double2*>(s_tab);
-    for (int i = threadIdx.x; i < NT_ROWS * NT_STRIDE / 2; i += blockDim.x) dst[i] = src[i];
+    for (int i = threadIdx.x; i < NT_ROWS * 3; i += blockDim.x) {
+        const double2 w = src[i];
+#pragma unroll
+        for (int c = 0; c < COPIES; ++c) dst[i * COPIES + c] = w;
+    }
 }
 
 // normals of the slot pair (2p, 2p+1) come from ONE Philox block: words (x, y)
@@ -140,28 +152,30 @@ __device__ __forceinline__ void normal_pair_at(uint64_t seed, uint64_t pair, uin
                                                double& z1) {
     normal_pair_at(g_ntab, seed, pair, t, stream, draw, z0, z1);
 }
-// NP consecutive pairs (slots 2 pair0 .. 2 pair0 + 2 NP - 1).  One tail test for the
-// whole batch: the fix-up (2^-16 of the draws) recomputes the Philox block.
-template <int NP>
+// NP consecutive pairs (slots 2 pair0 .. 2 pair0 + 2 NP - 1) from a table replicated
+// COPIES times in shared memory.  One tail test for the whole batch: the fix-up
+// (2^-16 of the draws) recomputes the Philox block.
+template <int NP, int COPIES>
 __device__ __forceinline__ void normal_pairs_at(const double* __restrict__ tab, uint64_t seed,
                                                 uint64_t pair0, uint32_t t, uint32_t stream,
                                                 uint32_t draw, double (&z0)[NP], double (&z1)[NP]) {
     int any = 0;
+    const int copy = (int)(threadIdx.x & (COPIES - 1));
 #pragma unroll
     for (int i = 0; i < NP; ++i) {
         const uint64_t pair = pair0 + i;
         U4 o = philox4x32_10((uint32_t)pair, (uint32_t)(pair >> 32), t, ctr3(stream, 0, draw),
                              (uint32_t)seed, (uint32_t)(seed >> 32));
         int i0, i1;
-        z0[i] = normal_core(tab, o.x, o.y, i0);
-        z1[i] = normal_core(tab, o.z, o.w, i1);
+        z0[i] = normal_core<COPIES>(tab, o.x, o.y, i0, copy);
+        z1[i] = normal_core<COPIES>(tab, o.z, o.w, i1, copy);
         any |= i0 | i1;
     }
     if (any < 0) {
 #pragma unroll 1
         for (int i = 0; i < NP; ++i) {
             double a, b;
-            normal_pair_at(tab, seed, pair0 + i, t, stream, draw, a, b);
+            normal_pair_at(g_ntab, seed, pair0 + i, t, stream, draw, a, b);
             z0[i] = a; z1[i] = b;
         }
     }

@@ -316,6 +316,51 @@ class Population:
                                                     logw.handle))
 
     # ------------------------------------------------------------ fused sweeps
+    @staticmethod
+    def _vec_or_col(v, d):
+        """(host pointer, column handle) of a shared vector or a per-particle column"""
+        if isinstance(v, Column):
+            return None, v.handle, None
+        a = np.ascontiguousarray(v, dtype=np.float64).reshape(-1)
+        assert a.size == d
+        return _dp(a), -1, a
+
+    def sample_mvt(self, nu, mean, sigma, out, draw=0):
+        """`(sample* (multivariate-t nu mean sigma))`, runtime.cljc:371-382"""
+        sg = np.ascontiguousarray(sigma, dtype=np.float64)
+        d = sg.shape[0]
+        mp, mc, _keep = self._vec_or_col(mean, d)
+        L.check(self.ctx, self.lib.apop_sample_mvt(self.ctx, float(nu), mp, mc, _dp(sg), d, draw,
+                                                   out.handle))
+
+    def observe_mvt(self, nu, mean, sigma, value, logw):
+        """`(observe* (multivariate-t nu mean sigma) value)`, runtime.cljc:383-401"""
+        sg = np.ascontiguousarray(sigma, dtype=np.float64)
+        d = sg.shape[0]
+        mp, mc, _k1 = self._vec_or_col(mean, d)
+        vp, vc, _k2 = self._vec_or_col(value, d)
+        L.check(self.ctx, self.lib.apop_observe_mvt(self.ctx, float(nu), mp, mc, _dp(sg), d, vp, vc,
+                                                    logw.handle))
+
+    def sample_wishart(self, n_df, V, out, draw=0):
+        """`(sample* (wishart n V))`: Bartlett decomposition, runtime.cljc:519-535"""
+        v = np.ascontiguousarray(V, dtype=np.float64)
+        L.check(self.ctx, self.lib.apop_sample_wishart(self.ctx, float(n_df), _dp(v), v.shape[0], draw,
+                                                       out.handle))
+
+    def observe_wishart(self, n_df, V, value, logw):
+        """`(observe* (wishart n V) value)`, runtime.cljc:536-539; value: column of width p*p"""
+        v = np.ascontiguousarray(V, dtype=np.float64)
+        L.check(self.ctx, self.lib.apop_observe_wishart(self.ctx, float(n_df), _dp(v), v.shape[0],
+                                                        value.handle, logw.handle))
+
+    def take(self, table, index, out):
+        """out[k] = table[index[k]]: per-particle parameters from a discrete state column"""
+        t = np.ascontiguousarray(table, dtype=np.float64)
+        t2 = t.reshape(t.shape[0], -1)
+        L.check(self.ctx, self.lib.apop_column_take(self.ctx, _dp(t2), t2.shape[0], t2.shape[1],
+                                                    index.handle, out.handle))
+
     def set_seed(self, seed):
         L.check(self.ctx, self.lib.apop_set_seed(self.ctx, int(seed)))
         self.seed = int(seed)

@@ -48,8 +48,7 @@ ALGO_BYTES = {"k_propagate": 52.0, "k_fold_agg": 8.0, "k_ancestors": 12.0, "k_ti
 # W lw 8 = 28, and its algorithmic fraction can read above 1: both are reported,
 # labelled, and the figure that answers the north star ("resample+reweight at >= 70 %
 # of HBM") is `path_roofline` (the whole particle-step, 64 B).
-# k_fold_agg also writes the weights exp(lw - m) once (8 B) for the emission kernels.
-MOVED_BYTES = {"k_propagate": 28.0, "k_fold_agg": 16.0, "k_ancestors": 12.0, "k_tile_lse": 8.0,
+MOVED_BYTES = {"k_propagate": 28.0, "k_fold_agg": 8.0, "k_ancestors": 12.0, "k_tile_lse": 8.0,
                "k_gather": 20.0}
 # dram__bytes_read.sum + dram__bytes_write.sum per launch from the tracked
 # `ncu --set full` capture of the shipped kernels (tools/ncu_summary.py writes the file)

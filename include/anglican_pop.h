@@ -147,6 +147,26 @@ int apop_sample_mvn(apop_ctx* ctx, const double* mean, apop_col mean_col, const 
 int apop_observe_mvn(apop_ctx* ctx, const double* mean, apop_col mean_col, const double* cov,
                      int d, const double* value, apop_col value_col, apop_col logw);
 
+/* multivariate-t (runtime.cljc:371-401): nu degrees of freedom, mean mu (host vector or f64
+ * column of width d), scale matrix sigma (d*d row-major on the host, upper triangle read). */
+int apop_sample_mvt(apop_ctx* ctx, double nu, const double* mean, apop_col mean_col,
+                    const double* sigma, int d, uint32_t draw_id, apop_col out);
+int apop_observe_mvt(apop_ctx* ctx, double nu, const double* mean, apop_col mean_col,
+                     const double* sigma, int d, const double* value, apop_col value_col,
+                     apop_col logw);
+/* wishart (runtime.cljc:479-545): n degrees of freedom, scale V (p*p on the host, p <= 16);
+ * values are f64 columns of width p*p (row-major matrices).  Sampling is the Bartlett
+ * decomposition the reference uses. */
+int apop_sample_wishart(apop_ctx* ctx, double n_df, const double* V, int p, uint32_t draw_id,
+                        apop_col out);
+int apop_observe_wishart(apop_ctx* ctx, double n_df, const double* V, int p, apop_col value,
+                         apop_col logw);
+/* per-particle table lookup: out[k][:] = table[index[k]][:] (table: rows*width doubles on the
+ * host, index: i32 column, out: f64 column of width `width`).  This is how a traced program
+ * turns a discrete state into distribution parameters - `(nth transition-rows state)`. */
+int apop_column_take(apop_ctx* ctx, const double* table, int rows, int width, apop_col index_i32,
+                     apop_col out);
+
 /* self-test hook for the engine's own fp64 math (csrc/fastmath.cuh), used by
  * tests/test_dists_gpu.py: out[k] = f(in[k]) with fn 0 exp, 1 log, 2 sqrt,
  * 3 sin(pi x), 4 cos(pi x), 5 1/x. */

@@ -419,6 +419,86 @@ double orc_mvn_logpdf(const double* x, const double* mean, const double* iL,
     return -0.5 * dot - Z;                                             /* runtime.cljc:364-366 */
 }
 
+/* ---- multivariate-t and wishart (runtime.cljc:371-401, 479-545) ----------
+ * The reference forms sigma^-1 with `m/inverse` and the determinant with `m/det`
+ * (vectorz: LU with partial pivoting); restated literally.  work: 2 d^2 + d doubles. */
+static double lu_det_inverse(const double* a_in, int d, double* lu, double* inv) {
+    /* Gauss-Jordan with partial pivoting on [A | I]; returns det(A), inv may be NULL */
+    double det = 1.0;
+    for (int i = 0; i < d * d; ++i) lu[i] = a_in[i];
+    if (inv) for (int i = 0; i < d; ++i) for (int j = 0; j < d; ++j) inv[i * d + j] = (i == j) ? 1.0 : 0.0;
+    for (int c = 0; c < d; ++c) {
+        int piv = c;
+        double best = fabs(lu[c * d + c]);
+        for (int r = c + 1; r < d; ++r)
+            if (fabs(lu[r * d + c]) > best) { best = fabs(lu[r * d + c]); piv = r; }
+        if (piv != c) {
+            for (int j = 0; j < d; ++j) {
+                double t = lu[c * d + j]; lu[c * d + j] = lu[piv * d + j]; lu[piv * d + j] = t;
+                if (inv) { t = inv[c * d + j]; inv[c * d + j] = inv[piv * d + j]; inv[piv * d + j] = t; }
+            }
+            det = -det;
+        }
+        const double d0 = lu[c * d + c];
+        det = det * d0;
+        if (d0 == 0.0) return 0.0;
+        for (int r = 0; r < d; ++r) {
+            if (r == c) continue;
+            if (r < c && !inv) continue;
+            const double f = lu[r * d + c] / d0;
+            for (int j = 0; j < d; ++j) {
+                lu[r * d + j] = lu[r * d + j] - f * lu[c * d + j];
+                if (inv) inv[r * d + j] = inv[r * d + j] - f * inv[c * d + j];
+            }
+        }
+    }
+    if (inv)
+        for (int r = 0; r < d; ++r) {
+            const double dd = lu[r * d + r];
+            for (int j = 0; j < d; ++j) inv[r * d + j] = inv[r * d + j] / dd;
+        }
+    return det;
+}
+
+/* multivariate-t observe*, runtime.cljc:383-401 */
+double orc_mvt_logpdf(const double* y, const double* mu, const double* sigma, double nu, int d,
+                      double* work) {
+    double* lu = work;
+    double* inv = work + (size_t)d * d;
+    double* dy = inv + (size_t)d * d;
+    const double det = lu_det_inverse(sigma, d, lu, inv);
+    for (int i = 0; i < d; ++i) dy[i] = mu[i] - y[i];
+    double q = 0.0;                                   /* dy' inv-sigma dy */
+    for (int i = 0; i < d; ++i) {
+        double s = 0.0;
+        for (int j = 0; j < d; ++j) s = s + inv[i * d + j] * dy[j];
+        q = q + dy[i] * s;
+    }
+    return lgamma(0.5 * (nu + d)) -
+           (lgamma(0.5 * nu) + 0.5 * d * log(nu) + 0.5 * d * log(M_PI) + 0.5 * log(det) +
+            0.5 * (nu + d) * log(1.0 + (1.0 / nu) * q));
+}
+
+/* log-mv-gamma-fn, runtime.cljc:479-486 */
+double orc_log_mv_gamma(int p, double a) {
+    double s = 0.25 * p * (p - 1) * log(M_PI);
+    for (int j = 0; j < p; ++j) s = s + lgamma(a - 0.5 * j);
+    return s;
+}
+
+/* wishart observe*, runtime.cljc:507-509, 536-539.  work: 2 p^2 doubles */
+double orc_wishart_logpdf(const double* x, double n, const double* V, int p, double* work) {
+    double* lu = work;
+    double* inv = work + (size_t)p * p;
+    const double detV = lu_det_inverse(V, p, lu, inv);
+    const double Z = 0.5 * n * p * log(2.0) + 0.5 * n * log(detV) + orc_log_mv_gamma(p, 0.5 * n);
+    double tr = 0.0;                                  /* (trace (mmul inv-V value)) */
+    for (int i = 0; i < p; ++i)
+        for (int j = 0; j < p; ++j) tr = tr + inv[i * p + j] * x[j * p + i];
+    const double detX = lu_det_inverse(x, p, lu, NULL);
+    return 0.5 * (n - p - 1.0) * log(detX) - 0.5 * tr - Z;
+}
+
 /* ---- samplers (distributional parity only) ----------------------------- */
 
 /* GammaDistribution.sample: Ahrens-Dieter GS (shape<1), Marsaglia-Tsang

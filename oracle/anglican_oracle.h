@@ -94,6 +94,12 @@ double orc_dirichlet_logpdf(const double* v, const double* alpha, int k); /* 292
 /* mvn, runtime.cljc:349-368.  cov row-major d*d (upper triangle read, EJML-
  * style inner lower Cholesky as used by vectorz).  work: 2*d*d+d doubles. */
 int    orc_mvn_prepare(const double* cov, int d, double* L, double* iL, double* Z);
+/* multivariate-t / wishart log-densities (runtime.cljc:383-401, 479-486, 536-539); work:
+ * 2 d^2 + d doubles.  Pinned on runtime_wishart_test.cljc:161-176 and scipy. */
+double orc_mvt_logpdf(const double* y, const double* mu, const double* sigma, double nu, int d,
+                      double* work);
+double orc_log_mv_gamma(int p, double a);
+double orc_wishart_logpdf(const double* x, double n, const double* V, int p, double* work);
 double orc_mvn_logpdf(const double* x, const double* mean, const double* iL,
                       double Z, int d, double* work);
 

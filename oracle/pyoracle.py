@@ -70,6 +70,10 @@ def _declare(L):
     d, i64, i32, u64, u32 = C.c_double, C.c_int64, C.c_int32, C.c_uint64, C.c_uint32
     L.orc_philox4x32.argtypes = [u32] * 6 + [C.POINTER(u32)]
     L.orc_philox4x32.restype = None
+    L.orc_mvt_logpdf.argtypes = [c_double_p, c_double_p, c_double_p, d, C.c_int, c_double_p]
+    L.orc_mvt_logpdf.restype = d
+    L.orc_wishart_logpdf.argtypes = [c_double_p, d, c_double_p, C.c_int, c_double_p]
+    L.orc_wishart_logpdf.restype = d
     L.orc_normal_from_bits.argtypes = [u32, u32]
     L.orc_normal_from_bits.restype = d
     L.orc_normal_at.argtypes = [u64, u64, u32, u32, u32]
@@ -150,6 +154,22 @@ def philox(c, k):
     out = (C.c_uint32 * 4)()
     lib().orc_philox4x32(c[0], c[1], c[2], c[3], k[0], k[1], out)
     return [int(v) for v in out]
+
+
+def mvt_logpdf(y, mu, sigma, nu):
+    """multivariate-t observe* (runtime.cljc:383-401)"""
+    y, mu, sigma = _f64(y), _f64(mu), _f64(sigma)
+    k = mu.size
+    work = np.empty(2 * k * k + k)
+    return lib().orc_mvt_logpdf(_dp(y), _dp(mu), _dp(sigma), float(nu), k, _dp(work))
+
+
+def wishart_logpdf(x, n, V):
+    """wishart observe* (runtime.cljc:536-539)"""
+    x, V = _f64(x), _f64(V)
+    p = int(round(math.sqrt(V.size)))
+    work = np.empty(2 * p * p)
+    return lib().orc_wishart_logpdf(_dp(x), float(n), _dp(V), p, _dp(work))
 
 
 def normal_from_bits(hi, lo):

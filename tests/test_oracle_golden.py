@@ -238,3 +238,23 @@ def test_more_distributions_vs_scipy():
     assert orc.bernoulli_logpmf(2.0, 0.3) == -math.inf
     assert orc.uniform_discrete_logpmf(5.0, 2, 5) == -math.inf       # max is exclusive
     assert orc.binomial_logpmf(6.0, 5, 0.7) == -math.inf
+
+
+def test_wishart_and_mvt_logpdf_goldens():
+    """wishart observe*: the two MATLAB values of runtime_wishart_test.cljc:161-176 (1e-3);
+    both families against scipy (1e-10)."""
+    from scipy import stats
+    assert abs(orc.wishart_logpdf(np.eye(2), 3.5, [[0.7, 0], [0, 0.07]]) - (-5.3950)) < 1e-3
+    assert abs(orc.wishart_logpdf([[3.1, -0.3], [-0.3, 11.0]], 7.5, [[3, 2], [2, 7]]) - (-12.5273)) < 1e-3
+    rng = np.random.default_rng(8)
+    for p in (2, 3, 5):
+        A = rng.normal(size=(p, p))
+        V = A @ A.T + p * np.eye(p)
+        B = rng.normal(size=(p, p))
+        X = B @ B.T + np.eye(p)
+        n = p + 2.5
+        ref = stats.wishart.logpdf(X, n, V)
+        assert abs(orc.wishart_logpdf(X, n, V) - ref) <= 1e-10 * abs(ref)
+        mu, y = rng.normal(size=p), rng.normal(size=p) * 2
+        ref = stats.multivariate_t.logpdf(y, mu, V, 4.5)
+        assert abs(orc.mvt_logpdf(y, mu, V, 4.5) - ref) <= 1e-10 * abs(ref)
