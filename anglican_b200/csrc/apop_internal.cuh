@@ -55,6 +55,7 @@ struct SweepDev {           // device-resident scalars of a fused sweep
     double log_z;           // sum_t log-mean-weight (ipmcmc.cljc:67-74)
     int err;
     int pad;
+    unsigned long long seed; // graph-replayed sweeps read the RNG key from here (see run_group)
 };
 
 // per-step outputs of a fused sweep, written by the tail of k_resolve
@@ -261,6 +262,7 @@ struct ResampleArgs {
     bool sharded;            // world > 1: exchange through the fabric, offspring stored to peers
     PeerI32 anc_peer;        // sharded: anc_peer.p[q] = rank q's ancestor array
     bool keep_err;           // second resample inside a sweep step: error bits stay sticky
+    const unsigned long long* seedp;   // non-null: the RNG key lives in device memory (graph replay)
 };
 int resample_enqueue(apop_ctx* c, const ResampleArgs& a);
 int resample_fetch_info(apop_ctx* c, ResampleInfo* out);   // syncs

@@ -358,9 +358,11 @@ __device__ __forceinline__ double block_sum_f64(double v, double* sm /*[33]*/) {
 __global__ void __launch_bounds__(FB) k_fin_a(WSView v, int64_t n, int64_t n_new, double u_in,
                                               uint64_t seed, uint32_t step, int weights_mode,
                                               double rel_eps, Fabric F, unsigned long long seq,
-                                              int64_t n_global) {
+                                              int64_t n_global,
+                                              const unsigned long long* __restrict__ seedp) {
     __shared__ double smd[33];
     __shared__ int s_last;
+    if (seedp) seed = *seedp;
     __shared__ double pm[kMaxWorld], ps[kMaxWorld];
     __shared__ int perr[kMaxWorld];
     const int64_t nt = v.nt;
@@ -2194,7 +2196,7 @@ int resample_enqueue(apop_ctx* c, const ResampleArgs& a) {
     kt_begin(c, KT_FINALIZE);
     const int fg = (int)((v.nt + FB - 1) / FB);
     k_fin_a<<<fg, FB, 0, c->stream>>>(v, a.n, a.n_new, a.u, c->seed, c->step, wm, a.rel_eps, F, seq,
-                                      n_glob);
+                                      n_glob, a.seedp);
     k_fin_b<<<fg, FB, 0, c->stream>>>(v, a.n, a.rel_eps, g0, n_glob);
     kt_end(c, KT_FINALIZE);
     kt_begin(c, KT_FOLD_AGG);

@@ -68,6 +68,15 @@ struct SweepState {
     size_t lin_w = 0, cap_lin = 0;
     uint64_t sweep_seed = 0;
     int sweep_csmc = 0;
+    // the whole sweep as one CUDA graph, replayed while the shape stays the same
+    cudaGraphExec_t gexec = nullptr;
+    struct GraphKey {
+        int kind, T, hist_mode, csmc, n_cond, reset, want_final, want_filt, no_resample;
+        int64_t n;
+        const void *xa, *xb, *lw, *anc, *y, *ret, *lin, *xf, *ws;
+    } gkey = {};
+    int64_t glaunches = 0;
+    const unsigned long long* seedp = nullptr;   // &sd->seed while a graph is captured / replayed
     double *y = nullptr, *retained = nullptr;
     double *log_mean_w = nullptr, *ess = nullptr, *filt = nullptr;   // device [T]
     double* tsx = nullptr;         // per-tile sum exp(lw - tmax) * x
@@ -91,6 +100,7 @@ void sweep_free(apop_ctx* c) {
     SweepState* s = c->sweep;
     if (!s) return;
     if (s->heap_backed) { s->xa = nullptr; s->xb = nullptr; s->anc = nullptr; }
+    if (s->gexec) cudaGraphExecDestroy(s->gexec);
     void* ptrs[] = {s->xa, s->xb, s->lw, s->anc, s->x_hist, s->anc_hist, s->y, s->retained,
                     s->log_mean_w, s->ess, s->filt, s->tsx, s->x_final, s->sd, s->model, s->traj,
                     s->mvn_mats, s->lse, s->as_anc, s->lin_new, s->lin_alive, s->lin_anc0, s->lin_idx};
@@ -135,8 +145,10 @@ __device__ __forceinline__ int discrete_draw(const double* w, int K, double u) {
 template <int KIND>
 __global__ void __launch_bounds__(TB) k_init(const ModelDev* __restrict__ Mp, double* x,
                                              int64_t n, int64_t g0, uint64_t seed,
-                                             const double* retained) {
+                                             const double* retained,
+                                             const unsigned long long* __restrict__ seedp) {
     const ModelDev& M = *Mp;
+    if (seedp) seed = *seedp;
     const int64_t k0 = ((int64_t)blockIdx.x * TB + threadIdx.x) * 2;
     if (k0 >= n) return;
     double v0, v1;
@@ -381,6 +393,8 @@ __global__ void __launch_bounds__(TB, APOP_PROP_CTAS) k_propagate(const ModelDev
     const ModelDev& M = *Mp;
     const double y = yt[0];
     const double wbase = sd->base;
+    if (accum & 2) seed = sd->seed;              // graph replay: the key lives in device memory
+    accum &= 1;
     __syncthreads();
     // rows of a lineage history start at multiples of n elements: 16-byte aligned
     // only when n is a multiple of 4 (ancestors) / 2 (states)
@@ -796,13 +810,6 @@ static int sweep_begin(apop_ctx* c, const double* retained, const apop_sweep_opt
     const int64_t n = c->n;
     ResampleWS& ws = c->ws;
     const bool csmc = o->csmc && retained;
-    {
-        Timer& tm = c->timers[KT_SWEEP];
-        if (!tm.open && cudaEventCreate(&tm.a) == cudaSuccess) {
-            cudaEventRecord(tm.a, c->stream);
-            tm.open = true;
-        }
-    }
     k_sweep_reset<<<1, 1, 0, c->stream>>>(s->sd, ws.info, ws.gmax, ws.ticket);
     s->sweep_seed = c->seed;
     s->sweep_csmc = csmc ? 1 : 0;
@@ -818,7 +825,7 @@ static int sweep_begin(apop_ctx* c, const double* retained, const apop_sweep_opt
         const int64_t pairs = (n + 1) / 2;
         k_init<(KIND == APOP_SSM_LGMVN) ? APOP_SSM_LGSSM1D : KIND>
             <<<(int)((pairs + TB - 1) / TB), TB, 0, c->stream>>>(
-            s->model, x0, n, c->g0, c->seed, csmc ? s->retained : nullptr);
+            s->model, x0, n, c->g0, c->seed, csmc ? s->retained : nullptr, s->seedp);
     }
     c->launches += 2;
     s->last_x = x0;
@@ -860,14 +867,16 @@ static int sweep_step(apop_ctx* c, int t, const apop_sweep_opts* o, bool csmc) {
         const PeerF64 xpeer = peer_f64(c, (t & 1) ? c->fab.off_xa : c->fab.off_xb);   // x_{t-1}
         k_propagate<(KIND == APOP_SSM_LGMVN) ? APOP_SSM_LGSSM1D : KIND, true><<<pgrid, TB, psmem, c->stream>>>(
             s->model, x_prev, anc_prev, t == 1, x_new, s->lw, s->y + (t - 1), nullptr, s->sd, n,
-            c->g0, c->seed, (uint32_t)t, ws.tmax, ws.tsum, ws.gmax, &ws.info->err, xpeer, 0);
+            c->g0, c->seed, (uint32_t)t, ws.tmax, ws.tsum, ws.gmax, &ws.info->err, xpeer,
+            s->seedp ? 2 : 0);
     } else {
         PeerF64 none;
         memset(&none, 0, sizeof none);
         k_propagate<(KIND == APOP_SSM_LGMVN) ? APOP_SSM_LGSSM1D : KIND, false><<<pgrid, TB, psmem, c->stream>>>(
             s->model, x_prev, anc_prev, t == 1 || o->no_resample, x_new, s->lw, s->y + (t - 1),
             csmc ? s->retained + t : nullptr, s->sd, n, c->g0, c->seed, (uint32_t)t, ws.tmax,
-            ws.tsum, ws.gmax, &ws.info->err, none, (o->no_resample && t > 1) ? 1 : 0);
+            ws.tsum, ws.gmax, &ws.info->err, none,
+            ((o->no_resample && t > 1) ? 1 : 0) | (s->seedp ? 2 : 0));
     }
     kt_end(c, KT_PROPAGATE);
     c->launches += 1;
@@ -891,6 +900,7 @@ static int sweep_step(apop_ctx* c, int t, const apop_sweep_opts* o, bool csmc) {
     a.step.reset = o->reset_weights; a.step.cond = cond ? 1 : 0;
     a.step.has_x = (o->want_filt && dim == 1) ? 1 : 0;
     a.sharded = shard;
+    a.seedp = s->seedp;
     if (shard) a.anc_peer = peer_i32(c, c->fab.off_anc);
     APOP_TRY(resample_enqueue(c, a));
     if (o->ancestor_sampling && cond && KIND != APOP_SSM_LGMVN) {
@@ -952,17 +962,26 @@ static int sweep_end(apop_ctx* c, int T, const apop_sweep_opts* opts, apop_sweep
         kt_end(c, KT_GATHER);
         c->launches += 1;
     }
-    {
-        Timer& tm = c->timers[KT_SWEEP];
-        cudaEvent_t b;
-        if (tm.open && cudaEventCreate(&b) == cudaSuccess) {
-            cudaEventRecord(b, c->stream);
-            tm.pending.push_back({tm.a, b});
-            tm.a = nullptr;
-            tm.open = false;
-        }
-    }
     return APOP_OK;
+}
+
+// device time of the whole sweep (KT_SWEEP): events around the enqueued work
+static void sweep_timer_begin(apop_ctx* c) {
+    Timer& tm = c->timers[KT_SWEEP];
+    if (!tm.open && cudaEventCreate(&tm.a) == cudaSuccess) {
+        cudaEventRecord(tm.a, c->stream);
+        tm.open = true;
+    }
+}
+static void sweep_timer_end(apop_ctx* c) {
+    Timer& tm = c->timers[KT_SWEEP];
+    cudaEvent_t b;
+    if (tm.open && cudaEventCreate(&b) == cudaSuccess) {
+        cudaEventRecord(b, c->stream);
+        tm.pending.push_back({tm.a, b});
+        tm.a = nullptr;
+        tm.open = false;
+    }
 }
 
 // results: one small D2H per requested array, then a single sync
@@ -1009,6 +1028,80 @@ static int sweep_fetch(apop_ctx* c, int T, const apop_sweep_opts* opts, apop_swe
     return APOP_OK;
 }
 
+__global__ void k_set_sweep_seed(SweepDev* sd, unsigned long long seed) { sd->seed = seed; }
+
+// Small populations are bound by launch latency, not by the kernels (BASELINE config 2:
+// ~10 launches per step for 8 MB of state), so the whole sweep - k_sweep_reset, k_init,
+// every step's kernels, the final gather - is captured ONCE as a CUDA graph and replayed
+// for every later sweep of the same shape (infer :smc / :pimh / :pgibbs / IPMCMC nodes run
+// thousands of them).  What changes between sweeps lives in device memory: observations,
+// retained path (staged before the launch) and the RNG key (SweepDev::seed).
+// opts->use_graph: 0 auto (populations up to 2^22 particles), 1 always, -1 never;
+// APOP_GRAPH=0 in the environment disables it.
+static bool graph_wanted(const apop_ctx* c, int kind, const apop_sweep_opts* o) {
+    if (o->use_graph < 0 || c->world > 1 || c->ktimers || o->ancestor_sampling ||
+        kind == APOP_SSM_LGMVN)
+        return false;
+    static int env = -1;
+    if (env < 0) { const char* e = getenv("APOP_GRAPH"); env = (e && e[0] == '0') ? 0 : 1; }
+    if (!env) return false;
+    return o->use_graph > 0 || c->n <= (1LL << 22);
+}
+
+template <int KIND>
+static int sweep_body(apop_ctx* c, int T, const double* retained, const apop_sweep_opts* o,
+                      apop_sweep_result* result) {
+    APOP_TRY(sweep_begin<KIND>(c, retained, o));
+    const bool csmc = o->csmc && retained;
+    for (int t = 1; t <= T; ++t) APOP_TRY(sweep_step<KIND>(c, t, o, csmc));
+    return sweep_end(c, T, o, result);
+}
+
+template <int KIND>
+static int run_graph(apop_ctx* c, int T, const double* retained, const apop_sweep_opts* o,
+                     apop_sweep_result* result) {
+    SweepState* s = c->sweep;
+    SweepState::GraphKey k = {};
+    k.kind = KIND; k.T = T; k.hist_mode = s->hist_mode; k.csmc = (o->csmc && retained) ? 1 : 0;
+    k.n_cond = o->n_cond_steps; k.reset = o->reset_weights;
+    k.want_final = (o->want_final || result->x_final) ? 1 : 0;
+    k.want_filt = o->want_filt; k.no_resample = o->no_resample; k.n = c->n;
+    k.xa = s->xa; k.xb = s->xb; k.lw = s->lw; k.anc = s->anc; k.y = s->y; k.ret = s->retained;
+    k.lin = s->hist_mode == 2 ? (const void*)s->lin_new : (const void*)s->x_hist;
+    k.xf = s->x_final; k.ws = c->ws.slab;
+    k_set_sweep_seed<<<1, 1, 0, c->stream>>>(s->sd, c->seed);
+    s->sweep_seed = c->seed;
+    if (!s->gexec || memcmp(&k, &s->gkey, sizeof k) != 0) {
+        if (s->gexec) { cudaGraphExecDestroy(s->gexec); s->gexec = nullptr; }
+        cudaGraph_t graph = nullptr;
+        const int64_t l0 = c->launches;
+        APOP_CUDA(c, cudaStreamBeginCapture(c->stream, cudaStreamCaptureModeThreadLocal));
+        s->seedp = &s->sd->seed;
+        const int rc = sweep_body<KIND>(c, T, retained, o, result);
+        s->seedp = nullptr;
+        const cudaError_t e = cudaStreamEndCapture(c->stream, &graph);
+        if (rc != APOP_OK) { if (graph) cudaGraphDestroy(graph); return rc; }
+        if (e != cudaSuccess || !graph)
+            return set_err(c, APOP_ERR_CUDA, "sweep graph capture failed: %s", cudaGetErrorString(e));
+        const cudaError_t ei = cudaGraphInstantiate(&s->gexec, graph, 0);
+        cudaGraphDestroy(graph);
+        if (ei != cudaSuccess) {
+            s->gexec = nullptr;
+            return set_err(c, APOP_ERR_CUDA, "sweep graph instantiation failed: %s", cudaGetErrorString(ei));
+        }
+        s->gkey = k;
+        s->glaunches = c->launches - l0;
+        c->launches = l0;
+    }
+    sweep_timer_begin(c);
+    APOP_CUDA(c, cudaGraphLaunch(s->gexec, c->stream));
+    sweep_timer_end(c);
+    c->launches += s->glaunches;
+    c->step = (uint32_t)T;
+    s->sweep_csmc = k.csmc;
+    return APOP_OK;
+}
+
 template <int KIND>
 static int run_group(apop_ctx* const* g, int ng, const double* y, int T, const double* retained,
                      const apop_sweep_opts* o, apop_sweep_result* results) {
@@ -1016,8 +1109,13 @@ static int run_group(apop_ctx* const* g, int ng, const double* y, int T, const d
         cudaSetDevice(g[i]->device);
         APOP_TRY(sweep_stage(g[i], y, T, retained, o));
     }
+    if (ng == 1 && graph_wanted(g[0], KIND, o)) {
+        APOP_TRY(run_graph<KIND>(g[0], T, retained, o, &results[0]));
+        return sweep_fetch(g[0], T, o, &results[0]);
+    }
     for (int i = 0; i < ng; ++i) {
         if (ng > 1) cudaSetDevice(g[i]->device);
+        sweep_timer_begin(g[i]);
         APOP_TRY(sweep_begin<KIND>(g[i], retained, o));
     }
     const bool csmc = o->csmc && retained;
@@ -1029,6 +1127,7 @@ static int run_group(apop_ctx* const* g, int ng, const double* y, int T, const d
     for (int i = 0; i < ng; ++i) {
         if (ng > 1) cudaSetDevice(g[i]->device);
         APOP_TRY(sweep_end(g[i], T, o, &results[i]));
+        sweep_timer_end(g[i]);
     }
     int rc = APOP_OK;
     for (int i = 0; i < ng; ++i) {

@@ -380,7 +380,7 @@ class Population:
 
     def sweep(self, model, y, retained=None, csmc=False, n_cond_steps=0, reset_weights=False,
               keep_history=False, want_final=True, want_stats=True, want_filt=None,
-              pinned_final=False, no_resample=False, ancestor_sampling=False):
+              pinned_final=False, no_resample=False, ancestor_sampling=False, use_graph=0):
         """One `sweep` (smc.cljc:35-51; conditional: pgibbs.cljc:76-110,
         ipmcmc.cljc:34-83).  Returns a SweepOutput.  pinned_final: x_final is a
         view of a page-locked buffer owned by the population, overwritten by its
@@ -402,7 +402,7 @@ class Population:
         if keep_history == "compact":
             keep_history = 2 if d == 1 else 1
         opts = L.ApopSweepOpts(int(csmc), int(n_cond_steps), int(reset_weights),
-                               int(keep_history), 0, int(want_final), int(bool(want_filt)),
+                               int(keep_history), int(use_graph), int(want_final), int(bool(want_filt)),
                                int(bool(no_resample)), int(bool(ancestor_sampling)))
         res = L.ApopSweepResult()
         out = SweepOutput(self, T, d)

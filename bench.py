@@ -75,6 +75,29 @@ def sv_observations(T, seed=20240602, phi=0.98, sigma=0.16, beta=0.65):
     return ys
 
 
+def lgssm_observations(T, seed=20240601):
+    """BASELINE config 2: x0 ~ N(0,1), x_t = 0.9 x_{t-1} + N(0,1), y_t = x_t + N(0,1)"""
+    rng = np.random.default_rng(seed)
+    x = rng.normal()
+    ys = np.empty(T)
+    for t in range(T):
+        x = 0.9 * x + rng.normal()
+        ys[t] = x + rng.normal()
+    return ys
+
+
+def kalman_logz(y, a=0.9, q=1.0, c=1.0, r=1.0, m0=0.0, s0=1.0):
+    """exact log-marginal of the 1-D linear-Gaussian model (the check BASELINE config 2 names)"""
+    m, P, lz = m0, s0 * s0, 0.0
+    for yt in y:
+        m, P = a * m, a * a * P + q * q
+        S = c * c * P + r * r
+        lz += -0.5 * math.log(2 * math.pi * S) - 0.5 * (yt - c * m) ** 2 / S
+        K = P * c / S
+        m, P = m + K * (yt - c * m), (1 - K * c) * P
+    return lz
+
+
 def lgmvn_workload(T, d=64):
     """BASELINE config 5: A = 0.9 Q, process cov 0.1 I, obs cov 0.5 I + 0.5 11^T/d"""
     rng = np.random.default_rng(20240603)
@@ -166,6 +189,9 @@ def oracle_sample(args, T_cap):
         return m, y[:T_s * 64], n_s, T_s, "64-dim linear-Gaussian sweep"
     # 2^20 particles: 24 MB of state per array, beyond the host's L2
     n_s, T_s = 1 << 20, min(args.T, T_cap)
+    if args.workload == "lgssm1d":
+        m = orc.Model(orc.SSM_LGSSM1D, m0=0.0, s0=1.0, a=0.9, b=0.0, q=1.0, c=1.0, d=0.0, r=1.0)
+        return m, lgssm_observations(args.T)[:T_s], n_s, T_s, "1-D linear-Gaussian sweep"
     phi, sigma, beta = 0.98, 0.16, 0.65
     m = orc.Model(orc.SSM_SV, m0=0.0, s0=sigma / math.sqrt(1 - phi * phi), a=phi, b=0.0, q=sigma,
                   beta=beta)
@@ -295,6 +321,10 @@ def run_ours(args):
         from anglican_b200.models import LinearGaussianMVN
         A, Qc, R, y = lgmvn_workload(T, dim)
         model = LinearGaussianMVN(A, Qc, R)
+    elif args.workload == "lgssm1d":
+        from anglican_b200.models import LinearGaussian1D
+        y = lgssm_observations(T)
+        model = LinearGaussian1D()
     else:
         y = sv_observations(T)
         model = StochasticVolatility()
@@ -465,6 +495,7 @@ def run_ours(args):
                 "config": {"workload": args.workload_name, "particles_total": n_total,
                            "particles_per_gpu": n_local, "T": T,
                            "model": ("64-dim linear-Gaussian SSM, mvn observe (DMMA)" if mvn else
+                                     "1-D linear-Gaussian a=0.9 q=1 r=1" if args.workload == "lgssm1d" else
                                      "stochastic volatility phi=0.98 sigma=0.16 beta=0.65"),
                            "resampling": "systematic, every step",
                            "sweeps_in_flight": F,
@@ -478,6 +509,10 @@ def run_ours(args):
                 "gpu_launches": int(launches), "clocks": clocks, "roofline": roof,
                 "path_roofline": path, "wall_ms_per_step": 1e3 * wall / args.steps,
                 "log_z_mean": float(np.mean(log_zs)), "log_z_check": logz_note}
+        if args.workload == "lgssm1d":
+            kz = kalman_logz(y)
+            line["kalman_check"] = {"exact_log_z": kz, "max_abs_error_of_timed_sweeps":
+                                    float(max(abs(z - kz) for z in log_zs))}
         if dev1_s > 0.0:
             v1 = float(n_total) * T * args.steps / dev1_s
             line["one_sweep_in_flight"] = {"value": v1, "unit": UNIT,
@@ -547,8 +582,9 @@ def main():
     ap.add_argument("--steps", type=int, default=2)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="sv", choices=["sv", "lgmvn64"],
-                    help="sv: BASELINE configs[2] (the headline); lgmvn64: configs[4]")
+    ap.add_argument("--workload", default="sv", choices=["sv", "lgmvn64", "lgssm1d"],
+                    help="sv: BASELINE configs[2] (the headline); lgmvn64: configs[4]; "
+                         "lgssm1d: configs[1] (2^20 particles, T=1000, Kalman check)")
     ap.add_argument("--particles", type=int, default=0)
     ap.add_argument("--T", type=int, default=0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -573,6 +609,12 @@ def main():
         args.T = args.T or 100
         args.workload_name = ("configs[4]: 64-dim linear-Gaussian SSM, mvn observe, T=%d, %d particles "
                               ":smc sharded over %d B200" % (args.T, args.particles, args.gpus))
+    elif args.workload == "lgssm1d":
+        args.particles = args.particles or (1 << 20)
+        args.T = args.T or 1000
+        args.workload_name = ("configs[1]: linear-Gaussian SSM, 1-D latent, T=%d, %d particles :smc on "
+                              "%d B200 (log-marginal checked vs the exact Kalman filter)"
+                              % (args.T, args.particles, args.gpus))
     else:
         args.particles = args.particles or (1 << 27)
         args.T = args.T or 2000

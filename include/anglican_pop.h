@@ -240,7 +240,10 @@ typedef struct {
                                 * 2 compact (scalar-state models): two bits per particle and
                                 * step, the states of the ONE traced lineage are recomputed
                                 * from the counter-based RNG (pgibbs.cljc:29-35, 122-123) */
-    int32_t use_graph;         /* capture the step loop in a CUDA graph */
+    int32_t use_graph;         /* the whole sweep as ONE CUDA graph, captured at the first sweep of a
+                                * shape and replayed afterwards (small populations are bound by
+                                * launch latency): 0 auto (up to 2^22 particles, one GPU, scalar
+                                * state), 1 always, -1 never.  Results are bit-identical. */
     int32_t want_final;        /* gather final states into x_final */
     int32_t want_filt;         /* per-step filtering means sum w x / sum w (reads x once more) */
     int32_t no_resample;       /* `infer :importance` (importance.cljc:16-22): every observe only
