@@ -13,7 +13,7 @@ LIB_PATH = os.path.join(HERE, "libanglican_pop.so")
 APOP_OK = 0
 ERR_NAMES = {0: "APOP_OK", -1: "APOP_ERR_INVALID", -2: "APOP_ERR_CUDA", -3: "APOP_ERR_NAN_WEIGHT",
              -4: "APOP_ERR_ZERO_WEIGHT", -5: "APOP_ERR_NCCL", -6: "APOP_ERR_OOM",
-             -7: "APOP_ERR_UNSUPPORTED", -8: "APOP_ERR_INTERNAL", -9: "APOP_ERR_NOT_GLOBAL"}
+             -7: "APOP_ERR_UNSUPPORTED", -8: "APOP_ERR_INTERNAL"}
 F64, I32 = 0, 1
 SYSTEMATIC, MULTINOMIAL = 0, 1
 ORDER_REFERENCE, ORDER_SORTED, ORDER_EMISSION = 0, 1, 2

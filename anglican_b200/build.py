@@ -11,7 +11,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 OUT = os.path.join(HERE, "libanglican_pop.so")
 SOURCES = ["ctx.cu", "comm.cu", "resample.cu", "dists.cu", "ssm.cu", "mvn.cu", "stats.cu", "dists2.cu", "dists3.cu"]
-HEADERS = ["apop_internal.cuh", "exact_fold.cuh", "rng.cuh", "fabric.cuh", "fastmath.cuh", "fastmath_coef.inc", "normal_table.inc", "gamma_draw.cuh",
+HEADERS = ["apop_internal.cuh", "exact_fold.cuh", "rng.cuh", "fabric.cuh", "fastmath.cuh", "fastmath_coef.inc", "gamma_draw.cuh",
            os.path.join("..", "..", "include", "anglican_pop.h")]
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = ["-O3", "-std=c++17", "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo",

@@ -27,7 +27,8 @@ enum {
     EB_CTX = 4,          // classification / chain context mismatch (internal)
     EB_COMB = 8,         // comb table overflow / stuck comb
     EB_COUNT = 16,       // emitted offspring count mismatch (internal)
-    EB_COMM = 32         // a peer rank never arrived at an exchange (spin timeout)
+    EB_COMM = 32,        // a peer rank never arrived at an exchange (spin timeout)
+    EB_INF = 64          // +inf log-weight in a fused sweep (infinite observe density)
 };
 
 struct ResampleInfo {
@@ -270,6 +271,7 @@ int info_to_status(apop_ctx* c, const ResampleInfo& info);
 int multinomial_enqueue(apop_ctx* c, const double* lw, const double* w, const double* uni,
                         int64_t n_new, int32_t* anc);
 int stat_lse_enqueue(apop_ctx* c, const double* lw, int64_t n, double* out2);   // stats.cu
+int stat_lse_prepare(apop_ctx* c);
 int gather_enqueue(apop_ctx* c, const int32_t* anc, int64_t n_new, Column* col);
 // mvn.cu: fp64 tensor-core (DMMA) kernels
 struct MvnSweepArgs {

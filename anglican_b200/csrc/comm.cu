@@ -25,10 +25,6 @@ struct NcclApi {
     int (*CommInitRank)(ncclComm_t*, int, ncclUniqueId, int) = nullptr;
     int (*CommDestroy)(ncclComm_t) = nullptr;
     int (*AllGather)(const void*, void*, size_t, int, ncclComm_t, cudaStream_t) = nullptr;
-    int (*Send)(const void*, size_t, int, int, ncclComm_t, cudaStream_t) = nullptr;
-    int (*Recv)(void*, size_t, int, int, ncclComm_t, cudaStream_t) = nullptr;
-    int (*GroupStart)() = nullptr;
-    int (*GroupEnd)() = nullptr;
     const char* (*GetErrorString)(int) = nullptr;
     bool ok = false;
 };
@@ -50,11 +46,9 @@ static bool nccl_load() {
     g_nccl.handle = h;
 #define LOAD(sym) *(void**)(&g_nccl.sym) = dlsym(h, "nccl" #sym)
     LOAD(GetUniqueId); LOAD(CommInitRank); LOAD(CommDestroy); LOAD(AllGather);
-    LOAD(Send); LOAD(Recv); LOAD(GroupStart); LOAD(GroupEnd); LOAD(GetErrorString);
+    LOAD(GetErrorString);
 #undef LOAD
-    g_nccl.ok = g_nccl.GetUniqueId && g_nccl.CommInitRank && g_nccl.CommDestroy &&
-                g_nccl.AllGather && g_nccl.Send && g_nccl.Recv && g_nccl.GroupStart &&
-                g_nccl.GroupEnd;
+    g_nccl.ok = g_nccl.GetUniqueId && g_nccl.CommInitRank && g_nccl.CommDestroy && g_nccl.AllGather;
     return g_nccl.ok;
 }
 
@@ -99,25 +93,6 @@ int comm_allgather_dev(apop_ctx* c, const void* send, void* recv, size_t bytes) 
         return APOP_OK;
     }
     APOP_NCCL(c, g_nccl.AllGather(send, recv, bytes, ncclChar, (ncclComm_t)c->nccl, c->stream));
-    return APOP_OK;
-}
-
-// grouped point-to-point exchange: for each peer, send_bytes[p] from send_ptr[p]
-// and recv_bytes[p] into recv_ptr[p] (zero-byte entries skipped)
-int comm_exchange_dev(apop_ctx* c, void* const* send_ptr, const size_t* send_bytes,
-                      void* const* recv_ptr, const size_t* recv_bytes) {
-    if (c->world == 1) return APOP_OK;
-    APOP_NCCL(c, g_nccl.GroupStart());
-    for (int p = 0; p < c->world; ++p) {
-        if (p == c->rank) continue;
-        if (send_bytes[p])
-            APOP_NCCL(c, g_nccl.Send(send_ptr[p], send_bytes[p], ncclChar, p, (ncclComm_t)c->nccl,
-                                     c->stream));
-        if (recv_bytes[p])
-            APOP_NCCL(c, g_nccl.Recv(recv_ptr[p], recv_bytes[p], ncclChar, p, (ncclComm_t)c->nccl,
-                                     c->stream));
-    }
-    APOP_NCCL(c, g_nccl.GroupEnd());
     return APOP_OK;
 }
 

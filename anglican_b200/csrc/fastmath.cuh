@@ -167,5 +167,93 @@ __device__ __forceinline__ void weights_v(const double (&lw)[N], double m, doubl
     exp_core_v<N>(w);
 }
 
+// N Box-Muller pairs: (u1, u2) -> (z0, z1) = sqrt(-2 log u1) (cos, sin)(2 pi u2)
+template <int N>
+__device__ __forceinline__ void box_muller_v(const double (&u1)[N], const double (&u2)[N],
+                                             double (&z0)[N], double (&z1)[N]) {
+    const double one = kC[M_ONE], half = kC[M_HALF], two = kC[M_TWO], magic = kC[M_MAGIC];
+    double s[N], zq[N], ed[N], rad[N];
+    // ---- log(u1): atanh series on the reduced mantissa
+#pragma unroll
+    for (int i = 0; i < N; ++i) {
+        int hi = __double2hiint(u1[i]);
+        const int lo = __double2loint(u1[i]);
+        int e = (hi >> 20) - 1023;
+        hi = (hi & 0x000fffff) | 0x3ff00000;
+        if (hi > 0x3ff6a09e) { hi -= 0x00100000; e += 1; }
+        const double f = __hiloint2double(hi, lo) - one;
+        const double d = two + f;
+        double y = rcp_approx(d);
+        double t = fma(-d, y, one);
+        y = fma(y, t, y);
+        t = fma(-d, y, one);
+        y = fma(y, t, y);
+        const double q = f * y;
+        s[i] = fma(fma(-d, q, f), y, q);
+        zq[i] = s[i] * s[i];
+        ed[i] = (double)e;
+    }
+    double q[N];
+    const double cq = kC[OFF_Q + FM_NQ - 1];
+#pragma unroll
+    for (int i = 0; i < N; ++i) q[i] = cq;
+#pragma unroll
+    for (int k = FM_NQ - 2; k >= 0; --k) {
+        const double c = kC[OFF_Q + k];
+#pragma unroll
+        for (int i = 0; i < N; ++i) q[i] = fma(q[i], zq[i], c);
+    }
+    const double lh = kC[M_LN2HI], ll = kC[M_LN2LO], neg2 = kC[M_NEG2];
+#pragma unroll
+    for (int i = 0; i < N; ++i) {
+        const double lm = fma(s[i] * zq[i], q[i], fma(ed[i], ll, s[i] + s[i]));
+        const double a = neg2 * fma(ed[i], lh, lm);               // -2 log u1 > 0
+        double y = rsqrt_approx(a);
+        double g = a * y, h = half * y;
+        double r = fma(-h, g, half);
+        g = fma(g, r, g); h = fma(h, r, h);
+        r = fma(-h, g, half);
+        g = fma(g, r, g); h = fma(h, r, h);
+        rad[i] = fma(fma(-g, g, a), h, g);
+    }
+    // ---- sincospi(2 u2)
+    double rr[N], sp[N], cp[N];
+    int qi[N];
+#pragma unroll
+    for (int i = 0; i < N; ++i) {
+        const double t = u2[i] + u2[i];
+        const double kk = fma(t, two, magic);
+        qi[i] = __double2loint(kk);
+        rr[i] = fma(kk - magic, -half, t);
+        zq[i] = rr[i] * rr[i];
+    }
+    const double cs0 = kC[OFF_S + FM_NS - 1], cc0 = kC[OFF_C + FM_NC - 1];
+#pragma unroll
+    for (int i = 0; i < N; ++i) { sp[i] = cs0; cp[i] = cc0; }
+#pragma unroll
+    for (int k = FM_NS - 2; k >= 0; --k) {
+        const double c = kC[OFF_S + k];
+#pragma unroll
+        for (int i = 0; i < N; ++i) sp[i] = fma(sp[i], zq[i], c);
+    }
+#pragma unroll
+    for (int k = FM_NC - 2; k >= 0; --k) {
+        const double c = kC[OFF_C + k];
+#pragma unroll
+        for (int i = 0; i < N; ++i) cp[i] = fma(cp[i], zq[i], c);
+    }
+#pragma unroll
+    for (int i = 0; i < N; ++i) {
+        const double sv = sp[i] * rr[i];
+        const double a = (qi[i] & 1) ? cp[i] : sv;
+        const double b = (qi[i] & 1) ? sv : cp[i];
+        const double sn = (qi[i] & 2) ? -a : a;
+        const double cs = ((qi[i] + 1) & 2) ? -b : b;
+        z0[i] = rad[i] * cs;
+        z1[i] = rad[i] * sn;
+    }
+}
+
+
 } // namespace fm
 } // namespace apop

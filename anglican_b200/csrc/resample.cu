@@ -1220,7 +1220,7 @@ __global__ void __launch_bounds__(TB) k_chain(const double* __restrict__ lw,
         tg2 = gtimer_ns();
     }
     __syncthreads();
-    if (I->err & (EB_ZERO | EB_COMB | EB_NAN)) {
+    if (I->err & (EB_ZERO | EB_COMB | EB_NAN | EB_INF)) {
         for (int i = threadIdx.x; i <= v.nb; i += TB) v.sblk[1][i] = INFINITY;
         for (int i = threadIdx.x; i < I->nh1; i += TB) { v.shin[1][i] = INFINITY; v.shout[1][i] = INFINITY; }
         if (threadIdx.x == 0) v.send[1] = INFINITY;
@@ -2236,6 +2236,12 @@ int info_to_status(apop_ctx* c, const ResampleInfo& I) {
     if (I.err & EB_NAN)
         return set_err(c, APOP_ERR_NAN_WEIGHT,
                        "NaN (or negative) weight: the reference's resample would not terminate");
+    if (I.err & EB_INF)
+        return set_err(c, APOP_ERR_NAN_WEIGHT,
+                       "+inf log-weight in a fused sweep (an observe with infinite density): the "
+                       "reference would give those particles weight 1, all others 0 and -inf "
+                       "afterwards (smc.cljc:78-82, 98-103); the fused sweep reports it instead "
+                       "(the column-level apop_resample follows the reference)");
     if (I.err & EB_ZERO)
         return set_err(c, APOP_ERR_ZERO_WEIGHT, "total weight is not a positive finite number");
     if (I.err & EB_COMM)

@@ -59,133 +59,49 @@ __host__ __device__ __forceinline__ double uniform_at(uint64_t seed, uint64_t sl
 #if defined(__CUDACC__)
 } // namespace apop
 #include "fastmath.cuh"
-#include "normal_table.inc"
 namespace apop {
-
-// ---- Gaussian draws: table-driven inverse CDF --------------------------------
-// The reference draws normals with commons-math nextGaussian on an unseeded
-// Well19937c (runtime.cljc:142-147, 403-409), so only distributional parity is
-// meaningful.  64 random bits -> z = sign * Q(v), Q = -Phi^-1, v uniform on
-// [0, 1/2) built from 52 of the bits: the exponent field and the top NT_LOG2K
-// mantissa bits of v select a row of NT_TABLE (tools/gen_normal_table.py), a
-// degree-4 polynomial in d = v - (row centre), |fit - Q| < 5e-12.  6 fp64
-// instructions and three 16-byte table reads per draw, against 28 fp64
-// instructions for fp64 Box-Muller.  v < 2^-(NT_OCT+1) (2^-NT_OCT of the draws)
-// takes normal_tail.  The oracle restates the same map from its own copy of the
-// table, so whole sweeps compare number for number.
-static __device__ const double g_ntab[NT_ROWS * NT_STRIDE] = {NT_TABLE};
-
-// far tail: v extended by 11 more random bits, Q(v) by Newton on erfc from the
-// Abramowitz-Stegun 26.2.23 start (3 steps: 4.5e-4 -> 1e-6 -> 1e-12 -> fp64)
-static __device__ __noinline__ double normal_tail(uint32_t hi, uint32_t lo) {
-    const double v = __hiloint2double((int)((hi & 0x000fffffu) | 0x3fe00000u), (int)lo) - 0.5;
-    const double ve = v + ((double)((hi >> 20) & 0x7ffu) + 0.5) * 5.42101086242752217e-20;   // 2^-64
-    const double t = sqrt(-2.0 * log(ve));
-    double z = t - (2.515517 + t * (0.802853 + t * 0.010328)) /
-                       (1.0 + t * (1.432788 + t * (0.189269 + t * 0.001308)));
-#pragma unroll 1
-    for (int it = 0; it < 3; ++it) {
-        const double tailp = 0.5 * erfc(z * 0.70710678118654752440);
-        const double dens = exp(-0.5 * z * z) * 0.39894228040143267794;
-        z = z + (tailp - ve) / dens;
-    }
-    return (hi & 0x80000000u) ? -z : z;
-}
-
-// tab: NT_TABLE in global memory (g_ntab, COPIES = 1) or replicated in shared memory
-// (hot kernels).  Shared-memory layout: the 16-byte word k of row r, copy c, sits at
-// double2 index (3 r + k) * COPIES + c; lane l reads copy l % COPIES, so the lanes
-// of a quarter warp that share a bank group are 1 in COPIES / 8 instead of all
-// (random rows: a 24 KB table read by 32 lanes at random is bank-conflict bound
-// otherwise - measured, k_propagate 992 -> 1368 us with a single copy).
-// idx < 0: the draw belongs to the tail and the returned value must be replaced by
-// normal_tail(hi, lo).
-template <int COPIES>
-__device__ __forceinline__ double normal_core(const double* __restrict__ tab, uint32_t hi,
-                                              uint32_t lo, int& idx, int copy = 0) {
-    const double v = __hiloint2double((int)((hi & 0x000fffffu) | 0x3fe00000u), (int)lo) - 0.5;
-    const int vh = __double2hiint(v);
-    idx = (vh >> (20 - NT_LOG2K)) - ((1022 - NT_OCT) << NT_LOG2K);
-    const double mid = __hiloint2double((vh & ~((1 << (20 - NT_LOG2K)) - 1)) | (1 << (19 - NT_LOG2K)), 0);
-    const double d = v - mid;                                   // exact
-    const double2* row = reinterpret_cast<const double2*>(tab) + (max(idx, 0) * 3 * COPIES + copy);
-    const double2 c01 = row[0];
-    const double2 c23 = row[COPIES];
-    const double c4 = row[2 * COPIES].x;
-    double p = fma(c4, d, c23.y);
-    p = fma(p, d, c23.x);
-    p = fma(p, d, c01.y);
-    p = fma(p, d, c01.x);
-    return __hiloint2double(__double2hiint(p) ^ (int)(hi & 0x80000000u), __double2loint(p));
-}
-__device__ __forceinline__ double normal_from_bits(const double* __restrict__ tab, uint32_t hi,
-                                                   uint32_t lo) {
-    int idx;
-    const double z = normal_core<1>(tab, hi, lo, idx);
-    return (idx < 0) ? normal_tail(hi, lo) : z;
-}
-
-// cooperative copy of the table into shared memory, COPIES times (caller synchronises)
-template <int COPIES>
-__device__ __forceinline__ void normal_table_to_smem(double* s_tab) {
-    const double2* src = reinterpret_cast<const double2*>(g_ntab);
-    double2* dst = reinterpret_cast<double2*>(s_tab);
-    for (int i = threadIdx.x; i < NT_ROWS * 3; i += blockDim.x) {
-        const double2 w = src[i];
-#pragma unroll
-        for (int c = 0; c < COPIES; ++c) dst[i * COPIES + c] = w;
-    }
-}
-
-// normals of the slot pair (2p, 2p+1) come from ONE Philox block: words (x, y)
-// -> even slot, (z, w) -> odd slot
-__device__ __forceinline__ void normal_pair_at(const double* __restrict__ tab, uint64_t seed,
-                                               uint64_t pair, uint32_t t, uint32_t stream,
-                                               uint32_t draw, double& z0, double& z1) {
-    U4 o = philox4x32_10((uint32_t)pair, (uint32_t)(pair >> 32), t, ctr3(stream, 0, draw),
-                         (uint32_t)seed, (uint32_t)(seed >> 32));
-    z0 = normal_from_bits(tab, o.x, o.y);
-    z1 = normal_from_bits(tab, o.z, o.w);
-}
+// Gaussian draws: fp64 Box-Muller on one Philox block per slot pair (the reference's
+// nextGaussian runs on an unseeded Well19937c, runtime.cljc:142-147, 403-409: only
+// distributional parity is meaningful).  A table-driven inverse CDF (piecewise degree-4
+// polynomial, 24 KB in shared memory) was built and measured in round 2: fewer
+// instructions (132 vs 150 per particle) but k_propagate went from 992 to 1341 us -
+// the per-lane table reads stall on the shared-memory scoreboard and leave the issue
+// slots 36 % busy (profiles/r02_table_normal_experiment.md).  Box-Muller stays.
+// Box-Muller pair for the slot pair (2p, 2p+1): z0 -> even slot, z1 -> odd.
 __device__ __forceinline__ void normal_pair_at(uint64_t seed, uint64_t pair, uint32_t t,
                                                uint32_t stream, uint32_t draw, double& z0,
                                                double& z1) {
-    normal_pair_at(g_ntab, seed, pair, t, stream, draw, z0, z1);
+    U4 o = philox4x32_10((uint32_t)pair, (uint32_t)(pair >> 32), t, ctr3(stream, 0, draw),
+                         (uint32_t)seed, (uint32_t)(seed >> 32));
+    double u1 = u01_open(o.x, o.y);
+    double u2 = u01_half(o.z, o.w);
+    double r = fm::sqrt_fast(-2.0 * fm::log_core(u1));     // u1 in [2^-54, 1): normal, < 1
+    double s, c;
+    fm::sincospi_core(u2 + u2, s, c);
+    z0 = r * c;
+    z1 = r * s;
 }
-// NP consecutive pairs (slots 2 pair0 .. 2 pair0 + 2 NP - 1) from a table replicated
-// COPIES times in shared memory.  One tail test for the whole batch: the fix-up
-// (2^-16 of the draws) recomputes the Philox block.
-template <int NP, int COPIES>
-__device__ __forceinline__ void normal_pairs_at(const double* __restrict__ tab, uint64_t seed,
-                                                uint64_t pair0, uint32_t t, uint32_t stream,
-                                                uint32_t draw, double (&z0)[NP], double (&z1)[NP]) {
-    int any = 0;
-    const int copy = (int)(threadIdx.x & (COPIES - 1));
+// four consecutive pairs (slots 8p .. 8p+7 when pair0 = 4p): vectorised Box-Muller
+template <int NP>
+__device__ __forceinline__ void normal_pairs_at(uint64_t seed, uint64_t pair0, uint32_t t,
+                                                uint32_t stream, uint32_t draw,
+                                                double (&z0)[NP], double (&z1)[NP]) {
+    double u1[NP], u2[NP];
 #pragma unroll
     for (int i = 0; i < NP; ++i) {
         const uint64_t pair = pair0 + i;
         U4 o = philox4x32_10((uint32_t)pair, (uint32_t)(pair >> 32), t, ctr3(stream, 0, draw),
                              (uint32_t)seed, (uint32_t)(seed >> 32));
-        int i0, i1;
-        z0[i] = normal_core<COPIES>(tab, o.x, o.y, i0, copy);
-        z1[i] = normal_core<COPIES>(tab, o.z, o.w, i1, copy);
-        any |= i0 | i1;
+        u1[i] = u01_open(o.x, o.y);
+        u2[i] = u01_half(o.z, o.w);
     }
-    if (any < 0) {
-#pragma unroll 1
-        for (int i = 0; i < NP; ++i) {
-            double a, b;
-            normal_pair_at(g_ntab, seed, pair0 + i, t, stream, draw, a, b);
-            z0[i] = a; z1[i] = b;
-        }
-    }
+    fm::box_muller_v<NP>(u1, u2, z0, z1);
 }
 __device__ __forceinline__ double normal_at(uint64_t seed, uint64_t slot, uint32_t t,
                                             uint32_t stream, uint32_t draw) {
-    const uint64_t pair = slot >> 1;
-    U4 o = philox4x32_10((uint32_t)pair, (uint32_t)(pair >> 32), t, ctr3(stream, 0, draw),
-                         (uint32_t)seed, (uint32_t)(seed >> 32));
-    return (slot & 1) ? normal_from_bits(g_ntab, o.z, o.w) : normal_from_bits(g_ntab, o.x, o.y);
+    double z0, z1;
+    normal_pair_at(seed, slot >> 1, t, stream, draw, z0, z1);
+    return (slot & 1) ? z1 : z0;
 }
 #endif
 

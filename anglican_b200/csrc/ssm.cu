@@ -30,12 +30,6 @@
 #ifndef APOP_PROP_CTAS
 #define APOP_PROP_CTAS 2
 #endif
-// copies of the inverse-normal table in shared memory (rng.cuh normal_core): 4 copies
-// x 24 KB per CTA, two CTAs per SM; the CTAs are persistent (they walk the tiles with
-// stride gridDim.x) so that the table is staged once per CTA, not once per tile
-#ifndef APOP_NTAB_COPIES
-#define APOP_NTAB_COPIES 4
-#endif
 
 namespace apop {
 
@@ -157,7 +151,7 @@ __global__ void __launch_bounds__(TB) k_init(const ModelDev* __restrict__ Mp, do
         v1 = discrete_draw(M.hmm_init, M.dim, uniform_at(seed, (uint64_t)(g0 + k0 + 1), 0, STREAM_INIT, 0));
     } else {
         double z0, z1;
-        normal_pair_at(seed, (uint64_t)(g0 + k0) >> 1, 0, STREAM_INIT, 0, z0, z1);   // global table
+        normal_pair_at(seed, (uint64_t)(g0 + k0) >> 1, 0, STREAM_INIT, 0, z0, z1);
         v0 = M.m0 + M.s0 * z0;
         v1 = M.m0 + M.s0 * z1;
     }
@@ -178,7 +172,7 @@ __device__ __forceinline__ float ex2_approx(float x) {
 }
 
 template <int KIND, bool FULL, bool SHARD>
-__device__ __forceinline__ void propagate_tile(const int tile, const PeerF64& xpeer,
+__device__ __forceinline__ void propagate_tile(const PeerF64& xpeer,
                                                const ModelDev& M, const double* __restrict__ xp,
                                                const int32_t* __restrict__ anc, int first_step,
                                                double* __restrict__ xn, double* __restrict__ lw,
@@ -186,12 +180,10 @@ __device__ __forceinline__ void propagate_tile(const int tile, const PeerF64& xp
                                                double wbase, int64_t n, int64_t g0, uint64_t seed,
                                                uint32_t t, double* __restrict__ tmax,
                                                double* __restrict__ tsum, long long* gmax,
-                                               int* errflag,
-                                               const double* __restrict__ s_tab, int accum,
-                                               bool aligned) {
+                                               int* errflag, int accum, bool aligned) {
     __shared__ double red_mx[NWARP];
     __shared__ float red_ref[NWARP], red_s[NWARP];
-    const int64_t base = (int64_t)tile * TILE;
+    const int64_t base = (int64_t)blockIdx.x * TILE;
     const int64_t i0 = base + (int64_t)threadIdx.x * IPT;
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     constexpr int HW = APOP_PROP_HW;              // particles per sub-step (register budget)
@@ -258,7 +250,7 @@ __device__ __forceinline__ void propagate_tile(const int tile, const PeerF64& xp
             }
         } else {
             double z0[HW / 2], z1[HW / 2];
-            normal_pairs_at<HW / 2, APOP_NTAB_COPIES>(s_tab, seed, (uint64_t)(g0 + ih) >> 1, t, STREAM_TRANSITION, 0, z0, z1);
+            normal_pairs_at<HW / 2>(seed, (uint64_t)(g0 + ih) >> 1, t, STREAM_TRANSITION, 0, z0, z1);
 #pragma unroll
             for (int j = 0; j < HW; j += 2) {
                 x[j] = (M.a * x[j] + M.b) + M.q * z0[j >> 1];              // sd*z + mean
@@ -338,7 +330,7 @@ __device__ __forceinline__ void propagate_tile(const int tile, const PeerF64& xp
         }
 #undef VALID
     }
-    if (bad) atomicOr(errflag, EB_NAN);
+    if (bad) atomicOr(errflag, (mx == INFINITY) ? EB_INF : EB_NAN);
     // ---- warp: common fp32 reference, rescaled sums; exact max
     float wref = ref;
 #pragma unroll
@@ -365,15 +357,15 @@ __device__ __forceinline__ void propagate_tile(const int tile, const PeerF64& xp
         // all log-weights -inf: every weight is 1 (smc.cljc:80)
         if (!(m > -INFINITY)) a = (double)((n - base < TILE) ? (n - base) : TILE);
         if (lane == 0) {
-            tmax[tile] = m; tsum[tile] = a;
+            tmax[blockIdx.x] = m; tsum[blockIdx.x] = a;
             atomicMax(gmax, dkey(m));                 // global max for k_fin_a (smc.cljc:75)
         }
     }
 }
 
-constexpr size_t kPropSmem = (size_t)APOP_NTAB_COPIES * NT_ROWS * 3 * sizeof(double2);
-
-template <int KIND, bool SHARD>
+// GSEED: the RNG key is read from SweepDev (sweeps replayed from a CUDA graph); otherwise it
+// is a kernel parameter, i.e. a constant-bank operand of the Philox rounds
+template <int KIND, bool SHARD, bool GSEED>
 __global__ void __launch_bounds__(TB, APOP_PROP_CTAS) k_propagate(const ModelDev* __restrict__ Mp,
                                                   const double* __restrict__ xp,
                                                   const int32_t* __restrict__ anc, int first_step,
@@ -387,30 +379,21 @@ __global__ void __launch_bounds__(TB, APOP_PROP_CTAS) k_propagate(const ModelDev
                                                   int* errflag,
                                                   const __grid_constant__ PeerF64 xpeer,
                                                   int accum) {
-    // inverse-normal-CDF table of the transition draws (rng.cuh), staged once per CTA
-    extern __shared__ __align__(16) double s_tab[];
-    if (KIND != APOP_SSM_HMM) normal_table_to_smem<APOP_NTAB_COPIES>(s_tab);
     const ModelDev& M = *Mp;
     const double y = yt[0];
     const double wbase = sd->base;
-    if (accum & 2) seed = sd->seed;              // graph replay: the key lives in device memory
-    accum &= 1;
-    __syncthreads();
+    if (GSEED) seed = sd->seed;
     // rows of a lineage history start at multiples of n elements: 16-byte aligned
     // only when n is a multiple of 4 (ancestors) / 2 (states)
     const bool aligned = (((uintptr_t)anc | (uintptr_t)xn | (uintptr_t)lw) & 15) == 0;
-    const int nt = (int)((n + TILE - 1) / TILE);
-    for (int tile = blockIdx.x; tile < nt; tile += gridDim.x) {
-        if ((int64_t)(tile + 1) * TILE <= n && aligned)
-            propagate_tile<KIND, true, SHARD>(tile, xpeer, M, xp, anc, first_step, xn, lw, y,
-                                              retained_t, wbase, n, g0, seed, t, tmax, tsum, gmax,
-                                              errflag, s_tab, accum, true);
-        else
-            propagate_tile<KIND, false, SHARD>(tile, xpeer, M, xp, anc, first_step, xn, lw, y,
-                                               retained_t, wbase, n, g0, seed, t, tmax, tsum, gmax,
-                                               errflag, s_tab, accum, aligned);
-        __syncthreads();               // the per-warp partials in shared memory are reused
-    }
+    if ((int64_t)(blockIdx.x + 1) * TILE <= n && aligned)
+        propagate_tile<KIND, true, SHARD>(xpeer, M, xp, anc, first_step, xn, lw, y, retained_t,
+                                          wbase, n, g0, seed, t, tmax, tsum, gmax, errflag, accum,
+                                          true);
+    else
+        propagate_tile<KIND, false, SHARD>(xpeer, M, xp, anc, first_step, xn, lw, y, retained_t,
+                                           wbase, n, g0, seed, t, tmax, tsum, gmax, errflag, accum,
+                                           aligned);
 }
 
 __global__ void k_sweep_reset(SweepDev* sd, ResampleInfo* I, long long* gmax, int* ticket) {
@@ -789,6 +772,7 @@ static int sweep_stage(apop_ctx* c, const double* y, int T, const double* retain
                        const apop_sweep_opts* o) {
     SweepState* s = c->sweep;
     APOP_TRY(ensure_resample_ws(c));
+    if (o->no_resample) APOP_TRY(stat_lse_prepare(c));
     const bool csmc = o->csmc && retained;
     void* staged = nullptr;
     const size_t dim = (size_t)s->dim;
@@ -845,9 +829,6 @@ static int sweep_step(apop_ctx* c, int t, const apop_sweep_opts* o, bool csmc) {
     const size_t dim = (size_t)s->dim;
     double* x_new = s->history ? s->x_hist + (size_t)t * n * dim : ((t & 1) ? s->xb : s->xa);
     int32_t* anc_new = s->history ? s->anc_hist + (size_t)(t - 1) * n : s->anc;
-    // persistent CTAs (the normal table is staged once per CTA)
-    const int pgrid = (nt < APOP_PROP_CTAS * c->sm_count) ? nt : APOP_PROP_CTAS * c->sm_count;
-    const size_t psmem = (KIND == APOP_SSM_HMM) ? 0 : kPropSmem;
     kt_begin(c, KT_PROPAGATE);
     if (KIND == APOP_SSM_LGMVN) {
         MvnSweepArgs ma;
@@ -865,18 +846,18 @@ static int sweep_step(apop_ctx* c, int t, const apop_sweep_opts* o, bool csmc) {
         c->launches -= 1;                 // counted below
     } else if (shard) {
         const PeerF64 xpeer = peer_f64(c, (t & 1) ? c->fab.off_xa : c->fab.off_xb);   // x_{t-1}
-        k_propagate<(KIND == APOP_SSM_LGMVN) ? APOP_SSM_LGSSM1D : KIND, true><<<pgrid, TB, psmem, c->stream>>>(
+        k_propagate<(KIND == APOP_SSM_LGMVN) ? APOP_SSM_LGSSM1D : KIND, true, false><<<nt, TB, 0, c->stream>>>(
             s->model, x_prev, anc_prev, t == 1, x_new, s->lw, s->y + (t - 1), nullptr, s->sd, n,
-            c->g0, c->seed, (uint32_t)t, ws.tmax, ws.tsum, ws.gmax, &ws.info->err, xpeer,
-            s->seedp ? 2 : 0);
+            c->g0, c->seed, (uint32_t)t, ws.tmax, ws.tsum, ws.gmax, &ws.info->err, xpeer, 0);
     } else {
         PeerF64 none;
         memset(&none, 0, sizeof none);
-        k_propagate<(KIND == APOP_SSM_LGMVN) ? APOP_SSM_LGSSM1D : KIND, false><<<pgrid, TB, psmem, c->stream>>>(
+        constexpr int K1 = (KIND == APOP_SSM_LGMVN) ? APOP_SSM_LGSSM1D : KIND;
+        auto kern = s->seedp ? k_propagate<K1, false, true> : k_propagate<K1, false, false>;
+        kern<<<nt, TB, 0, c->stream>>>(
             s->model, x_prev, anc_prev, t == 1 || o->no_resample, x_new, s->lw, s->y + (t - 1),
             csmc ? s->retained + t : nullptr, s->sd, n, c->g0, c->seed, (uint32_t)t, ws.tmax,
-            ws.tsum, ws.gmax, &ws.info->err, none,
-            ((o->no_resample && t > 1) ? 1 : 0) | (s->seedp ? 2 : 0));
+            ws.tsum, ws.gmax, &ws.info->err, none, (o->no_resample && t > 1) ? 1 : 0);
     }
     kt_end(c, KT_PROPAGATE);
     c->launches += 1;
@@ -1149,24 +1130,10 @@ static void preload(K kernel) {
 }
 void preload_resample_kernels();     // resample.cu
 void preload_comm_kernels();         // comm.cu
-// k_propagate needs more than the default 48 KB of dynamic shared memory
-static void propagate_smem_optin() {
-    static bool done_dev[64] = {};
-    int dev = 0;
-    cudaGetDevice(&dev);
-    bool& done = done_dev[dev & 63];
-    if (done) return;
-    cudaFuncSetAttribute(k_propagate<APOP_SSM_LGSSM1D, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kPropSmem);
-    cudaFuncSetAttribute(k_propagate<APOP_SSM_LGSSM1D, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kPropSmem);
-    cudaFuncSetAttribute(k_propagate<APOP_SSM_SV, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kPropSmem);
-    cudaFuncSetAttribute(k_propagate<APOP_SSM_SV, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kPropSmem);
-    cudaGetLastError();
-    done = true;
-}
 static void preload_sweep_kernels() {
     preload(k_init<APOP_SSM_LGSSM1D>); preload(k_init<APOP_SSM_SV>); preload(k_init<APOP_SSM_HMM>);
-    preload(k_propagate<APOP_SSM_LGSSM1D, true>); preload(k_propagate<APOP_SSM_SV, true>);
-    preload(k_propagate<APOP_SSM_HMM, true>);
+    preload(k_propagate<APOP_SSM_LGSSM1D, true, false>); preload(k_propagate<APOP_SSM_SV, true, false>);
+    preload(k_propagate<APOP_SSM_HMM, true, false>);
     preload(k_sweep_reset); preload(k_gather_shard);
     preload_resample_kernels();
     preload_comm_kernels();
@@ -1206,7 +1173,6 @@ static int sweep_group(apop_ctx* const* g, int ng, const apop_ssm* model, const 
             return set_err(c, APOP_ERR_INVALID, "sharded sweep: particles per rank must be a "
                                                 "multiple of 8");
         cudaSetDevice(c->device);
-        propagate_smem_optin();
         if (c->world > 1) { preload_sweep_kernels(); if (dim > 1) mvn_preload_kernels(dim); }
         APOP_TRY(sweep_prepare(c, T, dim, opts->keep_history));
         c->sweep->kind = model->kind;

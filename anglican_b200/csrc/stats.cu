@@ -293,6 +293,12 @@ __global__ void k_stat_lse_out(const double* __restrict__ mparts, int g,
 
 // {max lw, sum exp(lw - max)} of a log-weight array into out2 (device): the
 // pieces of log-sum-exp / log-marginal (runtime.cljc:130-138, inference.cljc:181-186)
+// allocations of stat_lse_enqueue, for callers that enqueue it inside a graph capture
+int stat_lse_prepare(apop_ctx* c) {
+    StatBufs B;
+    return stat_bufs(c, 1 + SCH, 1, &B);
+}
+
 int stat_lse_enqueue(apop_ctx* c, const double* lw, int64_t n, double* out2) {
     StatBufs B;
     APOP_TRY(stat_bufs(c, 1 + SCH, 1, &B));

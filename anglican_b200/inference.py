@@ -186,7 +186,7 @@ def _infer_ipmcmc(model, y, number_of_particles=2, number_of_nodes=32,
     retained = [None] * P
     try:
         while True:
-            results, cand, log_zs = [], [], np.empty(M)
+            results, cand, picks, log_zs = [], [], [], np.empty(M)
             for j in range(M):                                      # cp/pmap over nodes, 176-182
                 ret = retained[j] if j < P else None
                 pop.set_seed(seeds.next_key())
@@ -197,7 +197,8 @@ def _infer_ipmcmc(model, y, number_of_particles=2, number_of_nodes=32,
                 results.append([_result_of(out, k, traj) for k in range(n)])
                 # candidate next retained path of this node, drawn now so the
                 # ancestry need not outlive the sweep (rand-nth, ipmcmc.cljc:189)
-                cand.append(out.trace(int(seeds.rng.random() * n)))
+                picks.append(int(seeds.rng.random() * n))
+                cand.append(out.trace(picks[-1]))
             if exchange is not None:
                 log_zs = exchange(log_zs)                           # only log-Zs cross nodes, 183-187
             u = seeds.rng.random(P)
@@ -216,7 +217,9 @@ def _infer_ipmcmc(model, y, number_of_particles=2, number_of_nodes=32,
                     for r in results[j]:
                         yield State(lw, r)
                 else:
-                    yield State(lw, results[j][int(seeds.rng.random() * n)])
+                    # one particle per node, the very one whose path is the node's candidate
+                    # retained path (ipmcmc.cljc:76-78, 189)
+                    yield State(lw, results[j][picks[j]])
     finally:
         pop.close()
 

@@ -60,9 +60,10 @@ def node_key(seed, iteration, node):
 
 def shared_draws(seed, iteration, number_of_nodes, number_of_csmc_nodes):
     """host-side uniforms of one iteration, identical on every rank:
-    picks[j]  -> rand-nth over the particles of node j   (ipmcmc.cljc:189)
+    picks[j]  -> rand-nth over the particles of node j   (ipmcmc.cljc:189); with
+                 all-particles? false also the one particle the node emits (76-78)
     u[i]      -> index Gibbs draw of conditional slot i   (ipmcmc.cljc:125-133)
-    sel[j]    -> rand-nth of the single emitted particle  (all-particles? false)"""
+    (third array: spare)"""
     g = np.random.default_rng([int(seed) & _M64, int(iteration), 0x1B3C])
     return g.random(number_of_nodes), g.random(number_of_csmc_nodes), g.random(number_of_nodes)
 
@@ -130,8 +131,9 @@ class _Group:
     """the three things that cross ranks, on `torch.distributed` (gloo: host
     tensors; nccl: device tensors) or nothing at all for a single process"""
 
-    def __init__(self, group=None, enabled=True):
+    def __init__(self, group=None, enabled=True, abi_exchange=False, device=0):
         self.dist = None
+        self.abi = None
         self.rank, self.world = 0, 1
         if enabled:
             import torch.distributed as dist
@@ -140,6 +142,19 @@ class _Group:
                 self.dist, self.torch, self.group = dist, torch, group
                 self.rank, self.world = dist.get_rank(group), dist.get_world_size(group)
                 self.dev = "cuda" if dist.get_backend(group) == "nccl" else "cpu"
+                if abi_exchange and self.world > 1:
+                    # the call a JVM binding makes: apop_ipmcmc_exchange_logz on a
+                    # context that carries this rank's NCCL communicator (a few particles only:
+                    # the context exists for the exchange)
+                    from .distributed import nccl_unique_id
+                    from .population import Population
+                    self.abi = Population(8, device=device, rank=self.rank, world=self.world,
+                                          nccl_id=nccl_unique_id(self.rank, group=group))
+
+    def close(self):
+        if self.abi is not None:
+            self.abi.close()
+            self.abi = None
 
     def gather_log_zs(self, local, lo, number_of_nodes):
         """every rank gets all M log-marginals: all-reduce(sum) of a vector that
@@ -148,6 +163,14 @@ class _Group:
         full[lo:lo + len(local)] = local
         if self.dist is None:
             return full
+        if self.abi is not None and number_of_nodes % self.world == 0:
+            # equal blocks in rank order: one NCCL allgather of M / world doubles per rank
+            loc = np.ascontiguousarray(local, dtype=np.float64)
+            out = np.empty(number_of_nodes)
+            L.check(self.abi.ctx, self.abi.lib.apop_ipmcmc_exchange_logz(
+                self.abi.ctx, loc.ctypes.data_as(L.c_double_p), loc.size,
+                out.ctypes.data_as(L.c_double_p)))
+            return out
         t = self.torch.from_numpy(full).to(self.dev)
         self.dist.all_reduce(t, op=self.dist.ReduceOp.SUM, group=self.group)
         return t.cpu().numpy()
@@ -179,7 +202,7 @@ class _Group:
 # -------------------------------------------------------------------- driver
 def ipmcmc_iterations(model, y, number_of_particles=2, number_of_nodes=32,
                       number_of_csmc_nodes=None, seed=0xA11CE, device=None, group=None,
-                      paths=False, width=4, runner=None, distributed=True):
+                      paths=False, width=4, runner=None, distributed=True, abi_exchange=False):
     """Generator over MCMC iterations.  Yields, on every rank, a dict with
     `log_zs` [M] (all nodes), `zeta_sums` [M], `csmc_indices` [P], `nodes`
     (the range this rank owns) and `runs` (NodeRun per owned node).
@@ -190,7 +213,13 @@ def ipmcmc_iterations(model, y, number_of_particles=2, number_of_nodes=32,
     M, n = number_of_nodes, number_of_particles
     P = number_of_csmc_nodes or int(M / 2)                          # ipmcmc.cljc:162-165
     assert P < M, ":number-of-csmc-nodes must be smaller than :number-of-nodes"
-    g = _Group(group, distributed)
+    if device is None and distributed:
+        try:
+            import torch.distributed as _d
+            device = _d.get_rank(group) if _d.is_initialized() else 0
+        except Exception:
+            device = 0
+    g = _Group(group, distributed, abi_exchange, device or 0)
     lo, hi = node_range(M, g.rank, g.world)
     d = model.state_dim
     T = np.asarray(y).size // d
@@ -235,6 +264,7 @@ def ipmcmc_iterations(model, y, number_of_particles=2, number_of_nodes=32,
                    "paths_moved": sum(1 for m_ in moves if g.rank in (m_[1], m_[2]))}
             it += 1
     finally:
+        g.close()
         if own:
             runner.close()
 
@@ -249,7 +279,10 @@ def infer_ipmcmc(model, y, number_of_particles=2, number_of_nodes=32, number_of_
     n = number_of_particles
     for step in ipmcmc_iterations(model, y, n, number_of_nodes, number_of_csmc_nodes, seed, device,
                                   group, paths, width, runner, distributed):
-        _, _, sel = shared_draws(seed, step["iteration"], number_of_nodes, len(step["csmc_indices"]))
+        # all-particles? false: the reference keeps ONE particle per node (ipmcmc.cljc:76-78) and
+        # the next retained state is rand-nth of that one-element list - the emitted particle
+        # and the candidate retained path are the same particle (picks), not two draws
+        picks, _, _ = shared_draws(seed, step["iteration"], number_of_nodes, len(step["csmc_indices"]))
         for j, run in zip(step["nodes"], step["runs"]):
             z = step["zeta_sums"][j]
             lw = math.log(z / n) if z > 0.0 else -math.inf
@@ -258,7 +291,7 @@ def infer_ipmcmc(model, y, number_of_particles=2, number_of_nodes=32, number_of_
                 for k in range(n):
                     yield State(lw, _value(res[k]))
             else:
-                yield State(lw, _value(res[int(sel[j] * n)]))
+                yield State(lw, _value(res[int(picks[j] * n)]))
 
 
 def _value(r):

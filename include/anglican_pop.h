@@ -43,8 +43,7 @@ enum {
     APOP_ERR_NCCL = -5,
     APOP_ERR_OOM = -6,
     APOP_ERR_UNSUPPORTED = -7,
-    APOP_ERR_INTERNAL = -8,     /* internal consistency check failed */
-    APOP_ERR_NOT_GLOBAL = -9    /* "some `observe' directives are not global" smc.cljc:48-51 */
+    APOP_ERR_INTERNAL = -8     /* internal consistency check failed */
 };
 
 enum { APOP_F64 = 0, APOP_I32 = 1 };

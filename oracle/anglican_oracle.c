@@ -71,55 +71,21 @@ static inline uint32_t ctr3(uint32_t stream, uint32_t kind, uint32_t draw) {
     return (stream << 24) | (kind << 20) | (draw & 0xFFFFFu);
 }
 
-/* Gaussian draws (engine semantics; the reference's nextGaussian runs on an
- * unseeded Well19937c, runtime.cljc:142-147, 403-409, so only distributional
- * parity is meaningful).  64 random bits -> z = sign * Q(v), Q = -Phi^-1, v
- * uniform on [0, 1/2) from 52 of the bits; Q is a piecewise degree-4 polynomial
- * (oracle/normal_table.inc, tools/gen_normal_table.py, |fit - Q| < 5e-12) with a
- * Newton-on-erfc tail below 2^-(NT_OCT+1).  Checked against scipy's ndtri in
- * tests/test_normal_table_cpu.py. */
-#include "normal_table.inc"
-static const double orc_ntab[NT_ROWS * NT_STRIDE] = {NT_TABLE};
-
-static double bits_to_double(uint64_t b) { double x; memcpy(&x, &b, 8); return x; }
-static uint64_t double_to_bits(double x) { uint64_t b; memcpy(&b, &x, 8); return b; }
-
-double orc_normal_from_bits(uint32_t hi, uint32_t lo) {
-    const double v = bits_to_double(((uint64_t)((hi & 0x000fffffu) | 0x3fe00000u) << 32) | lo) - 0.5;
-    const int32_t vh = (int32_t)(double_to_bits(v) >> 32);
-    const int idx = (vh >> (20 - NT_LOG2K)) - ((1022 - NT_OCT) << NT_LOG2K);
-    double z;
-    if (idx < 0) {
-        /* far tail: v extended by 11 more bits, Newton on erfc from A&S 26.2.23 */
-        const double ve = v + ((double)((hi >> 20) & 0x7ffu) + 0.5) * 5.42101086242752217e-20;
-        const double t = sqrt(-2.0 * log(ve));
-        z = t - (2.515517 + t * (0.802853 + t * 0.010328)) /
-                    (1.0 + t * (1.432788 + t * (0.189269 + t * 0.001308)));
-        for (int it = 0; it < 3; ++it) {
-            const double tailp = 0.5 * erfc(z * 0.70710678118654752440);
-            const double dens = exp(-0.5 * z * z) * 0.39894228040143267794;
-            z = z + (tailp - ve) / dens;
-        }
-    } else {
-        const uint32_t mh = ((uint32_t)vh & ~((1u << (20 - NT_LOG2K)) - 1u)) | (1u << (19 - NT_LOG2K));
-        const double d = v - bits_to_double((uint64_t)mh << 32);
-        const double* c = orc_ntab + (size_t)idx * NT_STRIDE;
-        z = fma(c[4], d, c[3]);
-        z = fma(z, d, c[2]);
-        z = fma(z, d, c[1]);
-        z = fma(z, d, c[0]);
-    }
-    return (hi & 0x80000000u) ? -z : z;
-}
-
-/* slots (2p, 2p+1) share one Philox block: words (0, 1) -> even, (2, 3) -> odd */
+/* Gaussian draws (engine semantics; the reference's nextGaussian runs on an unseeded
+ * Well19937c, runtime.cljc:142-147, 403-409, so only distributional parity is
+ * meaningful): Box-Muller on one Philox block per slot pair (2p, 2p+1), cos -> even
+ * slot, sin -> odd slot. */
 double orc_normal_at(uint64_t seed, uint64_t slot, uint32_t t, uint32_t stream,
                      uint32_t draw) {
     uint64_t pair = slot >> 1;
     uint32_t o[4];
     orc_philox4x32((uint32_t)pair, (uint32_t)(pair >> 32), t, ctr3(stream, 0, draw),
                    (uint32_t)seed, (uint32_t)(seed >> 32), o);
-    return (slot & 1) ? orc_normal_from_bits(o[2], o[3]) : orc_normal_from_bits(o[0], o[1]);
+    double u1 = orc_u01_open(o[0], o[1]);
+    double u2 = orc_u01_half(o[2], o[3]);
+    double r = sqrt(-2.0 * log(u1));
+    double ang = 2.0 * M_PI * u2;
+    return (slot & 1) ? r * sin(ang) : r * cos(ang);
 }
 
 double orc_uniform_at(uint64_t seed, uint64_t slot, uint32_t t, uint32_t stream,

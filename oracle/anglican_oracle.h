@@ -42,7 +42,6 @@ double orc_u01_open(uint32_t hi, uint32_t lo);
 double orc_u01_half(uint32_t hi, uint32_t lo);
 /* j-th standard normal of (slot, t, stream): Box-Muller pair shared by slots
  * 2p and 2p+1 */
-double orc_normal_from_bits(uint32_t hi, uint32_t lo);
 double orc_normal_at(uint64_t seed, uint64_t slot, uint32_t t, uint32_t stream,
                      uint32_t draw);
 /* j-th uniform [0,1) of (slot, t, stream) */

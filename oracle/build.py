@@ -11,7 +11,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 OUT_DIR = os.path.join(HERE, "_build")
 OUT = os.path.join(OUT_DIR, "liboracle.so")
 SRC = [os.path.join(HERE, "anglican_oracle.c")]
-HDR = [os.path.join(HERE, "anglican_oracle.h"), os.path.join(HERE, "normal_table.inc")]
+HDR = [os.path.join(HERE, "anglican_oracle.h")]
 
 
 def needs_build() -> bool:

@@ -74,8 +74,6 @@ def _declare(L):
     L.orc_mvt_logpdf.restype = d
     L.orc_wishart_logpdf.argtypes = [c_double_p, d, c_double_p, C.c_int, c_double_p]
     L.orc_wishart_logpdf.restype = d
-    L.orc_normal_from_bits.argtypes = [u32, u32]
-    L.orc_normal_from_bits.restype = d
     L.orc_normal_at.argtypes = [u64, u64, u32, u32, u32]
     L.orc_normal_at.restype = d
     L.orc_uniform_at.argtypes = [u64, u64, u32, u32, u32]
@@ -170,11 +168,6 @@ def wishart_logpdf(x, n, V):
     p = int(round(math.sqrt(V.size)))
     work = np.empty(2 * p * p)
     return lib().orc_wishart_logpdf(_dp(x), float(n), _dp(V), p, _dp(work))
-
-
-def normal_from_bits(hi, lo):
-    """z = sign * Q(v) from 64 random bits (table-driven inverse normal CDF)"""
-    return lib().orc_normal_from_bits(int(hi) & 0xFFFFFFFF, int(lo) & 0xFFFFFFFF)
 
 
 def normal_at(seed, slot, t, stream, draw=0):

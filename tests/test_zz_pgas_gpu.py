@@ -4,7 +4,7 @@ retained particle's ancestor redrawn at every observe (pgas.cljc:107-131,
 
 Ancestry (integers) and the HMM's integer states must be bit-exact.  Continuous
 states (lgssm, sv) are compared at the suite's 1e-9 relative: the device draws its
-normals with the polynomial Box-Muller of fastmath.cuh (<= 2 ulp from libm, which
+normals and exponentials with its own polynomial kernels (fastmath.cuh, <= 2 ulp from libm, which
 the oracle uses), as every other Gaussian comparison in tests/ does.  The largest
 distance seen is printed in ulps so that a real kernel bug (>> 2 ulp) stands out."""
 import math

@@ -183,7 +183,7 @@ def c4dist(args):
     n, T = args.particles or (1 << 22), args.T or 200
     y = sv_observations(2000)[:T]
     gen = ipmcmc_iterations(StochasticVolatility(), y, n, M, M // 2, seed=77, device=local,
-                            width=args.width)
+                            width=args.width, abi_exchange=True)
     times, zs, moved = [], [], 0
     for it in range(args.warmup + args.steps):
         torch.cuda.synchronize()
@@ -210,6 +210,8 @@ def c4dist(args):
             "particle_steps_per_s": M * n * T * len(times) / tot,
             "s_per_mcmc_iteration": tot / len(times), "node_log_z": zs,
             "paths_moved_rank0": moved,
+            "log_z_exchange": "apop_ipmcmc_exchange_logz (C ABI, NCCL allgather of M/world doubles)",
+            "lineages": "compact (2 bits per particle and step)",
             "timing": "wall clock around the iteration, devices synchronised, max over ranks"}
 
 
