@@ -41,7 +41,8 @@ class ApopSweepOpts(C.Structure):
     _fields_ = [("csmc", C.c_int32), ("n_cond_steps", C.c_int32), ("reset_weights", C.c_int32),
                 ("keep_history", C.c_int32), ("use_graph", C.c_int32), ("want_final", C.c_int32),
                 ("want_filt", C.c_int32), ("no_resample", C.c_int32),
-                ("ancestor_sampling", C.c_int32)]
+                ("ancestor_sampling", C.c_int32), ("pad_", C.c_int32),
+                ("ess_threshold", C.c_double)]
 
 
 class ApopSweepResult(C.Structure):

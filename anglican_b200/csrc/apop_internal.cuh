@@ -48,14 +48,15 @@ struct ResampleInfo {
     int nh0, nh1;        // hard tile counts per lap
     int first_skip1;     // first tile skipped in lap 1
     int weights_mode;
-    int pad;
+    int skip;            // adaptive resampling: this observe keeps the particles as they are
 };
 
 struct SweepDev {           // device-resident scalars of a fused sweep
     double base;            // common accumulated log-weight (state.cljc:27-31)
     double log_z;           // sum_t log-mean-weight (ipmcmc.cljc:67-74)
     int err;
-    int pad;
+    int carry;              // 1: the last observe did not resample (ESS above the threshold) -
+                            //    every particle carries its own accumulated log-weight
     unsigned long long seed; // graph-replayed sweeps read the RNG key from here (see run_group)
 };
 
@@ -67,6 +68,7 @@ struct StepOut {
     double* filt;
     int32_t* anc;
     int t, reset, cond, has_x;
+    double ess_thr;         // > 0: resample only when ESS < ess_thr * N (adaptive resampling)
 };
 
 struct Column {
@@ -125,7 +127,7 @@ struct TileRec {
     int k0;                      // index, relative to the segment, of the first pointer of the window
     unsigned wm;                 // window length | mode << 28
 };
-enum { TM_NONE = 0, TM_FAST = 1, TM_GENERAL = 2 };
+enum { TM_NONE = 0, TM_FAST = 1, TM_GENERAL = 2, TM_IDENT = 3 };   // IDENT: no resample, anc[k] = k
 static_assert(sizeof(TileRec) == 64, "TileRec is read as four 16-byte words");
 
 constexpr int HEAVY_W = 1 << 18; // offspring of one (tile, lap) above which emission is deferred

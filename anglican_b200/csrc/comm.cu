@@ -103,6 +103,15 @@ Fabric fabric_view(const apop_ctx* c) {
     F.rank = c->rank;
     F.world = c->world;
     F.n_local = c->n;
+    {
+        static long long cyc = 0;
+        if (!cyc) {
+            const char* e = getenv("APOP_SPIN_SECONDS");
+            const double sec = (e && atof(e) > 0.0) ? atof(e) : 3.0;
+            cyc = (long long)(sec * 2.0e9);
+        }
+        F.spin_cycles = cyc;
+    }
     if (c->world > 1 && c->fab.linked)
         for (int q = 0; q < c->world; ++q) F.mbox[q] = (Mailbox*)c->fab.heap[q];
     return F;
@@ -114,7 +123,8 @@ __global__ void k_fabric_barrier(Fabric F, unsigned long long seq, int* err) {
     const int q = threadIdx.x;
     if (q < F.world) {
         st_release_sys(&F.mbox[q]->bar[F.rank], seq);
-        if (!spin_until(&F.mbox[F.rank]->bar[q], seq) && err) atomicOr(err, EB_COMM);
+        if (!spin_until(&F.mbox[F.rank]->bar[q], seq, F.spin_cycles) && err)
+            atomicOr(err, EB_COMM | (CW_BARRIER << 16) | (q << 24));
     }
 }
 

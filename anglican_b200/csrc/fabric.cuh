@@ -46,6 +46,7 @@ constexpr size_t kMailboxBytes = (sizeof(Mailbox) + 4095) & ~(size_t)4095;
 struct Fabric {
     int rank, world;
     long long n_local;
+    long long spin_cycles;        // bound of every wait on a peer (APOP_SPIN_SECONDS, default 3 s)
     Mailbox* mbox[kMaxWorld];     // mbox[q]: rank q's mailbox as mapped here
 };
 struct PeerF64 {
@@ -55,6 +56,8 @@ struct PeerI32 {
     int32_t* p[kMaxWorld];
 };
 
+// which wait timed out, recorded beside EB_COMM: (what << 16) | (peer << 24)
+enum { CW_FIN = 1, CW_ACC = 2, CW_COMP0 = 3, CW_COMP1 = 4, CW_BARRIER = 5 };
 #if defined(__CUDACC__)
 constexpr long long kSpinLimitCycles = 6000000000LL;     // ~3 s at 2 GHz: a hang becomes an error
 
@@ -74,10 +77,11 @@ __device__ __forceinline__ void mail_send(MailSlot* s, double a, double b, doubl
     st_release_sys(&s->seq, seq);
 }
 // false on timeout (the peer never arrived)
-__device__ __forceinline__ bool spin_until(const unsigned long long* flag, unsigned long long seq) {
+__device__ __forceinline__ bool spin_until(const unsigned long long* flag, unsigned long long seq,
+                                           long long limit = kSpinLimitCycles) {
     const long long t0 = clock64();
     while (ld_acquire_sys(flag) < seq) {
-        if (clock64() - t0 > kSpinLimitCycles) return false;
+        if (clock64() - t0 > limit) return false;
         __nanosleep(64);
     }
     return true;
@@ -91,14 +95,16 @@ __device__ __forceinline__ void mail_send_bits(MailSlot* s, long long a, long lo
     st_release_sys(&s->seq, seq);
 }
 __device__ __forceinline__ bool mail_wait_bits(MailSlot* s, unsigned long long seq,
-                                               long long (&out)[3]) {
-    const bool ok = spin_until(&s->seq, seq);
+                                               long long (&out)[3],
+                                               long long limit = kSpinLimitCycles) {
+    const bool ok = spin_until(&s->seq, seq, limit);
     volatile long long* v = reinterpret_cast<volatile long long*>(s->v);
     out[0] = v[0]; out[1] = v[1]; out[2] = v[2];
     return ok;
 }
-__device__ __forceinline__ bool mail_wait(MailSlot* s, unsigned long long seq, double (&out)[3]) {
-    const bool ok = spin_until(&s->seq, seq);
+__device__ __forceinline__ bool mail_wait(MailSlot* s, unsigned long long seq, double (&out)[3],
+                                          long long limit = kSpinLimitCycles) {
+    const bool ok = spin_until(&s->seq, seq, limit);
     volatile double* v = s->v;
     out[0] = v[0]; out[1] = v[1]; out[2] = v[2];
     return ok;

@@ -400,8 +400,9 @@ __global__ void __launch_bounds__(FB) k_fin_a(WSView v, int64_t n, int64_t n_new
         if (tid < F.world) {
             mail_send(&F.mbox[tid]->fin[par][F.rank], m, lsum, (double)v.info->err, seq);
             double o[3];
-            const bool ok = mail_wait(&F.mbox[F.rank]->fin[par][tid], seq, o);
-            pm[tid] = o[0]; ps[tid] = o[1]; perr[tid] = (int)o[2] | (ok ? 0 : EB_COMM);
+            const bool ok = mail_wait(&F.mbox[F.rank]->fin[par][tid], seq, o, F.spin_cycles);
+            pm[tid] = o[0]; ps[tid] = o[1];
+            perr[tid] = (int)o[2] | (ok ? 0 : (EB_COMM | (CW_FIN << 16) | (tid << 24)));
         }
         __syncthreads();
         const double m_loc = m;
@@ -1100,7 +1101,10 @@ __device__ double comp_walk(const Fabric& F, int par, int lap, double S, int q0,
                             unsigned long long seq, int* err, int* comm) {
     for (int q = q0; q < q1; ++q) {
         long long o[3];
-        if (!mail_wait_bits(&F.mbox[F.rank]->comp[par][lap][q], seq, o)) { *comm = 1; return S; }
+        if (!mail_wait_bits(&F.mbox[F.rank]->comp[par][lap][q], seq, o, F.spin_cycles)) {
+            *comm = EB_COMM | ((lap ? CW_COMP1 : CW_COMP0) << 16) | (q << 24);
+            return S;
+        }
         const int kind = (int)(o[2] >> 32), cls = (int)(unsigned)(o[2] & 0xffffffffLL);
         if (kind == CK_EXACT) {
             S = __longlong_as_double(o[0]);
@@ -1176,7 +1180,8 @@ __global__ void __launch_bounds__(TB) k_chain(const double* __restrict__ lw,
             const int q = threadIdx.x;
             mail_send(&F.mbox[q]->acc[par][F.rank], acc, acc2, accx, seq);
             double o[3];
-            if (!mail_wait(&F.mbox[F.rank]->acc[par][q], seq, o)) sh_comm = 1;
+            if (!mail_wait(&F.mbox[F.rank]->acc[par][q], seq, o, F.spin_cycles))
+                sh_comm = EB_COMM | (CW_ACC << 16) | (q << 24);
             pa[q] = o[0]; pb[q] = o[1]; px[q] = o[2];
         }
         __syncthreads();
@@ -1187,7 +1192,7 @@ __global__ void __launch_bounds__(TB) k_chain(const double* __restrict__ lw,
     if (threadIdx.x == 0) {
         v.send[0] = Send0;
         const i64 n_new = I->n_new;
-        int err = sh_comm ? EB_COMM : 0;
+        int err = sh_comm;
         if (!(total > 0.0) || !(total < INFINITY)) err |= EB_ZERO;
         Comb& c = *v.comb;
         if (!(err & EB_ZERO)) {
@@ -1205,17 +1210,29 @@ __global__ void __launch_bounds__(TB) k_chain(const double* __restrict__ lw,
         I->ess = (acc2 > 0.0) ? acc * acc / acc2 : 0.0;
         I->log_mean_approx = mfin ? log(acc / (double)n_total) + m : -INFINITY;
         if (err) atomicOr(&I->err, err);
+        I->skip = 0;
         if (so.sd) {                       // per-step outputs of a fused sweep
             SweepDev* sd = so.sd;
-            const double nl = I->new_lw;
-            const double inc = nl - sd->base;
-            so.log_mean_w[so.t - 1] = inc;
             so.ess[so.t - 1] = I->ess;
             if (so.has_x) so.filt[so.t - 1] = accx / acc;
-            sd->log_z += inc;
-            sd->base = so.reset ? 0.0 : nl;      // pgibbs.cljc:88 / smc.cljc:98-103
             sd->err |= I->err | err;
             if (so.cond) so.anc[0] = 0;          // retained particle back at position 0
+            // adaptive resampling (the reference resamples at every
+            // observe): keep the weighted particles while ESS >= threshold * N
+            const bool skip = so.ess_thr > 0.0 && !(err | I->err) &&
+                              I->ess >= so.ess_thr * (double)n_total;
+            if (skip) {
+                I->skip = 1;
+                sd->carry = 1;
+                so.log_mean_w[so.t - 1] = 0.0;   // deferred to the next resample
+            } else {
+                const double nl = I->new_lw;
+                const double inc = nl - sd->base;
+                so.log_mean_w[so.t - 1] = inc;
+                sd->log_z += inc;
+                sd->base = so.reset ? 0.0 : nl;  // pgibbs.cljc:88 / smc.cljc:98-103
+                sd->carry = 0;
+            }
         }
         tg2 = gtimer_ns();
     }
@@ -1247,8 +1264,8 @@ __global__ void __launch_bounds__(TB) k_chain(const double* __restrict__ lw,
             int comm = 0;
             sh_in = comp_walk(F, par, 1, total, 0, F.rank, seq, &I->err, &comm);
             if (comm) {
-                atomicOr(&I->err, EB_COMM);
-                if (so.sd) so.sd->err |= EB_COMM;
+                atomicOr(&I->err, comm);
+                if (so.sd) so.sd->err |= comm;
             }
         }
         __syncthreads();
@@ -1657,7 +1674,11 @@ __global__ void __launch_bounds__(XB) k_expand(WSView v, int order, int32_t* __r
     TileRec R;
     R.sD0 = 0.0; R.qD = 1.0; R.invq = 1.0; R.inv_u = 1.0; R.units = 0.0; R.m = I->m;
     R.dst = nullptr; R.k0 = 0; R.wm = (unsigned)TM_NONE << 28;
-    if (!dead && !I->err) {
+    if (I->skip) {
+        // no resample at this observe: every particle is its own ancestor (slot k <- k)
+        R.dst = anc + t * TILE;
+        R.wm = (unsigned)TM_IDENT << 28;
+    } else if (!dead && !I->err) {
         const double x0 = comb.x0, xlast = comb.xlast;
         // a lap emits if some pointer falls into this tile (x0 is uniform on the wheel:
         // all tiles but the one holding x0 emit in exactly one lap)
@@ -1932,6 +1953,13 @@ __global__ void __launch_bounds__(TB, APOP_ANC_CTAS) k_ancestors(const double* _
         int4* rq = reinterpret_cast<int4*>(&R);
 #pragma unroll
         for (int k = 0; k < 4; ++k) rq[k] = __ldg(rp + k);
+    }
+    if ((R.wm >> 28) == TM_IDENT) {
+        const int64_t i0 = base + (int64_t)threadIdx.x * IPT;
+#pragma unroll
+        for (int j = 0; j < IPT; ++j)
+            if (i0 + j < n) R.dst[threadIdx.x * IPT + j] = (int32_t)(g0 + i0 + j);
+        return;
     }
     if ((R.wm >> 28) != TM_FAST) return;           // nothing to emit, or listed for the general kernel
     ancestors_fast(R, raw, win != nullptr, base, n, (int32_t)(g0 + base), sm, err);
@@ -2245,8 +2273,10 @@ int info_to_status(apop_ctx* c, const ResampleInfo& I) {
     if (I.err & EB_ZERO)
         return set_err(c, APOP_ERR_ZERO_WEIGHT, "total weight is not a positive finite number");
     if (I.err & EB_COMM)
-        return set_err(c, APOP_ERR_NCCL, "a peer rank never arrived at a fabric exchange "
-                                         "(spin timeout): results of this sweep are invalid");
+        return set_err(c, APOP_ERR_NCCL, "a peer rank never arrived at a fabric exchange (spin timeout; "
+                                         "wait %d on rank %d: 1 finalize, 2 sums, 3 fold lap 0, 4 fold "
+                                         "lap 1, 5 barrier): results of this sweep are invalid",
+                       (I.err >> 16) & 0xff, (I.err >> 24) & 0x7f);
     if (I.err & (EB_CTX | EB_COMB | EB_COUNT))
         return set_err(c, APOP_ERR_INTERNAL, "exact-fold consistency check failed (bits %d)",
                        I.err);

@@ -383,6 +383,7 @@ __global__ void __launch_bounds__(TB, APOP_PROP_CTAS) k_propagate(const ModelDev
     const double y = yt[0];
     const double wbase = sd->base;
     if (GSEED) seed = sd->seed;
+    accum |= sd->carry;          // adaptive resampling: the last observe kept the weighted particles
     // rows of a lineage history start at multiples of n elements: 16-byte aligned
     // only when n is a multiple of 4 (ancestors) / 2 (states)
     const bool aligned = (((uintptr_t)anc | (uintptr_t)xn | (uintptr_t)lw) & 15) == 0;
@@ -397,7 +398,7 @@ __global__ void __launch_bounds__(TB, APOP_PROP_CTAS) k_propagate(const ModelDev
 }
 
 __global__ void k_sweep_reset(SweepDev* sd, ResampleInfo* I, long long* gmax, int* ticket) {
-    sd->base = 0.0; sd->log_z = 0.0; sd->err = 0;
+    sd->base = 0.0; sd->log_z = 0.0; sd->err = 0; sd->carry = 0;
     gmax[0] = dkey(-INFINITY); ticket[0] = 0; ticket[1] = 0;
     I->err = 0;
 }
@@ -772,7 +773,7 @@ static int sweep_stage(apop_ctx* c, const double* y, int T, const double* retain
                        const apop_sweep_opts* o) {
     SweepState* s = c->sweep;
     APOP_TRY(ensure_resample_ws(c));
-    if (o->no_resample) APOP_TRY(stat_lse_prepare(c));
+    if (o->no_resample || o->ess_threshold > 0.0) APOP_TRY(stat_lse_prepare(c));
     const bool csmc = o->csmc && retained;
     void* staged = nullptr;
     const size_t dim = (size_t)s->dim;
@@ -880,6 +881,7 @@ static int sweep_step(apop_ctx* c, int t, const apop_sweep_opts* o, bool csmc) {
     a.step.filt = s->filt; a.step.anc = anc_new; a.step.t = t;
     a.step.reset = o->reset_weights; a.step.cond = cond ? 1 : 0;
     a.step.has_x = (o->want_filt && dim == 1) ? 1 : 0;
+    a.step.ess_thr = o->ess_threshold;
     a.sharded = shard;
     a.seedp = s->seedp;
     if (shard) a.anc_peer = peer_i32(c, c->fab.off_anc);
@@ -931,6 +933,7 @@ static int sweep_end(apop_ctx* c, int T, const apop_sweep_opts* opts, apop_sweep
                                          cudaMemcpyDeviceToDevice, c->stream));
         APOP_TRY(stat_lse_enqueue(c, s->lw, n, s->lse));
     } else if (opts->want_final || result->x_final) {
+        if (opts->ess_threshold > 0.0) APOP_TRY(stat_lse_enqueue(c, s->lw, n, s->lse));
         int blocks = (int)((n * dim + 255) / 256);
         if (blocks > c->sm_count * 32) blocks = c->sm_count * 32;
         kt_begin(c, KT_GATHER);
@@ -988,7 +991,8 @@ static int sweep_fetch(apop_ctx* c, int T, const apop_sweep_opts* opts, apop_swe
         APOP_CUDA(c, cudaMemcpyAsync(result->x_final, s->x_final, sizeof(double) * n * dim,
                                      cudaMemcpyDeviceToHost, c->stream));
     double lse[2] = {0.0, 0.0};
-    if (opts->no_resample) {
+    const bool adaptive = opts->ess_threshold > 0.0 && !opts->no_resample;
+    if (opts->no_resample || adaptive) {
         APOP_CUDA(c, cudaMemcpyAsync(lse, s->lse, sizeof lse, cudaMemcpyDeviceToHost, c->stream));
         if (result->lw_final)
             APOP_CUDA(c, cudaMemcpyAsync(result->lw_final, s->lw, sizeof(double) * n,
@@ -1000,11 +1004,18 @@ static int sweep_fetch(apop_ctx* c, int T, const apop_sweep_opts* opts, apop_swe
     APOP_TRY(info_to_status(c, I));
     // :smc keeps the accumulated weight on the particles: final weight == log Z-hat
     result->log_z = opts->reset_weights ? hsd.log_z : hsd.base;
-    if (opts->no_resample) {
+    if (opts->no_resample || (adaptive && hsd.carry)) {
         // log-marginal of the weighted samples (inference.cljc:181-186): log mean exp
         if (lse[0] != lse[0]) return set_err(c, APOP_ERR_NAN_WEIGHT, "importance: NaN log-weight");
-        result->log_z = (lse[0] > -INFINITY && lse[0] < INFINITY)
-                            ? log(lse[1] / (double)n) + lse[0] : lse[0];
+        const double L = (lse[0] > -INFINITY && lse[0] < INFINITY)
+                             ? log(lse[1] / (double)n) + lse[0] : lse[0];
+        // adaptive sweep that ended without a resample: the particles still carry their
+        // weights since the last one (reset mode: on top of the log Z accumulated so far)
+        result->log_z = (adaptive && opts->reset_weights) ? hsd.log_z + L : L;
+    } else if (adaptive && result->lw_final) {
+        // the last observe resampled: all particles share one weight (smc.cljc:98-103)
+        const double v = opts->reset_weights ? 0.0 : hsd.base;
+        for (int64_t k = 0; k < n; ++k) result->lw_final[k] = v;
     }
     return APOP_OK;
 }
@@ -1156,6 +1167,12 @@ static int sweep_group(apop_ctx* const* g, int ng, const apop_ssm* model, const 
             return set_err(c, APOP_ERR_UNSUPPORTED,
                            "no_resample (importance) sweeps: unconditional, unsharded, scalar-state, "
                            "no lineages");
+        if (opts->ess_threshold < 0.0 || opts->ess_threshold > 1.0 ||
+            (opts->ess_threshold > 0.0 && (opts->ancestor_sampling || c->world > 1 ||
+                                           model->kind == APOP_SSM_LGMVN || !opts->want_final)))
+            return set_err(c, APOP_ERR_UNSUPPORTED,
+                           "ess_threshold (adaptive resampling): a fraction of N in [0, 1]; scalar-"
+                           "state models on one GPU, final states requested, no ancestor sampling");
         if (opts->ancestor_sampling && (!opts->csmc || c->world > 1 || opts->no_resample ||
                                         model->kind == APOP_SSM_LGMVN))
             return set_err(c, APOP_ERR_UNSUPPORTED,

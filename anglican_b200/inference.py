@@ -57,7 +57,11 @@ def _states(out, log_weight, with_paths):
 
 
 # ---------------------------------------------------------------- :smc
-def _infer_smc(model, y, number_of_particles=1, seed=0xA11CE, device=0, paths=False, pop=None):
+def _infer_smc(model, y, number_of_particles=1, seed=0xA11CE, device=0, paths=False, pop=None,
+               ess_threshold=0.0):
+    """ess_threshold (engine extension; the reference resamples at every
+    observe): resample only when ESS < ess_threshold * N; the states of a sweep that ends
+    without a resample carry their own log-weights."""
     assert number_of_particles >= 1, ":number-of-particles must be at least 1"   # smc.cljc:56-57
     own = pop is None
     pop = pop or Population(number_of_particles, seed=seed, device=device)
@@ -65,8 +69,13 @@ def _infer_smc(model, y, number_of_particles=1, seed=0xA11CE, device=0, paths=Fa
     try:
         while True:                                   # (sample-seq), smc.cljc:58-63
             pop.set_seed(seeds.next_key())
-            out = pop.sweep(model, y, keep_history=paths)
-            yield from _states(out, out.log_z, paths)
+            out = pop.sweep(model, y, keep_history=paths, ess_threshold=ess_threshold)
+            if ess_threshold > 0.0:
+                traj = out.trajectories() if paths else None
+                for k in range(pop.n):
+                    yield State(float(out.lw_final[k]), _result_of(out, k, traj))
+            else:
+                yield from _states(out, out.log_z, paths)
     finally:
         if own:
             pop.close()

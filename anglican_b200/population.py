@@ -380,7 +380,8 @@ class Population:
 
     def sweep(self, model, y, retained=None, csmc=False, n_cond_steps=0, reset_weights=False,
               keep_history=False, want_final=True, want_stats=True, want_filt=None,
-              pinned_final=False, no_resample=False, ancestor_sampling=False, use_graph=0):
+              pinned_final=False, no_resample=False, ancestor_sampling=False, use_graph=0,
+              ess_threshold=0.0):
         """One `sweep` (smc.cljc:35-51; conditional: pgibbs.cljc:76-110,
         ipmcmc.cljc:34-83).  Returns a SweepOutput.  pinned_final: x_final is a
         view of a page-locked buffer owned by the population, overwritten by its
@@ -391,7 +392,10 @@ class Population:
         trajectories) or "compact" / 2 (two bits per particle and step, trace only;
         scalar-state models).  ancestor_sampling:
         `infer :pgas` (pgas.cljc:107-131) — in a conditional sweep the retained
-        particle's ancestor is redrawn at every conditional observe."""
+        particle's ancestor is redrawn at every conditional observe.  ess_threshold
+        (extension; the reference resamples at every observe): in (0, 1], resample only
+        when ESS < ess_threshold * N; the output then carries lw_final, the log-weights of
+        the final particles (all equal if the last observe resampled)."""
         y = np.ascontiguousarray(y, dtype=np.float64)
         d = model.state_dim
         T = y.size // d
@@ -403,7 +407,8 @@ class Population:
             keep_history = 2 if d == 1 else 1
         opts = L.ApopSweepOpts(int(csmc), int(n_cond_steps), int(reset_weights),
                                int(keep_history), int(use_graph), int(want_final), int(bool(want_filt)),
-                               int(bool(no_resample)), int(bool(ancestor_sampling)))
+                               int(bool(no_resample)), int(bool(ancestor_sampling)), 0,
+                               float(ess_threshold))
         res = L.ApopSweepResult()
         out = SweepOutput(self, T, d)
         if want_stats:
@@ -420,7 +425,7 @@ class Population:
             else:
                 out.x_final = np.empty((self.n, d)) if d > 1 else np.empty(self.n)
             res.x_final = _dp(out.x_final)
-        if no_resample:
+        if no_resample or ess_threshold > 0.0:
             out.lw_final = np.empty(self.n)
             res.lw_final = _dp(out.lw_final)
         ret = None

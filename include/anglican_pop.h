@@ -256,6 +256,14 @@ typedef struct {
                                 * (the rescored transition `sample`; the retained path's later
                                 * terms are common to all i and left out).  Scalar-state models,
                                 * one GPU.  Only the recorded ancestry changes (lineages). */
+    int32_t pad_;
+    double ess_threshold;      /* adaptive resampling (the reference resamples at
+                                * EVERY observe, smc.cljc:41-43 - this is an extension): 0 = always
+                                * resample; in (0, 1]: resample only when ESS < ess_threshold * N,
+                                * otherwise the particles keep their own accumulated log-weights
+                                * and are their own ancestors.  A sweep that ends without a
+                                * resample returns weighted particles (lw_final).  The decision is
+                                * taken on the device; scalar-state models, one GPU. */
 } apop_sweep_opts;
 /* sizeof(apop_sweep_opts) of the loaded library, for bindings that mirror the struct */
 int apop_sizeof_sweep_opts(void);

@@ -784,6 +784,7 @@ int orc_smc_sweep(const orc_ssm* model, const double* y, const double* retained,
 
     double base = 0.0;       /* common accumulated log-weight of all particles */
     double log_z = 0.0;
+    int carry = 0;           /* adaptive resampling: the last observe kept the weighted particles */
     for (int t = 1; t <= T; ++t) {
         const double* yt = y + (size_t)(t - 1) * od;
         /* run every particle to the next observe: sample* then observe*
@@ -799,7 +800,7 @@ int orc_smc_sweep(const orc_ssm* model, const double* y, const double* retained,
                     memcpy(xk, retained + (size_t)t * d, sizeof(double) * (size_t)d);
                 else
                     ssm_transition(model, o->seed, k, (uint32_t)t, xa + par * d, xk, work);
-                lw[k] = base + ssm_obs_logpdf(model, xk, yt, iL, Z, work);  /* add-log-weight */
+                lw[k] = (carry ? lw[k] : base) + ssm_obs_logpdf(model, xk, yt, iL, Z, work);  /* add-log-weight */
             }
             free(work);
         }
@@ -809,10 +810,12 @@ int orc_smc_sweep(const orc_ssm* model, const double* y, const double* retained,
         double mx;
         rc = orc_particle_weights(lw, n, w, &mx);
         if (rc) goto done;
-        if (out->ess) {
+        double ess_t = 0.0;
+        if (out->ess || o->ess_threshold > 0.0) {
             double s = 0.0, s2 = 0.0;
             for (int64_t k = 0; k < n; ++k) { s = s + w[k]; s2 = s2 + w[k] * w[k]; }
-            out->ess[t - 1] = s * s / s2;
+            ess_t = s * s / s2;
+            if (out->ess) out->ess[t - 1] = ess_t;
         }
         if (out->filt_mean) {
             for (int i = 0; i < d; ++i) {
@@ -821,6 +824,18 @@ int orc_smc_sweep(const orc_ssm* model, const double* y, const double* retained,
                 out->filt_mean[(size_t)(t - 1) * d + i] = sx / s;
             }
         }
+        if (o->ess_threshold > 0.0 && ess_t >= o->ess_threshold * (double)n) {
+            /* no resample at this observe: every particle is its own ancestor and keeps
+             * its weight; the log Z increment is deferred to the next resample */
+            for (int64_t k = 0; k < n; ++k) anc[k] = (int32_t)k;
+            if (out->log_mean_w) out->log_mean_w[t - 1] = 0.0;
+            if (o->keep_history && out->anc_hist)
+                memcpy(out->anc_hist + (size_t)(t - 1) * n, anc, sizeof(int32_t) * (size_t)n);
+            carry = 1;
+            double* tmp0 = xa; xa = xb; xb = tmp0;
+            continue;
+        }
+        carry = 0;
         const int cond = o->csmc && retained && (t <= o->n_cond_steps);
         const int64_t n_new = cond ? n - 1 : n;     /* pgibbs.cljc:92-99 */
         double total, step;
@@ -848,6 +863,17 @@ int orc_smc_sweep(const orc_ssm* model, const double* y, const double* retained,
         double* tmp = xa; xa = xb; xb = tmp;
     }
     out->log_z = o->reset_weights ? log_z : base;
+    if (carry) {
+        /* the sweep ended on weighted particles: log mean exp of what they carry */
+        double mx = -INFINITY, sum = 0.0;
+        for (int64_t k = 0; k < n; ++k) if (lw[k] > mx) mx = lw[k];
+        for (int64_t k = 0; k < n; ++k) sum = sum + ((lw[k] == mx) ? 1.0 : exp(lw[k] - mx));
+        const double L = (mx > -INFINITY && mx < INFINITY) ? log(sum / (double)n) + mx : mx;
+        out->log_z = o->reset_weights ? log_z + L : L;
+    }
+    if (out->lw_final)
+        for (int64_t k = 0; k < n; ++k)
+            out->lw_final[k] = carry ? lw[k] : (o->reset_weights ? 0.0 : base);
     if (out->x_final) {
         for (int64_t k = 0; k < n; ++k) {
             const int64_t par = (T == 0) ? k : anc[k];

@@ -159,6 +159,9 @@ typedef struct {
     int32_t ancestor_sampling; /* pgas.cljc:107-131: at each conditional observe the retained
                              * particle's ancestor is redrawn from discrete(exp(v - max v)),
                              * v_i = lw_i + log f(retained_{t+1} | x_t^i) */
+    int32_t pad_;
+    double ess_threshold;   /* engine extension (the reference resamples at every
+                             * observe): > 0 = resample only when ESS < ess_threshold * N */
 } orc_sweep_opts;
 
 typedef struct {
@@ -169,6 +172,7 @@ typedef struct {
     int32_t* anc_hist;      /* [T*n] physical ancestors per step (keep_history) */
     double* x_hist;         /* [(T+1)*n*dim] pre-resample states per step (keep_history) */
     double* filt_mean;      /* [T*dim] weighted filtering mean before resampling */
+    double* lw_final;       /* [n] or NULL: log-weights of the final particles (adaptive sweeps) */
 } orc_sweep_out;
 
 /* y: [T*obs_dim] observations; retained: [(T+1)*dim] trajectory or NULL.

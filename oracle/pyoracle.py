@@ -57,13 +57,14 @@ class OrcSweepOpts(C.Structure):
     _fields_ = [("n", C.c_int64), ("T", C.c_int32), ("seed", C.c_uint64),
                 ("csmc", C.c_int32), ("n_cond_steps", C.c_int32),
                 ("reset_weights", C.c_int32), ("keep_history", C.c_int32),
-                ("threads", C.c_int32), ("ancestor_sampling", C.c_int32)]
+                ("threads", C.c_int32), ("ancestor_sampling", C.c_int32), ("pad_", C.c_int32),
+                ("ess_threshold", C.c_double)]
 
 
 class OrcSweepOut(C.Structure):
     _fields_ = [("log_z", C.c_double), ("log_mean_w", c_double_p), ("ess", c_double_p),
                 ("x_final", c_double_p), ("anc_hist", c_int32_p), ("x_hist", c_double_p),
-                ("filt_mean", c_double_p)]
+                ("filt_mean", c_double_p), ("lw_final", c_double_p)]
 
 
 def _declare(L):
@@ -369,13 +370,14 @@ class Model:
 
 def smc_sweep(model, y, n, seed, retained=None, csmc=False, n_cond_steps=0,
               reset_weights=False, keep_history=False, threads=1, want_final=True,
-              ancestor_sampling=False):
+              ancestor_sampling=False, ess_threshold=0.0):
     y = _f64(y)
     d = model.state_dim
     T = y.size // d
     o = OrcSweepOpts(n=n, T=T, seed=seed, csmc=int(csmc), n_cond_steps=n_cond_steps,
                      reset_weights=int(reset_weights), keep_history=int(keep_history),
-                     threads=threads, ancestor_sampling=int(ancestor_sampling))
+                     threads=threads, ancestor_sampling=int(ancestor_sampling),
+                     ess_threshold=float(ess_threshold))
     out = OrcSweepOut()
     res = dict(log_mean_w=np.empty(T), ess=np.empty(T), filt_mean=np.empty((T, d)))
     out.log_mean_w, out.ess = _dp(res["log_mean_w"]), _dp(res["ess"])
@@ -383,6 +385,9 @@ def smc_sweep(model, y, n, seed, retained=None, csmc=False, n_cond_steps=0,
     if want_final:
         res["x_final"] = np.empty((n, d))
         out.x_final = _dp(res["x_final"])
+    if ess_threshold > 0.0:
+        res["lw_final"] = np.empty(n)
+        out.lw_final = _dp(res["lw_final"])
     if keep_history:
         res["anc_hist"] = np.empty((T, n), dtype=np.int32)
         res["x_hist"] = np.empty((T + 1, n, d))
