@@ -13,7 +13,7 @@ try:
     d = json.loads(open("$O/$1.json").read().strip().splitlines()[-1])
     if "value" in d:
         one = d.get("one_sweep_in_flight", {}).get("value", 0)
-        print("$1", "%.1fG" % (d["value"]/1e9), "1fl %.1fG" % (one/1e9), "e2e %.1fG" % (d["e2e"]["value"]/1e9),
+        print("$1", "%.1fG" % (d["value"]/1e9), "1fl %.1fG" % (one/1e9), "e2e", d["e2e"]["value"], (d["e2e"].get("error") or "")[-160:],
               {k: round(v) for k, v in d["path_roofline"]["kernel_avg_us"].items()}, d.get("log_z_check"))
     else:
         print("$1", {k: d[k] for k in d if k != "node_log_z"})
