@@ -46,6 +46,8 @@ struct FoldSmem {
     int cross;
     int imin;
     double last_edge[TB];
+    double head[1024];           // generic_emit: literal fold of the first elements of a tile that
+                                 //   starts at zero (a binade crossing at every doubling of the sum)
 };
 
 __device__ __forceinline__ long long gtimer_ns() {
@@ -837,7 +839,6 @@ struct ChainSmem {
     double bcast;
     int cross, fallback;
     i64 last[TB];                // running units after each thread's elements (hard-tile search)
-    double head[1024];           // first weights of a fold that starts at zero
     Xd bc[CH_BC];                // staged per-block composites / class of the block's last tile
     int cend[CH_BC];
     int hl[HCAP];                // staged head of the hard list: tile, ex[tile], class of the
@@ -959,13 +960,13 @@ __device__ __forceinline__ double chain_hard_tile(const WSView& v, int lap, int 
     if (S == 0.0 && nvalid > HEAD) {
         if (threadIdx.x < HEAD / IPT) {
 #pragma unroll
-            for (int j = 0; j < IPT; ++j) sm.head[threadIdx.x * IPT + j] = w[j];
+            for (int j = 0; j < IPT; ++j) sm.fold.head[threadIdx.x * IPT + j] = w[j];
         }
         __syncthreads();
         if (threadIdx.x == 0) {
             double acc = S;
 #pragma unroll 8
-            for (int i = 0; i < HEAD; ++i) acc = acc + sm.head[i];              // smc.cljc:94
+            for (int i = 0; i < HEAD; ++i) acc = acc + sm.fold.head[i];         // smc.cljc:94
             sm.bcast = acc;
         }
         __syncthreads();
@@ -1590,7 +1591,35 @@ __device__ __noinline__ void generic_emit(const Comb& comb, double Sin, const do
     const int lane = threadIdx.x & 31;
     const int i0 = threadIdx.x * IPT;
     double edge[IPT];
-    (void)cta_tile_fold(Sin, w, nvalid, edge, sm);
+    {
+        // A fold that starts at zero crosses a binade at every doubling of the sum
+        // (elements 1, 2, 4, 8, ...): one thread adds the first elements literally
+        // (smc.cljc:120), the parallel fold takes over from there (as in k_chain).
+        constexpr int HEAD = 1024;
+        int pos = 0;
+        double S = Sin;
+        if (Sin == 0.0 && nvalid > HEAD) {
+            if (threadIdx.x < HEAD / IPT) {
+#pragma unroll
+                for (int j = 0; j < IPT; ++j) sm.head[threadIdx.x * IPT + j] = w[j];
+            }
+            __syncthreads();
+            if (threadIdx.x == 0) {
+                double acc = 0.0;
+#pragma unroll 8
+                for (int i = 0; i < HEAD; ++i) { acc = acc + sm.head[i]; sm.head[i] = acc; }
+            }
+            __syncthreads();
+            if (threadIdx.x < HEAD / IPT) {
+#pragma unroll
+                for (int j = 0; j < IPT; ++j) edge[j] = sm.head[threadIdx.x * IPT + j];
+            }
+            S = sm.head[HEAD - 1];
+            pos = HEAD;
+            __syncthreads();
+        }
+        (void)cta_tile_fold(S, w, nvalid, edge, sm, pos);
+    }
     sm.last_edge[threadIdx.x] = edge[IPT - 1];
     __syncthreads();
     const double pred = (threadIdx.x == 0) ? Sin : sm.last_edge[threadIdx.x - 1];

@@ -522,7 +522,8 @@ def run_ours(args):
                         "d2h_bytes_per_step": int(x_host_bytes + 2 * T * 8 + 64) * F},
                 "gpu_launches": int(launches), "clocks": clocks, "roofline": roof,
                 "path_roofline": path, "wall_ms_per_step": 1e3 * wall / args.steps,
-                "log_z_mean": float(np.mean(log_zs)), "log_z_check": logz_note}
+                "log_z_mean": float(np.mean(log_zs)), "log_z_check": logz_note,
+                "log_zs": {"f%d_i%d" % (f, i): z for f in range(len(zs)) for i, z in enumerate(zs[f])}}
         if args.workload == "lgssm1d":
             kz = kalman_logz(y)
             line["kalman_check"] = {"exact_log_z": kz, "max_abs_error_of_timed_sweeps":
