@@ -1036,8 +1036,14 @@ __device__ double chain_lap(const WSView& v, int lap, double S, int64_t stop, do
             if (threadIdx.x == 0) v.shin[lap][h] = S_at;
             shin_done = h + 1;
             if (S_at > limit) { over = true; break; }
+            long long tc0 = 0;
+            if (threadIdx.x == 0) tc0 = clock64();
             S = chain_hard_tile(v, lap, h, nh, t, S_at, hctx_of(h), hctx_of(h + 1), P, lw, win, n,
                                 m, sm);
+            if (threadIdx.x == 0 && h < 128) {       // diagnostics (apop_debug_chain_trace): cycles
+                v.trace[lap * 256 + 2 * h] = (double)(clock64() - tc0);
+                v.trace[lap * 256 + 2 * h + 1] = (double)tc0;
+            }
             su = units_of(S);
             se = ctx_of(S);
             if (threadIdx.x == 0) v.shout[lap][h] = S;

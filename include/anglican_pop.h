@@ -175,8 +175,8 @@ int apop_selftest_math(apop_ctx* ctx, int fn, apop_col in, apop_col out);
  * exact chain, ns in sums/exchange/comb table, ns in lap 1, comb segments,
  * hard tiles lap 0, hard tiles lap 1, first skipped tile of lap 1, J} */
 int apop_debug_resolve_phases(apop_ctx* ctx, double* out8);
-/* per hard-tile event of the last chain: out512[lap*256 + 2h] = ns spent folding
- * hard tile h, out512[lap*256 + 2h + 1] = device timestamp (ns) when it began */
+/* per hard-tile event of the last chain: out512[lap*256 + 2h] = SM cycles spent folding
+ * hard tile h, out512[lap*256 + 2h + 1] = cycle counter when it began */
 int apop_debug_chain_trace(apop_ctx* ctx, double* out512);
 
 /* ---- weights: particle-weights / log-sum-exp / ESS ---------------------

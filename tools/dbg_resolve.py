@@ -26,5 +26,5 @@ with Population(n, seed=3) as pop:
     tr = np.zeros(512)
     pop.lib.apop_debug_chain_trace(pop.ctx, tr.ctypes.data_as(L.c_double_p))
     nh = int(out[4])
-    print("lap0 hard-tile fold ns:", [int(tr[2*h]) for h in range(nh)])
-    print("lap0 gaps between starts ns:", [int(tr[2*h+3] - tr[2*h+1]) for h in range(nh-1)])
+    print("lap0 hard-tile fold cycles:", [int(tr[2*h]) for h in range(nh)])
+    print("lap0 cycles between hard-tile starts:", [int(tr[2*h+3] - tr[2*h+1]) for h in range(nh-1)])
