@@ -45,3 +45,23 @@ def test_workload_generators_are_deterministic():
     assert all(np.array_equal(x, y) for x, y in zip(a, b))
     A, Qc, R, y = a
     assert y.shape == (32,) and np.allclose(A @ A.T, 0.81 * np.eye(8))       # A = 0.9 Q, Q orthogonal
+
+
+def test_reference_arm_line_lgssm1d_and_kalman_helper():
+    d = _run("--workload", "lgssm1d", "--T", "10")
+    assert "configs[1]" in d["config"]["workload"] and d["value"] > 0
+    sys.path.insert(0, ROOT)
+    import bench
+    from oracle import pyoracle as orc
+    y = bench.lgssm_observations(200)
+    m = orc.Model(orc.SSM_LGSSM1D, m0=0.0, s0=1.0, a=0.9, b=0.0, q=1.0, c=1.0, d=0.0, r=1.0)
+    assert abs(bench.kalman_logz(y) - orc.kalman1d(m, y)[0]) < 1e-9
+
+
+def test_recorded_log_z_file_is_well_formed():
+    ref = json.load(open(os.path.join(ROOT, "profiles", "logz_reference.json")))
+    assert "sv/n134217728/T2000" in ref
+    for key, vals in ref.items():
+        wl, n, T = key.split("/")
+        assert wl in ("sv", "lgssm1d", "lgmvn64") and n.startswith("n") and T.startswith("T")
+        assert all(k.startswith("f") and isinstance(v, float) for k, v in vals.items())
