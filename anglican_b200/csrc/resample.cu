@@ -955,7 +955,7 @@ __device__ __forceinline__ double chain_hard_tile(const WSView& v, int lap, int 
     // A fold that starts near zero crosses a binade at every doubling of the sum
     // (elements 1, 2, 4, 8, ...): one thread adds the first elements literally,
     // the parallel fold takes over from there.
-    constexpr int HEAD = 128;            // 45 cycles per literal add vs ~3000 per parallel crossing: break-even near 64-128
+    constexpr int HEAD = 1024;           // measured (chain trace, cycles of tile 0): 1024 -> 58.8k, 128 -> 78.6k
     int pos = 0;
     if (S == 0.0 && nvalid > HEAD) {
         if (threadIdx.x < HEAD / IPT) {
@@ -1601,7 +1601,7 @@ __device__ __noinline__ void generic_emit(const Comb& comb, double Sin, const do
         // A fold that starts at zero crosses a binade at every doubling of the sum
         // (elements 1, 2, 4, 8, ...): one thread adds the first elements literally
         // (smc.cljc:120), the parallel fold takes over from there (as in k_chain).
-        constexpr int HEAD = 128;            // 45 cycles per literal add vs ~3000 per parallel crossing: break-even near 64-128
+        constexpr int HEAD = 1024;           // measured (chain trace, cycles of tile 0): 1024 -> 58.8k, 128 -> 78.6k
         int pos = 0;
         double S = Sin;
         if (Sin == 0.0 && nvalid > HEAD) {
