@@ -51,11 +51,22 @@ __device__ __forceinline__ double uniform_logpdf(double x, double lo, double hi)
     for (int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; k < (n);   \
          k += (int64_t)gridDim.x * blockDim.x)
 
+// one thread per slot PAIR: both halves of the Box-Muller pair are used (slots 2p, 2p+1;
+// g0 is even for every shard layout the engine accepts)
 __global__ void k_sample_normal(DArg mean, DArg sd, double* out, int64_t n, int64_t g0,
                                 uint64_t seed, uint32_t t, uint32_t draw) {
-    GRID_STRIDE(k, n) {
-        double z = normal_at(seed, (uint64_t)(g0 + k), t, STREAM_USER, draw);
-        out[k] = sd.at(k) * z + mean.at(k);            // NormalDistribution.sample
+    const int64_t np = (n + 1) >> 1;
+    GRID_STRIDE(p, np) {
+        const int64_t k = 2 * p;
+        double z0, z1;
+        if ((g0 & 1) == 0) {
+            normal_pair_at(seed, (uint64_t)(g0 + k) >> 1, t, STREAM_USER, draw, z0, z1);
+        } else {
+            z0 = normal_at(seed, (uint64_t)(g0 + k), t, STREAM_USER, draw);
+            z1 = normal_at(seed, (uint64_t)(g0 + k + 1), t, STREAM_USER, draw);
+        }
+        out[k] = sd.at(k) * z0 + mean.at(k);           // NormalDistribution.sample
+        if (k + 1 < n) out[k + 1] = sd.at(k + 1) * z1 + mean.at(k + 1);
     }
 }
 __global__ void k_observe_normal(DArg mean, DArg sd, DArg val, double* lw, int64_t n) {
@@ -252,7 +263,7 @@ int apop_sample_normal(apop_ctx* c, apop_arg mean, apop_arg sd, uint32_t draw, a
     APOP_TRY(resolve_arg(c, mean, &m)); APOP_TRY(resolve_arg(c, sd, &s));
     Column* o = get_col(c, out, APOP_F64, 1);
     if (!o) return APOP_ERR_INVALID;
-    k_sample_normal<<<grid_for(c, c->n, 256), 256, 0, c->stream>>>(m, s, (double*)o->ptr, c->n, c->g0,
+    k_sample_normal<<<grid_for(c, (c->n + 1) / 2, 256), 256, 0, c->stream>>>(m, s, (double*)o->ptr, c->n, c->g0,
                                                                  c->seed, c->step, draw);
     LAUNCH_DONE(c);
     return APOP_OK;
