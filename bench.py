@@ -4,7 +4,7 @@
     python bench.py --gpus N --steps K --warmup W          (our arm)
     python bench.py --impl reference --gpus N --steps K --warmup W
 
-One "step" = `--inflight` (default 2) independent full `sweep`s (smc.cljc:35-51;
+One "step" = `--inflight` (default 3) independent full `sweep`s (smc.cljc:35-51;
 `infer :smc` is an endless sequence of independent sweeps, smc.cljc:58-63) of
 BASELINE config 3: the stochastic-volatility SSM, T=2000 observations, 2^27
 particles in total per sweep, sharded contiguously over the N ranks (strong
@@ -609,10 +609,10 @@ def main():
     ap.add_argument("--record-logz", action="store_true",
                     help="N = 1: store the log Z of every timed sweep in profiles/logz_reference.json; "
                          "runs at any N compare against it")
-    ap.add_argument("--inflight", type=int, default=2,
-                    help="independent sweeps kept in flight, one population each (measured: "
-                         "1 GPU 59 -> 62 G, 8 GPUs 214 -> 318 (2) -> 365 (3) G particle-steps/s; "
-                         "4 and more stalled on peer waits at 8 GPUs, profiles/r02b_*)")
+    ap.add_argument("--inflight", type=int, default=3,
+                    help="independent sweeps kept in flight, one population each (round 2, "
+                         "G particle-steps/s: 1 GPU 65.6 (1) -> 69.3 (2) = (3); 8 GPUs 253 (1) -> 356 (2) "
+                         "-> 425 (3); 4 complete, 6 stall on peer waits at 8 GPUs - DESIGN.md section 5)")
     ap.add_argument("--max-connections", type=int, default=0,
                     help="experiment: CUDA_DEVICE_MAX_CONNECTIONS for this process (0 = leave the "
                          "driver default); to try with --inflight > 3 on several GPUs")
