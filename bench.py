@@ -513,7 +513,10 @@ def run_ours(args):
                            "resampling": "systematic, every step",
                            "sweeps_in_flight": F,
                            "step": "one step = %d independent sweep(s) of the workload in flight, "
-                                   "one population (context + stream) each" % F,
+                                   "one population (context + stream) each; `value` times the sweeps "
+                                   "up to log Z (no final-state gather / download), `e2e` includes "
+                                   "the gather, the download of all final states and the per-step "
+                                   "statistics" % F,
                            "l2": "inputs exceed L2 (columns of %d MiB per GPU)" % (n_local * 8 >> 20),
                            "timing": "CUDA events on the engine stream, max over ranks"},
                 "e2e": {"value": (work / e2e_s) if e2e_error is None else None, "unit": UNIT,
