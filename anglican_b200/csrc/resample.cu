@@ -151,7 +151,7 @@ __device__ __noinline__ double cta_tile_fold(double S_in, const double (&w)[IPT]
                 xd_push(t, f, up, tie);
             }
         }
-        if (threadIdx.x == 0) sm.cross = INT_MAX;
+        if (threadIdx.x == 0) { sm.cross = INT_MAX; sm.imin += 1; }
         Xd ex = cta_excl_scan_xd(t, sm.warp_tot);      // has a __syncthreads
         i64 s = xd_apply(s_in, ex);
         int mycross = INT_MAX;
@@ -951,7 +951,10 @@ __device__ __forceinline__ double chain_hard_tile(const WSView& v, int lap, int 
     double w[IPT], edge[IPT];
     const int64_t base = t * TILE;
     const int nvalid = (int)((n - base < TILE) ? (n - base) : TILE);
+    long long tq0 = 0, tq1 = 0, tq2 = 0;
+    if (threadIdx.x == 0) tq0 = clock64();
     load_weights(lw, win, base, n, m, w);
+    if (threadIdx.x == 0) tq1 = clock64();
     // A fold that starts near zero crosses a binade at every doubling of the sum
     // (elements 1, 2, 4, 8, ...): one thread adds the first elements literally,
     // the parallel fold takes over from there.
@@ -974,8 +977,15 @@ __device__ __forceinline__ double chain_hard_tile(const WSView& v, int lap, int 
         pos = HEAD;
         __syncthreads();
     }
+    if (threadIdx.x == 0) { tq2 = clock64(); sm.fold.imin = 0; }
     const double r = cta_tile_fold(S, w, nvalid, edge, sm.fold, pos);
     __syncthreads();
+    if (threadIdx.x == 0 && lap == 0 && h == 0) {      // diagnostics: phases of the general fold
+        v.trace[480] = (double)(tq1 - tq0);            // weights (exp)
+        v.trace[481] = (double)(tq2 - tq1);            // literal head
+        v.trace[482] = (double)(clock64() - tq2);      // parallel fold
+        v.trace[483] = (double)sm.fold.imin;           // its iterations
+    }
     hard_prefetch(v, lap, h + 1, nh, eA_next, P);
     return r;
 }

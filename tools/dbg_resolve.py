@@ -28,3 +28,5 @@ with Population(n, seed=3) as pop:
     nh = int(out[4])
     print("lap0 hard-tile fold cycles:", [int(tr[2*h]) for h in range(nh)])
     print("lap0 cycles between hard-tile starts:", [int(tr[2*h+3] - tr[2*h+1]) for h in range(nh-1)])
+    print("general fold of tile 0 (cycles): weights %d, literal head %d, parallel fold %d in %d iterations" %
+          (tr[480], tr[481], tr[482], tr[483]))
