@@ -193,6 +193,27 @@ __device__ __noinline__ double cta_tile_fold(double S_in, const double (&w)[IPT]
     }
 }
 
+// The same fold for a tile whose running sum starts at zero, from element `pos` on.  The sum
+// roughly doubles whenever the element count doubles, so there is a binade crossing in nearly
+// every window [lo, 2 lo): folding window by window keeps the threads beyond the window
+// idle (an iteration of cta_tile_fold costs ~10 k cycles when all 512 threads re-quantise
+// and replay their elements, ~2-4 k when one to eight warps do).
+#ifndef APOP_HEAD
+#define APOP_HEAD 256
+#endif
+__device__ __forceinline__ double cta_tile_fold_windowed(double S, const double (&w)[IPT], int nvalid,
+                                                         double (&edge)[IPT], FoldSmem& sm, int pos) {
+    int lo = pos;
+    while (lo < nvalid) {
+        int hi = 2 * lo;
+        if (hi > nvalid || lo == 0) hi = nvalid;
+        S = cta_tile_fold(S, w, hi, edge, sm, lo);
+        __syncthreads();
+        lo = hi;
+    }
+    return S;
+}
+
 // raw tile values: the weights themselves (weights mode) or the log-weights
 __device__ __forceinline__ void load_raw(const double* __restrict__ lw,
                                          const double* __restrict__ win, int64_t base,
@@ -958,7 +979,7 @@ __device__ __forceinline__ double chain_hard_tile(const WSView& v, int lap, int 
     // A fold that starts near zero crosses a binade at every doubling of the sum
     // (elements 1, 2, 4, 8, ...): one thread adds the first elements literally,
     // the parallel fold takes over from there.
-    constexpr int HEAD = 1024;           // measured (chain trace, cycles of tile 0): 1024 -> 58.8k, 128 -> 78.6k
+    constexpr int HEAD = APOP_HEAD;
     int pos = 0;
     if (S == 0.0 && nvalid > HEAD) {
         if (threadIdx.x < HEAD / IPT) {
@@ -978,7 +999,8 @@ __device__ __forceinline__ double chain_hard_tile(const WSView& v, int lap, int 
         __syncthreads();
     }
     if (threadIdx.x == 0) { tq2 = clock64(); sm.fold.imin = 0; }
-    const double r = cta_tile_fold(S, w, nvalid, edge, sm.fold, pos);
+    const double r = (pos > 0) ? cta_tile_fold_windowed(S, w, nvalid, edge, sm.fold, pos)
+                               : cta_tile_fold(S, w, nvalid, edge, sm.fold, pos);
     __syncthreads();
     if (threadIdx.x == 0 && lap == 0 && h == 0) {      // diagnostics: phases of the general fold
         v.trace[480] = (double)(tq1 - tq0);            // weights (exp)
@@ -1634,7 +1656,8 @@ __device__ __noinline__ void generic_emit(const Comb& comb, double Sin, const do
             pos = HEAD;
             __syncthreads();
         }
-        (void)cta_tile_fold(S, w, nvalid, edge, sm, pos);
+        if (pos > 0) (void)cta_tile_fold_windowed(S, w, nvalid, edge, sm, pos);
+        else (void)cta_tile_fold(S, w, nvalid, edge, sm, pos);
     }
     sm.last_edge[threadIdx.x] = edge[IPT - 1];
     __syncthreads();
