@@ -193,26 +193,16 @@ __device__ __noinline__ double cta_tile_fold(double S_in, const double (&w)[IPT]
     }
 }
 
-// The same fold for a tile whose running sum starts at zero, from element `pos` on.  The sum
-// roughly doubles whenever the element count doubles, so there is a binade crossing in nearly
-// every window [lo, 2 lo): folding window by window keeps the threads beyond the window
-// idle (an iteration of cta_tile_fold costs ~10 k cycles when all 512 threads re-quantise
-// and replay their elements, ~2-4 k when one to eight warps do).
+// Length of the literal head fold of a tile whose running sum starts at zero (chain general
+// path, generic_emit).  Measured with the chain trace (tools/dbg_resolve.py, cycles of tile 0
+// at 2^27 particles): a literal add costs 13 cycles, one parallel crossing iteration of
+// cta_tile_fold 8-10 k cycles whether 16 warps or one take part (it is bound by its barriers
+// and scans, not by instruction issue), so folding window by window only adds iterations:
+//   head 1024: 13.2 k + 4 iterations 41 k   | head 512 + windows: 6.8 k + 8 iterations 66 k
+//   head 256 + windows: 3.5 k + 10 it. 77 k | head 128: 1.8 k + 12 iterations 90 k
 #ifndef APOP_HEAD
-#define APOP_HEAD 256
+#define APOP_HEAD 1024
 #endif
-__device__ __forceinline__ double cta_tile_fold_windowed(double S, const double (&w)[IPT], int nvalid,
-                                                         double (&edge)[IPT], FoldSmem& sm, int pos) {
-    int lo = pos;
-    while (lo < nvalid) {
-        int hi = 2 * lo;
-        if (hi > nvalid || lo == 0) hi = nvalid;
-        S = cta_tile_fold(S, w, hi, edge, sm, lo);
-        __syncthreads();
-        lo = hi;
-    }
-    return S;
-}
 
 // raw tile values: the weights themselves (weights mode) or the log-weights
 __device__ __forceinline__ void load_raw(const double* __restrict__ lw,
@@ -999,8 +989,7 @@ __device__ __forceinline__ double chain_hard_tile(const WSView& v, int lap, int 
         __syncthreads();
     }
     if (threadIdx.x == 0) { tq2 = clock64(); sm.fold.imin = 0; }
-    const double r = (pos > 0) ? cta_tile_fold_windowed(S, w, nvalid, edge, sm.fold, pos)
-                               : cta_tile_fold(S, w, nvalid, edge, sm.fold, pos);
+    const double r = cta_tile_fold(S, w, nvalid, edge, sm.fold, pos);
     __syncthreads();
     if (threadIdx.x == 0 && lap == 0 && h == 0) {      // diagnostics: phases of the general fold
         v.trace[480] = (double)(tq1 - tq0);            // weights (exp)
@@ -1656,8 +1645,7 @@ __device__ __noinline__ void generic_emit(const Comb& comb, double Sin, const do
             pos = HEAD;
             __syncthreads();
         }
-        if (pos > 0) (void)cta_tile_fold_windowed(S, w, nvalid, edge, sm, pos);
-        else (void)cta_tile_fold(S, w, nvalid, edge, sm, pos);
+        (void)cta_tile_fold(S, w, nvalid, edge, sm, pos);
     }
     sm.last_edge[threadIdx.x] = edge[IPT - 1];
     __syncthreads();
