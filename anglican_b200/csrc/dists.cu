@@ -53,6 +53,8 @@ __device__ __forceinline__ double uniform_logpdf(double x, double lo, double hi)
 
 // one thread per slot PAIR: both halves of the Box-Muller pair are used (slots 2p, 2p+1;
 // g0 is even for every shard layout the engine accepts)
+// one thread per slot PAIR: both halves of the Box-Muller pair are used (slots 2p, 2p+1;
+// g0 is even for every shard layout the engine accepts)
 // observe: lw[k] += EXPR(k), four independent elements per thread and iteration with all
 // loads issued before the first store (a plain grid-stride read-modify-write keeps one
 // 16-byte request per thread in flight: 3.2 TB/s at 2^24 particles,
@@ -91,7 +93,7 @@ __global__ void k_sample_normal(DArg mean, DArg sd, double* out, int64_t n, int6
     }
 }
 __global__ void k_observe_normal(DArg mean, DArg sd, DArg val, double* lw, int64_t n) {
-    OBSERVE4(n, lw, normal_logpdf(val.at(k), mean.at(k), sd.at(k)))
+    GRID_STRIDE(k, n) lw[k] += normal_logpdf(val.at(k), mean.at(k), sd.at(k));
 }
 __global__ void k_sample_gamma(DArg shape, DArg rate, double* out, int64_t n, int64_t g0,
                                uint64_t seed, uint32_t t, uint32_t draw) {
@@ -100,7 +102,7 @@ __global__ void k_sample_gamma(DArg shape, DArg rate, double* out, int64_t n, in
                             draw * 256u);
 }
 __global__ void k_observe_gamma(DArg shape, DArg rate, DArg val, double* lw, int64_t n) {
-    OBSERVE4(n, lw, gamma_logpdf(val.at(k), shape.at(k), rate.at(k)))
+    GRID_STRIDE(k, n) lw[k] += gamma_logpdf(val.at(k), shape.at(k), rate.at(k));
 }
 __global__ void k_sample_beta(DArg a, DArg b, double* out, int64_t n, int64_t g0, uint64_t seed,
                               uint32_t t, uint32_t draw) {
@@ -112,7 +114,7 @@ __global__ void k_sample_beta(DArg a, DArg b, double* out, int64_t n, int64_t g0
     }
 }
 __global__ void k_observe_beta(DArg a, DArg b, DArg val, double* lw, int64_t n) {
-    OBSERVE4(n, lw, beta_logpdf(val.at(k), a.at(k), b.at(k)))
+    GRID_STRIDE(k, n) lw[k] += beta_logpdf(val.at(k), a.at(k), b.at(k));
 }
 __global__ void k_sample_uniform(DArg lo, DArg hi, double* out, int64_t n, int64_t g0,
                                  uint64_t seed, uint32_t t, uint32_t draw) {
@@ -122,7 +124,7 @@ __global__ void k_sample_uniform(DArg lo, DArg hi, double* out, int64_t n, int64
     }
 }
 __global__ void k_observe_uniform(DArg lo, DArg hi, DArg val, double* lw, int64_t n) {
-    OBSERVE4(n, lw, uniform_logpdf(val.at(k), lo.at(k), hi.at(k)))
+    GRID_STRIDE(k, n) lw[k] += uniform_logpdf(val.at(k), lo.at(k), hi.at(k));
 }
 
 // discrete: weights shared (wstride = 0) or per particle (wstride = K)
