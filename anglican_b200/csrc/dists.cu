@@ -53,29 +53,6 @@ __device__ __forceinline__ double uniform_logpdf(double x, double lo, double hi)
 
 // one thread per slot PAIR: both halves of the Box-Muller pair are used (slots 2p, 2p+1;
 // g0 is even for every shard layout the engine accepts)
-// one thread per slot PAIR: both halves of the Box-Muller pair are used (slots 2p, 2p+1;
-// g0 is even for every shard layout the engine accepts)
-// observe: lw[k] += EXPR(k), four independent elements per thread and iteration with all
-// loads issued before the first store (a plain grid-stride read-modify-write keeps one
-// 16-byte request per thread in flight: 3.2 TB/s at 2^24 particles,
-// profiles/r02_ncu_column_kernels.txt)
-#define OBSERVE4(n, lw, EXPR)                                                                   \
-    {                                                                                           \
-        const int64_t S_ = (int64_t)gridDim.x * blockDim.x;                                     \
-        for (int64_t k0_ = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; k0_ < (n);           \
-             k0_ += 4 * S_) {                                                                   \
-            double a_[4], f_[4];                                                                \
-            _Pragma("unroll") for (int u_ = 0; u_ < 4; ++u_) {                                  \
-                const int64_t k = k0_ + u_ * S_;                                                \
-                if (k < (n)) { a_[u_] = lw[k]; f_[u_] = (EXPR); }                               \
-            }                                                                                   \
-            _Pragma("unroll") for (int u_ = 0; u_ < 4; ++u_) {                                  \
-                const int64_t k = k0_ + u_ * S_;                                                \
-                if (k < (n)) lw[k] = a_[u_] + f_[u_];                                           \
-            }                                                                                   \
-        }                                                                                       \
-    }
-
 __global__ void k_sample_normal(DArg mean, DArg sd, double* out, int64_t n, int64_t g0,
                                 uint64_t seed, uint32_t t, uint32_t draw) {
     const int64_t np = (n + 1) >> 1;
