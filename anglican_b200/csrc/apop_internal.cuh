@@ -60,7 +60,7 @@ struct SweepDev {           // device-resident scalars of a fused sweep
     unsigned long long seed; // graph-replayed sweeps read the RNG key from here (see run_group)
 };
 
-// per-step outputs of a fused sweep, written by the tail of k_resolve
+// per-step outputs of a fused sweep, written by k_chain
 struct StepOut {
     SweepDev* sd;           // nullptr outside sweeps
     double* log_mean_w;

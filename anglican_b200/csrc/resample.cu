@@ -5,11 +5,12 @@
 // Pipeline (all on ctx->stream, no host round trip):
 //   K2  k_tile_lse      per-tile (max, sum exp, sum exp^2) of the log-weights
 //                       (inside a fused sweep k_propagate produces these)
-//       k_finalize      global max m, approximate tile prefix, per-tile binade
-//                       classification for both laps of the wheel
+//       k_fin_a/b       global max m (atomicMax of the producer), approximate tile prefix,
+//                       per-tile binade classification for both laps of the wheel
 //   K3a k_fold_agg      per-tile aggregate of the exact fold (integer units of
 //                       the tile's binade) + accurate sum w, sum w^2
-//       k_resolve       chains the aggregates -> exact running sum at every
+//       k_seg_scan, k_chain, k_expand ("resolve")
+//                       chain the aggregates -> exact running sum at every
 //                       tile boundary, exact total, pointer-comb table, J,
 //                       ESS / log-mean-weight, per-step sweep outputs
 //   K3b/K4 k_ancestors  per-element exact edges merged against the pointer

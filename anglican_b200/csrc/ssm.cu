@@ -162,7 +162,7 @@ __global__ void __launch_bounds__(TB) k_init(const ModelDev* __restrict__ Mp, do
 
 // K1: propagate + reweight + tile partials (scalar-state models).
 // The tile partials (max, approximate sum of exp(lw - max)) only steer the
-// binade classification of k_finalize, so the exponentials are fp32 MUFU.EX2
+// binade classification of k_fin_b, so the exponentials are fp32 MUFU.EX2
 // against a per-warp reference; the exact sums (ESS, log-mean-weight) come
 // from k_fold_agg.
 __device__ __forceinline__ float ex2_approx(float x) {

@@ -331,7 +331,7 @@ def run_ours(args):
     # `infer :smc` is an endless sequence of INDEPENDENT sweeps (sample-seq,
     # smc.cljc:58-63).  F of them are kept in flight, each on its own population
     # (context + stream): the single-CTA phases of one sweep's exact resampler
-    # (k_finalize, k_chain) overlap with the streaming kernels of the other.
+    # (k_fin_a/b tails, k_chain) overlap with the streaming kernels of the others.
     from concurrent.futures import ThreadPoolExecutor
     F = max(1, min(args.inflight, 8))
     pops = []
