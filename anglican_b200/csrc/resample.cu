@@ -46,6 +46,7 @@ struct FoldSmem {
     double bcast_S;
     int cross;
     int imin;
+    double dsum[NWARP];          // cta_tile_fold fast iteration: per-warp sums of integer-valued doubles
     double last_edge[TB];
     double head[1024];           // generic_emit: literal fold of the first elements of a tile that
                                  //   starts at zero (a binade crossing at every doubling of the sum)
@@ -136,6 +137,62 @@ __device__ __noinline__ double cta_tile_fold(double S_in, const double (&w)[IPT]
         const i64 s_in = units_of(S);
         const bool fast = ctx_fast_ok(e);
         const double inv_u = fast ? pow2(-e) : 0.0;
+        int mycross = INT_MAX;
+        i64 sprev = 0;
+        if (threadIdx.x == 0) { sm.cross = INT_MAX; sm.imin += 1; }
+        bool done = false;
+        if (fast) {
+            // ---- fast iteration: no element ties or saturates in this binade, so every
+            // increment is RN(w / ulp) by the 2^52 magic add and the prefix sums are plain
+            // fp64 additions of integer-valued doubles.  Only additions are used: a prefix
+            // below 2^53 is exact, one at or above 2^53 can only round to a value >= 2^53, so
+            // "s_in + prefix >= 2^53" (the crossing) is decided exactly.  ~5x fewer
+            // instructions than the parity-transducer iteration below.
+            double incD[IPT];
+            double loc = 0.0;
+            int bad = 0;
+#pragma unroll
+            for (int j = 0; j < IPT; ++j) {
+                const int idx = i0 + j;
+                double rn = 0.0;
+                if (idx >= pos && idx < nvalid) {
+                    const double scaled = w[j] * inv_u;
+                    rn = (scaled + 4503599627370496.0) - 4503599627370496.0;
+                    bad |= !(scaled < 4503599627370496.0) | (fabs(scaled - rn) == 0.5);
+                }
+                incD[j] = rn;
+                loc += rn;
+            }
+            if (!__syncthreads_or(bad)) {
+                const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+                double inc = loc;
+#pragma unroll
+                for (int d = 1; d < 32; d <<= 1) {
+                    const double o = __shfl_up_sync(0xffffffffu, inc, d);
+                    if (lane >= d) inc += o;
+                }
+                double exl = __shfl_up_sync(0xffffffffu, inc, 1);
+                if (lane == 0) exl = 0.0;
+                if (lane == 31) sm.dsum[wid] = inc;
+                __syncthreads();
+                double pre = 0.0;
+                for (int i = 0; i < wid; ++i) pre += sm.dsum[i];
+                pre += exl;
+                const double L = (double)(kTwo53 - s_in), sD0 = (double)s_in, ulp = pow2(e);
+                double sD = pre;
+#pragma unroll
+                for (int j = 0; j < IPT; ++j) {
+                    const int idx = i0 + j;
+                    if (idx >= pos && idx < nvalid && mycross == INT_MAX) {
+                        const double nx = sD + incD[j];
+                        if (nx >= L) { mycross = idx; sprev = s_in + (i64)sD; }
+                        else { sD = nx; edge[j] = (sD0 + sD) * ulp; }
+                    }
+                }
+                done = true;
+            }
+        }
+        if (!done) {
         i64 qf[IPT];
         int qfl[IPT];
         Xd t = xd_identity();
@@ -152,11 +209,8 @@ __device__ __noinline__ double cta_tile_fold(double S_in, const double (&w)[IPT]
                 xd_push(t, f, up, tie);
             }
         }
-        if (threadIdx.x == 0) { sm.cross = INT_MAX; sm.imin += 1; }
         Xd ex = cta_excl_scan_xd(t, sm.warp_tot);      // has a __syncthreads
         i64 s = xd_apply(s_in, ex);
-        int mycross = INT_MAX;
-        i64 sprev = 0;
 #pragma unroll
         for (int j = 0; j < IPT; ++j) {
             if ((qfl[j] & 4) && mycross == INT_MAX) {
@@ -164,6 +218,7 @@ __device__ __noinline__ double cta_tile_fold(double S_in, const double (&w)[IPT]
                 if (s2 >= kTwo53) { mycross = i0 + j; sprev = s; }
                 else { s = s2; edge[j] = from_units(s, e); }
             }
+        }
         }
         if (mycross != INT_MAX) atomicMin(&sm.cross, mycross);
         __syncthreads();
