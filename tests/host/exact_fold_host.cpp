@@ -71,6 +71,84 @@ double tile_exact_fold(double S_in, const double* w, int n, double* edges, int* 
     return S;
 }
 
+// The FAST iteration of cta_tile_fold (csrc/resample.cu): increments as integer-valued
+// doubles (2^52 magic add), prefix sums by ADDITIONS ONLY in the device's tree - 8 elements
+// per lane serially, Hillis-Steele over the 32 lanes of a warp, warp totals serially - and
+// the crossing decided by "prefix >= 2^53 - s_in".  A prefix below 2^53 is exact, one at or
+// above it can only round to >= 2^53, so the decision is exact although the sums are not.
+// Returns S_out, or NaN if an element ties / saturates (the device then falls back to the
+// transducer iteration, emulated by tile_exact_fold above).
+double tile_exact_fold_fast(double S_in, const double* w, int n, double* edges, int* iters) {
+    const int LANES = 32;
+    int pos = 0;
+    double S = S_in;
+    const int nl = (n + LANE_ITEMS - 1) / LANE_ITEMS;
+    std::vector<double> loc(nl), inc(nl), pre(nl);
+    std::vector<double> incD(nl * LANE_ITEMS);
+    while (pos < n) {
+        if (iters) *iters += 1;
+        const int e = ctx_of(S);
+        if (!ctx_fast_ok(e)) return NAN;
+        const i64 s_in = units_of(S);
+        const double inv_u = pow2(-e), ulp = pow2(e);
+        for (int l = 0; l < nl; ++l) {
+            double a = 0.0;
+            for (int j = 0; j < LANE_ITEMS; ++j) {
+                const int i = l * LANE_ITEMS + j;
+                double rn = 0.0;
+                if (i >= pos && i < n) {
+                    const double scaled = w[i] * inv_u;
+                    rn = (scaled + 4503599627370496.0) - 4503599627370496.0;
+                    if (!(scaled < 4503599627370496.0) || std::fabs(scaled - rn) == 0.5) return NAN;
+                }
+                incD[i < (int)incD.size() ? i : 0] = rn;
+                a += rn;
+            }
+            loc[l] = a;
+        }
+        // inclusive Hillis-Steele scan inside each warp, then serial warp prefixes
+        inc = loc;
+        for (int d = 1; d < LANES; d <<= 1) {
+            std::vector<double> nxt = inc;
+            for (int l = 0; l < nl; ++l)
+                if ((l % LANES) >= d) nxt[l] = inc[l] + inc[l - d];
+            inc = nxt;
+        }
+        const int nw = (nl + LANES - 1) / LANES;
+        std::vector<double> wtot(nw, 0.0);
+        for (int wq = 0; wq < nw; ++wq) {
+            int last = wq * LANES + LANES - 1;
+            if (last >= nl) last = nl - 1;
+            wtot[wq] = inc[last];
+        }
+        for (int l = 0; l < nl; ++l) {
+            double p = 0.0;
+            for (int wq = 0; wq < l / LANES; ++wq) p += wtot[wq];
+            p += (l % LANES) ? inc[l - 1] : 0.0;
+            pre[l] = p;
+        }
+        const double L = (double)(kTwo53 - s_in), sD0 = (double)s_in;
+        int cross = -1;
+        i64 sprev = 0;
+        for (int l = 0; l < nl && cross < 0; ++l) {
+            double sD = pre[l];
+            for (int j = 0; j < LANE_ITEMS; ++j) {
+                const int i = l * LANE_ITEMS + j;
+                if (i < pos || i >= n) continue;
+                const double nx = sD + incD[i];
+                if (nx >= L) { cross = i; sprev = s_in + (i64)sD; break; }
+                sD = nx;
+                edges[i] = (sD0 + sD) * ulp;
+            }
+        }
+        if (cross < 0) { S = edges[n - 1]; pos = n; break; }
+        S = from_units(sprev, e) + w[cross];          // the crossing add, hardware fp64
+        edges[cross] = S;
+        pos = cross + 1;
+    }
+    return S;
+}
+
 } // namespace
 
 extern "C" {
@@ -178,6 +256,15 @@ int host_exact_resample(const double* w, int64_t n, int64_t n_new, double u, int
     if (written != n_new) return -18;
     if (stats) { stats[0] = hard0; stats[1] = hard1; stats[2] = iters; stats[3] = comb.nseg; }
     return 0;
+}
+
+// exact fold of w[0..n) from S_in by the fast iteration; returns 0 and the edges, 1 if it
+// had to give up (tie / saturation / context outside the fast range)
+int host_fold_fast(double S_in, const double* w, int n, double* edges, double* S_out) {
+    int it = 0;
+    const double S = tile_exact_fold_fast(S_in, w, n, edges, &it);
+    *S_out = S;
+    return (S != S) ? 1 : 0;
 }
 
 // classification of one tile from its approximate prefix (k_finalize)

@@ -28,6 +28,7 @@ def host():
     lib = C.CDLL(OUT)
     lib.host_exact_resample.argtypes = [dp, C.c_int64, C.c_int64, C.c_double, C.c_int, ip, ip, dp, lp]
     lib.host_comb_values.argtypes = [C.c_double, C.c_double, C.c_int64, dp]
+    lib.host_fold_fast.argtypes = [C.c_double, dp, C.c_int, dp, dp]
     return lib
 
 
@@ -102,3 +103,37 @@ def test_single_pointer_is_a_discrete_draw(host):
                 # first k with u*total < w_0 + ... + w_k (left fold, strict)
                 edges = np.cumsum(w)
                 assert em[0] == int(np.searchsorted(edges, u * edges[-1], side="right"))
+
+
+def test_fast_iteration_is_exact_across_binade_crossings(host):
+    """cta_tile_fold's fast iteration (integer-valued doubles, additions only) against the
+    literal left fold `(+ acc weight)` of smc.cljc:120: every edge bit for bit, for tiles
+    that cross one or several binades, start just below a power of two, or hold one weight
+    that dwarfs the rest (partial sums far above 2^53 units, i.e. inexact, beyond the
+    crossing)."""
+    rng = np.random.default_rng(5)
+    cases = []
+    for n in (1, 7, 8, 255, 256, 1000, 4096):
+        w = np.exp(rng.normal(0, 2.0, n))
+        for s_in in (0.75, 1.0, 1.9999999, 3.0e5, 1e-7 * w.sum(), w.sum() * 0.99, 2.0 ** 30 - 0.5):
+            cases.append((s_in, w))
+        big = w.copy()
+        big[n // 2] = w.sum() * 1000.0                      # one element jumps several binades
+        cases.append((1.0, big))
+        cases.append((w.sum(), np.full(n, w.mean())))        # equal weights
+    done = crossed = 0
+    for s_in, w in cases:
+        w = np.ascontiguousarray(w)
+        edges = np.empty(w.size)
+        s_out = C.c_double()
+        rc = host.host_fold_fast(float(s_in), w.ctypes.data_as(dp), w.size, edges.ctypes.data_as(dp),
+                                 C.byref(s_out))
+        ref = np.cumsum(np.concatenate([[s_in], w]))[1:]      # sequential fp64 fold
+        if rc == 0:
+            assert np.array_equal(edges, ref), (s_in, w.size)
+            assert s_out.value == ref[-1]
+            done += 1
+            crossed += int(np.floor(np.log2(ref[-1])) > np.floor(np.log2(s_in)))
+    # rc = 1: an element saturates the binade of the running sum (a weight of the size of the
+    # sum itself) or ties - the device then runs the transducer iteration instead
+    assert done >= 20 and crossed >= 8, (done, crossed, len(cases))
