@@ -220,7 +220,12 @@ __device__ __noinline__ double cta_tile_fold(double S_in, const double (&w)[IPT]
             }
         }
         }
-        if (mycross != INT_MAX) atomicMin(&sm.cross, mycross);
+        {
+            // every thread behind the crossing "crosses" at its first element: reduce inside the
+            // warp first (up to 512 atomics on one shared word cost ~8 k cycles per iteration)
+            const int wmin = __reduce_min_sync(0xffffffffu, mycross);
+            if ((threadIdx.x & 31) == 0 && wmin != INT_MAX) atomicMin(&sm.cross, wmin);
+        }
         __syncthreads();
         const int cross = sm.cross;
         if (cross == INT_MAX) {
@@ -543,6 +548,7 @@ __global__ void __launch_bounds__(FB) k_fin_b(WSView v, int64_t n, double rel_ep
     sA[tid] = a_in;
     if (tid == 0) sA[FB] = v.coff[blockIdx.x + 1];
     __syncthreads();
+    int myskip = INT_MAX;
     if (t < nt) {
         const double ao = (t + 1 == nt) ? v.coff[G] : sA[tid + 1];
         v.ain[t] = a_in;
@@ -554,7 +560,7 @@ __global__ void __launch_bounds__(FB) k_fin_b(WSView v, int64_t n, double rel_ep
         const double eps1 = ((double)(n_global + g0 + hi) + 4096.0) * 4.44089209850062616e-16 + rel_eps;
         if ((atot + a_in) * (1.0 - eps1) > xlast_ub) {
             c1 = kCtxSkip;
-            atomicMin(v.skipmin, (int)t);
+            myskip = (int)t;
         } else {
             c1 = classify_tile2(atot + a_in, atot + ao, n_global + g0 + hi, rel_eps, &ea1, &eb1);
         }
@@ -576,6 +582,11 @@ __global__ void __launch_bounds__(FB) k_fin_b(WSView v, int64_t n, double rel_ep
                 v.hea[1][k] = (ea1 != kCtxHard && eb1 == ea1 + 1 && ea1 > -1000 && ea1 < 900) ? ea1 : kCtxHard;
             }
         }
+    }
+    {
+        // first skipped tile: one global atomic per warp (beyond the last pointer every tile skips)
+        const int wmin = __reduce_min_sync(0xffffffffu, myskip);
+        if ((tid & 31) == 0 && wmin != INT_MAX) atomicMin(v.skipmin, wmin);
     }
     __syncthreads();
     if (tid == 0) {
@@ -968,7 +979,10 @@ __device__ __forceinline__ double chain_hard_tile(const WSView& v, int lap, int 
             // coarse search: first thread whose elements take the sum across 2^53 units
             const i64 mine = xd_apply(s_in, P.c);
             sm.last[threadIdx.x] = mine;
-            if (mine >= kTwo53) atomicMin(&sm.cross, (int)threadIdx.x);
+            {
+                const int wmin = __reduce_min_sync(0xffffffffu, (mine >= kTwo53) ? (int)threadIdx.x : INT_MAX);
+                if ((threadIdx.x & 31) == 0 && wmin != INT_MAX) atomicMin(&sm.cross, wmin);
+            }
             hard_prefetch(v, lap, h + 1, nh, eA_next, P);
             __syncthreads();
             const int cc = sm.cross;
