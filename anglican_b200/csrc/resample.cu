@@ -40,6 +40,7 @@ using WSView = ResampleWS;      // passed to kernels by value (device pointers o
 #endif
 static WSView view_of(const ResampleWS& w) { return w; }
 
+static constexpr int kTieCap = 32;      // ties one fast iteration of cta_tile_fold resolves (one warp)
 struct FoldSmem {
     Xd warp_tot[NWARP];
     i64 wsum[NWARP];
@@ -47,6 +48,12 @@ struct FoldSmem {
     int cross;
     int imin;
     double dsum[NWARP];          // cta_tile_fold fast iteration: per-warp sums of integer-valued doubles
+    int ntie;                    //   its ties in front of the crossing: element, parity of the
+    int tie_idx[kTieCap];        //   uncorrected sum, order by element, corrections so far
+    int tie_par[kTieCap];
+    int tie_ord[kTieCap];
+    int tie_sidx[kTieCap];
+    int tie_cum[kTieCap];
     double last_edge[TB];
     double head[1024];           // generic_emit: literal fold of the first elements of a tile that
                                  //   starts at zero (a binade crossing at every doubling of the sum)
@@ -139,57 +146,118 @@ __device__ __noinline__ double cta_tile_fold(double S_in, const double (&w)[IPT]
         const double inv_u = fast ? pow2(-e) : 0.0;
         int mycross = INT_MAX;
         i64 sprev = 0;
-        if (threadIdx.x == 0) { sm.cross = INT_MAX; sm.imin += 1; }
+        if (threadIdx.x == 0) { sm.cross = INT_MAX; sm.imin += 1; sm.ntie = 0; }
         bool done = false;
         if (fast) {
-            // ---- fast iteration: no element ties or saturates in this binade, so every
-            // increment is RN(w / ulp) by the 2^52 magic add and the prefix sums are plain
-            // fp64 additions of integer-valued doubles.  Only additions are used: a prefix
-            // below 2^53 is exact, one at or above 2^53 can only round to a value >= 2^53, so
-            // "s_in + prefix >= 2^53" (the crossing) is decided exactly.  ~5x fewer
-            // instructions than the parity-transducer iteration below.
+            // ---- fast iteration: increments are RN(w / ulp) by the 2^52 magic add and the
+            // prefix sums are plain fp64 additions of integer-valued doubles.  Only additions
+            // are used: a prefix below 2^53 is exact, one at or above 2^53 can only round to a
+            // value >= 2^53, so "s_in + prefix >= 2^53" (the crossing) is decided exactly.
+            // An element of 2^52 ulps or more crosses wherever it stands: it counts as 2^53.
+            // A tie (remainder exactly half an ulp) adds floor(w / ulp) and one more when the
+            // sum before it is odd (round half to even, step_units): the few ties in front of
+            // the crossing are listed with the parity of their uncorrected sum, one lane walks
+            // the list in element order and every thread takes the corrections made before its
+            // first element.  Ties and saturating elements are the rule where this function
+            // runs - at the head of the fold an element is comparable to the running sum -, so
+            // without them the iteration fell back to the transducer scan three times out of
+            // four (chain trace at 2^27).  ~5x fewer instructions than that scan; 7-9 k instead of
+            // 9-10 k cycles per iteration (the rest is barrier and pipeline latency, see APOP_HEAD).
             double incD[IPT];
             double loc = 0.0;
-            int bad = 0;
+            unsigned tmask = 0;
 #pragma unroll
             for (int j = 0; j < IPT; ++j) {
                 const int idx = i0 + j;
                 double rn = 0.0;
                 if (idx >= pos && idx < nvalid) {
                     const double scaled = w[j] * inv_u;
-                    rn = (scaled + 4503599627370496.0) - 4503599627370496.0;
-                    bad |= !(scaled < 4503599627370496.0) | (fabs(scaled - rn) == 0.5);
+                    if (!(scaled < 4503599627370496.0)) rn = 9007199254740992.0;
+                    else {
+                        rn = (scaled + 4503599627370496.0) - 4503599627370496.0;
+                        const double diff = scaled - rn;
+                        if (diff == 0.5) tmask |= 1u << j;
+                        else if (diff == -0.5) { tmask |= 1u << j; rn -= 1.0; }
+                    }
                 }
                 incD[j] = rn;
                 loc += rn;
             }
-            if (!__syncthreads_or(bad)) {
-                const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-                double inc = loc;
+            const int any_tie = __syncthreads_or(tmask != 0);
+            const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+            double inc = loc;
 #pragma unroll
-                for (int d = 1; d < 32; d <<= 1) {
-                    const double o = __shfl_up_sync(0xffffffffu, inc, d);
-                    if (lane >= d) inc += o;
+            for (int d = 1; d < 32; d <<= 1) {
+                const double o = __shfl_up_sync(0xffffffffu, inc, d);
+                if (lane >= d) inc += o;
+            }
+            double exl = __shfl_up_sync(0xffffffffu, inc, 1);
+            if (lane == 0) exl = 0.0;
+            if (lane == 31) sm.dsum[wid] = inc;
+            __syncthreads();
+            double pre = 0.0;
+            for (int i = 0; i < wid; ++i) pre += sm.dsum[i];
+            pre += exl;
+            const double L = (double)(kTwo53 - s_in), sD0 = (double)s_in, ulp = pow2(e);
+            done = true;
+            if (any_tie) {
+                if (tmask) {
+                    double b = pre;
+#pragma unroll
+                    for (int j = 0; j < IPT; ++j) {
+                        b += incD[j];
+                        // a tie whose uncorrected sum already crosses lies behind the crossing
+                        if (((tmask >> j) & 1u) && b < L) {
+                            const int k = atomicAdd(&sm.ntie, 1);
+                            if (k < kTieCap) {
+                                sm.tie_idx[k] = i0 + j;
+                                sm.tie_par[k] = (int)((s_in + (i64)b) & 1);
+                            }
+                        }
+                    }
                 }
-                double exl = __shfl_up_sync(0xffffffffu, inc, 1);
-                if (lane == 0) exl = 0.0;
-                if (lane == 31) sm.dsum[wid] = inc;
                 __syncthreads();
-                double pre = 0.0;
-                for (int i = 0; i < wid; ++i) pre += sm.dsum[i];
-                pre += exl;
-                const double L = (double)(kTwo53 - s_in), sD0 = (double)s_in, ulp = pow2(e);
+                const int K = sm.ntie;
+                if (K > kTieCap) done = false;              // block-uniform: transducer scan instead
+                else if (K > 0) {
+                    if (wid == 0) {
+                        if (lane < K) {
+                            const int mine = sm.tie_idx[lane];
+                            int r = 0;
+                            for (int q = 0; q < K; ++q) r += sm.tie_idx[q] < mine;
+                            sm.tie_ord[r] = lane;
+                        }
+                        __syncwarp();
+                        if (lane == 0) {
+                            int C = 0;
+                            for (int r = 0; r < K; ++r) {
+                                const int q = sm.tie_ord[r];
+                                C += (sm.tie_par[q] + C) & 1;
+                                sm.tie_sidx[r] = sm.tie_idx[q];
+                                sm.tie_cum[r] = C;
+                            }
+                        }
+                    }
+                    __syncthreads();
+                    int corr = 0;
+                    for (int r = 0; r < K; ++r)
+                        if (sm.tie_sidx[r] < i0) corr = sm.tie_cum[r];
+                    pre += (double)corr;
+                }
+            }
+            if (done) {
                 double sD = pre;
 #pragma unroll
                 for (int j = 0; j < IPT; ++j) {
                     const int idx = i0 + j;
                     if (idx >= pos && idx < nvalid && mycross == INT_MAX) {
-                        const double nx = sD + incD[j];
+                        double d = incD[j];
+                        if ((tmask >> j) & 1u) d += (double)((s_in + (i64)(sD + d)) & 1);
+                        const double nx = sD + d;
                         if (nx >= L) { mycross = idx; sprev = s_in + (i64)sD; }
                         else { sD = nx; edge[j] = (sD0 + sD) * ulp; }
                     }
                 }
-                done = true;
             }
         }
         if (!done) {
@@ -256,11 +324,16 @@ __device__ __noinline__ double cta_tile_fold(double S_in, const double (&w)[IPT]
 
 // Length of the literal head fold of a tile whose running sum starts at zero (chain general
 // path, generic_emit).  Measured with the chain trace (tools/dbg_resolve.py, cycles of tile 0
-// at 2^27 particles): a literal add costs 13 cycles, one parallel crossing iteration of
-// cta_tile_fold 8-10 k cycles whether 16 warps or one take part (it is bound by its barriers
-// and scans, not by instruction issue), so folding window by window only adds iterations:
-//   head 1024: 13.2 k + 4 iterations 41 k   | head 512 + windows: 6.8 k + 8 iterations 66 k
-//   head 256 + windows: 3.5 k + 10 it. 77 k | head 128: 1.8 k + 12 iterations 90 k
+// at 2^27 particles): a literal add costs 13 cycles; one parallel crossing iteration of
+// cta_tile_fold costs 7-9 k cycles (9-10 k before ties were resolved inside the fast
+// iteration) and that cost is latency, not work: per iteration thread 0 sees ~0.7-1.1 k cycles
+// for the 8 quantisations of a thread, ~0.9 k waiting for the slowest warp, ~0.6 k for the
+// scan, ~1.6-2.3 k for the tie list when the tile has a tie, ~1.1-1.5 k for the replay and
+// ~0.9 k for the crossing minimum - a dozen short phases of fp64 work (half rate per
+// scheduler, four warps each) separated by block barriers, whether sixteen warps or one take
+// part.  Shorter heads or window-by-window folding therefore only add iterations:
+//   head 1024: 13.1 k + 3-4 iterations 30-36 k   | head 256: 3.5 k + 5-7 iterations 41-54 k
+//   head 64: 1.1 k + 7-9 iterations 53-65 k       (gpurun_out/r03tie; before: 41 / 66 / 90 k)
 #ifndef APOP_HEAD
 #define APOP_HEAD 1024
 #endif

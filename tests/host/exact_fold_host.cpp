@@ -76,15 +76,23 @@ double tile_exact_fold(double S_in, const double* w, int n, double* edges, int* 
 // per lane serially, Hillis-Steele over the 32 lanes of a warp, warp totals serially - and
 // the crossing decided by "prefix >= 2^53 - s_in".  A prefix below 2^53 is exact, one at or
 // above it can only round to >= 2^53, so the decision is exact although the sums are not.
-// Returns S_out, or NaN if an element ties / saturates (the device then falls back to the
-// transducer iteration, emulated by tile_exact_fold above).
-double tile_exact_fold_fast(double S_in, const double* w, int n, double* edges, int* iters) {
+// An element of 2^52 ulps or more counts as 2^53 (it crosses wherever it stands).  Ties add
+// floor(w / ulp); those in front of the uncorrected crossing are listed (in an arbitrary
+// order, as the device's atomics would) with the parity of their uncorrected sum, ranked by
+// element, walked once for the running number of round-ups, and each lane starts from the
+// corrections made before its first element.  Returns S_out, or NaN when more than
+// `tie_cap` ties are listed (the device then runs the transducer iteration, emulated by
+// tile_exact_fold above).  *ties (optional) counts the listed ties over all iterations.
+const int TIE_CAP = 32;
+double tile_exact_fold_fast(double S_in, const double* w, int n, double* edges, int* iters,
+                            int* ties = nullptr) {
     const int LANES = 32;
     int pos = 0;
     double S = S_in;
     const int nl = (n + LANE_ITEMS - 1) / LANE_ITEMS;
     std::vector<double> loc(nl), inc(nl), pre(nl);
     std::vector<double> incD(nl * LANE_ITEMS);
+    std::vector<unsigned> tmask(nl);
     while (pos < n) {
         if (iters) *iters += 1;
         const int e = ctx_of(S);
@@ -93,15 +101,21 @@ double tile_exact_fold_fast(double S_in, const double* w, int n, double* edges, 
         const double inv_u = pow2(-e), ulp = pow2(e);
         for (int l = 0; l < nl; ++l) {
             double a = 0.0;
+            tmask[l] = 0;
             for (int j = 0; j < LANE_ITEMS; ++j) {
                 const int i = l * LANE_ITEMS + j;
                 double rn = 0.0;
                 if (i >= pos && i < n) {
                     const double scaled = w[i] * inv_u;
-                    rn = (scaled + 4503599627370496.0) - 4503599627370496.0;
-                    if (!(scaled < 4503599627370496.0) || std::fabs(scaled - rn) == 0.5) return NAN;
+                    if (!(scaled < 4503599627370496.0)) rn = 9007199254740992.0;
+                    else {
+                        rn = (scaled + 4503599627370496.0) - 4503599627370496.0;
+                        const double diff = scaled - rn;
+                        if (diff == 0.5) tmask[l] |= 1u << j;
+                        else if (diff == -0.5) { tmask[l] |= 1u << j; rn -= 1.0; }
+                    }
                 }
-                incD[i < (int)incD.size() ? i : 0] = rn;
+                incD[i] = rn;
                 a += rn;
             }
             loc[l] = a;
@@ -128,18 +142,54 @@ double tile_exact_fold_fast(double S_in, const double* w, int n, double* edges, 
             pre[l] = p;
         }
         const double L = (double)(kTwo53 - s_in), sD0 = (double)s_in;
+        // tie list: lanes visited from the back so that the list is NOT in element order
+        std::vector<int> tie_idx, tie_par;
+        for (int l = nl - 1; l >= 0; --l) {
+            if (!tmask[l]) continue;
+            double b = pre[l];
+            for (int j = 0; j < LANE_ITEMS; ++j) {
+                b += incD[l * LANE_ITEMS + j];
+                if (((tmask[l] >> j) & 1u) && b < L) {
+                    tie_idx.push_back(l * LANE_ITEMS + j);
+                    tie_par.push_back((int)((s_in + (i64)b) & 1));
+                }
+            }
+        }
+        const int K = (int)tie_idx.size();
+        if (ties) *ties += K;
+        if (K > TIE_CAP) return NAN;
+        std::vector<int> ord(K), sidx(K), cum(K);
+        for (int q = 0; q < K; ++q) {
+            int r = 0;
+            for (int k = 0; k < K; ++k) r += tie_idx[k] < tie_idx[q];
+            ord[r] = q;
+        }
+        for (int r = 0, C = 0; r < K; ++r) {
+            const int q = ord[r];
+            C += (tie_par[q] + C) & 1;
+            sidx[r] = tie_idx[q];
+            cum[r] = C;
+        }
         int cross = -1;
         i64 sprev = 0;
-        for (int l = 0; l < nl && cross < 0; ++l) {
-            double sD = pre[l];
+        for (int l = 0; l < nl; ++l) {
+            int corr = 0;
+            for (int r = 0; r < K; ++r)
+                if (sidx[r] < l * LANE_ITEMS) corr = cum[r];
+            double sD = pre[l] + (double)corr;
+            int mycross = -1;
+            i64 mysprev = 0;
             for (int j = 0; j < LANE_ITEMS; ++j) {
                 const int i = l * LANE_ITEMS + j;
-                if (i < pos || i >= n) continue;
-                const double nx = sD + incD[i];
-                if (nx >= L) { cross = i; sprev = s_in + (i64)sD; break; }
-                sD = nx;
-                edges[i] = (sD0 + sD) * ulp;
+                if (i < pos || i >= n || mycross >= 0) continue;
+                double d = incD[i];
+                if ((tmask[l] >> j) & 1u) d += (double)((s_in + (i64)(sD + d)) & 1);
+                const double nx = sD + d;
+                if (nx >= L) { mycross = i; mysprev = s_in + (i64)sD; }
+                else { sD = nx; edges[i] = (sD0 + sD) * ulp; }
             }
+            // the block-wide minimum over the lanes' first crossings (atomicMin on the device)
+            if (mycross >= 0 && (cross < 0 || mycross < cross)) { cross = mycross; sprev = mysprev; }
         }
         if (cross < 0) { S = edges[n - 1]; pos = n; break; }
         S = from_units(sprev, e) + w[cross];          // the crossing add, hardware fp64
@@ -259,11 +309,15 @@ int host_exact_resample(const double* w, int64_t n, int64_t n_new, double u, int
 }
 
 // exact fold of w[0..n) from S_in by the fast iteration; returns 0 and the edges, 1 if it
-// had to give up (tie / saturation / context outside the fast range)
-int host_fold_fast(double S_in, const double* w, int n, double* edges, double* S_out) {
-    int it = 0;
-    const double S = tile_exact_fold_fast(S_in, w, n, edges, &it);
+// had to give up (more than TIE_CAP listed ties in one iteration / context outside the fast
+// range).  *ties = ties listed over all iterations, *iters = iterations.
+int host_fold_fast(double S_in, const double* w, int n, double* edges, double* S_out,
+                   int* ties, int* iters) {
+    int it = 0, tk = 0;
+    const double S = tile_exact_fold_fast(S_in, w, n, edges, &it, &tk);
     *S_out = S;
+    if (ties) *ties = tk;
+    if (iters) *iters = it;
     return (S != S) ? 1 : 0;
 }
 

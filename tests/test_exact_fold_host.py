@@ -28,7 +28,7 @@ def host():
     lib = C.CDLL(OUT)
     lib.host_exact_resample.argtypes = [dp, C.c_int64, C.c_int64, C.c_double, C.c_int, ip, ip, dp, lp]
     lib.host_comb_values.argtypes = [C.c_double, C.c_double, C.c_int64, dp]
-    lib.host_fold_fast.argtypes = [C.c_double, dp, C.c_int, dp, dp]
+    lib.host_fold_fast.argtypes = [C.c_double, dp, C.c_int, dp, dp, C.POINTER(C.c_int), C.POINTER(C.c_int)]
     return lib
 
 
@@ -105,35 +105,74 @@ def test_single_pointer_is_a_discrete_draw(host):
                 assert em[0] == int(np.searchsorted(edges, u * edges[-1], side="right"))
 
 
+def _fold_fast(host, s_in, w):
+    w = np.ascontiguousarray(w, dtype=np.float64)
+    edges = np.empty(w.size)
+    s_out, ties, iters = C.c_double(), C.c_int(), C.c_int()
+    rc = host.host_fold_fast(float(s_in), w.ctypes.data_as(dp), w.size, edges.ctypes.data_as(dp),
+                             C.byref(s_out), C.byref(ties), C.byref(iters))
+    return rc, edges, s_out.value, ties.value, iters.value
+
+
 def test_fast_iteration_is_exact_across_binade_crossings(host):
     """cta_tile_fold's fast iteration (integer-valued doubles, additions only) against the
     literal left fold `(+ acc weight)` of smc.cljc:120: every edge bit for bit, for tiles
-    that cross one or several binades, start just below a power of two, or hold one weight
-    that dwarfs the rest (partial sums far above 2^53 units, i.e. inexact, beyond the
-    crossing)."""
+    that cross one or several binades, start just below a power of two, start from a sum
+    smaller than their elements (elements saturate the binade of the running sum), or hold
+    one weight that dwarfs the rest (partial sums far above 2^53 units, i.e. inexact, beyond
+    the crossing)."""
     rng = np.random.default_rng(5)
     cases = []
     for n in (1, 7, 8, 255, 256, 1000, 4096):
         w = np.exp(rng.normal(0, 2.0, n))
-        for s_in in (0.75, 1.0, 1.9999999, 3.0e5, 1e-7 * w.sum(), w.sum() * 0.99, 2.0 ** 30 - 0.5):
+        for s_in in (0.75, 1.0, 1.9999999, 3.0e5, 1e-7 * w.sum(), w.sum() * 0.99, 2.0 ** 30 - 0.5,
+                     1e-30, 1e-280):
             cases.append((s_in, w))
         big = w.copy()
         big[n // 2] = w.sum() * 1000.0                      # one element jumps several binades
         cases.append((1.0, big))
         cases.append((w.sum(), np.full(n, w.mean())))        # equal weights
-    done = crossed = 0
+    crossed = 0
     for s_in, w in cases:
-        w = np.ascontiguousarray(w)
-        edges = np.empty(w.size)
-        s_out = C.c_double()
-        rc = host.host_fold_fast(float(s_in), w.ctypes.data_as(dp), w.size, edges.ctypes.data_as(dp),
-                                 C.byref(s_out))
+        rc, edges, s_out, ties, iters = _fold_fast(host, s_in, w)
         ref = np.cumsum(np.concatenate([[s_in], w]))[1:]      # sequential fp64 fold
-        if rc == 0:
-            assert np.array_equal(edges, ref), (s_in, w.size)
-            assert s_out.value == ref[-1]
-            done += 1
-            crossed += int(np.floor(np.log2(ref[-1])) > np.floor(np.log2(s_in)))
-    # rc = 1: an element saturates the binade of the running sum (a weight of the size of the
-    # sum itself) or ties - the device then runs the transducer iteration instead
-    assert done >= 20 and crossed >= 8, (done, crossed, len(cases))
+        assert rc == 0, (s_in, w.size, ties)
+        assert np.array_equal(edges, ref), (s_in, w.size)
+        assert s_out == ref[-1]
+        crossed += int(s_in > 0 and np.floor(np.log2(ref[-1])) > np.floor(np.log2(s_in)))
+    assert crossed >= 20, (crossed, len(cases))
+
+
+def test_fast_iteration_resolves_ties_by_parity(host):
+    """Round half to even inside the fast iteration: weights that are odd multiples of half
+    an ulp of the running sum tie, and whether a tie rounds up depends on the parity of the
+    exact sum before it, i.e. on every earlier tie.  Sparse ties (a few per iteration, as at
+    the head of a real fold) must come out bit for bit; a tile with more ties in front of one
+    crossing than the device lists (32) must report that, not a wrong sum."""
+    rng = np.random.default_rng(11)
+    half = 2.0 ** -53                                     # half an ulp of sums in [1, 2)
+    seen_ties = seen_runs = 0
+    for n in (8, 64, 1000, 4096):
+        for p_tie in (0.0005, 0.002, 0.006):
+            for rep in range(6):
+                # multiples of 64 half-ulps: exact increments up to sums of 32; adding 1, 2 or 4
+                # half-ulps makes a tie in the binade [1, 2), [2, 4) or [4, 8) respectively
+                m = rng.integers(1, 2 ** 38, n) * 64
+                odd = rng.random(n) < p_tie
+                m = np.where(odd, m + 2 ** rng.integers(0, 3, n), m)
+                if rep % 2:                                # runs of consecutive ties
+                    k = int(rng.integers(0, n))
+                    m[k:k + 3] |= 1
+                    seen_runs += 1
+                w = m.astype(np.float64) * half
+                s_in = 1.0 + float(rng.integers(0, 2 ** 30)) * 2.0 ** -52
+                rc, edges, s_out, ties, iters = _fold_fast(host, s_in, w)
+                ref = np.cumsum(np.concatenate([[s_in], w]))[1:]
+                assert rc == 0, (n, p_tie, rep, ties)
+                assert np.array_equal(edges, ref), (n, p_tie, rep, ties, iters)
+                seen_ties += ties
+    assert seen_ties >= 100 and seen_runs >= 10, (seen_ties, seen_runs)
+    # every element ties: more than the list holds in front of the first crossing
+    m = rng.integers(1, 2 ** 30, 4096) * 2 + 1
+    rc, _, _, ties, _ = _fold_fast(host, 1.0, m.astype(np.float64) * half)
+    assert rc == 1 and ties > 32
