@@ -65,10 +65,15 @@ typedef struct {
     double scalar;
 } apop_arg;
 
-/* ---- lifecycle --------------------------------------------------------- */
+/* ---- lifecycle ---------------------------------------------------------
+ * A context owns one particle population: the `particles` sequence that `sweep` builds with
+ * `(repeatedly number-of-particles ...)` and threads through its loop (smc.cljc:37-43), as
+ * device-resident columns, plus the stream and the RNG key that replace the reference's one
+ * global synchronised generator (runtime.cljc:142-147). */
 int apop_version(void);
 int apop_device_count(void);
-/* nccl_id: 128-byte ncclUniqueId shared by all ranks, or NULL when world==1 */
+/* n_particles_local: this rank's share of `:number-of-particles` (smc.cljc:53-57; >= 1).
+ * nccl_id: 128-byte ncclUniqueId shared by all ranks, or NULL when world==1 */
 int apop_create(apop_ctx** out, int64_t n_particles_local, uint64_t seed, int device,
                 int rank, int world, const void* nccl_id);
 /* In-process group: create `world` contexts with ranks 0..world-1 and
@@ -81,7 +86,8 @@ const char* apop_last_error(apop_ctx* ctx);
 int apop_get_unique_id(void* out_128_bytes);
 int apop_synchronize(apop_ctx* ctx);
 int64_t apop_num_particles(apop_ctx* ctx);
-/* re-key the counter-based RNG (one key per sweep makes sweeps independent) */
+/* re-key the counter-based RNG (one key per sweep makes sweeps independent, as successive
+ * sweeps of `infer` are: smc.cljc:58-63).  Replaces reseeding runtime.cljc:142-147. */
 int apop_set_seed(apop_ctx* ctx, uint64_t seed);
 /* Page-locked host buffers for results that the caller reads back every sweep
  * (the final particle states: 8 B x n).  A JVM binding allocates its result
@@ -119,12 +125,16 @@ int apop_column_device_ptr(apop_ctx* ctx, apop_col col, void** out);
  * `draw_id` distinguishes successive sample statements of one program step
  * (counter-based RNG: key = seed, counter = (slot, step, stream, draw)). */
 int apop_set_step(apop_ctx* ctx, uint32_t step);
+/* normal (runtime.cljc:403-409 -> commons-math NormalDistribution): mean, sd */
 int apop_sample_normal(apop_ctx* ctx, apop_arg mean, apop_arg sd, uint32_t draw_id, apop_col out);
 int apop_observe_normal(apop_ctx* ctx, apop_arg mean, apop_arg sd, apop_arg value, apop_col logw);
+/* gamma (runtime.cljc:325-330 -> GammaDistribution(shape, 1/rate)): shape, RATE */
 int apop_sample_gamma(apop_ctx* ctx, apop_arg shape, apop_arg rate, uint32_t draw_id, apop_col out);
 int apop_observe_gamma(apop_ctx* ctx, apop_arg shape, apop_arg rate, apop_arg value, apop_col logw);
+/* beta (runtime.cljc:251-256 -> BetaDistribution) */
 int apop_sample_beta(apop_ctx* ctx, apop_arg alpha, apop_arg beta, uint32_t draw_id, apop_col out);
 int apop_observe_beta(apop_ctx* ctx, apop_arg alpha, apop_arg beta, apop_arg value, apop_col logw);
+/* uniform-continuous (runtime.cljc:450-453 -> UniformRealDistribution): min, max */
 int apop_sample_uniform(apop_ctx* ctx, apop_arg lo, apop_arg hi, uint32_t draw_id, apop_col out);
 int apop_observe_uniform(apop_ctx* ctx, apop_arg lo, apop_arg hi, apop_arg value, apop_col logw);
 /* discrete / categorical: weights either shared (host array of k doubles,
@@ -199,13 +209,17 @@ int apop_normalize(apop_ctx* ctx, apop_col logw, double* max_lw, double* log_mea
  * same weights and uniform. */
 int apop_resample(apop_ctx* ctx, apop_col logw, int scheme, double u, int64_t n_new, int order,
                   apop_col anc_out, double* new_logw, int64_t* n_first_lap);
-/* same on explicit fp64 weights (already max-normalised or not) */
+/* same on explicit fp64 weights (already max-normalised or not): the wheel of smc.cljc:105-137
+ * on the `weights` that `particle-weights` (smc.cljc:70-84) would have returned */
 int apop_resample_weights(apop_ctx* ctx, apop_col weights, int scheme, double u, int64_t n_new,
                           int order, apop_col anc_out, double* total, int64_t* n_first_lap);
-/* multinomial with one supplied uniform per offspring (f64 column) */
+/* multinomial with one supplied uniform per offspring (f64 column): n_new independent
+ * `(sample* (discrete weights))` draws, runtime.cljc:279-287 (first edge exceeding u * total,
+ * strict `<`), the draw pgas.cljc:120-125 uses for its ancestor */
 int apop_resample_multinomial_u(apop_ctx* ctx, apop_col weights, apop_col uniforms,
                                 int64_t n_new, apop_col anc_out);
-/* x_new[k] = x[anc[k]] for each listed column.  The result is written to the column's second
+/* x_new[k] = x[anc[k]] for each listed column: the offspring copies of smc.cljc:124-129
+ * (`(update-in particle [:state] set-log-weight log-weight)` per chosen particle).  The result is written to the column's second
  * buffer and the buffers are swapped: a pointer from apop_column_device_ptr is stale after this. */
 int apop_gather(apop_ctx* ctx, apop_col anc, int64_t n_new, const apop_col* cols, int ncols);
 
@@ -289,7 +303,8 @@ int apop_smc_sweep(apop_ctx* ctx, const apop_ssm* model, const double* y, int32_
 int apop_smc_sweep_group(apop_ctx* const* ctxs, int32_t n_ctx, const apop_ssm* model,
                          const double* y, int32_t T, const apop_sweep_opts* opts,
                          apop_sweep_result* results);
-/* lineage (x_0..x_T) of final slot `slot` of the last keep_history sweep */
+/* lineage (x_0..x_T) of final slot `slot` of the last keep_history sweep: the
+ * `::past-samples` a retained particle replays (pgibbs.cljc:29-35, 66-72, 122-123) */
 int apop_trace_lineage(apop_ctx* ctx, int64_t slot, double* out_traj);
 /* whole ancestry of the last keep_history sweep, for host-side result
  * materialisation (the `:result` / `:predicts` of every particle stay on the
