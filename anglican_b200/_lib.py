@@ -136,6 +136,8 @@ _SIGS = [
                                             c_double_p]),
     ("apop_collect_discrete", C.c_int, [_vp, C.c_int32, C.c_int32, C.c_int32, c_double_p,
                                         c_double_p]),
+    ("apop_empirical_moments_noalloc", C.c_int, [C.c_int, _vp, _vp, _vp, C.c_int64, C.c_int32,
+                                                 _vp, _vp, _vp, _vp, C.c_char_p, C.c_int32]),
     ("apop_pimh_accept", C.c_int, [C.c_double, C.c_double, C.c_double]),
     ("apop_ipmcmc_gibbs", C.c_int, [c_double_p, C.c_int, C.c_int, c_double_p, c_int32_p,
                                     c_double_p]),

@@ -436,3 +436,191 @@ int apop_collect_discrete(apop_ctx* c, apop_col xcol, apop_col lwcol, int32_t K,
 }
 
 } // extern "C"
+
+// ===================================================================================
+// apop_empirical_moments_noalloc: the moments of apop_empirical_moments for callers
+// that must not allocate.
+//
+// The context-based call above takes its partial-sum workspace from ensure_scratch(),
+// i.e. from cudaMalloc, and grows it with cudaFree + cudaMalloc when a wider column
+// arrives.  Two kinds of user of this library cannot afford that:
+//   * a host that has handed the whole GPU to its own arena (a JVM binding that
+//     reserves device memory once at start-up, torch's caching allocator at its cap):
+//     any further cudaMalloc fails or fragments what the host thinks it owns;
+//   * code that computes result statistics while OTHER populations are sweeping on the
+//     same GPU.  cudaMalloc / cudaFree stop the whole device until everything queued
+//     has drained; a sharded sweep in flight is spinning on its peers with a bounded
+//     wait (fabric.cuh), so such a stall can turn into an APOP_ERR_NCCL timeout on
+//     another rank.
+// For them the workspace is the fixed array below.  It is part of the library image:
+// every GPU that loads libanglican_pop.so carries NOALLOC_DOUBLES * 8 bytes (~123 KB)
+// of it from module load until the process exits, used or not.
+//
+// The kernels are the ones of the context-based call, launched with the same grid and
+// in the same order, so the sums - and the results - are the same bit for bit.
+// ===================================================================================
+#include <stdarg.h>
+
+#include <mutex>
+
+namespace apop {
+
+constexpr int NOALLOC_MAXW = APOP_NOALLOC_MAX_WIDTH;
+constexpr int NOALLOC_PARTC = 3 * SCH + 1;                     // widest partial row (k_stat_m2)
+// layout (doubles): mparts[SGRID] | part[SGRID][PARTC] | sums[PARTC] | mean[MAXW] | sumw[8]
+constexpr size_t NOALLOC_DOUBLES =
+    (size_t)SGRID + (size_t)SGRID * NOALLOC_PARTC + NOALLOC_PARTC + NOALLOC_MAXW + 8;
+constexpr int NOALLOC_MAXDEV = 64;
+
+static __device__ __align__(256) double g_noalloc_scratch[NOALLOC_DOUBLES];
+
+// In host code `g_noalloc_scratch` is only a handle for the runtime, NOT an address a
+// kernel may dereference.  The real address differs per device and is looked up once per
+// device, with that device current, and cached here.
+static std::mutex g_noalloc_mu;
+static double* g_noalloc_dev[NOALLOC_MAXDEV];                  // zero-initialised
+
+static void noalloc_msg(char* buf, int32_t len, const char* fmt, ...) {
+    if (!buf || len <= 0) return;
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, (size_t)len, fmt, ap);
+    va_end(ap);
+}
+
+static int noalloc_scratch_for(int device, double** out, char* err, int32_t errlen) {
+    std::lock_guard<std::mutex> lk(g_noalloc_mu);
+    if (!g_noalloc_dev[device]) {
+        // the caller made `device` current just before
+        void* p = nullptr;
+        const cudaError_t e = cudaGetSymbolAddress(&p, g_noalloc_scratch);
+        if (e != cudaSuccess || !p) {
+            noalloc_msg(err, errlen, "moments_noalloc: cudaGetSymbolAddress on device %d failed: %s",
+                        device, cudaGetErrorString(e));
+            return APOP_ERR_CUDA;
+        }
+        g_noalloc_dev[device] = (double*)p;
+    }
+    *out = g_noalloc_dev[device];
+    return APOP_OK;
+}
+
+// a pointer the kernels can dereference on `device`: device or managed memory
+static bool noalloc_device_visible(const void* p) {
+    cudaPointerAttributes a;
+    if (cudaPointerGetAttributes(&a, p) != cudaSuccess) { cudaGetLastError(); return false; }
+    return a.type == cudaMemoryTypeDevice || a.type == cudaMemoryTypeManaged;
+}
+
+// columns [c0, c0 + nc): mean from the scratch copy; variance / skew / kurtosis from the
+// three central sums (stat.cljc:93-120) - the arithmetic apop_empirical_moments does on
+// the host after its download, done where the numbers already are
+__global__ void k_stat_moments_out(const double* __restrict__ sums /*[3*SCH] or null*/,
+                                   const double* __restrict__ sumw,
+                                   const double* __restrict__ mean, int c0, int nc,
+                                   double* __restrict__ o_mean, double* __restrict__ o_var,
+                                   double* __restrict__ o_skew, double* __restrict__ o_kurt) {
+    const int k = threadIdx.x;
+    if (k >= nc) return;
+    if (o_mean) o_mean[c0 + k] = mean[c0 + k];
+    if (!sums) return;
+    const double sw = *sumw;
+    const double v = sums[k] / sw;
+    const double s = sqrt(v);
+    if (o_var) o_var[c0 + k] = v;
+    if (o_skew) o_skew[c0 + k] = (sums[SCH + k] / sw) / (s * s * s);
+    if (o_kurt) o_kurt[c0 + k] = (sums[2 * SCH + k] / sw) / (v * v);
+}
+
+} // namespace apop
+
+extern "C" int apop_empirical_moments_noalloc(int device, void* stream, const double* d_x,
+                                              const double* d_logw, int64_t n, int32_t width,
+                                              double* d_mean, double* d_var, double* d_skew,
+                                              double* d_kurt, char* errbuf, int32_t errbuf_len) {
+    if (errbuf && errbuf_len > 0) errbuf[0] = 0;
+    // sizes first: a request the fixed workspace cannot serve is refused before CUDA is touched
+    if (width < 1 || width > NOALLOC_MAXW) {
+        noalloc_msg(errbuf, errbuf_len,
+                    "moments_noalloc: width %d is outside [1, %d] (APOP_NOALLOC_MAX_WIDTH): the "
+                    "static workspace holds the means of at most %d columns; use "
+                    "apop_empirical_moments for wider columns",
+                    (int)width, NOALLOC_MAXW, NOALLOC_MAXW);
+        return APOP_ERR_INVALID;
+    }
+    if (n < 1 || n > (int64_t)APOP_NOALLOC_MAX_PARTICLES) {
+        noalloc_msg(errbuf, errbuf_len,
+                    "moments_noalloc: n = %lld is outside [1, %lld] (APOP_NOALLOC_MAX_PARTICLES)",
+                    (long long)n, (long long)APOP_NOALLOC_MAX_PARTICLES);
+        return APOP_ERR_INVALID;
+    }
+    if (!d_x || !(d_mean || d_var || d_skew || d_kurt)) {
+        noalloc_msg(errbuf, errbuf_len, "moments_noalloc: d_x and at least one output are required");
+        return APOP_ERR_INVALID;
+    }
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev <= 0) {
+        cudaGetLastError();
+        noalloc_msg(errbuf, errbuf_len, "moments_noalloc: no CUDA device (there is no CPU fallback)");
+        return APOP_ERR_CUDA;
+    }
+    if (device < 0 || device >= ndev || device >= NOALLOC_MAXDEV) {
+        noalloc_msg(errbuf, errbuf_len, "moments_noalloc: device %d of %d", device, ndev);
+        return APOP_ERR_INVALID;
+    }
+    cudaError_t e = cudaSetDevice(device);
+    if (e != cudaSuccess) {
+        noalloc_msg(errbuf, errbuf_len, "moments_noalloc: cudaSetDevice(%d): %s", device,
+                    cudaGetErrorString(e));
+        return APOP_ERR_CUDA;
+    }
+    const void* ptrs[6] = {d_x, d_logw, d_mean, d_var, d_skew, d_kurt};
+    static const char* const names[6] = {"d_x", "d_logw", "d_mean", "d_var", "d_skew", "d_kurt"};
+    for (int i = 0; i < 6; ++i)
+        if (ptrs[i] && !noalloc_device_visible(ptrs[i])) {
+            noalloc_msg(errbuf, errbuf_len,
+                        "moments_noalloc: %s is not device memory (inputs and outputs stay on the GPU)",
+                        names[i]);
+            return APOP_ERR_INVALID;
+        }
+    double* ws = nullptr;
+    const int rc = noalloc_scratch_for(device, &ws, errbuf, errbuf_len);
+    if (rc != APOP_OK) return rc;
+
+    double* mparts = ws;
+    double* part = mparts + SGRID;
+    double* sums = part + (size_t)SGRID * NOALLOC_PARTC;
+    double* mean = sums + NOALLOC_PARTC;
+    double* sumw = mean + NOALLOC_MAXW;
+    int g = (int)((n + SB - 1) / SB);                    // the grid rule of stat_bufs()
+    if (g > SGRID) g = SGRID;
+    cudaStream_t st = (cudaStream_t)stream;
+
+    // Nothing in the workspace has to be zero on entry although the previous call's numbers are
+    // still in it: k_stat_max / k_stat_m1 / k_stat_m2 store every slot [0, g) of the rows that
+    // k_stat_fin then reads, and mean / sumw / sums are stored before they are read.
+    if (d_logw) k_stat_max<<<g, SB, 0, st>>>(d_logw, n, mparts);
+    for (int c0 = 0; c0 < width; c0 += SCH) {
+        const int nc = (width - c0 < SCH) ? (width - c0) : SCH;
+        k_stat_m1<<<g, SB, 0, st>>>(d_x, d_logw, n, width, c0, nc, mparts, g, part);
+        k_stat_fin<<<1 + SCH, SB, 0, st>>>(part, g, 1 + SCH, 1 + SCH, sums);
+        k_stat_mean<<<1, 32, 0, st>>>(sums, c0, nc, mean, sumw);
+    }
+    const bool higher = d_var || d_skew || d_kurt;
+    for (int c0 = 0; c0 < width; c0 += SCH) {
+        const int nc = (width - c0 < SCH) ? (width - c0) : SCH;
+        if (higher) {
+            k_stat_m2<<<g, SB, 0, st>>>(d_x, d_logw, n, width, c0, nc, mparts, g, mean, part);
+            k_stat_fin<<<3 * SCH, SB, 0, st>>>(part, g, 3 * SCH, 3 * SCH, sums);
+        }
+        k_stat_moments_out<<<1, 32, 0, st>>>(higher ? sums : nullptr, sumw, mean, c0, nc, d_mean,
+                                             d_var, d_skew, d_kurt);
+    }
+    e = cudaGetLastError();
+    if (e != cudaSuccess) {
+        noalloc_msg(errbuf, errbuf_len, "moments_noalloc: kernel launch failed: %s",
+                    cudaGetErrorString(e));
+        return APOP_ERR_CUDA;
+    }
+    return APOP_OK;
+}

@@ -358,6 +358,52 @@ int apop_empirical_covariance(apop_ctx* ctx, apop_col x, apop_col logw, int32_t 
 int apop_collect_discrete(apop_ctx* ctx, apop_col x, apop_col logw, int32_t K, double* log_weight,
                           double* prob);
 
+/* ---- result moments without any allocation -------------------------------
+ * NO COUNTERPART IN THE REFERENCE (its statistics fold a JVM seq, stat.cljc:56-120, and
+ * the JVM allocates as it pleases); this entry point exists for hosts that must not.
+ *
+ * Same numbers as apop_empirical_moments - same kernels, same grid, same order of
+ * summation, so bit for bit - but no apop_ctx and no cudaMalloc / cudaFree / pinned-host
+ * allocation anywhere on the path, not on the first call either.  Use it when
+ *   - the process has given all device memory to its own arena (a JVM binding that
+ *     reserves the GPU at start-up, torch's caching allocator at its limit), so that a
+ *     library-side cudaMalloc would fail or eat into memory the host believes it owns; or
+ *   - other populations are sweeping on the same GPU: cudaMalloc and cudaFree hold the
+ *     whole device until its queues drain, and a sharded sweep that is waiting on its
+ *     peers with a bounded spin can time out (APOP_ERR_NCCL) behind such a stall.
+ * The partial sums live in one fixed array inside the library image (about 123 KB of
+ * device memory on every GPU that loads the library, held until the process exits).
+ *
+ * Arguments: d_x [n*width] f64 row-major and d_logw [n] f64 (or NULL for equal weights,
+ * otherwise weights are exp(lw - max lw), stat.cljc:63-68) are DEVICE pointers; so are
+ * the outputs d_mean / d_var / d_skew / d_kurt, [width] doubles each, any of which may be
+ * NULL (not all).  `stream` is the caller's cudaStream_t (NULL: the default stream); the
+ * work is queued on it and the call returns without waiting - read the outputs after
+ * synchronising that stream.  `device` becomes the calling thread's current device.
+ * errbuf (may be NULL) receives the reason of a non-zero return.
+ *
+ * Limits: 1 <= width <= APOP_NOALLOC_MAX_WIDTH (the array keeps one mean per column);
+ * 1 <= n <= APOP_NOALLOC_MAX_PARTICLES (the library's particle indices are 32-bit).
+ * Anything larger is refused with APOP_ERR_INVALID and a message; nothing is queued.
+ * A population whose total weight is zero gives NaN outputs (the ctx call reports
+ * APOP_ERR_ZERO_WEIGHT, which takes a device->host read that this call does not make).
+ *
+ * Sharing: every call on a GPU uses the SAME array, and it still holds the previous
+ * call's partial sums.  Each call overwrites every slot before reading it, so nothing
+ * needs clearing, and calls queued one after another on one stream are safe.  Two calls
+ * that can run at the same time on one GPU - different streams, or different host
+ * threads - overwrite each other's sums: order them yourself (one stream, or events).
+ *
+ * First call on each device: the library looks up where the array lives on that device
+ * (cudaGetSymbolAddress, which may also load the module).  Make that first call during
+ * set-up, before any stream capture is begun on the stream you pass. */
+#define APOP_NOALLOC_MAX_WIDTH 256
+#define APOP_NOALLOC_MAX_PARTICLES 2147483647LL
+int apop_empirical_moments_noalloc(int device, void* stream, const double* d_x,
+                                   const double* d_logw, int64_t n, int32_t width,
+                                   double* d_mean, double* d_var, double* d_skew, double* d_kurt,
+                                   char* errbuf, int32_t errbuf_len);
+
 /* ---- PIMH / IPMCMC scalars (host arithmetic, restated on the host side) -
  * accept?: lmh.cljc:146-151; gibbs-update-csmc-indices: ipmcmc.cljc:106-146
  * with the intended sampling rule; exchange: the only data
