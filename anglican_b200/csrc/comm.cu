@@ -104,12 +104,13 @@ Fabric fabric_view(const apop_ctx* c) {
     F.world = c->world;
     F.n_local = c->n;
     {
-        static long long cyc = 0;
-        if (!cyc) {
+        // read once, thread-safely (function-local static initialiser): contexts are driven
+        // from several host threads
+        static const long long cyc = [] {
             const char* e = getenv("APOP_SPIN_SECONDS");
             const double sec = (e && atof(e) > 0.0) ? atof(e) : 3.0;
-            cyc = (long long)(sec * 2.0e9);
-        }
+            return (long long)(sec * 2.0e9);
+        }();
         F.spin_cycles = cyc;
     }
     if (c->world > 1 && c->fab.linked)

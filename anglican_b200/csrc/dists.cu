@@ -473,6 +473,7 @@ int apop_sample_mvn(apop_ctx* c, const double* mean, apop_col mean_col, const do
                     uint32_t draw, apop_col out) {
     CHECK_CTX(c);
     if (!cov || d <= 0 || d > 256) return set_err(c, APOP_ERR_INVALID, "mvn: bad cov/d");
+    if (draw >= 256u) return set_err(c, APOP_ERR_INVALID, "mvn: draw_id must be < 256 (each draw of a matrix family takes 4096 counters of a 20-bit field; a larger id would repeat the numbers of draw_id - 256)");
     Column* o = get_col(c, out, APOP_F64, d);
     if (!o) return APOP_ERR_INVALID;
     std::vector<double> L, iL; double Z;

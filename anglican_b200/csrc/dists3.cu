@@ -216,6 +216,7 @@ int apop_sample_mvt(apop_ctx* c, double nu, const double* mean, apop_col mean_co
                     const double* sigma, int d, uint32_t draw, apop_col out) {
     CHECK_CTX(c);
     if (!sigma || d <= 0 || d > 256 || !(nu > 0.0)) return set_err(c, APOP_ERR_INVALID, "multivariate-t: bad nu/sigma/d");
+    if (draw >= 256u) return set_err(c, APOP_ERR_INVALID, "multivariate-t: draw_id must be < 256 (each draw of a matrix family takes 4096 counters of a 20-bit field; a larger id would repeat the numbers of draw_id - 256)");
     Column* o = get_col(c, out, APOP_F64, d);
     if (!o) return APOP_ERR_INVALID;
     std::vector<double> L, iL; double Z;
@@ -260,6 +261,7 @@ int apop_observe_mvt(apop_ctx* c, double nu, const double* mean, apop_col mean_c
 int apop_sample_wishart(apop_ctx* c, double n_df, const double* V, int p, uint32_t draw, apop_col out) {
     CHECK_CTX(c);
     if (!V || p <= 0 || p > MAXP || !(n_df > p - 1)) return set_err(c, APOP_ERR_INVALID, "wishart: need 1 <= p <= %d and n > p - 1", MAXP);
+    if (draw >= 256u) return set_err(c, APOP_ERR_INVALID, "wishart: draw_id must be < 256 (each draw of a matrix family takes 4096 counters of a 20-bit field; a larger id would repeat the numbers of draw_id - 256)");
     Column* o = get_col(c, out, APOP_F64, p * p);
     if (!o) return APOP_ERR_INVALID;
     std::vector<double> L, iL; double Z;
@@ -274,7 +276,10 @@ int apop_sample_wishart(apop_ctx* c, double n_df, const double* V, int p, uint32
 
 int apop_observe_wishart(apop_ctx* c, double n_df, const double* V, int p, apop_col value, apop_col logw) {
     CHECK_CTX(c);
-    if (!V || p <= 0 || p > MAXP) return set_err(c, APOP_ERR_INVALID, "wishart: need 1 <= p <= %d", MAXP);
+    // the density's normaliser has lgamma((n - j) / 2), j = 0..p-1: at n <= p - 1 that is a pole or
+    // a negative argument (log-mv-gamma-fn, runtime.cljc:479-485; commons' logGamma gives NaN there, so the
+    // reference's weights turn NaN) - refused here instead of returning a finite but meaningless number
+    if (!V || p <= 0 || p > MAXP || !(n_df > p - 1)) return set_err(c, APOP_ERR_INVALID, "wishart: need 1 <= p <= %d and n > p - 1", MAXP);
     Column* l = get_col(c, logw, APOP_F64, 1);
     Column* x = get_col(c, value, APOP_F64, p * p);
     if (!l || !x) return APOP_ERR_INVALID;

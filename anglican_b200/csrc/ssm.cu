@@ -64,10 +64,24 @@ struct SweepState {
     int sweep_csmc = 0;
     // the whole sweep as one CUDA graph, replayed while the shape stays the same
     cudaGraphExec_t gexec = nullptr;
+    // everything a captured sweep bakes into its kernel arguments BY VALUE: a sweep that differs
+    // in any of these must be captured again.  (Observations, the retained path and the seed are
+    // read through device memory and may change between replays.)  Compared field by field:
+    // the struct has padding, which `= {}` and assignment need not zero or copy.
     struct GraphKey {
         int kind, T, hist_mode, csmc, n_cond, reset, want_final, want_filt, no_resample;
         int64_t n;
-        const void *xa, *xb, *lw, *anc, *y, *ret, *lin, *xf, *ws;
+        uint64_t ess_bits;         // ess_threshold bit for bit: k_chain takes it by value, and
+                                   // a threshold > 0 adds the final log-sum-exp node
+        const void *xa, *xb, *lw, *anc, *y, *ret, *lin, *xf, *ws, *lse, *sd, *model;
+        bool same(const GraphKey& o) const {
+            return kind == o.kind && T == o.T && hist_mode == o.hist_mode && csmc == o.csmc &&
+                   n_cond == o.n_cond && reset == o.reset && want_final == o.want_final &&
+                   want_filt == o.want_filt && no_resample == o.no_resample && n == o.n &&
+                   ess_bits == o.ess_bits && xa == o.xa && xb == o.xb && lw == o.lw &&
+                   anc == o.anc && y == o.y && ret == o.ret && lin == o.lin && xf == o.xf &&
+                   ws == o.ws && lse == o.lse && sd == o.sd && model == o.model;
+        }
     } gkey = {};
     int64_t glaunches = 0;
     const unsigned long long* seedp = nullptr;   // &sd->seed while a graph is captured / replayed
@@ -1034,8 +1048,9 @@ static bool graph_wanted(const apop_ctx* c, int kind, const apop_sweep_opts* o) 
     if (o->use_graph < 0 || c->world > 1 || c->ktimers || o->ancestor_sampling ||
         kind == APOP_SSM_LGMVN)
         return false;
-    static int env = -1;
-    if (env < 0) { const char* e = getenv("APOP_GRAPH"); env = (e && e[0] == '0') ? 0 : 1; }
+    // read once; a function-local static initialiser is thread-safe (populations are driven
+    // from several host threads)
+    static const bool env = [] { const char* e = getenv("APOP_GRAPH"); return !(e && e[0] == '0'); }();
     if (!env) return false;
     return o->use_graph > 0 || c->n <= (1LL << 22);
 }
@@ -1060,10 +1075,11 @@ static int run_graph(apop_ctx* c, int T, const double* retained, const apop_swee
     k.want_filt = o->want_filt; k.no_resample = o->no_resample; k.n = c->n;
     k.xa = s->xa; k.xb = s->xb; k.lw = s->lw; k.anc = s->anc; k.y = s->y; k.ret = s->retained;
     k.lin = s->hist_mode == 2 ? (const void*)s->lin_new : (const void*)s->x_hist;
-    k.xf = s->x_final; k.ws = c->ws.slab;
+    k.xf = s->x_final; k.ws = c->ws.slab; k.lse = s->lse; k.sd = s->sd; k.model = s->model;
+    memcpy(&k.ess_bits, &o->ess_threshold, sizeof k.ess_bits);
     k_set_sweep_seed<<<1, 1, 0, c->stream>>>(s->sd, c->seed);
     s->sweep_seed = c->seed;
-    if (!s->gexec || memcmp(&k, &s->gkey, sizeof k) != 0) {
+    if (!s->gexec || !k.same(s->gkey)) {
         if (s->gexec) { cudaGraphExecDestroy(s->gexec); s->gexec = nullptr; }
         cudaGraph_t graph = nullptr;
         const int64_t l0 = c->launches;

@@ -97,3 +97,27 @@ def test_wishart_sampler_moments(pop, n_df, V, tm, tv):
     assert np.all(np.abs(s.mean(0) - mean_th) < 5 * np.sqrt(var_th / N) + 1e-12)
     assert np.allclose(s, np.transpose(s, (0, 2, 1)))          # symmetric, positive definite
     assert np.all(np.linalg.eigvalsh(s[:2000]) > 0)
+
+
+def test_degenerate_wishart_df_and_aliasing_draw_ids_are_refused(pop):
+    """n <= p - 1 puts a pole / negative argument into the multivariate gamma (runtime.cljc:479-485):
+    observe refuses it like sample does.  draw ids >= 256 of the matrix families would reuse the
+    counters of draw - 256: refused instead of silently repeating the numbers."""
+    from anglican_b200 import _lib as L
+    V = np.eye(3)
+    x = pop.column(L.F64, width=9, data=np.tile(np.eye(3).reshape(9), (N, 1)))
+    lw = pop.column(L.F64, fill=0.0)
+    for bad in (2.0, 1.0, -1.0):
+        with pytest.raises(L.ApopError) as e:
+            pop.observe_wishart(bad, V, x, lw)
+        assert e.value.code == -1 and "n > p - 1" in str(e.value)
+    pop.observe_wishart(2.5, V, x, lw)                       # n > p - 1 is fine
+    assert np.isfinite(lw.download()).all()
+    v3 = pop.column(L.F64, width=3)
+    for call in (lambda d: pop.sample_wishart(5.0, V, x, draw=d),
+                 lambda d: pop.sample_mvt(4.0, np.zeros(3), V, v3, draw=d),
+                 lambda d: pop.sample_mvn(np.zeros(3), V, v3, draw=d)):
+        call(255)
+        with pytest.raises(L.ApopError) as e:
+            call(256)
+        assert e.value.code == -1 and "draw_id" in str(e.value)

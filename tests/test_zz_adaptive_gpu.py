@@ -90,3 +90,28 @@ def test_threshold_zero_is_the_reference_rule_and_bad_thresholds_are_refused():
         assert a.log_z == b.log_z and np.array_equal(a.x_final, b.x_final)
         with pytest.raises(L.ApopError):
             pop.sweep(StochasticVolatility(), y, ess_threshold=1.5)
+
+
+def test_alternating_thresholds_on_one_population_recapture_the_graph():
+    """The ESS threshold is a by-value argument of the captured k_chain launch, and a threshold
+    > 0 adds the final log-sum-exp node: it belongs to the graph key.  One Population, graph
+    replay forced, thresholds alternating (0 included): every sweep must equal the oracle's
+    and the never-graphed sweep's, not the sweep that was captured first."""
+    from anglican_b200 import Population
+    from oracle import pyoracle as orc
+    name, m, om, y = _models()[0]
+    n = 4096 * 3 + 17
+    with Population(n, seed=11) as pop, Population(n, seed=11) as plain:
+        for thr in (0.3, 0.0, 0.9, 0.3, 0.0, 0.6):
+            out = pop.sweep(m, y, ess_threshold=thr, use_graph=1)
+            eager = plain.sweep(m, y, ess_threshold=thr, use_graph=-1)
+            ref = orc.smc_sweep(om, y, n, seed=11, ess_threshold=thr)
+            assert np.array_equal(out.log_mean_w == 0.0, ref["log_mean_w"] == 0.0), thr
+            assert abs(out.log_z - ref["log_z"]) <= 1e-9 * abs(ref["log_z"]), thr
+            assert out.log_z == eager.log_z, thr
+            assert np.array_equal(out.log_mean_w, eager.log_mean_w), thr
+            assert np.array_equal(out.x_final, eager.x_final), thr
+            assert _rel(out.x_final, ref["x_final"][:, 0]) < 1e-9, thr
+            if thr > 0.0:
+                assert np.array_equal(out.lw_final, eager.lw_final), thr
+                assert _rel(out.lw_final, ref["lw_final"]) < 1e-9, thr

@@ -17,7 +17,7 @@ sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), ".."
 from anglican_b200 import Population                                   # noqa: E402
 from anglican_b200.models import LinearGaussian1D, LinearGaussianMVN   # noqa: E402
 
-KT = {1: "k_propagate", 2: "k_tile_lse", 3: "k_finalize", 4: "k_fold_agg", 5: "k_resolve",
+KT = {1: "k_propagate", 2: "k_tile_lse", 3: "k_fin_a+k_fin_b", 4: "k_fold_agg", 5: "k_seg_scan+k_chain+k_expand",
       6: "k_ancestors", 8: "k_gather"}
 
 
