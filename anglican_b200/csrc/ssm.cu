@@ -16,6 +16,9 @@
 #include <stdlib.h>
 #include <string.h>
 
+#include <condition_variable>
+#include <mutex>
+
 #include "apop_internal.cuh"
 #include "fastmath.cuh"
 #include "rng.cuh"
@@ -1167,12 +1170,83 @@ static void preload_sweep_kernels() {
     cudaGetLastError();
 }
 
+// ---- how many SHARDED sweeps this process lets run at once -----------------
+// Kernels of a sharded sweep wait for their peers inside the kernel, with a bounded spin.
+// Measured on 8 B200: up to 4 sharded populations in flight complete; 6 stall; with the final
+// states gathered and downloaded after every sweep even 2 ran into the 3 s bound.  Until one
+// communication kernel per rank serves every population, that envelope is enforced here
+// instead of being left to the caller to find out through APOP_ERR_NCCL timeouts:
+//   at most APOP_SHARDED_MAX_INFLIGHT (default 4) sharded sweeps at a time, and a sweep that
+//   returns final states runs alone.
+// In-process groups WAIT for their turn: one process drives every rank of the sweep, so an
+// admitted sweep always finishes and frees its place.  With one process per GPU waiting is
+// not safe - two ranks could admit different populations and wait for each other for ever -
+// so the sweep is REFUSED with a message and the caller orders its sweeps (as bench.py does).
+// Unsharded populations (IPMCMC nodes) never wait on peers and are not counted.
+// APOP_SHARDED_GATE=0 switches the check off (for reproducing the stall).
+struct ShardedGate {
+    std::mutex mu;
+    std::condition_variable cv;
+    int inflight = 0, with_final = 0;
+};
+static ShardedGate g_sharded_gate;
+static int sharded_max_inflight() {
+    static const int v = [] {
+        const char* g = getenv("APOP_SHARDED_GATE");
+        if (g && g[0] == '0') return 0;                       // 0 = gate off
+        const char* e = getenv("APOP_SHARDED_MAX_INFLIGHT");
+        const int k = e ? atoi(e) : 4;
+        return k >= 1 ? k : 4;
+    }();
+    return v;
+}
+struct ShardedAdmission {
+    bool held = false, fin = false;
+    // returns false when the sweep may not start now (only when may_wait is false)
+    bool enter(bool want_final, bool may_wait) {
+        const int cap = sharded_max_inflight();
+        if (cap == 0) return true;
+        ShardedGate& G = g_sharded_gate;
+        std::unique_lock<std::mutex> lk(G.mu);
+        auto ok = [&] {
+            return G.with_final == 0 && G.inflight < cap && (!want_final || G.inflight == 0);
+        };
+        if (!ok()) {
+            if (!may_wait) return false;
+            G.cv.wait(lk, ok);
+        }
+        G.inflight += 1;
+        if (want_final) G.with_final += 1;
+        held = true; fin = want_final;
+        return true;
+    }
+    ~ShardedAdmission() {
+        if (!held) return;
+        ShardedGate& G = g_sharded_gate;
+        { std::lock_guard<std::mutex> lk(G.mu); G.inflight -= 1; if (fin) G.with_final -= 1; }
+        G.cv.notify_all();
+    }
+};
+
 static int sweep_group(apop_ctx* const* g, int ng, const apop_ssm* model, const double* y, int T,
                        const double* retained, const apop_sweep_opts* opts,
                        apop_sweep_result* results) {
     apop_ctx* c0 = g[0];
     if (!model || !y || T < 1 || !opts || !results)
         return set_err(c0, APOP_ERR_INVALID, "smc_sweep: bad arguments");
+    ShardedAdmission admission;
+    if (c0->world > 1) {
+        bool fin = opts->want_final != 0;
+        for (int i = 0; i < ng; ++i) fin = fin || results[i].x_final;
+        if (!admission.enter(fin, /*may_wait=*/c0->fab.in_process))
+            return set_err(c0, APOP_ERR_UNSUPPORTED,
+                           "sharded sweep refused: another sharded sweep of this process is in "
+                           "flight (at most %d at a time, and a sweep that returns final states "
+                           "runs alone). Their kernels wait on peer GPUs with a bounded spin and "
+                           "stall each other beyond that; run them one after another, or shard "
+                           "fewer populations per GPU (unsharded populations are not limited)",
+                           sharded_max_inflight());
+    }
     const int dim = (model->kind == APOP_SSM_LGMVN) ? model->dim : 1;
     for (int i = 0; i < ng; ++i) {
         apop_ctx* c = g[i];

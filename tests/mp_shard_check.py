@@ -41,6 +41,44 @@ def main():
         print(f"rank {rank} seed {seed}: log_z {out.log_z!r} ref {ref.log_z!r} "
               f"bit-identical={same}", flush=True)
         ok = ok and same
+    # The library admits sharded sweeps itself (csrc/ssm.cu, ShardedAdmission): with one
+    # process per GPU a sweep that returns final states must run alone, and a second sharded
+    # sweep arriving meanwhile is REFUSED with a message (waiting could deadlock across ranks).
+    import threading
+    import time
+    from anglican_b200 import _lib as L
+    uid2 = nccl_unique_id(rank)
+    pop2 = Population(n_local, seed=7, device=local, rank=rank, world=world, nccl_id=uid2)
+    y_long = rng.normal(size=6000) * 0.7
+    box = {}
+
+    def long_sweep():
+        try:
+            box["out"] = pop.sweep(m, y_long, want_filt=False)
+        except Exception as ex:
+            box["err"] = repr(ex)
+
+    pop.set_seed(3)
+    pop2.sweep(m, y, want_filt=False)            # alone: fine (also warms pop2 up)
+    dist.barrier()
+    th = threading.Thread(target=long_sweep)
+    th.start()
+    time.sleep(0.15)                             # the long sweep is in flight on every rank
+    refused = False
+    try:
+        pop2.sweep(m, y, want_filt=False)
+    except L.ApopError as ex:
+        refused = ex.code == -7 and "refused" in str(ex)
+        print(f"rank {rank}: second sharded sweep -> {ex}"[:160], flush=True)
+    th.join()
+    long_ok = "out" in box and np.isfinite(box["out"].log_z)
+    print(f"rank {rank}: refused={refused} long sweep finished={long_ok} {box.get('err', '')}",
+          flush=True)
+    ok = ok and refused and long_ok
+    dist.barrier()
+    after = pop2.sweep(m, y, want_filt=False)    # and afterwards it is admitted again
+    ok = ok and np.isfinite(after.log_z)
+    pop2.close()
     pop.close()
     flag = torch.tensor([0 if ok else 1], device="cuda")
     dist.all_reduce(flag)
