@@ -349,15 +349,20 @@ def run_ours(args):
     pop = pops[0]
     pool = ThreadPoolExecutor(max_workers=F)
 
+    e2e_seen = {}          # "f<f>_i<i>" -> (log Z, checksum of this rank's final states)
+
     def sweeps(f, count, seed0, **kw):
         zs = []
         for i in range(count):
             pops[f].set_seed(seed0 + 100 * f + i)
             o = pops[f].sweep(model, y, **kw)
             if kw.get("want_final"):
-                zs.append(float(o.x_final.reshape(-1)[::4096].mean()))   # the host reads the result
-            else:
-                zs.append(o.log_z)
+                # the host reads the result: every 4096th final state, summed as 64-bit
+                # patterns modulo 2^64 - exact, and independent of how the population is
+                # sharded (shards are multiples of 4096 values; the ranks' sums add up)
+                bits = np.ascontiguousarray(o.x_final.reshape(-1)[::4096]).view(np.uint64)
+                e2e_seen["f%d_i%d" % (f, i)] = (o.log_z, int(bits.sum(dtype=np.uint64)))
+            zs.append(o.log_z)
         return zs
 
     # ---- warm-up (>= 3 sweeps per population): the first sweep of each population
@@ -456,6 +461,26 @@ def run_ours(args):
     # population is sharded nor of what else is in flight.  Checked against the values
     # recorded by a 1-GPU run (profiles/logz_reference.json); a mismatch fails the run.
     logz_note = check_logz(args, rank, world, F, zs)
+    # the e2e leg returns final states: its log Z and a checksum of the states of EVERY timed
+    # sweep are compared with the values a 1-GPU run recorded, so that a sharded (IPC / NVLink)
+    # run is checked on the particles it returns, not on log Z alone
+    x_final_check = None
+    if e2e_error is None and e2e_seen:
+        keys = sorted(e2e_seen)
+        sums = np.array([e2e_seen[k][1] for k in keys], dtype=np.uint64).view(np.int64)
+        if world > 1:
+            if (n_local * dim) % 4096 == 0:
+                tsum = torch.from_numpy(sums.copy()).cuda()
+                dist.all_reduce(tsum)                       # int64 addition wraps: sum modulo 2^64
+                sums = tsum.cpu().numpy()
+            else:
+                sums = None
+        if sums is not None:
+            usums = sums.view(np.uint64)
+            x_final_check = check_recorded(
+                args, rank, world, "/e2e",
+                dict([("logz_" + k, e2e_seen[k][0]) for k in keys] +
+                     [("xsum_" + k, int(usums[j])) for j, k in enumerate(keys)]))
 
     if rank == 0:
         peak, peak_kind = measured_peak()
@@ -541,6 +566,7 @@ def run_ours(args):
                 "roofline_streaming_kernels": roof_all,
                 "path_roofline": path, "wall_ms_per_step": 1e3 * wall / args.steps,
                 "log_z_mean": float(np.mean(log_zs)), "log_z_check": logz_note,
+                "x_final_check": x_final_check,
                 "log_zs": {"f%d_i%d" % (f, i): z for f in range(len(zs)) for i, z in enumerate(zs[f])}}
         if args.workload == "lgssm1d":
             kz = kalman_logz(y)
@@ -576,24 +602,33 @@ LOGZ_FILE = os.path.join(ROOT, "profiles", "logz_reference.json")
 
 def check_logz(args, rank, world, F, zs):
     """zs[f][i] = log Z of timed sweep i of population f (seed 0xA11CE.. + 2000 + 100 f + i)"""
+    return check_recorded(args, rank, world, "",
+                          {"f%d_i%d" % (f, i): z for f in range(len(zs)) for i, z in enumerate(zs[f])})
+
+
+def check_recorded(args, rank, world, suffix, mine):
+    """Compare this run's per-sweep values (log Z; for the e2e leg also the checksum of the
+    final states) with those a 1-GPU run recorded in profiles/logz_reference.json.  They are
+    functions of (seed, T, particles) only, so every N must reproduce them exactly; a mismatch
+    fails the run.  Values with no recorded counterpart are counted, not hidden."""
     if rank != 0:
         return None
-    key = "%s/n%d/T%d" % (args.workload, args.particles, args.T)
+    key = "%s/n%d/T%d%s" % (args.workload, args.particles, args.T, suffix)
     try:
         ref = json.load(open(LOGZ_FILE))
     except Exception:
         ref = {}
     have = ref.get(key, {})
-    mine = {"f%d_i%d" % (f, i): z for f in range(len(zs)) for i, z in enumerate(zs[f])}
     bad = {k: (v, have[k]) for k, v in mine.items() if k in have and have[k] != v}
     if bad:
-        raise SystemExit("log Z differs from the recorded 1-GPU values (%s): %r" % (LOGZ_FILE, bad))
+        raise SystemExit("values differ from the recorded 1-GPU ones (%s, %s): %r" % (LOGZ_FILE, key, bad))
     checked = sum(1 for k in mine if k in have)
     if world == 1 and args.record_logz:
         have.update(mine)
         ref[key] = have
         json.dump(ref, open(LOGZ_FILE, "w"), indent=1, sort_keys=True)
-    return {"compared_with_recorded_1gpu_values": checked, "of": len(mine), "file": "profiles/logz_reference.json"}
+    return {"compared_with_recorded_1gpu_values": checked, "of": len(mine),
+            "not_on_file": len(mine) - checked, "file": "profiles/logz_reference.json", "key": key}
 
 
 def cpu_baseline(args):

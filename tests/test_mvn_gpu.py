@@ -61,15 +61,34 @@ def test_lgmvn_sweep_matches_oracle(d, n):
     m = LinearGaussianMVN(A, Qc, R)
     om = orc.Model(orc.SSM_LGMVN, dim=d, s0=1.0, A=A, Lq=np.linalg.cholesky(Qc), R=R)
     with Population(n, seed=11) as pop:
-        out = pop.sweep(m, y.ravel())
-    ref = orc.smc_sweep(om, y.ravel(), n, seed=11)
+        out = pop.sweep(m, y.ravel(), keep_history=True)
+        anc, xh = out.history()
+    ref = orc.smc_sweep(om, y.ravel(), n, seed=11, keep_history=True)
     assert np.max(np.abs(out.log_mean_w - ref["log_mean_w"]) /
                   np.maximum(1.0, np.abs(ref["log_mean_w"]))) < 1e-9
     assert abs(out.log_z - ref["log_z"]) <= 1e-9 * abs(ref["log_z"])
-    # resampling decisions are identical unless a pointer falls within rounding
-    # distance of an edge: states agree for (essentially) every particle
-    same = np.isclose(out.x_final, ref["x_final"], rtol=1e-9, atol=1e-9).all(axis=1)
-    assert same.mean() > 0.999
+    # The log-weights agree to ~1e-12, not bit for bit (tensor-pipe summation order), so a
+    # resampling pointer that falls within rounding distance of a cumulative edge may pick the
+    # NEIGHBOURING ancestor.  Such boundary ties are counted, not averaged away: walk the
+    # ancestry step by step; up to the first step with a tie every particle must agree with the
+    # oracle (all of them, 1e-9), and at that step every differing slot must be a shift by
+    # exactly one ancestor, at most one particle in 10^5.  After a tie the two runs are
+    # different populations and are no longer compared particle by particle.
+    ties, tie_step = 0, None
+    for t in range(T):
+        assert np.allclose(xh[t], ref["x_hist"][t], rtol=1e-9, atol=1e-9), (d, n, t)
+        diff = anc[t] != ref["anc_hist"][t]
+        if diff.any():
+            ties, tie_step = int(diff.sum()), t
+            shift = np.abs(anc[t][diff].astype(np.int64) - ref["anc_hist"][t][diff])
+            assert shift.max() == 1, (d, n, t, "not a boundary tie", shift.max())
+            assert ties <= max(1, n // 100000), (d, n, t, ties)
+            break
+    print(f"lgmvn d={d} n={n}: boundary ties {ties} (first at step {tie_step}) of {n * T} pointers")
+    if ties == 0:
+        assert np.array_equal(anc, ref["anc_hist"])
+        assert np.allclose(xh[T], ref["x_hist"][T], rtol=1e-9, atol=1e-9)
+        assert np.allclose(out.x_final, ref["x_final"], rtol=1e-9, atol=1e-9)      # every particle
 
 
 def test_lgmvn_log_marginal_vs_kalman():

@@ -85,9 +85,16 @@ def test_resample_from_logweights(orc, n):
     from anglican_b200 import _lib as L
     rng = np.random.default_rng(5 + n)
     with _pop(n) as pop:
-        for kind in ["normal", "with_neg_inf", "all_neg_inf", "offset"]:
+        for kind in ["normal", "with_neg_inf", "all_neg_inf", "offset", "with_pos_inf"]:
             lw = rng.normal(-3.0, 2.0, n)
-            if kind == "with_neg_inf":
+            if kind == "with_pos_inf":
+                # max = +inf: weight 1 for the particles AT the max, 0 for all others, and the
+                # common log-weight afterwards is -inf "so that the sweep dies out"
+                # (smc.cljc:78-82, 98-103)
+                lw[rng.integers(0, n, size=max(1, n // 50))] = np.inf
+                lw[rng.random(n) < 0.1] = -np.inf
+                lw[n // 2] = np.inf
+            elif kind == "with_neg_inf":
                 lw[rng.random(n) < 0.3] = -np.inf
                 lw[0] = -1.0
             elif kind == "all_neg_inf":

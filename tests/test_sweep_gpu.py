@@ -225,6 +225,27 @@ def test_sweep_does_not_depend_on_the_grid(kind):
     assert _rel(a.x_final, r["x_final"][:, 0]) < 1e-9
 
 
+def test_sweep_matches_oracle_at_a_baseline_shard_size():
+    """One whole sweep against the oracle at the per-GPU population of BASELINE config 3 on an
+    8-GPU box: 2^24 particles (4096 tiles, the multi-chunk finalize, every CTA of the persistent
+    grids busy), 3 observes of the SV model.  log Z to 1e-9, per-step log-mean-weights to 1e-9,
+    and EVERY final state - 2^24 of them - within 1e-9 of the oracle's (same counter-based
+    draws, bit-exact ancestry, smc.cljc:35-51, 86-137)."""
+    from anglican_b200 import Population
+    from anglican_b200.models import StochasticVolatility
+    from oracle import pyoracle as orc
+    n, T = 1 << 24, 3
+    m, y = StochasticVolatility(), _sv_data(T)
+    om = orc.Model(orc.SSM_SV, m0=0.0, s0=m.c.s0, a=m.c.a, b=0.0, q=m.c.q, beta=m.c.beta)
+    with Population(n, seed=424242) as pop:
+        a = pop.sweep(m, y)
+    r = orc.smc_sweep(om, y, n, seed=424242, threads=8)
+    assert abs(a.log_z - r["log_z"]) <= 1e-9 * abs(r["log_z"])
+    assert _rel(a.log_mean_w, r["log_mean_w"]) < 1e-9
+    assert _rel(a.ess, r["ess"]) < 1e-9
+    assert _rel(a.x_final, r["x_final"][:, 0]) < 1e-9
+
+
 @pytest.mark.parametrize("kind,n", [("sv", 1000), ("lgssm", 4097), ("hmm", 30000)])
 def test_importance_sweep_matches_oracle(orc, kind, n):
     """`infer :importance` (importance.cljc:16-22): no resampling, the observes
