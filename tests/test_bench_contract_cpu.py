@@ -62,6 +62,19 @@ def test_recorded_log_z_file_is_well_formed():
     ref = json.load(open(os.path.join(ROOT, "profiles", "logz_reference.json")))
     assert "sv/n134217728/T2000" in ref
     for key, vals in ref.items():
-        wl, n, T = key.split("/")
+        parts = key.split("/")
+        wl, n, T = parts[:3]
         assert wl in ("sv", "lgssm1d", "lgmvn64") and n.startswith("n") and T.startswith("T")
-        assert all(k.startswith("f") and isinstance(v, float) for k, v in vals.items())
+        if len(parts) == 3:                # device-timed leg: log Z per population and sweep
+            assert all(k.startswith("f") and isinstance(v, float) for k, v in vals.items())
+        else:                              # e2e leg: log Z and the final-state checksum per sweep
+            assert parts[3:] == ["e2e"]
+            for k, v in vals.items():
+                if k.startswith("logz_f"):
+                    assert isinstance(v, float)
+                else:
+                    assert k.startswith("xsum_f") and isinstance(v, int) and 0 <= v < 2 ** 64
+                    assert "logz_" + k[5:] in vals
+    # the default configuration has every timed sweep of a 20-step run on file, both legs
+    assert len(ref["sv/n134217728/T2000"]) >= 60
+    assert len(ref["sv/n134217728/T2000/e2e"]) >= 120
